@@ -1,0 +1,320 @@
+/*
+ * cc_api.c — the C ABI of libceracuda (include/ceracuda.h): handle life cycle, per-frame orchestration
+ * (upload -> kernels -> packed symbols in mapped pinned memory -> host CAVLC -> Annex-B access unit),
+ * the bitrate latch written by ceracoder's 20 ms balancer tick
+ * (/root/reference/src/gst/encoder_control.c:45-57 -> cc_enc_set_bitrate), and test hooks.
+ * Host C; all device work goes through the cck_* launch wrappers.
+ */
+#include "../../include/ceracuda.h"
+#include "cc_host.h"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#define CC_MIN_BPS 300000   /* /root/reference/src/core/bitrate_control.h:30 */
+#define CC_MAX_BPS 30000000 /* /root/reference/src/core/bitrate_control.h:31 */
+
+struct cc_enc {
+    cc_enc_params p;
+    cc_kparams k;
+    cc_seq seq;
+    cudaStream_t st;
+    cudaEvent_t ev0, ev1;
+    void *dev_alloc[24];
+    int n_dev_alloc;
+    size_t dev_bytes;
+    uint8_t *out_host;   /* mapped pinned: packed symbols */
+    uint32_t out_cap;
+    uint8_t *au;         /* access unit */
+    size_t au_cap;
+    uint8_t *rbsp;       /* per-slice scratch */
+    size_t rbsp_cap;
+    cc_cavlc_ctx cav;
+    cc_rc rc;
+    volatile int pending_bps;
+    int frame_idx, gop_pos, frame_num, idr_pic_id, have_ref;
+    int next_qp;         /* test hook */
+    int inflight, cur_is_idr, cur_qp;
+    int64_t cur_pts;
+    long launches;
+    int last_was_p;
+};
+
+static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
+
+const char *cc_version(void) { return "ceracuda 0.1 (sm_100a)"; }
+const char *cc_strerror(int c) {
+    switch (c) {
+    case CC_OK: return "ok";
+    case CC_ERR_PARAM: return "invalid parameter";
+    case CC_ERR_CUDA: return "CUDA error or no CUDA device";
+    case CC_ERR_NOMEM: return "out of memory";
+    case CC_ERR_STATE: return "invalid call order";
+    case CC_ERR_OVERFLOW: return "output buffer overflow";
+    default: return "unknown error";
+    }
+}
+
+#define CUCHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "ceracuda: %s failed: %s\n", #x, cudaGetErrorString(e_)); return CC_ERR_CUDA; } } while (0)
+
+void cc_enc_params_default(cc_enc_params *p) {
+    memset(p, 0, sizeof *p);
+    p->fps_n = 30; p->fps_d = 1; p->format = CC_FMT_I420; p->bitrate_bps = 6000000; /* reference default max, bitrate_control.h:32 */
+    p->key_int_max = 60; p->rows_per_slice = 4; p->qp_min = 10; p->qp_max = 51;
+}
+
+static int dev_alloc(cc_enc *e, void **p, size_t n) {
+    if (e->n_dev_alloc >= 24) return CC_ERR_NOMEM;
+    if (cudaMalloc(p, n) != cudaSuccess) { fprintf(stderr, "ceracuda: cudaMalloc(%zu) failed\n", n); return CC_ERR_NOMEM; }
+    e->dev_alloc[e->n_dev_alloc++] = *p;
+    e->dev_bytes += n;
+    return CC_OK;
+}
+static size_t roundup(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
+    if (!h || !p) return CC_ERR_PARAM;
+    *h = NULL;
+    if (p->width < 16 || p->height < 16 || (p->width & 1) || (p->height & 1) || p->width > 8192 || p->height > 8192) return CC_ERR_PARAM;
+    if (p->format != CC_FMT_I420 && p->format != CC_FMT_NV12) return CC_ERR_PARAM;
+    if (p->fps_n <= 0 || p->fps_d <= 0) return CC_ERR_PARAM;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || p->device < 0 || p->device >= ndev) {
+        fprintf(stderr, "ceracuda: no usable CUDA device (count %d, asked for %d); there is no CPU fallback\n", ndev, p->device);
+        return CC_ERR_CUDA;
+    }
+    CUCHECK(cudaSetDevice(p->device));
+    cc_enc *e = (cc_enc *)calloc(1, sizeof *e);
+    if (!e) return CC_ERR_NOMEM;
+    e->p = *p;
+    if (e->p.key_int_max <= 0) e->p.key_int_max = 60;
+    if (e->p.rows_per_slice <= 0) e->p.rows_per_slice = 4;
+    if (e->p.qp_min <= 0) e->p.qp_min = 10;
+    if (e->p.qp_max <= 0 || e->p.qp_max > 51) e->p.qp_max = 51;
+    if (e->p.qp_min < 10) e->p.qp_min = 10;
+    if (e->p.bitrate_bps <= 0) e->p.bitrate_bps = 6000000;
+    cc_kparams *k = &e->k;
+    k->w = p->width; k->h = p->height;
+    k->mb_w = (p->width + 15) / 16; k->mb_h = (p->height + 15) / 16;
+    k->W = k->mb_w * 16; k->H = k->mb_h * 16; k->rps = e->p.rows_per_slice;
+    k->sy = (int)roundup((size_t)k->W + 2 * CC_PAD, 128);
+    k->sc = (int)roundup((size_t)k->W / 2 + 2 * CC_PADC, 64);
+    e->seq.w = k->w; e->seq.h = k->h; e->seq.mb_w = k->mb_w; e->seq.mb_h = k->mb_h; e->seq.fps_n = p->fps_n; e->seq.fps_d = p->fps_d;
+    const int nmb = k->mb_w * k->mb_h;
+    int rc = CC_OK;
+    size_t lsz = (size_t)k->sy * (k->H + 2 * CC_PAD) + 256, csz = (size_t)k->sc * (k->H / 2 + 2 * CC_PADC) + 256;
+    uint8_t *lum[6], *chr[8];
+    for (int i = 0; i < 6 && rc == CC_OK; i++) { rc = dev_alloc(e, (void **)&lum[i], lsz); if (rc == CC_OK) cudaMemset(lum[i], 0, lsz); }
+    for (int i = 0; i < 8 && rc == CC_OK; i++) { rc = dev_alloc(e, (void **)&chr[i], csz); if (rc == CC_OK) cudaMemset(chr[i], 0, csz); }
+    if (rc == CC_OK) {
+        size_t lo = (size_t)CC_PAD * k->sy + CC_PAD, co = (size_t)CC_PADC * k->sc + CC_PADC;
+        k->cur[0] = lum[0] + lo; k->rec[0] = lum[1] + lo; k->ref[0] = lum[2] + lo;
+        k->hb = lum[3] + lo; k->hh = lum[4] + lo; k->hj = lum[5] + lo;
+        k->cur[1] = chr[0] + co; k->cur[2] = chr[1] + co; k->rec[1] = chr[2] + co; k->rec[2] = chr[3] + co;
+        k->ref[1] = chr[4] + co; k->ref[2] = chr[5] + co; k->l1cur = chr[6] + co; k->l1ref = chr[7] + co;
+    }
+    if (rc == CC_OK && p->format == CC_FMT_NV12) rc = dev_alloc(e, (void **)&k->uvstage, (size_t)k->sy * (k->H / 2 + 1));
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me, sizeof(cc_me) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowhdr, sizeof(cc_rowhdr) * k->mb_h);
+    if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
+    /* packed symbol buffer: headers + per-MB records + payload (worst case) */
+    e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(cc_mbhost) * nmb, 16) + (size_t)nmb * CC_ROW_PAYLOAD_PER_MB + 16 * k->mb_h);
+    if (rc == CC_OK && cudaHostAlloc((void **)&e->out_host, e->out_cap, cudaHostAllocMapped) != cudaSuccess) rc = CC_ERR_NOMEM;
+    if (rc == CC_OK && cudaHostGetDevicePointer((void **)&k->out_host_dev, e->out_host, 0) != cudaSuccess) rc = CC_ERR_CUDA;
+    k->out_cap = e->out_cap;
+    e->au_cap = (size_t)nmb * 1024 + 4096;
+    e->rbsp_cap = (size_t)k->rps * k->mb_w * 1024 + 4096;
+    e->au = (uint8_t *)malloc(e->au_cap);
+    e->rbsp = (uint8_t *)malloc(e->rbsp_cap);
+    e->cav.mb_w = k->mb_w; e->cav.mb_h = k->mb_h; e->cav.rps = k->rps;
+    e->cav.nnz = (uint8_t *)calloc((size_t)nmb, 24);
+    if (!e->au || !e->rbsp || !e->cav.nnz) rc = CC_ERR_NOMEM;
+    if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
+    if (rc != CC_OK) { cc_enc_close(e); return rc; }
+    e->pending_bps = e->p.bitrate_bps;
+    cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max);
+    cudaStreamSynchronize(e->st);
+    cudaDeviceSynchronize();
+    *h = e;
+    return CC_OK;
+}
+
+void cc_enc_close(cc_enc *e) {
+    if (!e) return;
+    if (e->st) cudaStreamSynchronize(e->st);
+    for (int i = 0; i < e->n_dev_alloc; i++) cudaFree(e->dev_alloc[i]);
+    if (e->out_host) cudaFreeHost(e->out_host);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->st) cudaStreamDestroy(e->st);
+    free(e->au); free(e->rbsp); free(e->cav.nnz);
+    free(e);
+}
+
+int cc_enc_set_bitrate(cc_enc *e, int bps) {
+    if (!e) return CC_ERR_PARAM;
+    if (bps < CC_MIN_BPS) bps = CC_MIN_BPS;
+    if (bps > CC_MAX_BPS) bps = CC_MAX_BPS;
+    __atomic_store_n(&e->pending_bps, bps, __ATOMIC_RELAXED);
+    return CC_OK;
+}
+int cc_enc_get_bitrate(const cc_enc *e) { return e ? __atomic_load_n(&e->pending_bps, __ATOMIC_RELAXED) : CC_ERR_PARAM; }
+int cc_enc_set_next_qp(cc_enc *e, int qp) { if (!e || qp < 10 || qp > 51) return CC_ERR_PARAM; e->next_qp = qp; return CC_OK; }
+int cc_enc_mb_w(const cc_enc *e) { return e ? e->k.mb_w : CC_ERR_PARAM; }
+int cc_enc_mb_h(const cc_enc *e) { return e ? e->k.mb_h : CC_ERR_PARAM; }
+size_t cc_enc_device_bytes(const cc_enc *e) { return e ? e->dev_bytes : 0; }
+long cc_enc_kernel_launches(const cc_enc *e) { return e ? e->launches : 0; }
+
+static void set_quant(cc_kparams *k) {
+    static const uint8_t chroma_qp[52] = {0,  1,  2,  3,  4,  5,  6,  7,  8,  9,  10, 11, 12, 13, 14, 15, 16, 17,
+                                          18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 29, 30, 31, 32, 32, 33,
+                                          34, 34, 35, 35, 36, 36, 37, 37, 37, 38, 38, 38, 39, 39, 39, 39}; /* Table 8-15 */
+    cc_quant_tables(k->qp, 1, k->qmf[0], k->qbias[0]);
+    cc_quant_tables(k->qp, 0, k->qmf[1], k->qbias[1]);
+    cc_quant_tables(chroma_qp[k->qp], 1, k->qmf[2], k->qbias[2]);
+    cc_quant_tables(chroma_qp[k->qp], 0, k->qmf[3], k->qbias[3]);
+}
+
+int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
+    if (!e || !in || !in->plane[0] || !in->plane[1]) return CC_ERR_PARAM;
+    if (e->inflight) return CC_ERR_STATE;
+    cc_kparams *k = &e->k;
+    const int nv12 = e->p.format == CC_FMT_NV12;
+    if (!nv12 && !in->plane[2]) return CC_ERR_PARAM;
+    if (in->stride[0] < k->w || in->stride[1] < (nv12 ? k->w : k->w / 2)) return CC_ERR_PARAM;
+    int is_idr = !e->have_ref || (flags & CC_FORCE_IDR) || e->gop_pos >= e->p.key_int_max;
+    if (is_idr) { e->gop_pos = 0; e->frame_num = 0; }
+    int bps = __atomic_load_n(&e->pending_bps, __ATOMIC_RELAXED);
+    int qp = e->p.qp_fixed > 0 ? e->p.qp_fixed : cc_rc_frame_qp(&e->rc, bps, is_idr, k->mb_w * k->mb_h);
+    if (e->next_qp) { qp = e->next_qp; e->next_qp = 0; }
+    if (qp < 10) qp = 10;
+    if (qp > 51) qp = 51;
+    k->qp = qp; k->is_idr = is_idr;
+    set_quant(k);
+    e->cur_is_idr = is_idr; e->cur_qp = qp; e->cur_pts = in->pts;
+
+    enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    CUCHECK(cudaEventRecord(e->ev0, e->st));
+    CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
+    if (nv12) {
+        CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, in->plane[1], (size_t)in->stride[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
+    } else {
+        CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+        CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+    }
+    e->launches += cck_ingest(k, nv12, e->st);
+    if (!is_idr) e->launches += cck_motion(k, e->st);
+    e->launches += cck_encode(k, e->st);
+    e->launches += cck_finish_ref(k, e->st);
+    e->launches += cck_pack(k, e->st);
+    CUCHECK(cudaEventRecord(e->ev1, e->st));
+    CUCHECK(cudaGetLastError());
+    /* the new reconstruction becomes the reference of the next frame */
+    for (int i = 0; i < 3; i++) { uint8_t *t = k->rec[i]; k->rec[i] = k->ref[i]; k->ref[i] = t; }
+    e->have_ref = 1;
+    e->last_was_p = !is_idr;
+    e->inflight = 1;
+    return CC_OK;
+}
+
+int cc_enc_collect(cc_enc *e, cc_packet *out) {
+    if (!e || !out) return CC_ERR_PARAM;
+    if (!e->inflight) return CC_ERR_STATE;
+    cc_kparams *k = &e->k;
+    CUCHECK(cudaEventSynchronize(e->ev1));
+    e->inflight = 0;
+    float gpu_ms = 0;
+    cudaEventElapsedTime(&gpu_ms, e->ev0, e->ev1);
+    double t0 = now_ms();
+    const int nmb = k->mb_w * k->mb_h, is_idr = e->cur_is_idr;
+    const cc_rowhdr *rh = (const cc_rowhdr *)e->out_host;
+    const cc_mbhost *mbh = (const cc_mbhost *)(e->out_host + roundup(sizeof(cc_rowhdr) * k->mb_h, 16));
+    const uint8_t *pay = (const uint8_t *)mbh + roundup(sizeof(cc_mbhost) * nmb, 16);
+    const uint8_t *rowp[512];
+    if (k->mb_h > 512) return CC_ERR_PARAM;
+    int ns = 0, ni = 0, np = 0;
+    for (int r = 0; r < k->mb_h; r++) {
+        rowp[r] = pay;
+        pay += roundup(rh[r].bytes, 16);
+        ns += (int)rh[r].n_skip; np += (int)rh[r].n_inter; ni += (int)rh[r].n_intra;
+        if ((size_t)(pay - e->out_host) > e->out_cap) return CC_ERR_OVERFLOW;
+    }
+    size_t n = 0;
+    uint8_t hdr[64];
+    if (is_idr) {
+        size_t m = cc_write_sps(&e->seq, hdr, sizeof hdr);
+        size_t w = cc_write_nal(e->au + n, e->au_cap - n, 0x67, hdr, m);
+        if (!m || !w) return CC_ERR_OVERFLOW;
+        n += w;
+        m = cc_write_pps(hdr, sizeof hdr);
+        w = cc_write_nal(e->au + n, e->au_cap - n, 0x68, hdr, m);
+        if (!m || !w) return CC_ERR_OVERFLOW;
+        n += w;
+    }
+    for (int r0 = 0; r0 < k->mb_h; r0 += k->rps) {
+        int r1 = r0 + k->rps < k->mb_h ? r0 + k->rps : k->mb_h;
+        cc_bw b;
+        cc_bw_init(&b, e->rbsp, e->rbsp_cap);
+        cc_write_slice_header(&b, r0 * k->mb_w, is_idr, e->frame_num, e->idr_pic_id, e->cur_qp);
+        if (cc_cavlc_write_slice(&e->cav, &b, is_idr, r0, r1, mbh, rh, rowp) != 0) { fprintf(stderr, "ceracuda: malformed symbol stream\n"); return CC_ERR_STATE; }
+        size_t m = cc_bw_finish(&b);
+        if (b.overflow) return CC_ERR_OVERFLOW;
+        size_t w = cc_write_nal(e->au + n, e->au_cap - n, is_idr ? 0x65 : 0x41, e->rbsp, m);
+        if (!w) return CC_ERR_OVERFLOW;
+        n += w;
+    }
+    cc_rc_update(&e->rc, is_idr, e->cur_qp, (long)n * 8);
+    e->frame_num = (e->frame_num + 1) & 15;
+    if (is_idr) e->idr_pic_id = (e->idr_pic_id + 1) & 0xffff;
+    e->gop_pos++;
+    e->frame_idx++;
+    out->data = e->au; out->size = (int)n; out->is_idr = is_idr; out->qp = e->cur_qp; out->pts = e->cur_pts;
+    out->n_skip = ns; out->n_inter = np; out->n_intra = ni;
+    out->gpu_ms = gpu_ms; out->host_ms = (float)(now_ms() - t0);
+    return CC_OK;
+}
+
+int cc_enc_encode(cc_enc *e, const cc_frame *in, unsigned flags, cc_packet *out) {
+    int rc = cc_enc_submit(e, in, flags);
+    return rc != CC_OK ? rc : cc_enc_collect(e, out);
+}
+
+/* ---- test hooks ----------------------------------------------------------------------------------- */
+int cc_enc_get_recon(cc_enc *e, uint8_t *y, uint8_t *u, uint8_t *v) {
+    if (!e || !y || !u || !v || e->inflight) return CC_ERR_PARAM;
+    cc_kparams *k = &e->k; /* after submit the newest reconstruction is k->ref */
+    CUCHECK(cudaStreamSynchronize(e->st));
+    CUCHECK(cudaMemcpy2D(y, (size_t)k->W, k->ref[0], (size_t)k->sy, (size_t)k->W, (size_t)k->H, cudaMemcpyDeviceToHost));
+    CUCHECK(cudaMemcpy2D(u, (size_t)k->W / 2, k->ref[1], (size_t)k->sc, (size_t)k->W / 2, (size_t)k->H / 2, cudaMemcpyDeviceToHost));
+    CUCHECK(cudaMemcpy2D(v, (size_t)k->W / 2, k->ref[2], (size_t)k->sc, (size_t)k->W / 2, (size_t)k->H / 2, cudaMemcpyDeviceToHost));
+    return CC_OK;
+}
+int cc_enc_get_me(cc_enc *e, int16_t *mv4, int32_t *satd) {
+    if (!e || !mv4 || !satd || e->inflight) return CC_ERR_PARAM;
+    const int nmb = e->k.mb_w * e->k.mb_h;
+    cc_me *tmp = (cc_me *)malloc(sizeof(cc_me) * nmb);
+    if (!tmp) return CC_ERR_NOMEM;
+    cudaError_t er = cudaMemcpy(tmp, e->k.me, sizeof(cc_me) * nmb, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < nmb && er == cudaSuccess; i++) {
+        mv4[4 * i] = tmp[i].l1_mv[0]; mv4[4 * i + 1] = tmp[i].l1_mv[1]; mv4[4 * i + 2] = tmp[i].mv[0]; mv4[4 * i + 3] = tmp[i].mv[1];
+        satd[i] = tmp[i].satd;
+    }
+    free(tmp);
+    return er == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+int cc_enc_get_mbinfo(cc_enc *e, uint8_t *dst8) {
+    if (!e || !dst8 || e->inflight) return CC_ERR_PARAM;
+    CUCHECK(cudaMemcpy(dst8, e->k.mbh, sizeof(cc_mbhost) * e->k.mb_w * e->k.mb_h, cudaMemcpyDeviceToHost));
+    return CC_OK;
+}
+
+void *cc_host_alloc(size_t bytes) { void *p = NULL; return cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess ? p : NULL; }
+void cc_host_free(void *p) { if (p) cudaFreeHost(p); }
+void *cc_dev_alloc(size_t bytes) { void *p = NULL; return cudaMalloc(&p, bytes) == cudaSuccess ? p : NULL; }
+void cc_dev_free(void *p) { if (p) cudaFree(p); }
+int cc_dev_upload(void *dst, const void *src, size_t bytes) { return cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? CC_OK : CC_ERR_CUDA; }

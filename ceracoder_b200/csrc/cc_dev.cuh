@@ -1,0 +1,118 @@
+/*
+ * cc_dev.cuh — device-side helpers and constant tables shared by the kernels of libceracuda (sm_100a).
+ * Integer pipes only: byte-SIMD (__vsadu4, __vavgu4), funnel shifts for unaligned windows, warp shuffles.
+ * Tables restate ITU-T H.264 (clause at each table).
+ */
+#ifndef CC_DEV_CUH
+#define CC_DEV_CUH
+#include "cc_internal.h"
+#ifndef CC_EMU
+#include <cuda_runtime.h>
+#define CC_LAUNCH(kern, grid, block, stream, ...) kern<<<grid, block, 0, stream>>>(__VA_ARGS__)
+#define CC_SPIN_PAUSE() __nanosleep(20)
+#else
+#define CC_LAUNCH(kern, grid, block, stream, ...) emu::launch(grid, block, 0, [&] { kern(__VA_ARGS__); })
+#define CC_SPIN_PAUSE() __nanosleep(20)
+#endif
+
+#define FULL 0xffffffffu
+
+/* ---- tables ------------------------------------------------------------------------------------- */
+/* zig-zag scan (H.264 Table 8-2, frame): scan position -> raster index, and its inverse */
+__constant__ uint8_t c_zigzag[16] = {0, 1, 4, 8, 5, 2, 3, 6, 9, 12, 13, 10, 7, 11, 14, 15};
+__constant__ uint8_t c_unzigzag[16] = {0, 1, 5, 6, 2, 4, 7, 12, 3, 8, 11, 13, 9, 10, 14, 15};
+/* luma 4x4 block index (decoding order, Figure 6-10) -> x,y in units of 4 pixels */
+__constant__ uint8_t c_blk_x[16] = {0, 1, 0, 1, 2, 3, 2, 3, 0, 1, 0, 1, 2, 3, 2, 3};
+__constant__ uint8_t c_blk_y[16] = {0, 0, 1, 1, 0, 0, 1, 1, 2, 2, 3, 3, 2, 2, 3, 3};
+/* (by,bx) -> block index */
+__constant__ uint8_t c_blk_of[16] = {0, 1, 4, 5, 2, 3, 6, 7, 8, 9, 12, 13, 10, 11, 14, 15};
+/* normAdjust4x4 (8.5.9): [qp%6][class], class 0 = (even,even), 1 = (odd,odd), 2 = mixed */
+__constant__ uint8_t c_dequant_v[6][3] = {{10, 16, 13}, {11, 18, 14}, {13, 20, 16}, {14, 23, 18}, {16, 25, 20}, {18, 29, 23}};
+/* chroma qp (Table 8-15) */
+__constant__ uint8_t c_chroma_qp[52] = {0,  1,  2,  3,  4,  5,  6,  7,  8,  9,  10, 11, 12, 13, 14, 15, 16, 17,
+                                        18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 29, 30, 31, 32, 32, 33,
+                                        34, 34, 35, 35, 36, 36, 37, 37, 37, 38, 38, 38, 39, 39, 39, 39};
+/* SATD-domain lambda per qp: round(2^((qp-12)/6)), at least 1 */
+__constant__ uint8_t c_lambda[52] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1,  1,  1,  1,  1,  1,  1,  2,  2,
+                                     2, 2, 3, 3, 3, 4, 4, 4, 5, 6,  6,  7,  8,  9,  10, 11, 13, 14,
+                                     16, 18, 20, 23, 25, 29, 32, 36, 40, 45, 51, 57, 64, 72, 81, 91};
+/* deblocking thresholds (Tables 8-16, 8-17) */
+__constant__ uint8_t c_alpha[52] = {0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,   0,   0,   0,   4,   4,
+                                    5,  6,  7,  8,  9,  10, 12, 13, 15, 17, 20, 22, 25,  28,  32,  36,  40,  45,
+                                    50, 56, 63, 71, 80, 90, 101, 113, 127, 144, 162, 182, 203, 226, 255, 255};
+__constant__ uint8_t c_beta[52] = {0, 0, 0, 0, 0, 0, 0, 0, 0,  0,  0,  0,  0,  0,  0,  0,  2,  2,
+                                   2, 3, 3, 3, 3, 4, 4, 4, 6,  6,  7,  7,  8,  8,  9,  9,  10, 10,
+                                   11, 11, 12, 12, 13, 13, 14, 14, 15, 15, 16, 16, 17, 17, 18, 18};
+__constant__ uint8_t c_tc0[52][3] = {
+    {0, 0, 0},  {0, 0, 0},  {0, 0, 0},  {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 0},
+    {0, 0, 0},  {0, 0, 0},  {0, 0, 0},  {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 0},   {0, 0, 1},
+    {0, 0, 1},  {0, 0, 1},  {0, 0, 1},  {0, 1, 1},   {0, 1, 1},   {1, 1, 1},   {1, 1, 1},   {1, 1, 1},   {1, 1, 1},
+    {1, 1, 2},  {1, 1, 2},  {1, 1, 2},  {1, 1, 2},   {1, 2, 3},   {1, 2, 3},   {2, 2, 3},   {2, 2, 4},   {2, 3, 4},
+    {2, 3, 4},  {3, 3, 5},  {3, 4, 6},  {3, 4, 6},   {4, 5, 7},   {4, 5, 8},   {4, 6, 9},   {5, 7, 10},  {6, 8, 11},
+    {6, 8, 13}, {7, 10, 14}, {8, 11, 16}, {9, 12, 18}, {10, 13, 20}, {11, 15, 23}, {13, 17, 25}};
+/* decimation weights by run length [EXT: x264_decimate_table4] */
+__constant__ uint8_t c_decimate[16] = {3, 2, 2, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+
+/* Quarter-pel interpolation as the average of two samples taken from the four planes
+ * G (integer), b (horizontal half), h (vertical half), j (centre) — H.264 8.4.2.2.1, Figure 8-4.
+ * entry [fy*4+fx] = planeA | dxA<<2 | dyA<<3 | planeB<<4 | dxB<<6 | dyB<<7 ; plane 0 G, 1 b, 2 h, 3 j */
+#define QP_E(pa, xa, ya, pb, xb, yb) ((pa) | ((xa) << 2) | ((ya) << 3) | ((pb) << 4) | ((xb) << 6) | ((yb) << 7))
+__constant__ uint8_t c_qpel[16] = {
+    QP_E(0, 0, 0, 0, 0, 0), QP_E(0, 0, 0, 1, 0, 0), QP_E(1, 0, 0, 1, 0, 0), QP_E(1, 0, 0, 0, 1, 0),
+    QP_E(0, 0, 0, 2, 0, 0), QP_E(1, 0, 0, 2, 0, 0), QP_E(1, 0, 0, 3, 0, 0), QP_E(1, 0, 0, 2, 1, 0),
+    QP_E(2, 0, 0, 2, 0, 0), QP_E(2, 0, 0, 3, 0, 0), QP_E(3, 0, 0, 3, 0, 0), QP_E(3, 0, 0, 2, 1, 0),
+    QP_E(2, 0, 0, 0, 0, 1), QP_E(2, 0, 0, 1, 0, 1), QP_E(3, 0, 0, 1, 0, 1), QP_E(2, 1, 0, 1, 0, 1)};
+
+/* ---- small integer helpers ---------------------------------------------------------------------- */
+__device__ __forceinline__ int cc_iabs(int x) { return x < 0 ? -x : x; }
+__device__ __forceinline__ int cc_clip255(int x) { return x < 0 ? 0 : (x > 255 ? 255 : x); }
+__device__ __forceinline__ int cc_clip3(int lo, int hi, int v) { return v < lo ? lo : (v > hi ? hi : v); }
+__device__ __forceinline__ int cc_median3(int a, int b, int c) {
+    int mn = a < b ? a : b, mx = a < b ? b : a;
+    return c < mn ? mn : (c > mx ? mx : c);
+}
+/* bit length of se(v), H.264 9.1 */
+__device__ __forceinline__ int cc_se_bits(int d) {
+    unsigned k = d > 0 ? 2u * (unsigned)d : (d < 0 ? 2u * (unsigned)(-d) + 1u : 1u);
+    return 2 * (31 - __clz((int)k)) + 1;
+}
+__device__ __forceinline__ int cc_pos_class(int i) { /* raster index in a 4x4 -> quant class */
+    int x = i & 1, y = (i >> 2) & 1;
+    return (x & y) ? 1 : ((x | y) ? 2 : 0);
+}
+/* 32-bit load from an arbitrary byte address: two aligned words + funnel shift */
+__device__ __forceinline__ uint32_t cc_ld32u(const uint8_t *p) {
+    uintptr_t a = (uintptr_t)p;
+    const uint32_t *q = (const uint32_t *)(a & ~(uintptr_t)3);
+    return __funnelshift_r(q[0], q[1], (unsigned)(a & 3) * 8u);
+}
+/* 8 bytes from an arbitrary byte address: three aligned words */
+__device__ __forceinline__ void cc_ld64u(const uint8_t *p, uint32_t &lo, uint32_t &hi) {
+    uintptr_t a = (uintptr_t)p;
+    const uint32_t *q = (const uint32_t *)(a & ~(uintptr_t)3);
+    unsigned sh = (unsigned)(a & 3) * 8u;
+    uint32_t w0 = q[0], w1 = q[1], w2 = q[2];
+    lo = __funnelshift_r(w0, w1, sh);
+    hi = __funnelshift_r(w1, w2, sh);
+}
+__device__ __forceinline__ int cc_byte(uint32_t w, int i) { return (int)((w >> (8 * i)) & 255u); }
+
+/* one 4x4 SATD (Hadamard of the difference, sum|.| >> 1) from packed rows: c[r], p[r] = 4 pixels each */
+__device__ __forceinline__ int cc_satd4x4_words(const uint32_t c[4], const uint32_t p[4]) {
+    int t[16];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        int d0 = cc_byte(c[r], 0) - cc_byte(p[r], 0), d1 = cc_byte(c[r], 1) - cc_byte(p[r], 1);
+        int d2 = cc_byte(c[r], 2) - cc_byte(p[r], 2), d3 = cc_byte(c[r], 3) - cc_byte(p[r], 3);
+        int s01 = d0 + d1, m01 = d0 - d1, s23 = d2 + d3, m23 = d2 - d3;
+        t[r * 4 + 0] = s01 + s23; t[r * 4 + 1] = s01 - s23; t[r * 4 + 2] = m01 - m23; t[r * 4 + 3] = m01 + m23;
+    }
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int s01 = t[i] + t[4 + i], m01 = t[i] - t[4 + i], s23 = t[8 + i] + t[12 + i], m23 = t[8 + i] - t[12 + i];
+        s += cc_iabs(s01 + s23) + cc_iabs(s01 - s23) + cc_iabs(m01 - m23) + cc_iabs(m01 + m23);
+    }
+    return s >> 1;
+}
+#endif

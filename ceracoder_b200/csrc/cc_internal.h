@@ -1,0 +1,93 @@
+/*
+ * cc_internal.h — structures shared by the host C code and the CUDA kernels of libceracuda.
+ * Plain C (included from .c and .cu).
+ */
+#ifndef CC_INTERNAL_H
+#define CC_INTERNAL_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef CC_EMU_BUILD
+#include "cuda_emu_rt.h"
+#else
+#include <cuda_runtime_api.h>
+#endif
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Plane geometry in HBM.  Every plane is stored with a replicated border so that motion vectors may
+ * point outside the picture (unrestricted MVs) without clamping in the inner loops:
+ *   luma-sized planes (cur Y, rec Y, half-pel b/h/j): origin at byte 48 of row 48, pitch = roundup(W+96,128)
+ *   chroma planes: origin at byte 32 of row 32, pitch = roundup(W/2+64,64)
+ *   half-resolution luma (coarse search): same layout as chroma planes.
+ * Origins are 16-byte aligned so that vector loads of whole macroblock rows are aligned. */
+#define CC_PAD 48
+#define CC_PADC 32
+#define CC_HPAD 40 /* half-pel planes are valid on [-40, W+40) x [-40, H+40) */
+#define CC_L1R 16  /* coarse search range in half-res pixels */
+
+enum { CC_MB_PSKIP = 0, CC_MB_P16 = 1, CC_MB_I16 = 2, CC_MB_I4 = 3 };
+
+/* motion-search result per macroblock */
+typedef struct {
+    int16_t l1_mv[2]; /* coarse vector, half-res pixels */
+    int16_t mv[2];    /* refined vector, quarter-pel */
+    int32_t satd;     /* SATD of the 16x16 prediction at mv */
+} cc_me;
+
+/* device-side macroblock record: neighbour context for prediction and deblocking */
+typedef struct {
+    uint8_t type, pad0;
+    uint16_t nz_luma;   /* bit blk (z-order): luma 4x4 block has a non-zero level */
+    int16_t mv[2];
+    uint8_t i4_mode[16];
+} cc_mbdev; /* 24 bytes */
+
+/* host-side macroblock record (what the CAVLC writer needs besides the coefficient payload) */
+typedef struct {
+    uint8_t type, modes /* i16_mode | chroma_mode<<2 */, cbp, pad;
+    int16_t mvd[2];
+} cc_mbhost; /* 8 bytes */
+
+/* per-MB-row symbol stream header, written by the encode kernel */
+typedef struct {
+    uint32_t bytes;   /* payload bytes used by this row (multiple of 2) */
+    uint32_t n_skip, n_inter, n_intra;
+} cc_rowhdr;
+
+#define CC_ROW_PAYLOAD_PER_MB 1024 /* worst case: 8 (i4 modes) + 27 blocks * (2 + 32) = 926 bytes */
+
+typedef struct {
+    int w, h;          /* display size */
+    int W, H;          /* coded size (multiples of 16) */
+    int mb_w, mb_h, rps;
+    int sy, sc;        /* pitches: luma-sized planes, chroma-sized planes (also half-res luma) */
+    uint8_t *cur[3];   /* origins (pixel 0,0) */
+    uint8_t *rec[3];   /* reconstruction being written */
+    uint8_t *ref[3];   /* previous reconstruction (deblocked, borders extended) */
+    uint8_t *hb, *hh, *hj; /* half-pel planes of ref: horizontal, vertical, centre */
+    uint8_t *l1cur, *l1ref;
+    uint8_t *uvstage;  /* NV12 interleaved chroma staging (pitch sy), or NULL */
+    cc_me *me;
+    cc_mbdev *mbd;
+    cc_mbhost *mbh;    /* device copy */
+    uint8_t *rowbuf;   /* mb_h rows * mb_w * CC_ROW_PAYLOAD_PER_MB */
+    cc_rowhdr *rowhdr; /* device */
+    int qp, is_idr;
+    uint16_t qmf[4][3], qbias[4][3]; /* quantiser: 0 luma intra, 1 luma inter, 2 chroma intra, 3 chroma inter; class-indexed */
+    /* packed output in mapped pinned host memory: [cc_rowhdr * mb_h][cc_mbhost * nmb][payload rows, 16-byte aligned] */
+    uint8_t *out_host_dev; /* device pointer of that mapping */
+    uint32_t out_cap;
+} cc_kparams;
+
+/* kernel launch wrappers (cc_kernels.cu); each returns the number of kernels launched */
+int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st);
+int cck_finish_ref(const cc_kparams *k, cudaStream_t st); /* rec -> borders, half-pel planes, half-res plane */
+int cck_motion(const cc_kparams *k, cudaStream_t st);
+int cck_encode(const cc_kparams *k, cudaStream_t st);
+int cck_pack(const cc_kparams *k, cudaStream_t st);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

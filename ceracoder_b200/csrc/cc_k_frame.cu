@@ -1,0 +1,155 @@
+/*
+ * cc_k_frame.cu — frame-level, fully parallel kernels (SURVEY.md §8a rows K1 and the reference-frame
+ * preparation that x264 calls frame_expand_border / hpel_filter [EXT]):
+ *   k_ingest      pad the uploaded picture to a macroblock multiple, de-interleave NV12 chroma,
+ *                 build the half-resolution luma plane of the current picture
+ *   k_border      replicate the borders of a finished reconstruction (unrestricted motion vectors)
+ *   k_hpel        half-pel planes b (horizontal), h (vertical), j (centre) of the reconstruction with the
+ *                 6-tap filter of H.264 8.4.2.2.1; every quarter-pel predictor is then the average of
+ *                 two samples of {G,b,h,j}
+ *   k_l1ref       half-resolution reconstruction (2x2 box mean) incl. border for the coarse search
+ * All are HBM/L2 streaming kernels: one pass, 4-byte or wider accesses, grid >> 148 SMs.
+ * Oracle counterparts: oracle/ref_enc.c load_plane / extend_border / downsample2, ref_prims.c hpel_*.
+ */
+#include "cc_dev.cuh"
+
+/* ---- k_ingest --------------------------------------------------------------------------------------- */
+/* one thread = one half-res pixel = 2x2 luma pixels + one chroma sample position */
+__global__ void k_ingest(cc_kparams k, int nv12) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    int W2 = k.W >> 1, w2 = k.w >> 1, h2 = k.h >> 1;
+    if (x >= W2) return;
+    /* luma: clamp source coordinates to the displayed picture; write back only in the padding */
+    int sx0 = min(2 * x, k.w - 1), sx1 = min(2 * x + 1, k.w - 1);
+    int sy0 = min(2 * y, k.h - 1), sy1 = min(2 * y + 1, k.h - 1);
+    uint8_t *Y = k.cur[0];
+    int a = Y[(size_t)sy0 * k.sy + sx0], b = Y[(size_t)sy0 * k.sy + sx1];
+    int c = Y[(size_t)sy1 * k.sy + sx0], d = Y[(size_t)sy1 * k.sy + sx1];
+    if (2 * x + 1 >= k.w || 2 * y + 1 >= k.h) {
+        Y[(size_t)(2 * y) * k.sy + 2 * x] = (uint8_t)a; Y[(size_t)(2 * y) * k.sy + 2 * x + 1] = (uint8_t)b;
+        Y[(size_t)(2 * y + 1) * k.sy + 2 * x] = (uint8_t)c; Y[(size_t)(2 * y + 1) * k.sy + 2 * x + 1] = (uint8_t)d;
+    }
+    k.l1cur[(size_t)y * k.sc + x] = (uint8_t)((a + b + c + d + 2) >> 2);
+    /* chroma */
+    int cx = min(x, w2 - 1), cy = min(y, h2 - 1);
+    if (nv12) {
+        const uint8_t *uv = k.uvstage + (size_t)cy * k.sy + 2 * cx;
+        k.cur[1][(size_t)y * k.sc + x] = uv[0];
+        k.cur[2][(size_t)y * k.sc + x] = uv[1];
+    } else if (x >= w2 || y >= h2) {
+        k.cur[1][(size_t)y * k.sc + x] = k.cur[1][(size_t)cy * k.sc + cx];
+        k.cur[2][(size_t)y * k.sc + x] = k.cur[2][(size_t)cy * k.sc + cx];
+    }
+}
+
+/* ---- k_border ---------------------------------------------------------------------------------------- */
+/* grid.y = plane (0 luma, 1 Cb, 2 Cr); one thread per border byte-quad */
+__global__ void k_border(cc_kparams k) {
+    int pl = blockIdx.y;
+    int W = pl ? k.W >> 1 : k.W, H = pl ? k.H >> 1 : k.H, pad = pl ? CC_PADC : CC_PAD, s = pl ? k.sc : k.sy;
+    uint8_t *P = k.rec[pl];
+    int fullw = W + 2 * pad;
+    /* work items: rows -pad..H+pad-1, for each row the 4-byte groups that lie in the border */
+    int groups_lr = (2 * pad) >> 2;   /* left+right groups in a picture row */
+    int groups_full = fullw >> 2;     /* groups of a row entirely in the top/bottom border */
+    int n_mid = H * groups_lr, n_tb = 2 * pad * groups_full;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_mid + n_tb; i += gridDim.x * blockDim.x) {
+        int y, x;
+        if (i < n_mid) {
+            y = i / groups_lr;
+            int g = i % groups_lr;
+            x = g < (pad >> 2) ? -pad + 4 * g : W + 4 * (g - (pad >> 2));
+        } else {
+            int j = i - n_mid, r = j / groups_full;
+            y = r < pad ? r - pad : H + (r - pad);
+            x = -pad + 4 * (j % groups_full);
+        }
+        int sy_ = min(max(y, 0), H - 1);
+        const uint8_t *row = P + (size_t)sy_ * s;
+        uint32_t v;
+        if (x < 0) v = row[0] * 0x01010101u;
+        else if (x >= W) v = row[W - 1] * 0x01010101u;
+        else v = *(const uint32_t *)(row + x);
+        *(uint32_t *)(P + (ptrdiff_t)y * s + x) = v;
+    }
+}
+
+/* ---- k_hpel ------------------------------------------------------------------------------------------ */
+#define HP_TW 64
+#define HP_TH 16
+__device__ __forceinline__ int cc_tap6(int a, int b, int c, int d, int e, int f) { return a - 5 * b + 20 * c + 20 * d - 5 * e + f; }
+
+/* CTA = 256 threads, output tile 64x16; reads the border-extended reconstruction (run after k_border) */
+__global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
+    __shared__ uint8_t g[HP_TH + 5][HP_TW + 8];  /* rows y-2..y+18, cols x-2..x+69 (72 used) */
+    __shared__ int16_t t[HP_TH + 5][HP_TW];      /* unrounded horizontal 6-tap of every staged row */
+    const int x0 = -CC_HPAD + (int)blockIdx.x * HP_TW, y0 = -CC_HPAD + (int)blockIdx.y * HP_TH;
+    const int xmax = k.W + CC_PAD - 1, ymax = k.H + CC_PAD - 1; /* last valid sample of the bordered plane */
+    const uint8_t *G = k.rec[0];
+    for (int i = threadIdx.x; i < (HP_TH + 5) * 18; i += 256) { /* 18 words per staged row */
+        int r = i / 18, c = i % 18;
+        int y = min(y0 - 2 + r, ymax), x = x0 - 4 + 4 * c; /* staged cols start at x0-4 (aligned); col index = x-(x0-4) */
+        uint32_t v = 0;
+        if (x + 3 <= xmax) v = *(const uint32_t *)(G + (ptrdiff_t)y * k.sy + x);
+        else for (int b = 0; b < 4; b++) v |= (uint32_t)G[(ptrdiff_t)y * k.sy + min(x + b, xmax)] << (8 * b);
+        *(uint32_t *)&g[r][4 * c] = v;
+    }
+    __syncthreads();
+    /* g[r][cx] holds sample (x0-4+cx, y0-2+r) */
+    for (int i = threadIdx.x; i < (HP_TH + 5) * HP_TW; i += 256) {
+        int r = i / HP_TW, c = i % HP_TW;
+        const uint8_t *p = &g[r][c + 4];
+        t[r][c] = (int16_t)cc_tap6(p[-2], p[-1], p[0], p[1], p[2], p[3]);
+    }
+    __syncthreads();
+    /* each thread: 4 horizontally adjacent outputs of each plane */
+    int r = threadIdx.x >> 4, c4 = (threadIdx.x & 15) * 4;
+    int y = y0 + r, x = x0 + c4;
+    if (x >= k.W + CC_HPAD || y >= k.H + CC_HPAD) return;
+    uint32_t vb = 0, vh = 0, vj = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int c = c4 + i;
+        int b = cc_clip255((t[r + 2][c] + 16) >> 5);
+        int hv = cc_clip255((cc_tap6(g[r][c + 4], g[r + 1][c + 4], g[r + 2][c + 4], g[r + 3][c + 4], g[r + 4][c + 4], g[r + 5][c + 4]) + 16) >> 5);
+        int j = cc_clip255((cc_tap6(t[r][c], t[r + 1][c], t[r + 2][c], t[r + 3][c], t[r + 4][c], t[r + 5][c]) + 512) >> 10);
+        vb |= (uint32_t)b << (8 * i); vh |= (uint32_t)hv << (8 * i); vj |= (uint32_t)j << (8 * i);
+    }
+    ptrdiff_t o = (ptrdiff_t)y * k.sy + x;
+    *(uint32_t *)(k.hb + o) = vb;
+    *(uint32_t *)(k.hh + o) = vh;
+    *(uint32_t *)(k.hj + o) = vj;
+}
+
+/* ---- k_l1ref ----------------------------------------------------------------------------------------- */
+/* half-res reconstruction over the picture and a 24-pixel border; one thread = 4 output pixels */
+__global__ void k_l1ref(cc_kparams k) {
+    const int B = 24, W2 = k.W >> 1, H2 = k.H >> 1;
+    int gx = blockIdx.x * blockDim.x + threadIdx.x, y = (int)blockIdx.y - B;
+    int x = -B + 4 * gx;
+    if (x >= W2 + B || y >= H2 + B) return;
+    const uint8_t *r0 = k.rec[0] + (ptrdiff_t)(2 * y) * k.sy + 2 * x, *r1 = r0 + k.sy;
+    uint32_t a0 = *(const uint32_t *)r0, a1 = *(const uint32_t *)(r0 + 4), b0 = *(const uint32_t *)r1, b1 = *(const uint32_t *)(r1 + 4);
+    uint32_t v = 0;
+    v |= (uint32_t)((cc_byte(a0, 0) + cc_byte(a0, 1) + cc_byte(b0, 0) + cc_byte(b0, 1) + 2) >> 2);
+    v |= (uint32_t)((cc_byte(a0, 2) + cc_byte(a0, 3) + cc_byte(b0, 2) + cc_byte(b0, 3) + 2) >> 2) << 8;
+    v |= (uint32_t)((cc_byte(a1, 0) + cc_byte(a1, 1) + cc_byte(b1, 0) + cc_byte(b1, 1) + 2) >> 2) << 16;
+    v |= (uint32_t)((cc_byte(a1, 2) + cc_byte(a1, 3) + cc_byte(b1, 2) + cc_byte(b1, 3) + 2) >> 2) << 24;
+    *(uint32_t *)(k.l1ref + (ptrdiff_t)y * k.sc + x) = v;
+}
+
+/* ---- launch wrappers --------------------------------------------------------------------------------- */
+extern "C" int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st) {
+    dim3 grid((unsigned)((k->W / 2 + 127) / 128), (unsigned)(k->H / 2));
+    CC_LAUNCH(k_ingest, grid, dim3(128), st, *k, nv12);
+    return 1;
+}
+extern "C" int cck_finish_ref(const cc_kparams *k, cudaStream_t st) {
+    CC_LAUNCH(k_border, dim3(148, 3), dim3(256), st, *k);
+    dim3 gh((unsigned)((k->W + 2 * CC_HPAD + HP_TW - 1) / HP_TW), (unsigned)((k->H + 2 * CC_HPAD + HP_TH - 1) / HP_TH));
+    CC_LAUNCH(k_hpel, gh, dim3(256), st, *k);
+    int n4 = (k->W / 2 + 48) / 4;
+    dim3 gl((unsigned)((n4 + 127) / 128), (unsigned)(k->H / 2 + 48));
+    CC_LAUNCH(k_l1ref, gl, dim3(128), st, *k);
+    return 3;
+}

@@ -1,0 +1,171 @@
+/*
+ * cc_k_motion.cu — motion estimation: fully parallel over macroblocks, one warp
+ * per macroblock, integer pipes only.
+ *   k_me_l1  coarse level: exhaustive +-16 search at half resolution on the MB's 8x8 footprint.  The
+ *            40x40 reference window is staged in shared memory; every lane scores whole candidates with
+ *            __vsadu4 on funnel-shifted words.  cost = 4*SAD + |dx| + |dy|, lowest candidate index wins ties.
+ *   k_me_l0  fine level: 27 full-pel candidates (SAD + lambda*mvd bits) around twice the coarse vector, then
+ *            9 half-pel and 8 quarter-pel candidates scored by 4x4-Hadamard SATD.  Quarter-pel predictors are
+ *            averages (__vavgu4) of two samples from the {G,b,h,j} planes built by k_hpel.
+ * The predictor used for the mvd cost is the median of the neighbours' COARSE vectors, which removes the
+ * raster dependency of true MV prediction from the search (the exact mvd is charged later, in k_mb_encode).
+ * Oracle counterparts: oracle/ref_enc.c me_l1 / me_l0.
+ */
+#include "cc_dev.cuh"
+
+#define L1_WIN 40          /* 8 + 2*16 */
+#define L1_PITCH 44        /* bytes per staged row: 11 words (odd word count spreads rows over banks) */
+#define ME_WARPS 4
+
+__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
+    __shared__ __align__(16) uint8_t win[ME_WARPS][L1_WIN * L1_PITCH + 8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
+    if (mb >= nmb) return; /* whole warp exits together */
+    const int mbx = mb % k.mb_w, mby = mb / k.mb_w;
+    const uint8_t *cur = k.l1cur + (size_t)(mby * 8) * k.sc + mbx * 8;
+    const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx * 8 - CC_L1R);
+    uint8_t *w = win[wid];
+    for (int i = lane; i < L1_WIN * 10; i += 32) { /* 10 words per row */
+        int r = i / 10, c = i % 10;
+        *(uint32_t *)(w + r * L1_PITCH + 4 * c) = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
+    }
+    if (lane < L1_WIN) *(uint32_t *)(w + lane * L1_PITCH + 40) = 0; /* pad word read by the funnel shift */
+    if (lane < 2) *(uint32_t *)(w + L1_WIN * L1_PITCH + 4 * lane) = 0;
+    uint32_t c0[8], c1[8];
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        c0[r] = *(const uint32_t *)(cur + (size_t)r * k.sc);
+        c1[r] = *(const uint32_t *)(cur + (size_t)r * k.sc + 4);
+    }
+    __syncwarp();
+    unsigned best = 0xffffffffu;
+    for (int c = lane; c < 33 * 33; c += 32) {
+        int dy = c / 33, dx = c - dy * 33; /* window coordinates 0..32 */
+        const uint8_t *p = w + dy * L1_PITCH + dx;
+        unsigned sad = 0;
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            uint32_t lo, hi;
+            cc_ld64u(p + r * L1_PITCH, lo, hi);
+            sad += __vsadu4(lo, c0[r]) + __vsadu4(hi, c1[r]);
+        }
+        unsigned key = ((4u * sad + (unsigned)(cc_iabs(dx - 16) + cc_iabs(dy - 16))) << 11) | (unsigned)c;
+        best = min(best, key);
+    }
+    best = __reduce_min_sync(FULL, best);
+    if (lane == 0) {
+        int idx = (int)(best & 2047u);
+        k.me[mb].l1_mv[0] = (int16_t)(idx % 33 - 16);
+        k.me[mb].l1_mv[1] = (int16_t)(idx / 33 - 16);
+    }
+}
+
+/* predicted 4x4 block (4 rows of 4 pixels) at quarter-pel vector (mvx,mvy) relative to pixel (px,py) */
+__device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, int mvx, int mvy, uint32_t out[4]) {
+    int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
+    const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
+    ptrdiff_t base = (ptrdiff_t)(py + (mvy >> 2)) * k.sy + px + (mvx >> 2);
+    const uint8_t *A = pl[e & 3] + base + ((e >> 2) & 1) + (ptrdiff_t)((e >> 3) & 1) * k.sy;
+    const uint8_t *B = pl[(e >> 4) & 3] + base + ((e >> 6) & 1) + (ptrdiff_t)((e >> 7) & 1) * k.sy;
+#pragma unroll
+    for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy), cc_ld32u(B + (ptrdiff_t)r * k.sy));
+}
+
+__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
+    __shared__ uint32_t scur[ME_WARPS][64]; /* current MB, 16 rows x 4 words */
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
+    if (mb >= nmb) return;
+    const int mw = k.mb_w, mbx = mb % mw, mby = mb / mw, lambda = c_lambda[k.qp];
+    const int px = mbx * 16, py = mby * 16;
+    {
+        const uint8_t *cur = k.cur[0] + (size_t)py * k.sy + px;
+        scur[wid][lane] = *(const uint32_t *)(cur + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
+        scur[wid][lane + 32] = *(const uint32_t *)(cur + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
+    }
+    /* approximate predictor: median of the neighbours' coarse vectors, in full-pel units */
+    const cc_me *me = k.me + mb;
+    const int L = mbx > 0, T = mby > (mby / k.rps) * k.rps, C = T && mbx + 1 < mw, TL = T && L;
+    int pm[2];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        int a = L ? 2 * me[-1].l1_mv[c] : 0, b = T ? 2 * me[-mw].l1_mv[c] : 0;
+        int cc = C ? 2 * me[-mw + 1].l1_mv[c] : (TL ? 2 * me[-mw - 1].l1_mv[c] : 0);
+        pm[c] = (!T && !(C || TL) && L) ? a : cc_median3(a, b, cc);
+    }
+    const int l1x = 2 * me->l1_mv[0], l1y = 2 * me->l1_mv[1];
+    __syncwarp();
+    const uint32_t *sc = scur[wid];
+
+    /* full-pel: lane = candidate */
+    unsigned key = 0xffffffffu;
+    int mx = 0, my = 0;
+    if (lane < 27) {
+        if (lane == 0) { mx = pm[0]; my = pm[1]; }
+        else if (lane >= 2) { mx = l1x + (lane - 2) % 5 - 2; my = l1y + (lane - 2) / 5 - 2; }
+        const uint8_t *r = k.ref[0] + (ptrdiff_t)(py + my) * k.sy + px + mx;
+        unsigned sad = 0;
+        for (int y = 0; y < 16; y++) {
+            uint32_t a, b, c, d;
+            cc_ld64u(r + (ptrdiff_t)y * k.sy, a, b);
+            cc_ld64u(r + (ptrdiff_t)y * k.sy + 8, c, d);
+            sad += __vsadu4(a, sc[y * 4]) + __vsadu4(b, sc[y * 4 + 1]) + __vsadu4(c, sc[y * 4 + 2]) + __vsadu4(d, sc[y * 4 + 3]);
+        }
+        unsigned cost = sad + (unsigned)(lambda * (cc_se_bits(4 * (mx - pm[0])) + cc_se_bits(4 * (my - pm[1]))));
+        key = (cost << 5) | (unsigned)lane;
+    }
+    unsigned bk = __reduce_min_sync(FULL, key);
+    int bl = (int)(bk & 31u);
+    int bx = 4 * __shfl_sync(FULL, mx, bl), by = 4 * __shfl_sync(FULL, my, bl);
+
+    /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */
+    const int blk = lane & 15, half = lane >> 4, ox = (blk & 3) * 4, oy = (blk >> 2) * 4;
+    uint32_t cw[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) cw[r] = sc[(oy + r) * 4 + (blk & 3)];
+    unsigned bestkey = 0xffffffffu; /* cost<<5 | order; this half-warp's best so far */
+    int bestsatd = 0, bestx = bx, besty = by;
+    for (int step = 2; step >= 1; step--) {
+        const int cx = bx, cy = by;
+        const int npass = step == 2 ? 5 : 4;
+        for (int p = 0; p < npass; p++) {
+            /* order o: step 2: 0 = centre, 1..8 = ring; step 1: 1..8 = ring (incumbent holds order 0) */
+            int o = 2 * p + half + (step == 2 ? 0 : 1);
+            bool valid = o <= 8;
+            int dx = 0, dy = 0;
+            if (o >= 1) { int i = o <= 4 ? o - 1 : o; dx = (i % 3 - 1) * step; dy = (i / 3 - 1) * step; }
+            int satd = 0;
+            if (valid) { /* uniform within each half-warp; no collectives inside */
+                uint32_t pw[4];
+                cc_qpel4x4(k, px + ox, py + oy, cx + dx, cy + dy, pw);
+                satd = cc_satd4x4_words(cw, pw);
+            }
+#pragma unroll
+            for (int s = 8; s; s >>= 1) satd += __shfl_xor_sync(FULL, satd, s); /* 16-lane sum (both halves at once) */
+            if (valid) {
+                int mvx = cx + dx, mvy = cy + dy;
+                unsigned cost = (unsigned)(satd + lambda * (cc_se_bits(mvx - 4 * pm[0]) + cc_se_bits(mvy - 4 * pm[1])));
+                unsigned kk = (cost << 5) | (unsigned)o;
+                if (kk < bestkey) { bestkey = kk; bestsatd = satd; bestx = mvx; besty = mvy; }
+            }
+        }
+        /* merge the two half-warps: lower key wins */
+        unsigned other = __shfl_xor_sync(FULL, bestkey, 16);
+        int osatd = __shfl_xor_sync(FULL, bestsatd, 16), oxv = __shfl_xor_sync(FULL, bestx, 16), oyv = __shfl_xor_sync(FULL, besty, 16);
+        if (other < bestkey) { bestkey = other; bestsatd = osatd; bestx = oxv; besty = oyv; }
+        bx = bestx; by = besty;
+        bestkey &= ~31u; /* the winner becomes the incumbent (order 0) of the next step */
+    }
+    if (lane == 0) {
+        k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd;
+    }
+}
+
+extern "C" int cck_motion(const cc_kparams *k, cudaStream_t st) {
+    int nmb = k->mb_w * k->mb_h;
+    dim3 grid((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS));
+    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k);
+    CC_LAUNCH(k_me_l0, grid, dim3(ME_WARPS * 32), st, *k);
+    return 2;
+}

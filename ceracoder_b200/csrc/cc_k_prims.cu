@@ -1,0 +1,169 @@
+/*
+ * cc_k_prims.cu — batch entry points for the primitives exactly as the encoder kernels compute them
+ * (same device functions), so tests can compare them bit-for-bit with the oracle (include/ceracuda.h
+ * cc_prim_*).  They stand where north_star names libx264's C reference functions [EXT]:
+ * pixel_sad_WxH, pixel_satd_4x4/16x16, sub4x4_dct, quant_4x4 + dequant_4x4 + add4x4_idct.
+ * One thread = one block; host pointers in, host pointers out (device staging inside).
+ */
+#include "../../include/ceracuda.h"
+#include "cc_xform.cuh"
+#include "cc_i4_table.h"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+extern "C" void cc_quant_tables(int qp, int intra, uint16_t mf[3], uint16_t bias[3]);
+
+struct QT { uint16_t mf[3], bias[3]; };
+
+__global__ void kp_sad(const uint8_t *a, const uint8_t *b, int w, int h, int n, int32_t *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t *pa = a + (size_t)i * w * h, *pb = b + (size_t)i * w * h;
+    unsigned s = 0;
+    for (int j = 0; j < w * h; j += 4) s += __vsadu4(cc_ld32u(pa + j), cc_ld32u(pb + j));
+    out[i] = (int32_t)s;
+}
+__global__ void kp_satd(const uint8_t *a, const uint8_t *b, int dim, int n, int32_t *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t *pa = a + (size_t)i * dim * dim, *pb = b + (size_t)i * dim * dim;
+    int s = 0;
+    for (int by = 0; by < dim; by += 4)
+        for (int bx = 0; bx < dim; bx += 4) {
+            uint32_t c[4], p[4];
+            for (int r = 0; r < 4; r++) { c[r] = cc_ld32u(pa + (by + r) * dim + bx); p[r] = cc_ld32u(pb + (by + r) * dim + bx); }
+            s += cc_satd4x4_words(c, p);
+        }
+    out[i] = s;
+}
+__global__ void kp_tq(const uint8_t *cur, const uint8_t *pred, int n, int qp, QT qt, int16_t *levels, uint8_t *recon, int dct_only) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t c[4], p[4], o[4];
+    for (int r = 0; r < 4; r++) { c[r] = cc_ld32u(cur + (size_t)i * 16 + r * 4); p[r] = cc_ld32u(pred + (size_t)i * 16 + r * 4); }
+    int d[16];
+    dct4x4_res(c, p, d);
+    if (!dct_only) quant4x4(d, qt.mf, qt.bias, false);
+    for (int j = 0; j < 16; j++) levels[(size_t)i * 16 + j] = (int16_t)d[j];
+    if (dct_only) return;
+    dequant4x4(d, qp);
+    idct4x4_add(d, p, o);
+    for (int r = 0; r < 4; r++) for (int x = 0; x < 4; x++) recon[(size_t)i * 16 + r * 4 + x] = (uint8_t)cc_byte(o[r], x);
+}
+__global__ void kp_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint8_t E[14];
+    for (int j = 0; j < 13; j++) E[j] = edge[(size_t)i * 13 + j];
+    E[13] = (uint8_t)((E[5] + E[6] + E[7] + E[8] + E[0] + E[1] + E[2] + E[3] + 4) >> 3);
+    for (int j = 0; j < 16; j++) {
+        unsigned t = c_i4tab[mode][j];
+        out[(size_t)i * 16 + j] = (uint8_t)((E[t & 15] + 2 * E[(t >> 4) & 15] + E[(t >> 8) & 15] + 2) >> 2);
+    }
+}
+/* quarter-pel blocks out of planes prepared by the encoder's own k_border/k_hpel (cc_k_frame.cu) */
+__global__ void kp_mc(cc_kparams k, const int16_t *xy, const int16_t *mv, int n, uint8_t *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int px = xy[2 * i], py = xy[2 * i + 1], mvx = mv[2 * i], mvy = mv[2 * i + 1];
+    const int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
+    const int pa = e & 3, pb = (e >> 4) & 3;
+    const ptrdiff_t base = (ptrdiff_t)(py + (mvy >> 2)) * k.sy + px + (mvx >> 2);
+    const uint8_t *A = (pa == 0 ? k.rec[0] : (pa == 1 ? k.hb : (pa == 2 ? k.hh : k.hj))) + base + ((e >> 2) & 1) + (ptrdiff_t)((e >> 3) & 1) * k.sy;
+    const uint8_t *B = (pb == 0 ? k.rec[0] : (pb == 1 ? k.hb : (pb == 2 ? k.hh : k.hj))) + base + ((e >> 6) & 1) + (ptrdiff_t)((e >> 7) & 1) * k.sy;
+    for (int r = 0; r < 16; r++)
+        for (int x = 0; x < 16; x += 4) {
+            uint32_t w = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy + x), cc_ld32u(B + (ptrdiff_t)r * k.sy + x));
+            for (int j = 0; j < 4; j++) out[(size_t)i * 256 + r * 16 + x + j] = (uint8_t)cc_byte(w, j);
+        }
+}
+
+/* ---- host wrappers ------------------------------------------------------------------------------------- */
+#define PCHECK(x) do { if ((x) != cudaSuccess) { fprintf(stderr, "ceracuda: %s failed\n", #x); rc = CC_ERR_CUDA; goto done; } } while (0)
+static int have_device(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { fprintf(stderr, "ceracuda: no CUDA device; there is no CPU fallback\n"); return 0; }
+    return 1;
+}
+struct DevBuf {
+    void *p = nullptr;
+    int alloc(size_t n, const void *src) {
+        if (cudaMalloc(&p, n + 16) != cudaSuccess) return -1;
+        if (src && cudaMemcpy(p, src, n, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+        return 0;
+    }
+    ~DevBuf() { if (p) cudaFree(p); }
+};
+static dim3 grid_for(int n) { return dim3((unsigned)((n + 127) / 128)); }
+
+extern "C" int cc_prim_sad(const uint8_t *a, const uint8_t *b, int w, int h, int n, int32_t *out) {
+    if (!a || !b || !out || n <= 0 || w <= 0 || h <= 0 || (w * h) % 4) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    DevBuf da, db, dout;
+    if (da.alloc((size_t)n * w * h, a) || db.alloc((size_t)n * w * h, b) || dout.alloc((size_t)n * 4, nullptr)) return CC_ERR_NOMEM;
+    CC_LAUNCH(kp_sad, grid_for(n), dim3(128), 0, (const uint8_t *)da.p, (const uint8_t *)db.p, w, h, n, (int32_t *)dout.p);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    return cudaMemcpy(out, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+static int satd_any(const uint8_t *a, const uint8_t *b, int dim, int n, int32_t *out) {
+    if (!a || !b || !out || n <= 0) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    DevBuf da, db, dout;
+    if (da.alloc((size_t)n * dim * dim, a) || db.alloc((size_t)n * dim * dim, b) || dout.alloc((size_t)n * 4, nullptr)) return CC_ERR_NOMEM;
+    CC_LAUNCH(kp_satd, grid_for(n), dim3(128), 0, (const uint8_t *)da.p, (const uint8_t *)db.p, dim, n, (int32_t *)dout.p);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    return cudaMemcpy(out, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+extern "C" int cc_prim_satd4x4(const uint8_t *a, const uint8_t *b, int n, int32_t *out) { return satd_any(a, b, 4, n, out); }
+extern "C" int cc_prim_satd16x16(const uint8_t *a, const uint8_t *b, int n, int32_t *out) { return satd_any(a, b, 16, n, out); }
+
+static int tq_any(const uint8_t *cur, const uint8_t *pred, int n, int qp, int intra, int16_t *levels, uint8_t *recon, int dct_only) {
+    if (!cur || !pred || !levels || n <= 0 || (!dct_only && (!recon || qp < 0 || qp > 51))) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    QT qt;
+    memset(&qt, 0, sizeof qt);
+    if (!dct_only) cc_quant_tables(qp, intra, qt.mf, qt.bias);
+    DevBuf dc, dp, dl, dr;
+    if (dc.alloc((size_t)n * 16, cur) || dp.alloc((size_t)n * 16, pred) || dl.alloc((size_t)n * 32, nullptr) || dr.alloc((size_t)n * 16, nullptr)) return CC_ERR_NOMEM;
+    CC_LAUNCH(kp_tq, grid_for(n), dim3(128), 0, (const uint8_t *)dc.p, (const uint8_t *)dp.p, n, qp, qt, (int16_t *)dl.p, (uint8_t *)dr.p, dct_only);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    if (cudaMemcpy(levels, dl.p, (size_t)n * 32, cudaMemcpyDeviceToHost) != cudaSuccess) return CC_ERR_CUDA;
+    if (!dct_only && cudaMemcpy(recon, dr.p, (size_t)n * 16, cudaMemcpyDeviceToHost) != cudaSuccess) return CC_ERR_CUDA;
+    return CC_OK;
+}
+extern "C" int cc_prim_tq4x4(const uint8_t *cur, const uint8_t *pred, int n, int qp, int intra, int16_t *levels, uint8_t *recon) {
+    return tq_any(cur, pred, n, qp, intra, levels, recon, 0);
+}
+extern "C" int cc_prim_dct4x4(const uint8_t *cur, const uint8_t *pred, int n, int16_t *coef) { return tq_any(cur, pred, n, 0, 0, coef, nullptr, 1); }
+
+extern "C" int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out) {
+    if (!edge || !out || n <= 0 || mode < 0 || mode > 8) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    DevBuf de, dout;
+    if (de.alloc((size_t)n * 13, edge) || dout.alloc((size_t)n * 16, nullptr)) return CC_ERR_NOMEM;
+    CC_LAUNCH(kp_pred4x4, grid_for(n), dim3(128), 0, (const uint8_t *)de.p, mode, n, (uint8_t *)dout.p);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    return cudaMemcpy(out, dout.p, (size_t)n * 16, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+
+extern "C" int cc_prim_mc_luma(const uint8_t *plane, int w, int h, const int16_t *xy, const int16_t *mv, int n, uint8_t *out) {
+    if (!plane || !xy || !mv || !out || n <= 0 || w < 16 || h < 16 || (w & 15) || (h & 15)) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    cc_kparams k;
+    memset(&k, 0, sizeof k);
+    k.w = k.W = w; k.h = k.H = h; k.mb_w = w / 16; k.mb_h = h / 16; k.rps = 1;
+    k.sy = (w + 2 * CC_PAD + 127) / 128 * 128; k.sc = (w / 2 + 2 * CC_PADC + 63) / 64 * 64;
+    const size_t lsz = (size_t)k.sy * (h + 2 * CC_PAD) + 256, csz = (size_t)k.sc * (h / 2 + 2 * CC_PADC) + 256, lo = (size_t)CC_PAD * k.sy + CC_PAD, co = (size_t)CC_PADC * k.sc + CC_PADC;
+    DevBuf g, hb, hh, hj, c1, c2, l1, dxy, dmv, dout;
+    if (g.alloc(lsz, nullptr) || hb.alloc(lsz, nullptr) || hh.alloc(lsz, nullptr) || hj.alloc(lsz, nullptr) || c1.alloc(csz, nullptr) || c2.alloc(csz, nullptr) ||
+        l1.alloc(csz, nullptr) || dxy.alloc((size_t)n * 4, xy) || dmv.alloc((size_t)n * 4, mv) || dout.alloc((size_t)n * 256, nullptr)) return CC_ERR_NOMEM;
+    cudaMemset(c1.p, 0, csz); cudaMemset(c2.p, 0, csz);
+    k.rec[0] = (uint8_t *)g.p + lo; k.rec[1] = (uint8_t *)c1.p + co; k.rec[2] = (uint8_t *)c2.p + co;
+    k.hb = (uint8_t *)hb.p + lo; k.hh = (uint8_t *)hh.p + lo; k.hj = (uint8_t *)hj.p + lo; k.l1ref = (uint8_t *)l1.p + co;
+    if (cudaMemcpy2D(k.rec[0], (size_t)k.sy, plane, (size_t)w, (size_t)w, (size_t)h, cudaMemcpyHostToDevice) != cudaSuccess) return CC_ERR_CUDA;
+    cck_finish_ref(&k, 0);
+    CC_LAUNCH(kp_mc, grid_for(n), dim3(128), 0, k, (const int16_t *)dxy.p, (const int16_t *)dmv.p, n, (uint8_t *)dout.p);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    return cudaMemcpy(out, dout.p, (size_t)n * 256, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}

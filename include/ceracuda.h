@@ -1,0 +1,134 @@
+/*
+ * include/ceracuda.h — C ABI of libceracuda.so, the B200-native H.264 encoder that stands in the
+ * `x264enc` slot of a ceracoder pipeline.
+ *
+ * What this replaces in the reference (CERALIVE/ceracoder, paths under /root/reference):
+ *   - the encoder element named in pipeline text, `x264enc speed-preset=3 key-int-max=60 name=venc_kbps`
+ *     (pipeline/generic/x264_veryfast_v4l_mjpeg_1080p30:6 and siblings; instantiated by
+ *     gst_parse_launch at src/io/pipeline_loader.c:59).  GStreamer's x264enc binds libx264's
+ *     x264_encoder_open / x264_encoder_encode / x264_encoder_reconfig / x264_encoder_close [EXT];
+ *     cc_enc_open / cc_enc_encode / cc_enc_set_bitrate / cc_enc_close are those four entry points.
+ *   - the one place ceracoder touches the encoder at run time: g_object_set(element, "bps", ...) at
+ *     src/gst/encoder_control.c:53 (20 ms timer, src/ceracoder.c:263) -> cc_enc_set_bitrate().
+ * The GStreamer element `cudah264enc` (ceracoder_b200/gst/gstcudah264enc.c) and the ctypes mirror
+ * (ceracoder_b200/encoder.py) sit on top of exactly these symbols.
+ *
+ * Conventions follow the reference's own C modules (src/net/srt_client.c:40-109,
+ * src/gst/encoder_control.c:39-57): opaque handle, int return, 0 = success, small negative codes,
+ * diagnostics on stderr.  No torch / C++ types cross this boundary.
+ *
+ * There is NO CPU fallback: every entry point that computes needs a CUDA device and fails with
+ * CC_ERR_CUDA otherwise.
+ */
+#ifndef CERACUDA_H
+#define CERACUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CC_OK 0
+#define CC_ERR_PARAM (-1)  /* bad argument (size, format, null pointer) */
+#define CC_ERR_CUDA (-2)   /* CUDA runtime error or no device */
+#define CC_ERR_NOMEM (-3)  /* host or device allocation failed */
+#define CC_ERR_STATE (-4)  /* call order violated (collect without submit, ...) */
+#define CC_ERR_OVERFLOW (-5) /* access unit did not fit the internal output buffer */
+
+enum { CC_FMT_I420 = 0, CC_FMT_NV12 = 1 };
+enum { CC_FORCE_IDR = 1u, CC_FRAME_DEVICE = 2u /* plane pointers are device memory */ };
+
+typedef struct cc_enc cc_enc;
+
+typedef struct {
+    int device;          /* CUDA ordinal */
+    int width, height;   /* even, >= 16 */
+    int fps_n, fps_d;
+    int format;          /* CC_FMT_* of the frames handed to cc_enc_encode */
+    int bitrate_bps;     /* initial target bitrate (ceracoder writes max_bitrate before PLAYING, src/ceracoder.c:515-518) */
+    int key_int_max;     /* IDR period in frames; 60 in every reference pipeline file; 0 -> 60 */
+    int rows_per_slice;  /* macroblock rows per slice; 0 -> 4 */
+    int qp_fixed;        /* > 0: constant-QP mode (rate control off); used by parity tests */
+    int qp_min, qp_max;  /* 0 -> 10 / 51 */
+} cc_enc_params;
+
+typedef struct {
+    const uint8_t *plane[3]; /* I420: Y,U,V.  NV12: Y, interleaved UV, unused */
+    int stride[3];           /* bytes per row; GStreamer strides are not tight (GstVideoInfo) */
+    int64_t pts;
+} cc_frame;
+
+typedef struct {
+    const uint8_t *data; /* Annex-B access unit, owned by the handle, valid until the next encode/collect/close */
+    int size;
+    int is_idr;
+    int qp;
+    int64_t pts;
+    int n_skip, n_inter, n_intra; /* macroblock statistics of the frame */
+    float gpu_ms;        /* device time of the frame's kernels (CUDA events) */
+    float host_ms;       /* host entropy coding + packaging time */
+} cc_packet;
+
+const char *cc_version(void);
+const char *cc_strerror(int code);
+
+void cc_enc_params_default(cc_enc_params *p);
+int cc_enc_open(cc_enc **h, const cc_enc_params *p);
+void cc_enc_close(cc_enc *h);
+
+/* Thread-safe and wait-free (one atomic store); takes effect at the next frame boundary.  Accepts
+ * bit/s; values are clamped to the reference's legal range 300 000..30 000 000 (src/core/bitrate_control.h:30-31). */
+int cc_enc_set_bitrate(cc_enc *h, int bps);
+int cc_enc_get_bitrate(const cc_enc *h);
+
+/* One frame in, one access unit out (zero-latency).  = cc_enc_submit + cc_enc_collect. */
+int cc_enc_encode(cc_enc *h, const cc_frame *in, unsigned flags, cc_packet *out);
+/* Split form, so one host thread can keep several streams' GPU work in flight. */
+int cc_enc_submit(cc_enc *h, const cc_frame *in, unsigned flags);
+int cc_enc_collect(cc_enc *h, cc_packet *out);
+
+/* Test hooks. */
+int cc_enc_set_next_qp(cc_enc *h, int qp); /* overrides rate control for the next submitted frame only */
+int cc_enc_get_recon(cc_enc *h, uint8_t *y, uint8_t *u, uint8_t *v); /* coded size (MB multiple), tight rows */
+int cc_enc_mb_w(const cc_enc *h);
+int cc_enc_mb_h(const cc_enc *h);
+/* per-macroblock motion-search results of the last P frame: 4 int16 per MB (coarse mv x,y in half-res px;
+ * final mv x,y in quarter-pel) and one int32 SATD per MB */
+int cc_enc_get_me(cc_enc *h, int16_t *mv4, int32_t *satd);
+/* per-macroblock decisions of the last frame: 8 bytes per MB {type, i16_mode, chroma_mode, cbp, mvd_x(2), mvd_y(2)} */
+int cc_enc_get_mbinfo(cc_enc *h, uint8_t *dst8);
+size_t cc_enc_device_bytes(const cc_enc *h);
+/* number of kernel launches issued by this handle since open */
+long cc_enc_kernel_launches(const cc_enc *h);
+
+/* pinned host memory for frames (lets cc_enc_submit's upload run asynchronously) */
+void *cc_host_alloc(size_t bytes);
+void cc_host_free(void *p);
+/* device memory helpers for callers that keep frames resident in HBM (CC_FRAME_DEVICE) */
+void *cc_dev_alloc(size_t bytes);
+void cc_dev_free(void *p);
+int cc_dev_upload(void *dst, const void *src, size_t bytes);
+
+/*
+ * Batch primitives — the transform / quant / SAD / SATD / interpolation / deblock building blocks as the
+ * kernels compute them, exposed for bit-exact parity tests against the oracle (tests/test_prims_gpu.py).
+ * All pointers are HOST memory; n = number of blocks.  They replace libx264's C reference functions
+ * named in BASELINE.json's north_star [EXT]: pixel_sad_16x16 / pixel_sad_8x8 / pixel_satd_4x4 /
+ * sub4x4_dct / quant_4x4 / dequant_4x4 / add4x4_idct.
+ */
+int cc_prim_sad(const uint8_t *a, const uint8_t *b, int w, int h, int n, int32_t *out); /* blocks tight w*h */
+int cc_prim_satd4x4(const uint8_t *a, const uint8_t *b, int n, int32_t *out);
+int cc_prim_satd16x16(const uint8_t *a, const uint8_t *b, int n, int32_t *out);
+/* residual -> 4x4 core transform -> quant -> dequant -> inverse -> reconstruct; intra selects the dead zone.
+ * levels: n*16 int16 raster order; recon: n*16 u8 */
+int cc_prim_tq4x4(const uint8_t *cur, const uint8_t *pred, int n, int qp, int intra, int16_t *levels, uint8_t *recon);
+int cc_prim_dct4x4(const uint8_t *cur, const uint8_t *pred, int n, int16_t *coef);
+/* intra 4x4 predictors: edge = n*13 bytes {left3,left2,left1,left0,topleft,top0..top7}; out n*16 */
+int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out);
+/* quarter-pel luma interpolation of n 16x16 blocks taken at (x,y)[i] + mv[i] from one w*h plane (borders replicated) */
+int cc_prim_mc_luma(const uint8_t *plane, int w, int h, const int16_t *xy, const int16_t *mv, int n, uint8_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
