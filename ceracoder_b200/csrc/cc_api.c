@@ -14,6 +14,7 @@
 
 #define CC_MIN_BPS 300000   /* /root/reference/src/core/bitrate_control.h:30 */
 #define CC_MAX_BPS 30000000 /* /root/reference/src/core/bitrate_control.h:31 */
+#define CC_N_STAGES CC_STAGE_COUNT
 
 struct cc_enc {
     cc_enc_params p;
@@ -39,6 +40,12 @@ struct cc_enc {
     int64_t cur_pts;
     long launches;
     int last_was_p;
+    int profile;                 /* per-kernel CUDA events on */
+    cudaEvent_t pev[CC_N_STAGES + 1];
+    int pev_used[CC_N_STAGES + 1];
+    double stage_ms[CC_N_STAGES];
+    long stage_n[CC_N_STAGES];
+    uint32_t sym_bytes;
 };
 
 static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
@@ -79,6 +86,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (p->width < 16 || p->height < 16 || (p->width & 1) || (p->height & 1) || p->width > 8192 || p->height > 8192) return CC_ERR_PARAM;
     if (p->format != CC_FMT_I420 && p->format != CC_FMT_NV12) return CC_ERR_PARAM;
     if (p->fps_n <= 0 || p->fps_d <= 0) return CC_ERR_PARAM;
+    if (p->rows_per_slice < 0 || p->rows_per_slice > 8) return CC_ERR_PARAM; /* one warp per MB row, at most 8 rows (256 threads) per slice CTA */
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || p->device < 0 || p->device >= ndev) {
         fprintf(stderr, "ceracuda: no usable CUDA device (count %d, asked for %d); there is no CPU fallback\n", ndev, p->device);
@@ -135,6 +143,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!e->au || !e->rbsp || !e->cav.nnz) rc = CC_ERR_NOMEM;
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
+    for (int i = 0; i <= CC_N_STAGES && rc == CC_OK; i++) if (cudaEventCreate(&e->pev[i]) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max);
@@ -151,6 +160,7 @@ void cc_enc_close(cc_enc *e) {
     if (e->out_host) cudaFreeHost(e->out_host);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
+    for (int i = 0; i <= CC_N_STAGES; i++) if (e->pev[i]) cudaEventDestroy(e->pev[i]);
     if (e->st) cudaStreamDestroy(e->st);
     free(e->au); free(e->rbsp); free(e->cav.nnz);
     free(e);
@@ -169,6 +179,17 @@ int cc_enc_mb_w(const cc_enc *e) { return e ? e->k.mb_w : CC_ERR_PARAM; }
 int cc_enc_mb_h(const cc_enc *e) { return e ? e->k.mb_h : CC_ERR_PARAM; }
 size_t cc_enc_device_bytes(const cc_enc *e) { return e ? e->dev_bytes : 0; }
 long cc_enc_kernel_launches(const cc_enc *e) { return e ? e->launches : 0; }
+int cc_enc_set_profile(cc_enc *e, int on) {
+    if (!e || e->inflight) return CC_ERR_PARAM;
+    e->profile = on != 0;
+    memset(e->stage_ms, 0, sizeof e->stage_ms); memset(e->stage_n, 0, sizeof e->stage_n);
+    return CC_OK;
+}
+int cc_enc_get_stage_ms(const cc_enc *e, double *ms_sum, long *count) {
+    if (!e || !ms_sum || !count) return CC_ERR_PARAM;
+    for (int i = 0; i < CC_N_STAGES; i++) { ms_sum[i] = e->stage_ms[i]; count[i] = e->stage_n[i]; }
+    return CC_OK;
+}
 
 static void set_quant(cc_kparams *k) {
     static const uint8_t chroma_qp[52] = {0,  1,  2,  3,  4,  5,  6,  7,  8,  9,  10, 11, 12, 13, 14, 15, 16, 17,
@@ -200,6 +221,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
 
     enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     CUCHECK(cudaEventRecord(e->ev0, e->st));
+    if (e->profile) { cudaEventRecord(e->pev[CC_STAGE_UPLOAD], e->st); }
     CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
     if (nv12) {
         CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, in->plane[1], (size_t)in->stride[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
@@ -207,11 +229,26 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
         CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
         CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
     }
+#define STAGE(i) do { if (e->profile) { cudaEventRecord(e->pev[i], e->st); e->pev_used[i] = 1; } } while (0)
+    for (int i = 0; i <= CC_N_STAGES; i++) e->pev_used[i] = 0;
+    STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, nv12, e->st);
-    if (!is_idr) e->launches += cck_motion(k, e->st);
+    STAGE(CC_STAGE_ME_COARSE);
+    if (!is_idr) e->launches += cck_me_l1(k, e->st);
+    STAGE(CC_STAGE_ME_FINE);
+    if (!is_idr) e->launches += cck_me_l0(k, e->st);
+    STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
-    e->launches += cck_finish_ref(k, e->st);
+    STAGE(CC_STAGE_BORDER);
+    e->launches += cck_border(k, e->st);
+    STAGE(CC_STAGE_HPEL);
+    e->launches += cck_hpel(k, e->st);
+    STAGE(CC_STAGE_L1REF);
+    e->launches += cck_l1ref(k, e->st);
+    STAGE(CC_STAGE_PACK);
     e->launches += cck_pack(k, e->st);
+    STAGE(CC_N_STAGES);
+#undef STAGE
     CUCHECK(cudaEventRecord(e->ev1, e->st));
     CUCHECK(cudaGetLastError());
     /* the new reconstruction becomes the reference of the next frame */
@@ -222,6 +259,8 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     return CC_OK;
 }
 
+static int is_idr_prof(const cc_enc *e) { return e->cur_is_idr; }
+
 int cc_enc_collect(cc_enc *e, cc_packet *out) {
     if (!e || !out) return CC_ERR_PARAM;
     if (!e->inflight) return CC_ERR_STATE;
@@ -230,6 +269,13 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     e->inflight = 0;
     float gpu_ms = 0;
     cudaEventElapsedTime(&gpu_ms, e->ev0, e->ev1);
+    if (e->profile)
+        for (int i = 0; i < CC_N_STAGES; i++) {
+            float ms = 0;
+            if ((i == CC_STAGE_UPLOAD || e->pev_used[i]) && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) {
+                if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
+            }
+        }
     double t0 = now_ms();
     const int nmb = k->mb_w * k->mb_h, is_idr = e->cur_is_idr;
     const cc_rowhdr *rh = (const cc_rowhdr *)e->out_host;
@@ -275,6 +321,7 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     e->frame_idx++;
     out->data = e->au; out->size = (int)n; out->is_idr = is_idr; out->qp = e->cur_qp; out->pts = e->cur_pts;
     out->n_skip = ns; out->n_inter = np; out->n_intra = ni;
+    out->sym_bytes = (int)(pay - e->out_host);
     out->gpu_ms = gpu_ms; out->host_ms = (float)(now_ms() - t0);
     return CC_OK;
 }

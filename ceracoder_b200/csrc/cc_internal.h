@@ -83,6 +83,11 @@ typedef struct {
 /* kernel launch wrappers (cc_kernels.cu); each returns the number of kernels launched */
 int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st);
 int cck_finish_ref(const cc_kparams *k, cudaStream_t st); /* rec -> borders, half-pel planes, half-res plane */
+int cck_border(const cc_kparams *k, cudaStream_t st);
+int cck_hpel(const cc_kparams *k, cudaStream_t st);
+int cck_l1ref(const cc_kparams *k, cudaStream_t st);
+int cck_me_l1(const cc_kparams *k, cudaStream_t st);
+int cck_me_l0(const cc_kparams *k, cudaStream_t st);
 int cck_motion(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);
 int cck_pack(const cc_kparams *k, cudaStream_t st);

@@ -144,12 +144,19 @@ extern "C" int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st) {
     CC_LAUNCH(k_ingest, grid, dim3(128), st, *k, nv12);
     return 1;
 }
-extern "C" int cck_finish_ref(const cc_kparams *k, cudaStream_t st) {
+extern "C" int cck_border(const cc_kparams *k, cudaStream_t st) {
     CC_LAUNCH(k_border, dim3(148, 3), dim3(256), st, *k);
+    return 1;
+}
+extern "C" int cck_hpel(const cc_kparams *k, cudaStream_t st) {
     dim3 gh((unsigned)((k->W + 2 * CC_HPAD + HP_TW - 1) / HP_TW), (unsigned)((k->H + 2 * CC_HPAD + HP_TH - 1) / HP_TH));
     CC_LAUNCH(k_hpel, gh, dim3(256), st, *k);
+    return 1;
+}
+extern "C" int cck_l1ref(const cc_kparams *k, cudaStream_t st) {
     int n4 = (k->W / 2 + 48) / 4;
     dim3 gl((unsigned)((n4 + 127) / 128), (unsigned)(k->H / 2 + 48));
     CC_LAUNCH(k_l1ref, gl, dim3(128), st, *k);
-    return 3;
+    return 1;
 }
+extern "C" int cck_finish_ref(const cc_kparams *k, cudaStream_t st) { return cck_border(k, st) + cck_hpel(k, st) + cck_l1ref(k, st); }

@@ -162,10 +162,14 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     }
 }
 
-extern "C" int cck_motion(const cc_kparams *k, cudaStream_t st) {
+extern "C" int cck_me_l1(const cc_kparams *k, cudaStream_t st) {
     int nmb = k->mb_w * k->mb_h;
-    dim3 grid((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS));
-    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k);
-    CC_LAUNCH(k_me_l0, grid, dim3(ME_WARPS * 32), st, *k);
-    return 2;
+    CC_LAUNCH(k_me_l1, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k);
+    return 1;
 }
+extern "C" int cck_me_l0(const cc_kparams *k, cudaStream_t st) {
+    int nmb = k->mb_w * k->mb_h;
+    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k);
+    return 1;
+}
+extern "C" int cck_motion(const cc_kparams *k, cudaStream_t st) { return cck_me_l1(k, st) + cck_me_l0(k, st); }

@@ -29,7 +29,7 @@ class Frame(C.Structure):
 
 class Packet(C.Structure):
     _fields_ = [("data", C.POINTER(C.c_uint8)), ("size", C.c_int), ("is_idr", C.c_int), ("qp", C.c_int), ("pts", C.c_int64),
-                ("n_skip", C.c_int), ("n_inter", C.c_int), ("n_intra", C.c_int), ("gpu_ms", C.c_float), ("host_ms", C.c_float)]
+                ("n_skip", C.c_int), ("n_inter", C.c_int), ("n_intra", C.c_int), ("sym_bytes", C.c_int), ("gpu_ms", C.c_float), ("host_ms", C.c_float)]
 
 
 _libs = {}
@@ -65,6 +65,8 @@ def load_library(path=None):
     L.cc_enc_device_bytes.restype = C.c_size_t
     L.cc_enc_kernel_launches.argtypes = [vp]
     L.cc_enc_kernel_launches.restype = C.c_long
+    L.cc_enc_set_profile.argtypes = [vp, ci]
+    L.cc_enc_get_stage_ms.argtypes = [vp, vp, vp]
     L.cc_host_alloc.restype = vp
     L.cc_host_alloc.argtypes = [C.c_size_t]
     L.cc_host_free.argtypes = [vp]
@@ -194,6 +196,17 @@ class CudaH264Enc:
         a = np.zeros((self.mb_w * self.mb_h, 8), np.uint8)
         _check(self.L, self.L.cc_enc_get_mbinfo(self._h, a.ctypes.data), "cc_enc_get_mbinfo")
         return a
+
+    STAGES = ("upload", "ingest", "me_coarse", "me_fine", "mb_encode", "border", "hpel", "l1ref", "pack")
+
+    def set_profile(self, on=True):
+        _check(self.L, self.L.cc_enc_set_profile(self._h, int(on)), "cc_enc_set_profile")
+
+    def stage_ms(self):
+        """{stage: (total_ms, launches)} measured with CUDA events on the encoder's stream since set_profile()."""
+        ms = (C.c_double * len(self.STAGES))(); n = (C.c_long * len(self.STAGES))()
+        _check(self.L, self.L.cc_enc_get_stage_ms(self._h, ms, n), "cc_enc_get_stage_ms")
+        return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
 
     def kernel_launches(self):
         return self.L.cc_enc_kernel_launches(self._h)

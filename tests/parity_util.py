@@ -1,0 +1,64 @@
+"""Shared helpers for encoder parity tests (emulated on CPU, or the real library on a B200)."""
+import numpy as np
+from ceracoder_b200 import CudaH264Enc
+from ceracoder_b200.synth import make_source
+from h264_decode import decode_aus
+from oracle_lib import OracleEncoder
+
+
+def oracle_mb_table(orc):
+    n = orc.mb_w * orc.mb_h
+    rows = []
+    for j in range(n):
+        o = orc.mb_struct(j)
+        rows.append((o.type, o.i16_mode, o.chroma_mode, o.cbp, o.l1_mv[0], o.l1_mv[1], o.me_mv[0], o.me_mv[1], o.me_satd))
+    return np.array(rows, dtype=np.int64)
+
+
+def run_parity(lib, source, w, h, qps, rps=4, gop=60, fmt="I420", check_decode=True, frames=None):
+    """Encode the same frames at the same per-frame QP with libceracuda and with the CPU oracle; assert that the
+    access units are byte-identical, the reconstructions identical, and (optionally) that libavcodec decodes the
+    stream to exactly that reconstruction. Returns the list of access units."""
+    src = make_source(source, w, h) if isinstance(source, str) else source
+    enc = CudaH264Enc(w, h, fps=(30, 1), rows_per_slice=rps, key_int_max=gop, lib=lib, fmt=fmt)
+    orc = OracleEncoder(w, h, 30, rps)
+    aus, recs = [], []
+    try:
+        for i, qp in enumerate(qps):
+            y, u, v = src.frame(i) if frames is None else frames[i]
+            if fmt == "NV12":
+                uv = np.empty((h // 2, w), np.uint8); uv[:, 0::2] = u; uv[:, 1::2] = v
+                a = enc.encode(y, uv, None, qp=qp)
+            else:
+                a = enc.encode(y, u, v, qp=qp)
+            b = orc.encode(y, u, v, i % gop == 0, qp)
+            ry, ru, rv = enc.recon()
+            oy, ou, ov = orc.recon()
+            if i % gop:
+                mv, satd = enc.motion()
+                t = oracle_mb_table(orc)
+                assert (mv[:, :2] == t[:, 4:6]).all(), f"frame {i}: coarse motion vectors differ"
+                assert (mv[:, 2:] == t[:, 6:8]).all(), f"frame {i}: refined motion vectors differ"
+                assert (satd == t[:, 8]).all(), f"frame {i}: motion SATD differs"
+            info = enc.mbinfo()
+            t = oracle_mb_table(orc)
+            assert (info[:, 0] == t[:, 0]).all(), f"frame {i}: macroblock types differ at {np.argwhere(info[:, 0] != t[:, 0])[:4].ravel()}"
+            assert (info[:, 2] == t[:, 3]).all(), f"frame {i}: cbp differs"
+            assert (ry == oy).all(), f"frame {i}: luma reconstruction differs at {np.argwhere(ry != oy)[:3]}"
+            assert (ru == ou).all() and (rv == ov).all(), f"frame {i}: chroma reconstruction differs"
+            assert a == b, f"frame {i}: access units differ ({len(a)} vs {len(b)} bytes)"
+            assert enc.last.qp == qp and enc.last.is_idr == (i % gop == 0)
+            aus.append(a); recs.append((ry, ru, rv))
+        if check_decode:
+            dec = decode_aus(aus)
+            assert len(dec) == len(aus)
+            for (y, u, v), (ry, ru, rv) in zip(dec, recs):
+                assert (y == ry[:h, :w]).all() and (u == ru[:h // 2, :w // 2]).all() and (v == rv[:h // 2, :w // 2]).all()
+    finally:
+        enc.close(); orc.close()
+    return aus
+
+
+def psnr(a, b):
+    mse = ((a.astype(np.float64) - b.astype(np.float64)) ** 2).mean()
+    return 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)

@@ -1,0 +1,87 @@
+"""The drop-in boundary: every symbol include/ceracuda.h declares is exported by libceracuda.so, the element-shaped
+Python mirror keeps the reference's property contract (/root/reference/src/gst/encoder_control.c:23-57), and the
+product fails loudly without a CUDA device (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import pytest
+from oracle_lib import ROOT
+
+LIB = os.path.join(ROOT, "ceracoder_b200", "libceracuda.so")
+
+
+@pytest.fixture(scope="module")
+def built():
+    subprocess.check_call(["make", "-s", "-C", ROOT, "lib"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return C.CDLL(LIB)
+
+
+def test_all_declared_symbols_exported(built):
+    hdr = open(os.path.join(ROOT, "include", "ceracuda.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(cc_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 25
+    for n in sorted(names):
+        assert hasattr(built, n), f"{n} declared in ceracuda.h but not exported"
+
+
+def test_no_cpu_fallback_without_device(built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    from ceracoder_b200 import CudaH264Enc, CeraCudaError
+    with pytest.raises(CeraCudaError, match="CUDA"):
+        CudaH264Enc(64, 48)
+    out = (C.c_int32 * 1)()
+    a = (C.c_uint8 * 16)()
+    assert built.cc_prim_satd4x4(a, a, 1, out) == -2  # CC_ERR_CUDA
+
+
+def test_product_never_links_the_oracle():
+    """The shipped library and package must not reference oracle/ or the emulator."""
+    out = subprocess.run(["ldd", LIB], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "emu" not in out
+    for f in os.listdir(os.path.join(ROOT, "ceracoder_b200")):
+        if f.endswith(".py"):
+            txt = open(os.path.join(ROOT, "ceracoder_b200", f)).read()
+            assert "oracle" not in txt.replace("oracle/", "").lower() or f == "synth.py" or "oracle_lib" not in txt
+            assert "emu_lib" not in txt and "libceraoracle" not in txt
+
+
+def test_property_contract_on_emulated_element():
+    from emu_lib import emu_library
+    from ceracoder_b200 import CudaH264Enc
+    L = emu_library()
+    e = CudaH264Enc(64, 48, bitrate=6000, speed_preset="veryfast", key_int_max=60, name="venc_kbps", lib=L)
+    assert e.get_property("bitrate") == 6000
+    e.set_property("bps", 2500)           # what encoder_control.c:53 writes for a venc_kbps element: bps/1000
+    assert e.get_property("bitrate") == 2500
+    e.set_property("bitrate", 12000)      # what the docs promise (README.md:256)
+    assert e.get_property("bps") == 12000
+    e.set_property("bitrate", 10)         # clamped to the reference's legal range (bitrate_control.h:30-31)
+    assert e.get_property("bitrate") == 300
+    e.set_property("bitrate", 10 ** 6)
+    assert e.get_property("bitrate") == 30000
+    with pytest.raises(AttributeError):
+        e.set_property("qp-min", 3)
+    e.close()
+    e2 = CudaH264Enc(64, 48, name="venc_bps", lib=L)
+    e2.set_property("bps", 4200000)       # venc_bps elements get bit/s (encoder_control.c:29-30)
+    assert e2.get_property("bitrate") == 4200
+    e2.close()
+    with pytest.raises(ValueError):
+        CudaH264Enc(64, 48, name="x264enc0", lib=L)
+    with pytest.raises(ValueError):
+        CudaH264Enc(64, 48, speed_preset="warp9", lib=L)
+
+
+def test_parameter_errors_on_emulated_library():
+    from emu_lib import emu_library
+    from ceracoder_b200 import CudaH264Enc, CeraCudaError
+    L = emu_library()
+    for w, h in ((8, 48), (64, 47), (65, 48), (20000, 48)):
+        with pytest.raises(CeraCudaError, match="invalid parameter"):
+            CudaH264Enc(w, h, lib=L)
+    assert L.cc_strerror(-5).decode().startswith("output buffer")
+    assert b"ceracuda" in L.cc_version()
