@@ -185,6 +185,7 @@ def main_reference(args, rank, world):
 
 
 def main():
+    global FRAMES_PER_STEP
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=6)
@@ -192,7 +193,9 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--streams", type=int, default=STREAMS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--frames-per-step", type=int, default=FRAMES_PER_STEP, help="frames each stream encodes per step (shorten for ncu runs)")
     args = ap.parse_args()
+    FRAMES_PER_STEP = args.frames_per_step
     rank, world, local = dist_info()
     if args.impl == "reference":
         return main_reference(args, rank, world)
