@@ -1,0 +1,211 @@
+/*
+ * cc_deblock.cuh — in-loop deblocking filter of one macroblock by one warp (H.264 8.7).
+ *
+ * The filter is normatively raster-ordered (each macroblock filters its four vertical then its four horizontal
+ * edges on pixels its left / top neighbours already modified), so macroblock rows advance as a 2-MB-lag wavefront
+ * exactly like the encode pass.  What this file removes is the per-edge round trip to L2: the warp stages the
+ * macroblock plus the 4 pixels left of / above it into shared memory once (172 coalesced word loads), every lane
+ * then filters one whole pixel line in registers (lanes 0-15: a luma row / column across its 4 edges, lanes 16-31:
+ * a chroma row / column of Cb or Cr across its 2 edges), and the tile is stored back once.
+ * Boundary strengths come from the first 8 bytes of three cc_mbdev records (current, left, top).
+ * Oracle counterpart: oracle/ref_mb.c ref_mb_deblock.
+ */
+#ifndef CC_DEBLOCK_CUH
+#define CC_DEBLOCK_CUH
+#include "cc_dev.cuh"
+
+struct __align__(16) DbMem {
+    uint8_t Y[20][24];    /* Y[r + 4][c + 4] = luma sample (c, r) of the macroblock, r,c in -4..15 */
+    uint8_t C[2][12][16]; /* C[pl][r + 4][c + 4], r,c in -4..7 */
+    uint32_t nb[3][2];    /* first two words of cc_mbdev: 0 current, 1 left, 2 top */
+};
+
+/* boundary strength between 4x4 blocks bp (of the record p) and bq (of q), H.264 8.7.2.1, single reference picture */
+__device__ __forceinline__ int db_bs(uint32_t p0, uint32_t p1, int bp, uint32_t q0, uint32_t q1, int bq, int mb_edge) {
+    if ((p0 & 255u) >= CC_MB_I16 || (q0 & 255u) >= CC_MB_I16) return mb_edge ? 4 : 3;
+    if (((p0 >> (16 + bp)) | (q0 >> (16 + bq))) & 1u) return 2;
+    const int dx = (int)(int16_t)(p1 & 0xffffu) - (int)(int16_t)(q1 & 0xffffu);
+    const int dy = (int)(int16_t)(p1 >> 16) - (int)(int16_t)(q1 >> 16);
+    return (cc_iabs(dx) >= 4 || cc_iabs(dy) >= 4) ? 1 : 0;
+}
+
+/* luma edge, 8.7.2.3 (bS < 4) and 8.7.2.4 (bS == 4) */
+__device__ __forceinline__ void db_luma(int p3, int &p2, int &p1, int &p0, int &q0, int &q1, int &q2, int q3, int bs, int alpha, int beta, int tc0v) {
+    if (cc_iabs(p0 - q0) >= alpha || cc_iabs(p1 - p0) >= beta || cc_iabs(q1 - q0) >= beta) return;
+    const int ap = cc_iabs(p2 - p0) < beta, aq = cc_iabs(q2 - q0) < beta;
+    if (bs < 4) {
+        const int tc = tc0v + ap + aq;
+        const int d = cc_clip3(-tc, tc, (((q0 - p0) << 2) + (p1 - q1) + 4) >> 3);
+        const int avg = (p0 + q0 + 1) >> 1;
+        if (ap) p1 = p1 + cc_clip3(-tc0v, tc0v, (p2 + avg - (p1 << 1)) >> 1);
+        if (aq) q1 = q1 + cc_clip3(-tc0v, tc0v, (q2 + avg - (q1 << 1)) >> 1);
+        p0 = cc_clip255(p0 + d); q0 = cc_clip255(q0 - d);
+    } else {
+        const int small = cc_iabs(p0 - q0) < ((alpha >> 2) + 2);
+        const int P0 = p0, P1 = p1, P2 = p2, Q0 = q0, Q1 = q1, Q2 = q2;
+        if (ap && small) {
+            p0 = (P2 + 2 * P1 + 2 * P0 + 2 * Q0 + Q1 + 4) >> 3;
+            p1 = (P2 + P1 + P0 + Q0 + 2) >> 2;
+            p2 = (2 * p3 + 3 * P2 + P1 + P0 + Q0 + 4) >> 3;
+        } else p0 = (2 * P1 + P0 + Q1 + 2) >> 2;
+        if (aq && small) {
+            q0 = (P1 + 2 * P0 + 2 * Q0 + 2 * Q1 + Q2 + 4) >> 3;
+            q1 = (P0 + Q0 + Q1 + Q2 + 2) >> 2;
+            q2 = (2 * q3 + 3 * Q2 + Q1 + Q0 + P0 + 4) >> 3;
+        } else q0 = (2 * Q1 + Q0 + P1 + 2) >> 2;
+    }
+}
+/* chroma edge */
+__device__ __forceinline__ void db_chroma(int p1, int &p0, int &q0, int q1, int bs, int alpha, int beta, int tc0v) {
+    if (cc_iabs(p0 - q0) >= alpha || cc_iabs(p1 - p0) >= beta || cc_iabs(q1 - q0) >= beta) return;
+    if (bs < 4) {
+        const int tc = tc0v + 1;
+        const int d = cc_clip3(-tc, tc, (((q0 - p0) << 2) + (p1 - q1) + 4) >> 3);
+        p0 = cc_clip255(p0 + d); q0 = cc_clip255(q0 - d);
+    } else {
+        const int P0 = p0, Q0 = q0;
+        p0 = (2 * p1 + P0 + q1 + 2) >> 2; q0 = (2 * q1 + Q0 + p1 + 2) >> 2;
+    }
+}
+
+/* filters the staged line v[0..19] (luma: positions -4..15) across its 4 edges at positions 0,4,8,12 */
+__device__ __forceinline__ void db_line_luma(int v[20], const int bs[4], int first, int alpha, int beta, const int tc0[3]) {
+#pragma unroll
+    for (int ed = 0; ed < 4; ed++) {
+        if (ed < first || !bs[ed]) continue;
+        const int b = bs[ed];
+        db_luma(v[4 * ed], v[4 * ed + 1], v[4 * ed + 2], v[4 * ed + 3], v[4 * ed + 4], v[4 * ed + 5], v[4 * ed + 6], v[4 * ed + 7], b, alpha, beta,
+                tc0[b < 4 ? b - 1 : 0]);
+    }
+}
+/* chroma line v[0..11] (positions -4..7): edges at 0 and 4, strengths of the luma edges 0 and 2 */
+__device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int first, int alpha, int beta, const int tc0[3]) {
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+        const int b = bs[2 * e];
+        if (2 * e < first || !b) continue;
+        db_chroma(v[4 * e + 2], v[4 * e + 3], v[4 * e + 4], v[4 * e + 5], b, alpha, beta, tc0[b < 4 ? b - 1 : 0]);
+    }
+}
+
+/* One macroblock.  L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, int lane, int mbx, int mby, int L, int T) {
+    const int mb = mby * k.mb_w + mbx, qp = k.qp, qpc = c_chroma_qp[qp];
+    const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
+    if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
+    /* ---- stage ---- */
+    {
+        uint32_t ly[4], lc[3];
+#pragma unroll
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
+        }
+#pragma unroll
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+        }
+        if (lane < 6) {
+            const int which = lane >> 1; /* 0 current, 1 left, 2 top */
+            const int nmb = which == 0 ? mb : (which == 1 ? (L ? mb - 1 : mb) : (T ? mb - k.mb_w : mb));
+            db->nb[which][lane & 1] = ((const uint32_t *)(k.mbd + nmb))[lane & 1];
+        }
+#pragma unroll
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
+        }
+#pragma unroll
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
+        }
+    }
+    __syncwarp();
+    const uint32_t q0 = db->nb[0][0], q1 = db->nb[0][1];
+    const bool luma = lane < 16;
+    const int li = lane & 15;                 /* luma line, or chroma: plane = li >> 3, line = li & 7 */
+    const int g = luma ? li >> 2 : (li & 7) >> 1;
+    const int cpl = li >> 3, ci = li & 7;
+    const int alpha = c_alpha[luma ? qp : qpc], beta = c_beta[luma ? qp : qpc];
+    int tc0[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) tc0[i] = c_tc0[luma ? qp : qpc][i];
+
+    /* ---- vertical edges: one lane = one pixel row ---- */
+    {
+        int bs[4];
+#pragma unroll
+        for (int ed = 0; ed < 4; ed++) {
+            const uint32_t p0 = ed == 0 ? db->nb[1][0] : q0, p1 = ed == 0 ? db->nb[1][1] : q1;
+            bs[ed] = db_bs(p0, p1, c_blk_of[g * 4 + (ed ? ed - 1 : 3)], q0, q1, c_blk_of[g * 4 + ed], ed == 0);
+        }
+        const int first = L ? 0 : 1;
+        if (luma) {
+            uint32_t w[5];
+            int v[20];
+#pragma unroll
+            for (int i = 0; i < 5; i++) w[i] = *(const uint32_t *)&db->Y[li + 4][4 * i];
+#pragma unroll
+            for (int i = 0; i < 20; i++) v[i] = cc_byte(w[i >> 2], i & 3);
+            db_line_luma(v, bs, first, alpha, beta, tc0);
+#pragma unroll
+            for (int i = 0; i < 5; i++)
+                *(uint32_t *)&db->Y[li + 4][4 * i] = (uint32_t)v[4 * i] | ((uint32_t)v[4 * i + 1] << 8) | ((uint32_t)v[4 * i + 2] << 16) | ((uint32_t)v[4 * i + 3] << 24);
+        } else {
+            uint32_t w[3];
+            int v[12];
+#pragma unroll
+            for (int i = 0; i < 3; i++) w[i] = *(const uint32_t *)&db->C[cpl][ci + 4][4 * i];
+#pragma unroll
+            for (int i = 0; i < 12; i++) v[i] = cc_byte(w[i >> 2], i & 3);
+            db_line_chroma(v, bs, first, alpha, beta, tc0);
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+                *(uint32_t *)&db->C[cpl][ci + 4][4 * i] = (uint32_t)v[4 * i] | ((uint32_t)v[4 * i + 1] << 8) | ((uint32_t)v[4 * i + 2] << 16) | ((uint32_t)v[4 * i + 3] << 24);
+        }
+    }
+    __syncwarp();
+    /* ---- horizontal edges: one lane = one pixel column ---- */
+    {
+        int bs[4];
+#pragma unroll
+        for (int ed = 0; ed < 4; ed++) {
+            const uint32_t p0 = ed == 0 ? db->nb[2][0] : q0, p1 = ed == 0 ? db->nb[2][1] : q1;
+            bs[ed] = db_bs(p0, p1, c_blk_of[(ed ? ed - 1 : 3) * 4 + g], q0, q1, c_blk_of[ed * 4 + g], ed == 0);
+        }
+        const int first = T ? 0 : 1;
+        if (luma) {
+            int v[20];
+#pragma unroll
+            for (int i = 0; i < 20; i++) v[i] = db->Y[i][li + 4];
+            db_line_luma(v, bs, first, alpha, beta, tc0);
+#pragma unroll
+            for (int i = 1; i < 20; i++) db->Y[i][li + 4] = (uint8_t)v[i];
+        } else {
+            int v[12];
+#pragma unroll
+            for (int i = 0; i < 12; i++) v[i] = db->C[cpl][i][ci + 4];
+            db_line_chroma(v, bs, first, alpha, beta, tc0);
+#pragma unroll
+            for (int i = 2; i < 12; i++) db->C[cpl][i][ci + 4] = (uint8_t)v[i];
+        }
+    }
+    __syncwarp();
+    /* ---- store: own macroblock, the 4 columns left of it (if L), the 4 rows above it (if T) ---- */
+#pragma unroll
+    for (int it = 0; it < 4; it++) {
+        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+        const bool ok = idx < 100 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
+        if (ok) *(uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) = *(const uint32_t *)&db->Y[r][4 * cw];
+    }
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+        const bool ok = idx < 72 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
+        if (ok) *(uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) = *(const uint32_t *)&db->C[pl][r][4 * cw];
+    }
+    __syncwarp();
+}
+#endif

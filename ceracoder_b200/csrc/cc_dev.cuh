@@ -9,9 +9,13 @@
 #ifndef CC_EMU
 #include <cuda_runtime.h>
 #define CC_LAUNCH(kern, grid, block, stream, ...) kern<<<grid, block, 0, stream>>>(__VA_ARGS__)
+#define CC_LAUNCH_SMEM(kern, grid, block, smem, stream, ...) kern<<<grid, block, smem, stream>>>(__VA_ARGS__)
+#define CC_DYN_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
 #define CC_SPIN_PAUSE() __nanosleep(20)
 #else
 #define CC_LAUNCH(kern, grid, block, stream, ...) emu::launch(grid, block, 0, [&] { kern(__VA_ARGS__); })
+#define CC_LAUNCH_SMEM(kern, grid, block, smem, stream, ...) emu::launch(grid, block, smem, [&] { kern(__VA_ARGS__); })
+#define CC_DYN_SMEM(name) uint8_t *name = (uint8_t *)(((uintptr_t)emu::dyn_smem() + 15) & ~(uintptr_t)15)
 #define CC_SPIN_PAUSE() __nanosleep(20)
 #endif
 

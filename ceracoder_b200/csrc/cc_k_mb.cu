@@ -20,6 +20,7 @@
  * by libavcodec's decoder.
  */
 #include "cc_xform.cuh"
+#include "cc_deblock.cuh"
 
 #define MB_MAX_RPS 8
 
@@ -503,90 +504,6 @@ __device__ __forceinline__ unsigned emit_block(const MbCtx &c, int16_t *out, uns
     return off + 1 + (unsigned)__popc(mask);
 }
 
-/* ---- deblocking, H.264 8.7 -------------------------------------------------------------------------------------------- */
-__device__ __forceinline__ int edge_bs(const cc_mbdev *mp, int bp, const cc_mbdev *mq, int bq, int mb_edge) {
-    if (mp->type >= CC_MB_I16 || mq->type >= CC_MB_I16) return mb_edge ? 4 : 3;
-    if (((mp->nz_luma >> bp) & 1) || ((mq->nz_luma >> bq) & 1)) return 2;
-    if (cc_iabs(mp->mv[0] - mq->mv[0]) >= 4 || cc_iabs(mp->mv[1] - mq->mv[1]) >= 4) return 1;
-    return 0;
-}
-/* filter one line across an edge: pix points at q0, xs = step across the edge */
-__device__ __forceinline__ void filter_line(uint8_t *pix, ptrdiff_t xs, int bs, int chroma, int alpha, int beta, int tc0v) {
-    const int p0 = pix[-xs], p1 = pix[-2 * xs], q0 = pix[0], q1 = pix[xs];
-    if (cc_iabs(p0 - q0) >= alpha || cc_iabs(p1 - p0) >= beta || cc_iabs(q1 - q0) >= beta) return;
-    if (chroma) {
-        if (bs < 4) {
-            const int tc = tc0v + 1;
-            const int d = cc_clip3(-tc, tc, (((q0 - p0) << 2) + (p1 - q1) + 4) >> 3);
-            pix[-xs] = (uint8_t)cc_clip255(p0 + d); pix[0] = (uint8_t)cc_clip255(q0 - d);
-        } else { pix[-xs] = (uint8_t)((2 * p1 + p0 + q1 + 2) >> 2); pix[0] = (uint8_t)((2 * q1 + q0 + p1 + 2) >> 2); }
-        return;
-    }
-    const int p2 = pix[-3 * xs], q2 = pix[2 * xs];
-    const int ap = cc_iabs(p2 - p0) < beta, aq = cc_iabs(q2 - q0) < beta;
-    if (bs < 4) {
-        const int tc = tc0v + ap + aq;
-        const int d = cc_clip3(-tc, tc, (((q0 - p0) << 2) + (p1 - q1) + 4) >> 3);
-        pix[-xs] = (uint8_t)cc_clip255(p0 + d); pix[0] = (uint8_t)cc_clip255(q0 - d);
-        if (ap) pix[-2 * xs] = (uint8_t)(p1 + cc_clip3(-tc0v, tc0v, (p2 + ((p0 + q0 + 1) >> 1) - (p1 << 1)) >> 1));
-        if (aq) pix[xs] = (uint8_t)(q1 + cc_clip3(-tc0v, tc0v, (q2 + ((p0 + q0 + 1) >> 1) - (q1 << 1)) >> 1));
-    } else {
-        const int small = cc_iabs(p0 - q0) < ((alpha >> 2) + 2);
-        if (ap && small) {
-            const int p3 = pix[-4 * xs];
-            pix[-xs] = (uint8_t)((p2 + 2 * p1 + 2 * p0 + 2 * q0 + q1 + 4) >> 3);
-            pix[-2 * xs] = (uint8_t)((p2 + p1 + p0 + q0 + 2) >> 2);
-            pix[-3 * xs] = (uint8_t)((2 * p3 + 3 * p2 + p1 + p0 + q0 + 4) >> 3);
-        } else pix[-xs] = (uint8_t)((2 * p1 + p0 + q1 + 2) >> 2);
-        if (aq && small) {
-            const int q3 = pix[3 * xs];
-            pix[0] = (uint8_t)((p1 + 2 * p0 + 2 * q0 + 2 * q1 + q2 + 4) >> 3);
-            pix[xs] = (uint8_t)((p0 + q0 + q1 + q2 + 2) >> 2);
-            pix[2 * xs] = (uint8_t)((2 * q3 + 3 * q2 + q1 + q0 + p0 + 4) >> 3);
-        } else pix[0] = (uint8_t)((2 * q1 + q0 + p1 + 2) >> 2);
-    }
-}
-/* lanes 0..15: luma lines; lanes 16..31: chroma lines (plane = (lane-16)>>3) on even edges */
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, int lane, int mbx, int mby, int L, int T) {
-    const int mb = mby * k.mb_w + mbx, qp = k.qp, qpc = c_chroma_qp[qp];
-    const cc_mbdev *mq = k.mbd + mb;
-    uint8_t *Y = k.rec[0] + (size_t)(mby * 16) * k.sy + mbx * 16;
-    const int alpha = c_alpha[qp], beta = c_beta[qp], alphac = c_alpha[qpc], betac = c_beta[qpc];
-    for (int dir = 0; dir < 2; dir++) {
-        for (int ed = 0; ed < 4; ed++) {
-            const cc_mbdev *mp = mq;
-            if (ed == 0) {
-                if (dir == 0) { if (!L) continue; mp = mq - 1; }
-                else { if (!T) continue; mp = mq - k.mb_w; }
-            }
-            int bS[4], any = 0;
-#pragma unroll
-            for (int g = 0; g < 4; g++) {
-                int bq = dir == 0 ? c_blk_of[g * 4 + ed] : c_blk_of[ed * 4 + g];
-                int bp = dir == 0 ? c_blk_of[g * 4 + (ed ? ed - 1 : 3)] : c_blk_of[(ed ? ed - 1 : 3) * 4 + g];
-                bS[g] = edge_bs(mp, bp, mq, bq, ed == 0);
-                any |= bS[g];
-            }
-            if (!any) continue; /* uniform across the warp */
-            if (lane < 16) {
-                const int bs = bS[lane >> 2];
-                if (bs) {
-                    if (dir == 0) filter_line(Y + (size_t)lane * k.sy + ed * 4, 1, bs, 0, alpha, beta, c_tc0[qp][bs < 4 ? bs - 1 : 0]);
-                    else filter_line(Y + (size_t)(ed * 4) * k.sy + lane, k.sy, bs, 0, alpha, beta, c_tc0[qp][bs < 4 ? bs - 1 : 0]);
-                }
-            } else if (!(ed & 1)) {
-                const int l = lane - 16, pl = l >> 3, i = l & 7, bs = bS[i >> 1];
-                uint8_t *C = k.rec[1 + pl] + (size_t)(mby * 8) * k.sc + mbx * 8;
-                if (bs) {
-                    if (dir == 0) filter_line(C + (size_t)i * k.sc + ed * 2, 1, bs, 1, alphac, betac, c_tc0[qpc][bs < 4 ? bs - 1 : 0]);
-                    else filter_line(C + (size_t)(ed * 2) * k.sc + i, k.sc, bs, 1, alphac, betac, c_tc0[qpc][bs < 4 ? bs - 1 : 0]);
-                }
-            }
-            __syncwarp();
-        }
-    }
-}
-
 /* ---- the kernel --------------------------------------------------------------------------------------------------------- */
 __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int lane) {
     if (lane == 0) while (*flag < need) CC_SPIN_PAUSE();
@@ -594,7 +511,17 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
     __threadfence_block();
 }
 
-__device__ void encode_row(const cc_kparams &k, WarpMem *m, volatile int *progress, int w, int row, int row0, int lane) {
+/* Unfiltered neighbour samples.  Intra prediction uses the reconstruction BEFORE deblocking (H.264 8.3), while the
+ * deblocking warps of the same slice modify k.rec a few macroblocks behind the encode warps.  So the encode warps
+ * never read k.rec: the bottom sample row of every macroblock row goes to a shared-memory line (`TopLines`), the
+ * right column of the previous macroblock stays in the warp's own tile. */
+struct TopLines {
+    uint8_t *y, *c; int sy, sc; /* y: rps lines of W+32 bytes (origin +16); c: 2*rps lines of W/2+16 bytes (origin +8) */
+    __device__ __forceinline__ uint8_t *Y(int w) const { return y + w * sy + 16; }
+    __device__ __forceinline__ uint8_t *C(int pl, int w, int rps) const { return c + (pl * rps + w) * sc + 8; }
+};
+
+__device__ void encode_row(const cc_kparams &k, WarpMem *m, const TopLines &tl, volatile int *progress, int w, int row, int row0, int lane) {
     const int mw = k.mb_w, qp = k.qp;
     MbCtx c;
     c.lane = lane; c.mby = row; c.py = row * 16; c.qp = qp; c.qpc = c_chroma_qp[qp]; c.lambda = c_lambda[qp]; c.m = m;
@@ -611,21 +538,17 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, volatile int *progre
             m->curY[lane + 32] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
             const int pl = lane >> 4, r = (lane >> 1) & 7, h = lane & 1;
             m->curC[pl][r * 2 + h] = *(const uint32_t *)(k.cur[1 + pl] + (size_t)(row * 8 + r) * k.sc + mbx * 8 + 4 * h);
-            const uint8_t *ry = k.rec[0] + (size_t)c.py * k.sy + c.px;
-            if (lane < 21) { /* top-left, top, top-right */
+            if (lane < 21) { /* top-left, top, top-right: unfiltered line of the row above */
                 int x = lane - 1;
                 bool ok = c.T && (x < 0 ? c.L : (x < 16 ? true : c.TR));
-                m->tile[0][3 + lane] = ok ? ry[-(ptrdiff_t)k.sy + x] : 0;
+                m->tile[0][3 + lane] = ok ? tl.Y(w - 1)[c.px + x] : 0;
             }
-            if (lane >= 16) m->tile[1 + lane - 16][3] = c.L ? ry[(size_t)(lane - 16) * k.sy - 1] : 0; /* left column */
-            { /* chroma edges: lanes 0..16 plane 0 handled in two steps to keep it simple */
-                for (int p2 = 0; p2 < 2; p2++) {
-                    const uint8_t *rc = k.rec[1 + p2] + (size_t)(row * 8) * k.sc + mbx * 8;
-                    if (lane == 0) m->edgeC[p2][0] = (c.T && c.L) ? rc[-(ptrdiff_t)k.sc - 1] : 0;
-                    else if (lane <= 8) m->edgeC[p2][lane] = c.T ? rc[-(ptrdiff_t)k.sc + lane - 1] : 0;
-                    else if (lane <= 16) m->edgeC[p2][lane] = c.L ? rc[(size_t)(lane - 9) * k.sc - 1] : 0;
-                }
-            }
+            if (lane >= 16 && !c.L) m->tile[1 + lane - 16][3] = 0; /* left column: kept from the previous macroblock */
+            if (lane < 18) {
+                const int p2 = lane >= 9, i = lane - 9 * p2; /* i = 0: top-left, 1..8: top */
+                const uint8_t *tc = tl.C(p2, w - 1, k.rps) + mbx * 8;
+                m->edgeC[p2][i] = (i == 0 ? (c.T && c.L) : c.T) ? tc[i - 1] : 0;
+            } else if (lane < 26 && !c.L) { m->edgeC[0][9 + lane - 18] = 0; m->edgeC[1][9 + lane - 18] = 0; }
         }
         __syncwarp();
 
@@ -706,6 +629,11 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, volatile int *progre
             *(uint32_t *)(ry + (size_t)r * k.sy + h * 8 + 4) = w1;
             const int pl = lane >> 4, cr = (lane >> 1) & 7;
             *(uint32_t *)(k.rec[1 + pl] + (size_t)(row * 8 + cr) * k.sc + mbx * 8 + 4 * h) = m->recC[pl][cr * 2 + h];
+            /* unfiltered neighbours of the next macroblock (right column) and of the row below (bottom line) */
+            if (lane < 16) m->tile[1 + lane][3] = from_tile ? m->tile[1 + lane][19] : (uint8_t)(m->recY[lane * 4 + 3] >> 24);
+            else m->edgeC[(lane - 16) >> 3][9 + (lane & 7)] = (uint8_t)(m->recC[(lane - 16) >> 3][(lane & 7) * 2 + 1] >> 24);
+            if (lane < 4) *(uint32_t *)(tl.Y(w) + c.px + 4 * lane) = from_tile ? *(const uint32_t *)&m->tile[16][4 + 4 * lane] : m->recY[60 + lane];
+            else if (lane < 8) *(uint32_t *)(tl.C((lane - 4) >> 1, w, k.rps) + mbx * 8 + 4 * (lane & 1)) = m->recC[(lane - 4) >> 1][14 + (lane & 1)];
         }
         if (lane == 0) {
             cc_mbdev d;
@@ -754,22 +682,31 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, volatile int *progre
     }
 }
 
-__global__ void __launch_bounds__(MB_MAX_RPS * 32) k_mb_encode(cc_kparams k) {
+/* CTA = one slice.  Warps [0, rps) encode one macroblock row each; warps [rps, 2*rps) run the in-loop filter over the
+ * same rows, each a few macroblocks behind its encode warp and 2 macroblocks behind the filter warp of the row above. */
+__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_mb_encode(cc_kparams k) {
     __shared__ WarpMem wm[MB_MAX_RPS];
+    __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress[MB_MAX_RPS], progress2[MB_MAX_RPS];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    CC_DYN_SMEM(dsm);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const bool filt = wid >= k.rps;
+    const int w = filt ? wid - k.rps : wid;
     const int row0 = blockIdx.x * k.rps, row = row0 + w;
-    const bool valid = w < k.rps && row < k.mb_h;
-    if (lane == 0) { progress[w] = 0; progress2[w] = 0; }
+    const bool valid = row < k.mb_h;
+    TopLines tl;
+    tl.sy = k.W + 32; tl.sc = (k.W >> 1) + 16;
+    tl.y = dsm; tl.c = dsm + (size_t)k.rps * tl.sy;
+    if (lane == 0 && !filt) { progress[w] = 0; progress2[w] = 0; }
     __syncthreads();
-    if (valid) encode_row(k, &wm[w], progress, w, row, row0, lane);
-    __syncthreads();
-    /* in-loop filter over the slice, same wavefront */
-    if (valid) {
+    if (!valid) return;
+    if (!filt) {
+        encode_row(k, &wm[w], tl, progress, w, row, row0, lane);
+    } else {
         for (int mbx = 0; mbx < k.mb_w; mbx++) {
+            wait_progress(progress + w, mbx + 1, lane);
             if (w > 0) wait_progress(progress2 + w - 1, min(mbx + 2, k.mb_w), lane);
-            deblock_mb(k, lane, mbx, row, mbx > 0, w > 0);
-            __syncwarp();
+            deblock_mb(k, &dbm[w], lane, mbx, row, mbx > 0, w > 0);
             __threadfence_block();
             if (lane == 0) progress2[w] = mbx + 1;
         }
@@ -803,7 +740,15 @@ __global__ void k_pack(cc_kparams k) {
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    CC_LAUNCH(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), st, *k);
+    const size_t smem = (size_t)k->rps * (2 * (size_t)k->W + 64);
+#ifndef CC_EMU
+    static size_t smem_set = 0; /* opt in above the 48 KB default once (wide pictures with many rows per slice) */
+    if (smem > smem_set) {
+        if (cudaFuncSetAttribute(k_mb_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
+        smem_set = smem;
+    }
+#endif
+    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), smem, st, *k);
     return 1;
 }
 extern "C" int cck_pack(const cc_kparams *k, cudaStream_t st) {
