@@ -110,21 +110,27 @@ class ClockSampler:
 
 def run_streams(encs, frames_of, n_frames, start_idx, device_frames):
     """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes)."""
-    tot = [0, 0, 0]
+    tot = [0, 0, 0, 0, 0, 0, 0, 0]
     lock = threading.Lock()
     errs = []
 
     def work(k, e):
         try:
             nb = ns = 0
+            st = [0, 0, 0, 0, 0]
             for i in range(n_frames):
                 fi = start_idx + i
                 e.set_property("bitrate", schedule_kbps(fi + 37 * k))
                 y, u, v = frames_of(k, fi)
                 e.submit(y, u, v, pts=fi, device_frame=device_frames)
                 nb += e.collect(copy=False); ns += e.last.sym_bytes
+                L = e.last
+                for j, v in enumerate((L.n_skip, L.n_inter, L.n_intra, L.n_intra_analysed, L.n_skip_probed)):
+                    st[j] += v
             with lock:
                 tot[0] += n_frames; tot[1] += nb; tot[2] += ns
+                for j in range(5):
+                    tot[3 + j] += st[j]
         except Exception as ex:  # noqa: BLE001
             errs.append(ex)
     th = [threading.Thread(target=work, args=(k, e)) for k, e in enumerate(encs)]
@@ -239,7 +245,7 @@ def main():
             dist.barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter(); ev0.record()
-        frames, au_bytes, sym_bytes = run_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), device_frames)
+        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), device_frames)
         torch.cuda.synchronize(); ev1.record(); torch.cuda.synchronize()
         wall_ms = 1e3 * (time.perf_counter() - t0)
         ms = max(ev0.elapsed_time(ev1), 1e-3)
@@ -253,7 +259,7 @@ def main():
                     a = stages.setdefault(s, [0.0, 0]); a[0] += tms; a[1] += n
         qps = [e.last.qp for e in encs]
         [e.close() for e in encs]
-        return dict(frames=frames, ms=ms, wall_ms=wall_ms, au_bytes=au_bytes, sym_bytes=sym_bytes, launches=launches, stages=stages, qps=qps)
+        return dict(frames=frames, ms=ms, wall_ms=wall_ms, au_bytes=au_bytes, sym_bytes=sym_bytes, launches=launches, stages=stages, qps=qps, mbstats=mbstats)
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -305,6 +311,7 @@ def main():
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
+            "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"]])),
             "wall_ms": {"value_leg": r_dev["wall_ms"], "e2e_leg": r_e2e["wall_ms"]}}
     print(json.dumps(line))
     if world > 1:

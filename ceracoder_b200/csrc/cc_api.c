@@ -22,7 +22,7 @@ struct cc_enc {
     cc_seq seq;
     cudaStream_t st;
     cudaEvent_t ev0, ev1;
-    void *dev_alloc[24];
+    void *dev_alloc[32];
     int n_dev_alloc;
     size_t dev_bytes;
     uint8_t *out_host;   /* mapped pinned: packed symbols */
@@ -72,7 +72,7 @@ void cc_enc_params_default(cc_enc_params *p) {
 }
 
 static int dev_alloc(cc_enc *e, void **p, size_t n) {
-    if (e->n_dev_alloc >= 24) return CC_ERR_NOMEM;
+    if (e->n_dev_alloc >= 32) return CC_ERR_NOMEM;
     if (cudaMalloc(p, n) != cudaSuccess) { fprintf(stderr, "ceracuda: cudaMalloc(%zu) failed\n", n); return CC_ERR_NOMEM; }
     e->dev_alloc[e->n_dev_alloc++] = *p;
     e->dev_bytes += n;
@@ -127,7 +127,14 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->pre, sizeof(cc_pre) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->symlen, sizeof(uint16_t) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[0], (size_t)k->mb_h * k->sy);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[1], (size_t)k->mb_h * k->sc);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[2], (size_t)k->mb_h * k->sc);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->uright, (size_t)nmb * 32);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowhdr, sizeof(cc_rowhdr) * k->mb_h);
+    if (rc == CC_OK && getenv("CC_DEBUG_CYCLES")) { rc = dev_alloc(e, (void **)&k->cyc, (size_t)k->mb_h * 16 * 8); if (rc == CC_OK) cudaMemset(k->cyc, 0, (size_t)k->mb_h * 16 * 8); }
     if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
     /* packed symbol buffer: headers + per-MB records + payload (worst case) */
     e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(cc_mbhost) * nmb, 16) + (size_t)nmb * CC_ROW_PAYLOAD_PER_MB + 16 * k->mb_h);
@@ -156,6 +163,17 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
 void cc_enc_close(cc_enc *e) {
     if (!e) return;
     if (e->st) cudaStreamSynchronize(e->st);
+    if (e->k.cyc && e->frame_idx > 0) { /* CC_DEBUG_CYCLES=1: where the wavefront kernel's warps spent their cycles */
+        size_t n = (size_t)e->k.mb_h * 16;
+        unsigned long long *h = (unsigned long long *)calloc(n, 8), s[16] = {0};
+        if (h && cudaMemcpy(h, e->k.cyc, n * 8, cudaMemcpyDeviceToHost) == cudaSuccess) {
+            for (size_t i = 0; i < n; i++) s[i & 15] += h[i];
+            double f = 1.0 / ((double)e->frame_idx * e->k.mb_h);
+            fprintf(stderr, "ceracuda cycles per MB row per frame: encode wait %.0f fast %.0f (n %.1f) probe %.0f (n %.1f) intra %.0f (n %.1f) | filter wait-enc %.0f wait-up %.0f work %.0f\n",
+                    s[0] * f, s[1] * f, s[4] * f, s[2] * f, s[5] * f, s[3] * f, s[6] * f, s[8] * f, s[9] * f, s[10] * f);
+        }
+        free(h);
+    }
     for (int i = 0; i < e->n_dev_alloc; i++) cudaFree(e->dev_alloc[i]);
     if (e->out_host) cudaFreeHost(e->out_host);
     if (e->ev0) cudaEventDestroy(e->ev0);
@@ -237,6 +255,8 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (!is_idr) e->launches += cck_me_l1(k, e->st);
     STAGE(CC_STAGE_ME_FINE);
     if (!is_idr) e->launches += cck_me_l0(k, e->st);
+    STAGE(CC_STAGE_P_CODE);
+    if (!is_idr) e->launches += cck_p_code(k, e->st);
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
     STAGE(CC_STAGE_BORDER);
@@ -273,7 +293,7 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
         for (int i = 0; i < CC_N_STAGES; i++) {
             float ms = 0;
             if ((i == CC_STAGE_UPLOAD || e->pev_used[i]) && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) {
-                if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
+                if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
             }
         }
     double t0 = now_ms();
@@ -283,11 +303,11 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     const uint8_t *pay = (const uint8_t *)mbh + roundup(sizeof(cc_mbhost) * nmb, 16);
     const uint8_t *rowp[512];
     if (k->mb_h > 512) return CC_ERR_PARAM;
-    int ns = 0, ni = 0, np = 0;
+    int ns = 0, ni = 0, np = 0, ng = 0, npr = 0;
     for (int r = 0; r < k->mb_h; r++) {
         rowp[r] = pay;
         pay += roundup(rh[r].bytes, 16);
-        ns += (int)rh[r].n_skip; np += (int)rh[r].n_inter; ni += (int)rh[r].n_intra;
+        ns += (int)rh[r].n_skip; np += (int)rh[r].n_inter; ni += (int)rh[r].n_intra; ng += (int)rh[r].n_gate; npr += (int)rh[r].n_probe;
         if ((size_t)(pay - e->out_host) > e->out_cap) return CC_ERR_OVERFLOW;
     }
     size_t n = 0;
@@ -320,7 +340,7 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     e->gop_pos++;
     e->frame_idx++;
     out->data = e->au; out->size = (int)n; out->is_idr = is_idr; out->qp = e->cur_qp; out->pts = e->cur_pts;
-    out->n_skip = ns; out->n_inter = np; out->n_intra = ni;
+    out->n_skip = ns; out->n_inter = np; out->n_intra = ni; out->n_intra_analysed = ng; out->n_skip_probed = npr;
     out->sym_bytes = (int)(pay - e->out_host);
     out->gpu_ms = gpu_ms; out->host_ms = (float)(now_ms() - t0);
     return CC_OK;

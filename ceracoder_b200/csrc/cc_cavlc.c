@@ -92,6 +92,7 @@ int cc_cavlc_write_slice(cc_cavlc_ctx *c, cc_bw *b, int is_idr, int row0, int ro
             memset(nz, 0, 24);
             if (m->type == CC_MB_PSKIP) { if (!P) return -1; skip_run++; continue; }
             if (P) { cc_bw_ue(b, skip_run); skip_run = 0; }
+            pay = row_payload[mby] + (((size_t)(pay - row_payload[mby]) + 3) & ~(size_t)3); /* every MB's symbols start 4-byte aligned */
             const int cl = m->cbp & 15, cc = m->cbp >> 4, i16 = m->type == CC_MB_I16;
             if (m->type == CC_MB_P16) {
                 if (!P) return -1;

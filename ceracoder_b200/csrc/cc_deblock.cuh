@@ -7,7 +7,7 @@
  * macroblock plus the 4 pixels left of / above it into shared memory once (172 coalesced word loads), every lane
  * then filters one whole pixel line in registers (lanes 0-15: a luma row / column across its 4 edges, lanes 16-31:
  * a chroma row / column of Cb or Cr across its 2 edges), and the tile is stored back once.
- * Boundary strengths come from the first 8 bytes of three cc_mbdev records (current, left, top).
+ * Boundary strengths come from the slice's shared-memory neighbour lines (type, nz flags, mv of current, left, top).
  * Oracle counterpart: oracle/ref_mb.c ref_mb_deblock.
  */
 #ifndef CC_DEBLOCK_CUH
@@ -17,7 +17,6 @@
 struct __align__(16) DbMem {
     uint8_t Y[20][24];    /* Y[r + 4][c + 4] = luma sample (c, r) of the macroblock, r,c in -4..15 */
     uint8_t C[2][12][16]; /* C[pl][r + 4][c + 4], r,c in -4..7 */
-    uint32_t nb[3][2];    /* first two words of cc_mbdev: 0 current, 1 left, 2 top */
 };
 
 /* boundary strength between 4x4 blocks bp (of the record p) and bq (of q), H.264 8.7.2.1, single reference picture */
@@ -28,6 +27,10 @@ __device__ __forceinline__ int db_bs(uint32_t p0, uint32_t p1, int bp, uint32_t 
     const int dy = (int)(int16_t)(p1 >> 16) - (int)(int16_t)(q1 >> 16);
     return (cc_iabs(dx) >= 4 || cc_iabs(dy) >= 4) ? 1 : 0;
 }
+
+/* raster 4x4 block index (by*4+bx) -> decoding-order index (Figure 6-10), computed (a constant-memory table with a
+ * lane-dependent index would serialise) */
+__device__ __forceinline__ int db_blk(int i) { return ((i >> 3) << 3) | (((i >> 1) & 1) << 2) | (((i >> 2) & 1) << 1) | (i & 1); }
 
 /* luma edge, 8.7.2.3 (bS < 4) and 8.7.2.4 (bS == 4) */
 __device__ __forceinline__ void db_luma(int p3, int &p2, int &p1, int &p0, int &q0, int &q1, int &q2, int q3, int bs, int alpha, int beta, int tc0v) {
@@ -89,45 +92,50 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
 }
 
 /* One macroblock.  L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, int lane, int mbx, int mby, int L, int T) {
-    const int mb = mby * k.mb_w + mbx, qp = k.qp, qpc = c_chroma_qp[qp];
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const uint2 *nbl, int lane, int mbx, int mby, int L, int T) {
+    const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
-    /* ---- stage ---- */
-    {
-        uint32_t ly[4], lc[3];
-#pragma unroll
-        for (int it = 0; it < 4; it++) {
-            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
-        }
-#pragma unroll
-        for (int it = 0; it < 3; it++) {
-            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
-        }
-        if (lane < 6) {
-            const int which = lane >> 1; /* 0 current, 1 left, 2 top */
-            const int nmb = which == 0 ? mb : (which == 1 ? (L ? mb - 1 : mb) : (T ? mb - k.mb_w : mb));
-            db->nb[which][lane & 1] = ((const uint32_t *)(k.mbd + nmb))[lane & 1];
-        }
-#pragma unroll
-        for (int it = 0; it < 4; it++) {
-            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
-        }
-#pragma unroll
-        for (int it = 0; it < 3; it++) {
-            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
-        }
-    }
-    __syncwarp();
-    const uint32_t q0 = db->nb[0][0], q1 = db->nb[0][1];
     const bool luma = lane < 16;
     const int li = lane & 15;                 /* luma line, or chroma: plane = li >> 3, line = li & 7 */
     const int g = luma ? li >> 2 : (li & 7) >> 1;
     const int cpl = li >> 3, ci = li & 7;
+    /* ---- boundary strengths first: most macroblocks of a P frame have nothing to filter ---- */
+    const uint2 nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
+    uint32_t ly[4], lc[3];
+#pragma unroll
+    for (int it = 0; it < 4; it++) {
+        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+        ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
+    }
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+        lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+    }
+    const uint32_t q0 = nq.x, q1 = nq.y;
+    int bsv[4], bsh[4], any = 0;
+    const int blk_row = g * 4; /* raster index of the first 4x4 block of this lane's block row / column */
+#pragma unroll
+    for (int ed = 0; ed < 4; ed++) {
+        const int pe = ed ? ed - 1 : 3;
+        bsv[ed] = (ed == 0 && !L) ? 0 : db_bs(ed == 0 ? nl.x : q0, ed == 0 ? nl.y : q1, db_blk(blk_row + pe), q0, q1, db_blk(blk_row + ed), ed == 0);
+        bsh[ed] = (ed == 0 && !T) ? 0 : db_bs(ed == 0 ? nt.x : q0, ed == 0 ? nt.y : q1, db_blk(pe * 4 + g), q0, q1, db_blk(ed * 4 + g), ed == 0);
+        any |= bsv[ed] | bsh[ed];
+    }
+    if (!__any_sync(FULL, any)) return;
+    /* ---- stage ---- */
+#pragma unroll
+    for (int it = 0; it < 4; it++) {
+        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+        if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
+    }
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+        if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
+    }
+    __syncwarp();
     const int alpha = c_alpha[luma ? qp : qpc], beta = c_beta[luma ? qp : qpc];
     int tc0[3];
 #pragma unroll
@@ -135,12 +143,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, int l
 
     /* ---- vertical edges: one lane = one pixel row ---- */
     {
-        int bs[4];
-#pragma unroll
-        for (int ed = 0; ed < 4; ed++) {
-            const uint32_t p0 = ed == 0 ? db->nb[1][0] : q0, p1 = ed == 0 ? db->nb[1][1] : q1;
-            bs[ed] = db_bs(p0, p1, c_blk_of[g * 4 + (ed ? ed - 1 : 3)], q0, q1, c_blk_of[g * 4 + ed], ed == 0);
-        }
+        const int *bs = bsv;
         const int first = L ? 0 : 1;
         if (luma) {
             uint32_t w[5];
@@ -169,12 +172,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, int l
     __syncwarp();
     /* ---- horizontal edges: one lane = one pixel column ---- */
     {
-        int bs[4];
-#pragma unroll
-        for (int ed = 0; ed < 4; ed++) {
-            const uint32_t p0 = ed == 0 ? db->nb[2][0] : q0, p1 = ed == 0 ? db->nb[2][1] : q1;
-            bs[ed] = db_bs(p0, p1, c_blk_of[(ed ? ed - 1 : 3) * 4 + g], q0, q1, c_blk_of[ed * 4 + g], ed == 0);
-        }
+        const int *bs = bsh;
         const int first = T ? 0 : 1;
         if (luma) {
             int v[20];

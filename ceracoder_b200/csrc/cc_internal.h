@@ -49,10 +49,25 @@ typedef struct {
     int16_t mvd[2];
 } cc_mbhost; /* 8 bytes */
 
+/* result of the parallel P-frame pre-pass (k_p_code) for one macroblock: the MB coded as P_L0_16x16 at the motion
+ * search vector (levels in the MB's symbol slot, reconstruction in k.rec), plus skip probes at the two most likely
+ * P_Skip vectors.  The wavefront kernel only decides; it recomputes nothing for macroblocks that stay inter. */
+typedef struct {
+    uint8_t cbp;        /* luma 8x8 bits | chroma << 4, coded at me.mv */
+    uint8_t skip_ok;    /* bit 0: nothing survives at cand[] ; bit 1: nothing survives at (0,0) */
+    uint16_t nz_luma;
+    int16_t cand[2];    /* P_Skip vector predicted from the neighbours' search vectors */
+    uint16_t sym_len;   /* int16 units used in the MB's symbol slot */
+    uint16_t pad;
+    int32_t est_intra;  /* Intra16x16 SATD cost with SOURCE neighbours: gate of the real intra analysis */
+} cc_pre; /* 16 bytes */
+
 /* per-MB-row symbol stream header, written by the encode kernel */
 typedef struct {
     uint32_t bytes;   /* payload bytes used by this row (multiple of 2) */
     uint32_t n_skip, n_inter, n_intra;
+    uint32_t n_gate, n_probe; /* P frames: MBs that ran the real intra analysis / the in-wavefront skip probe */
+    uint32_t pad;
 } cc_rowhdr;
 
 #define CC_ROW_PAYLOAD_PER_MB 1024 /* worst case: 8 (i4 modes) + 27 blocks * (2 + 32) = 926 bytes */
@@ -71,13 +86,18 @@ typedef struct {
     cc_me *me;
     cc_mbdev *mbd;
     cc_mbhost *mbh;    /* device copy */
-    uint8_t *rowbuf;   /* mb_h rows * mb_w * CC_ROW_PAYLOAD_PER_MB */
+    cc_pre *pre;
+    uint16_t *symlen;  /* per MB: int16 units used in its symbol slot (even; 0 for P_Skip) */
+    uint8_t *ubot[3];  /* unfiltered bottom sample line of every MB row: [mb_h][sy] luma, [mb_h][sc] per chroma plane */
+    uint8_t *uright;   /* unfiltered right column of every MB: 32 bytes {16 luma, 8 Cb, 8 Cr} */
+    uint8_t *rowbuf;   /* one symbol slot of CC_ROW_PAYLOAD_PER_MB bytes per macroblock */
     cc_rowhdr *rowhdr; /* device */
     int qp, is_idr;
     uint16_t qmf[4][3], qbias[4][3]; /* quantiser: 0 luma intra, 1 luma inter, 2 chroma intra, 3 chroma inter; class-indexed */
     /* packed output in mapped pinned host memory: [cc_rowhdr * mb_h][cc_mbhost * nmb][payload rows, 16-byte aligned] */
     uint8_t *out_host_dev; /* device pointer of that mapping */
     uint32_t out_cap;
+    unsigned long long *cyc; /* debug (CC_DEBUG_CYCLES=1): per MB row 8 cycle counters of the wavefront kernel, or NULL */
 } cc_kparams;
 
 /* kernel launch wrappers (cc_kernels.cu); each returns the number of kernels launched */
@@ -89,6 +109,7 @@ int cck_l1ref(const cc_kparams *k, cudaStream_t st);
 int cck_me_l1(const cc_kparams *k, cudaStream_t st);
 int cck_me_l0(const cc_kparams *k, cudaStream_t st);
 int cck_motion(const cc_kparams *k, cudaStream_t st);
+int cck_p_code(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);
 int cck_pack(const cc_kparams *k, cudaStream_t st);
 

@@ -403,13 +403,8 @@ __device__ __forceinline__ void nb_mv(const cc_mbdev *n, int avail, int &ref, in
     if (n->type >= CC_MB_I16) { ref = -1; return; }
     ref = 0; mv[0] = n->mv[0]; mv[1] = n->mv[1];
 }
-__device__ __forceinline__ void predict_mv(const cc_kparams &k, const MbCtx &c, int mvp[2], int skip[2]) {
-    const cc_mbdev *me = k.mbd + c.mb;
-    int rA, rB, rC, a[2], b[2], cc[2];
-    nb_mv(me - 1, c.L, rA, a);
-    nb_mv(me - k.mb_w, c.T, rB, b);
-    nb_mv(me - k.mb_w + 1, c.TR, rC, cc);
-    if (rC == -2) nb_mv(me - k.mb_w - 1, c.T && c.L, rC, cc);
+/* rX: -2 unavailable, -1 intra, 0 inter (the one reference picture) */
+__device__ __forceinline__ void predict_mv_core(int L, int T, int rA, int a[2], int rB, int b[2], int rC, int cc[2], int mvp[2], int skip[2]) {
     const int rA0 = rA, rB0 = rB, a0x = a[0], a0y = a[1], b0x = b[0], b0y = b[1];
     if (rB == -2 && rC == -2 && rA != -2) { rB = rC = rA; b[0] = cc[0] = a[0]; b[1] = cc[1] = a[1]; }
     const int n = (rA == 0) + (rB == 0) + (rC == 0);
@@ -419,8 +414,25 @@ __device__ __forceinline__ void predict_mv(const cc_kparams &k, const MbCtx &c, 
         else { mvp[0] = cc[0]; mvp[1] = cc[1]; }
     } else { mvp[0] = cc_median3(a[0], b[0], cc[0]); mvp[1] = cc_median3(a[1], b[1], cc[1]); }
     /* P_Skip vector, 8.4.1.1 */
-    if (!c.L || !c.T || (rA0 == 0 && a0x == 0 && a0y == 0) || (rB0 == 0 && b0x == 0 && b0y == 0)) skip[0] = skip[1] = 0;
+    if (!L || !T || (rA0 == 0 && a0x == 0 && a0y == 0) || (rB0 == 0 && b0x == 0 && b0y == 0)) skip[0] = skip[1] = 0;
     else { skip[0] = mvp[0]; skip[1] = mvp[1]; }
+}
+/* neighbour record as the slice keeps it in shared memory: x = type | nz_luma << 16, y = mv (x | y << 16) */
+__device__ __forceinline__ void nb_mv2(uint2 n, int avail, int &ref, int mv[2]) {
+    mv[0] = mv[1] = 0;
+    if (!avail) { ref = -2; return; }
+    if ((n.x & 255u) >= CC_MB_I16) { ref = -1; return; }
+    ref = 0; mv[0] = (int)(int16_t)(n.y & 0xffffu); mv[1] = (int)(int16_t)(n.y >> 16);
+}
+/* nbl: this row's line, nbu: the line of the row above (valid where c.T) */
+__device__ __forceinline__ void predict_mv(const MbCtx &c, const uint2 *nbl, const uint2 *nbu, int mvp[2], int skip[2]) {
+    int rA, rB, rC, a[2], b[2], cc[2];
+    const uint2 z = make_uint2(0u, 0u);
+    nb_mv2(c.L ? nbl[c.mbx - 1] : z, c.L, rA, a);
+    nb_mv2(c.T ? nbu[c.mbx] : z, c.T, rB, b);
+    nb_mv2(c.TR ? nbu[c.mbx + 1] : z, c.TR, rC, cc);
+    if (rC == -2) nb_mv2((c.T && c.L) ? nbu[c.mbx - 1] : z, c.T && c.L, rC, cc);
+    predict_mv_core(c.L, c.T, rA, a, rB, b, rC, cc, mvp, skip);
 }
 
 /* ---- intra chroma ------------------------------------------------------------------------------------------------ */
@@ -504,6 +516,23 @@ __device__ __forceinline__ unsigned emit_block(const MbCtx &c, int16_t *out, uns
     return off + 1 + (unsigned)__popc(mask);
 }
 
+/* all residual blocks of one macroblock in syntax order; the slot length is padded to a 4-byte multiple */
+__device__ __forceinline__ unsigned emit_mb(const MbCtx &c, int16_t *out, unsigned off, int type, int cbp) {
+    const int cl = cbp & 15, cc = cbp >> 4;
+    if (type == CC_MB_I16 || cbp) {
+        if (type == CC_MB_I16) off = emit_block(c, out, off, 24, 16);
+        for (int blk = 0; blk < 16; blk++)
+            if (cl & (1 << (blk >> 2))) off = emit_block(c, out, off, blk, type == CC_MB_I16 ? 15 : 16);
+        if (cc) {
+            off = emit_block(c, out, off, 25, 4);
+            off = emit_block(c, out, off, 26, 4);
+            if (cc & 2) for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, off, blk, 15);
+        }
+    }
+    if (off & 1u) { if (c.lane == 0) out[off] = 0; off++; }
+    return off;
+}
+
 /* ---- the kernel --------------------------------------------------------------------------------------------------------- */
 __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int lane) {
     if (lane == 0) while (*flag < need) CC_SPIN_PAUSE();
@@ -511,129 +540,173 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
     __threadfence_block();
 }
 
-/* Unfiltered neighbour samples.  Intra prediction uses the reconstruction BEFORE deblocking (H.264 8.3), while the
- * deblocking warps of the same slice modify k.rec a few macroblocks behind the encode warps.  So the encode warps
- * never read k.rec: the bottom sample row of every macroblock row goes to a shared-memory line (`TopLines`), the
- * right column of the previous macroblock stays in the warp's own tile. */
-struct TopLines {
-    uint8_t *y, *c; int sy, sc; /* y: rps lines of W+32 bytes (origin +16); c: 2*rps lines of W/2+16 bytes (origin +8) */
-    __device__ __forceinline__ uint8_t *Y(int w) const { return y + w * sy + 16; }
-    __device__ __forceinline__ uint8_t *C(int pl, int w, int rps) const { return c + (pl * rps + w) * sc + 8; }
-};
+/* does the macroblock coded at (mvx,mvy) leave nothing after quantisation + decimation?  (P_Skip test) */
+__device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
+    mc_luma16(k, c, mvx, mvy);
+    mc_chroma8(k, c, mvx, mvy);
+    __syncwarp();
+    unsigned nz;
+    const bool zl = inter_luma(k, c, true, &nz) == 0;
+    const bool zc = encode_chroma(k, c, false, true) == 0;
+    __syncwarp();
+    return zl && zc;
+}
 
-__device__ void encode_row(const cc_kparams &k, WarpMem *m, const TopLines &tl, volatile int *progress, int w, int row, int row0, int lane) {
+/* Unfiltered neighbour samples.  Intra prediction uses the reconstruction BEFORE deblocking (H.264 8.3), while the
+ * filter warps of the same slice modify k.rec a few macroblocks behind the encode warps, and in P frames most
+ * macroblocks are reconstructed by the parallel pre-pass, not by this warp.  So whoever reconstructs a macroblock
+ * also writes its bottom sample line to k.ubot and its right column to k.uright, and intra analysis reads only those. */
+__device__ __forceinline__ void publish_unfiltered(const cc_kparams &k, int lane, int mb, int mbx, int row, const uint32_t *recY /*64 words*/,
+                                                   const uint32_t *recC0, const uint32_t *recC1 /*16 words each*/) {
+    if (lane < 4) *(uint32_t *)(k.ubot[0] + (size_t)row * k.sy + mbx * 16 + 4 * lane) = recY[60 + lane];
+    else if (lane < 6) *(uint32_t *)(k.ubot[1] + (size_t)row * k.sc + mbx * 8 + 4 * (lane - 4)) = recC0[14 + lane - 4];
+    else if (lane < 8) *(uint32_t *)(k.ubot[2] + (size_t)row * k.sc + mbx * 8 + 4 * (lane - 6)) = recC1[14 + lane - 6];
+    uint8_t *ur = k.uright + (size_t)mb * 32;
+    if (lane < 16) ur[lane] = (uint8_t)(recY[lane * 4 + 3] >> 24);
+    else if (lane < 24) ur[lane] = (uint8_t)(recC0[(lane - 16) * 2 + 1] >> 24);
+    else ur[lane] = (uint8_t)(recC1[(lane - 24) * 2 + 1] >> 24);
+}
+/* recY/recC of the warp's WarpMem -> k.rec, k.ubot, k.uright */
+__device__ __forceinline__ void publish_pixels(const cc_kparams &k, const MbCtx &c) {
+    WarpMem *m = c.m;
+    const int lane = c.lane, r = lane >> 1, h = lane & 1;
+    uint8_t *ry = k.rec[0] + (size_t)c.py * k.sy + c.px;
+    *(uint32_t *)(ry + (size_t)r * k.sy + h * 8) = m->recY[r * 4 + h * 2];
+    *(uint32_t *)(ry + (size_t)r * k.sy + h * 8 + 4) = m->recY[r * 4 + h * 2 + 1];
+    const int pl = lane >> 4, cr = (lane >> 1) & 7;
+    *(uint32_t *)(k.rec[1 + pl] + (size_t)(c.mby * 8 + cr) * k.sc + c.mbx * 8 + 4 * h) = m->recC[pl][cr * 2 + h];
+    publish_unfiltered(k, lane, c.mb, c.mbx, c.mby, m->recY, m->recC[0], m->recC[1]);
+}
+__device__ __forceinline__ void stage_cur(const cc_kparams &k, const MbCtx &c) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
+    const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + c.px;
+    m->curY[lane] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
+    m->curY[lane + 32] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
+    const int pl = lane >> 4, r = (lane >> 1) & 7, h = lane & 1;
+    m->curC[pl][r * 2 + h] = *(const uint32_t *)(k.cur[1 + pl] + (size_t)(c.mby * 8 + r) * k.sc + c.mbx * 8 + 4 * h);
+}
+/* neighbour samples for intra prediction into m->tile (row 0, column 3) and m->edgeC */
+__device__ __forceinline__ void stage_neighbours(const cc_kparams &k, const MbCtx &c) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
+    const uint8_t *ur = k.uright + (size_t)(c.mb - 1) * 32;
+    if (lane < 21) { /* top-left, top, top-right */
+        const int x = lane - 1;
+        const bool ok = c.T && (x < 0 ? c.L : (x < 16 ? true : c.TR));
+        m->tile[0][3 + lane] = ok ? k.ubot[0][(size_t)(c.mby - 1) * k.sy + c.px + x] : 0;
+    }
+    if (lane >= 16) m->tile[1 + lane - 16][3] = c.L ? ur[lane - 16] : 0;
+    if (lane < 18) {
+        const int p2 = lane >= 9, i = lane - 9 * p2; /* i = 0: top-left, 1..8: top */
+        const bool ok = i == 0 ? (c.T && c.L) : c.T;
+        m->edgeC[p2][i] = ok ? k.ubot[1 + p2][(size_t)(c.mby - 1) * k.sc + c.mbx * 8 + i - 1] : 0;
+    }
+    if (lane < 16) m->edgeC[lane >> 3][9 + (lane & 7)] = c.L ? ur[16 + lane] : 0;
+}
+
+__device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volatile int *progress, int w, int row, int row0, int lane) {
     const int mw = k.mb_w, qp = k.qp;
     MbCtx c;
     c.lane = lane; c.mby = row; c.py = row * 16; c.qp = qp; c.qpc = c_chroma_qp[qp]; c.lambda = c_lambda[qp]; c.m = m;
     c.T = row > row0;
-    int16_t *out = (int16_t *)(k.rowbuf + (size_t)row * mw * CC_ROW_PAYLOAD_PER_MB);
-    unsigned off = 0, n_skip = 0, n_inter = 0, n_intra = 0;
+    unsigned total = 0, n_skip = 0, n_inter = 0, n_intra = 0, n_gate = 0, n_probe = 0;
+    uint2 *nbl = nbline + w * mw;
+    const uint2 *nbu = nbl - mw;
     for (int mbx = 0; mbx < mw; mbx++) {
         c.mbx = mbx; c.px = mbx * 16; c.mb = row * mw + mbx; c.L = mbx > 0; c.TR = c.T && mbx + 1 < mw;
+        int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
+        unsigned off = 0;
+        cc_me me = {{0, 0}, {0, 0}, 0};
+        cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0};
+        if (!k.is_idr) { me = k.me[c.mb]; pre = k.pre[c.mb]; } /* independent of the neighbours: issued before the wait */
+        stage_cur(k, c);
+        const long long t0 = k.cyc ? clock64() : 0;
         if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
-        /* ---- stage the current MB and its reconstructed neighbourhood ---- */
-        {
-            const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + c.px;
-            m->curY[lane] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
-            m->curY[lane + 32] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
-            const int pl = lane >> 4, r = (lane >> 1) & 7, h = lane & 1;
-            m->curC[pl][r * 2 + h] = *(const uint32_t *)(k.cur[1 + pl] + (size_t)(row * 8 + r) * k.sc + mbx * 8 + 4 * h);
-            if (lane < 21) { /* top-left, top, top-right: unfiltered line of the row above */
-                int x = lane - 1;
-                bool ok = c.T && (x < 0 ? c.L : (x < 16 ? true : c.TR));
-                m->tile[0][3 + lane] = ok ? tl.Y(w - 1)[c.px + x] : 0;
-            }
-            if (lane >= 16 && !c.L) m->tile[1 + lane - 16][3] = 0; /* left column: kept from the previous macroblock */
-            if (lane < 18) {
-                const int p2 = lane >= 9, i = lane - 9 * p2; /* i = 0: top-left, 1..8: top */
-                const uint8_t *tc = tl.C(p2, w - 1, k.rps) + mbx * 8;
-                m->edgeC[p2][i] = (i == 0 ? (c.T && c.L) : c.T) ? tc[i - 1] : 0;
-            } else if (lane < 26 && !c.L) { m->edgeC[0][9 + lane - 18] = 0; m->edgeC[1][9 + lane - 18] = 0; }
-        }
-        __syncwarp();
+        const long long t1 = k.cyc ? clock64() : 0;
+        int path = 0; /* 0 fast, 1 skip probe, 2 intra analysis */
 
-        int type, mode16 = 2, chroma_mode = 0, cbp = 0, mvx = 0, mvy = 0, mvdx = 0, mvdy = 0;
+        int type = CC_MB_P16, mode16 = 2, chroma_mode = 0, cbp = 0, mvx = 0, mvy = 0, mvdx = 0, mvdy = 0;
         unsigned nzmask = 0;
         int mvp[2] = {0, 0}, skipmv[2] = {0, 0};
         int cost_inter = 1 << 30, cost_i4 = 1 << 30;
-        bool done = false, from_tile = false;
-        const cc_me me = k.me[c.mb];
+        bool done = false;
 
         if (!k.is_idr) {
-            predict_mv(k, c, mvp, skipmv);
-            /* [EXT] x264 probe_skip: code the MB at the P_Skip vector; nothing left after decimation -> P_Skip */
-            mc_luma16(k, c, skipmv[0], skipmv[1]);
-            __syncwarp();
-            unsigned nz;
-            if (inter_luma(k, c, true, &nz) == 0) {
-                mc_chroma8(k, c, skipmv[0], skipmv[1]);
-                __syncwarp();
-                if (encode_chroma(k, c, false, true) == 0) {
-                    type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
+            predict_mv(c, nbl, nbu, mvp, skipmv);
+            /* [EXT] x264 probe_skip: would the MB coded at the P_Skip vector leave nothing after decimation?  The
+             * pre-pass answered that for its search vector and for the two likeliest skip vectors. */
+            bool zero;
+            if (skipmv[0] == me.mv[0] && skipmv[1] == me.mv[1]) zero = pre.cbp == 0;
+            else if (skipmv[0] == pre.cand[0] && skipmv[1] == pre.cand[1]) zero = pre.skip_ok & 1;
+            else if (skipmv[0] == 0 && skipmv[1] == 0) zero = (pre.skip_ok >> 1) & 1;
+            else { n_probe++; path = 1; zero = probe_zero(k, c, skipmv[0], skipmv[1]); }
+            if (zero) {
+                type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
+                if (mvx != me.mv[0] || mvy != me.mv[1]) { /* reconstruction = prediction at the skip vector */
+                    mc_luma16(k, c, mvx, mvy);
+                    mc_chroma8(k, c, mvx, mvy);
+                    __syncwarp();
                     m->recY[lane] = m->predY[lane]; m->recY[lane + 32] = m->predY[lane + 32];
                     m->recC[lane >> 4][lane & 15] = m->predC[lane >> 4][lane & 15];
                     __syncwarp();
-                    done = true;
+                    publish_pixels(k, c);
                 }
-            }
-            if (!done) cost_inter = me.satd + c.lambda * (cc_se_bits(me.mv[0] - mvp[0]) + cc_se_bits(me.mv[1] - mvp[1]));
+                done = true;
+            } else cost_inter = me.satd + c.lambda * (cc_se_bits(me.mv[0] - mvp[0]) + cc_se_bits(me.mv[1] - mvp[1]));
         }
         if (!done) {
+            /* P frames: real intra analysis only when the pre-pass' source-based estimate is within 25 % of inter */
+            const bool gate = k.is_idr || pre.est_intra * 4 <= cost_inter * 5;
             I16Params ip;
-            i16_params(c, ip);
-            int cost_i16 = analyse_i16(c, ip, &mode16);
-            if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c);
-            if (!k.is_idr) { cost_i16 += 8 * c.lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * c.lambda; }
+            int cost_i16 = 1 << 30;
+            if (gate) {
+                n_gate++; path = 2;
+                stage_neighbours(k, c);
+                __syncwarp();
+                i16_params(c, ip);
+                cost_i16 = analyse_i16(c, ip, &mode16);
+                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c);
+                if (!k.is_idr) { cost_i16 += 8 * c.lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * c.lambda; }
+            }
             if (!k.is_idr && cost_inter <= cost_i16 && cost_inter <= cost_i4) type = CC_MB_P16;
             else type = cost_i16 <= cost_i4 ? CC_MB_I16 : CC_MB_I4;
 
-            if (type == CC_MB_I4) {
-                from_tile = true;
-                if (lane < 16) {
-                    const uint32_t *s = (const uint32_t *)m->c4[lane];
-                    uint32_t *d = (uint32_t *)m->coef[lane];
-#pragma unroll
-                    for (int i = 0; i < 8; i++) d[i] = s[i];
-                }
-                unsigned bal = __ballot_sync(FULL, lane < 16 && m->n4[lane & 15] > 0) & 0xffffu;
-                nzmask = bal;
-#pragma unroll
-                for (int i = 0; i < 4; i++) if ((bal >> (4 * i)) & 15u) cbp |= 1 << i;
-            } else if (type == CC_MB_I16) {
-                cbp = encode_i16(k, c, ip, mode16, &nzmask);
+            if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec */
+                mvx = me.mv[0]; mvy = me.mv[1]; mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1];
+                cbp = pre.cbp; nzmask = pre.nz_luma; off = pre.sym_len;
             } else {
-                mvx = me.mv[0]; mvy = me.mv[1];
-                mc_luma16(k, c, mvx, mvy);
-                __syncwarp();
-                cbp = inter_luma(k, c, false, &nzmask);
-            }
-            if (type >= CC_MB_I16) {
+                if (type == CC_MB_I4) {
+                    if (lane < 16) {
+                        const uint32_t *s = (const uint32_t *)m->c4[lane];
+                        uint32_t *d = (uint32_t *)m->coef[lane];
+#pragma unroll
+                        for (int i = 0; i < 8; i++) d[i] = s[i];
+                    }
+                    const int r = lane >> 1, h = lane & 1;
+                    m->recY[r * 4 + h * 2] = *(const uint32_t *)&m->tile[1 + r][4 + h * 8];
+                    m->recY[r * 4 + h * 2 + 1] = *(const uint32_t *)&m->tile[1 + r][8 + h * 8];
+                    unsigned bal = __ballot_sync(FULL, lane < 16 && m->n4[lane & 15] > 0) & 0xffffu;
+                    nzmask = bal;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) if ((bal >> (4 * i)) & 15u) cbp |= 1 << i;
+                } else cbp = encode_i16(k, c, ip, mode16, &nzmask);
                 chroma_mode = intra_chroma_pred(c);
                 cbp |= encode_chroma(k, c, true, false) << 4;
-            } else {
-                mc_chroma8(k, c, mvx, mvy);
                 __syncwarp();
-                cbp |= encode_chroma(k, c, false, false) << 4;
-                mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1];
-                if (cbp == 0 && mvx == skipmv[0] && mvy == skipmv[1]) type = CC_MB_PSKIP;
+                publish_pixels(k, c);
+                /* symbols */
+                if (type == CC_MB_I4) {
+                    if (lane < 4) {
+                        unsigned v = 0;
+#pragma unroll
+                        for (int i = 0; i < 4; i++) v |= (unsigned)m->m4code[lane * 4 + i] << (4 * i);
+                        out[off + lane] = (int16_t)v;
+                    }
+                    off += 4;
+                }
+                off = emit_mb(c, out, off, type, cbp);
             }
-        }
-        /* ---- publish: reconstruction, records, symbols ---- */
-        {
-            uint8_t *ry = k.rec[0] + (size_t)c.py * k.sy + c.px;
-            const int r = lane >> 1, h = lane & 1;
-            uint32_t w0, w1;
-            if (from_tile) { w0 = *(const uint32_t *)&m->tile[1 + r][4 + h * 8]; w1 = *(const uint32_t *)&m->tile[1 + r][8 + h * 8]; }
-            else { w0 = m->recY[r * 4 + h * 2]; w1 = m->recY[r * 4 + h * 2 + 1]; }
-            *(uint32_t *)(ry + (size_t)r * k.sy + h * 8) = w0;
-            *(uint32_t *)(ry + (size_t)r * k.sy + h * 8 + 4) = w1;
-            const int pl = lane >> 4, cr = (lane >> 1) & 7;
-            *(uint32_t *)(k.rec[1 + pl] + (size_t)(row * 8 + cr) * k.sc + mbx * 8 + 4 * h) = m->recC[pl][cr * 2 + h];
-            /* unfiltered neighbours of the next macroblock (right column) and of the row below (bottom line) */
-            if (lane < 16) m->tile[1 + lane][3] = from_tile ? m->tile[1 + lane][19] : (uint8_t)(m->recY[lane * 4 + 3] >> 24);
-            else m->edgeC[(lane - 16) >> 3][9 + (lane & 7)] = (uint8_t)(m->recC[(lane - 16) >> 3][(lane & 7) * 2 + 1] >> 24);
-            if (lane < 4) *(uint32_t *)(tl.Y(w) + c.px + 4 * lane) = from_tile ? *(const uint32_t *)&m->tile[16][4 + 4 * lane] : m->recY[60 + lane];
-            else if (lane < 8) *(uint32_t *)(tl.C((lane - 4) >> 1, w, k.rps) + mbx * 8 + 4 * (lane & 1)) = m->recC[(lane - 4) >> 1][14 + (lane & 1)];
         }
         if (lane == 0) {
             cc_mbdev d;
@@ -646,39 +719,81 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, const TopLines &tl, 
             hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.pad = 0;
             hh.mvd[0] = (int16_t)mvdx; hh.mvd[1] = (int16_t)mvdy;
             k.mbh[c.mb] = hh;
+            k.symlen[c.mb] = (uint16_t)off;
+            nbl[mbx] = make_uint2((unsigned)type | ((unsigned)d.nz_luma << 16), ((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
         }
-        if (type == CC_MB_PSKIP) n_skip++;
-        else {
-            if (type == CC_MB_P16) n_inter++; else n_intra++;
-            if (type == CC_MB_I4) {
-                if (lane < 4) {
-                    unsigned v = 0;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) v |= (unsigned)m->m4code[lane * 4 + i] << (4 * i);
-                    out[off + lane] = (int16_t)v;
-                }
-                off += 4;
-            }
-            const int cl = cbp & 15, cc = cbp >> 4;
-            if (type == CC_MB_I16 || cbp) {
-                if (type == CC_MB_I16) off = emit_block(c, out, off, 24, 16);
-                for (int blk = 0; blk < 16; blk++)
-                    if (cl & (1 << (blk >> 2))) off = emit_block(c, out, off, blk, type == CC_MB_I16 ? 15 : 16);
-                if (cc) {
-                    off = emit_block(c, out, off, 25, 4);
-                    off = emit_block(c, out, off, 26, 4);
-                    if (cc & 2) for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, off, blk, 15);
-                }
-            }
-        }
+        if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
+        total += off;
         __syncwarp();
         __threadfence_block();
         if (lane == 0) progress[w] = mbx + 1;
+        if (k.cyc && lane == 0) {
+            const long long t2 = clock64();
+            unsigned long long *cy = k.cyc + (size_t)row * 16;
+            cy[0] += (unsigned long long)(t1 - t0); cy[1 + path] += (unsigned long long)(t2 - t1); cy[4 + path] += 1;
+        }
     }
     if (lane == 0) {
         cc_rowhdr h;
-        h.bytes = off * 2; h.n_skip = n_skip; h.n_inter = n_inter; h.n_intra = n_intra;
+        h.bytes = total * 2; h.n_skip = n_skip; h.n_inter = n_inter; h.n_intra = n_intra; h.n_gate = n_gate; h.n_probe = n_probe; h.pad = 0;
         k.rowhdr[row] = h;
+    }
+}
+
+/* ---- P-frame pre-pass: every macroblock coded as P_L0_16x16 at its search vector, fully parallel ------------------------ */
+#define PC_WARPS 4
+__global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
+    __shared__ WarpMem wm[PC_WARPS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int mb = blockIdx.x * PC_WARPS + wid, mw = k.mb_w;
+    if (mb >= mw * k.mb_h) return;
+    MbCtx c;
+    c.lane = lane; c.mbx = mb % mw; c.mby = mb / mw; c.mb = mb; c.px = c.mbx * 16; c.py = c.mby * 16;
+    c.qp = k.qp; c.qpc = c_chroma_qp[k.qp]; c.lambda = c_lambda[k.qp]; c.m = &wm[wid];
+    c.L = c.mbx > 0; c.T = c.mby > (c.mby / k.rps) * k.rps; c.TR = c.T && c.mbx + 1 < mw;
+    WarpMem *m = c.m;
+    const cc_me *me = k.me + mb;
+    const int mvx = me->mv[0], mvy = me->mv[1];
+    stage_cur(k, c);
+    mc_luma16(k, c, mvx, mvy);
+    mc_chroma8(k, c, mvx, mvy);
+    __syncwarp();
+    unsigned nzmask;
+    int cbp = inter_luma(k, c, false, &nzmask);
+    cbp |= encode_chroma(k, c, false, false) << 4;
+    __syncwarp();
+    publish_pixels(k, c);
+    int16_t *out = (int16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
+    const unsigned off = emit_mb(c, out, 0, CC_MB_P16, cbp);
+    /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
+    int est;
+    {
+        const uint8_t *sy0 = k.cur[0] + (size_t)c.py * k.sy + c.px;
+        if (lane < 17) m->tile[0][3 + lane] = (c.T && (lane > 0 || c.L)) ? sy0[-(ptrdiff_t)k.sy + lane - 1] : 0;
+        if (lane >= 16) m->tile[1 + lane - 16][3] = c.L ? sy0[(size_t)(lane - 16) * k.sy - 1] : 0;
+        __syncwarp();
+        I16Params ip;
+        int dummy;
+        i16_params(c, ip);
+        est = analyse_i16(c, ip, &dummy);
+    }
+    /* likeliest P_Skip vector: 8.4.1.1 applied to the neighbours' search vectors */
+    int cand[2], mvp[2], a[2] = {0, 0}, b[2] = {0, 0}, cc[2] = {0, 0};
+    int rA = -2, rB = -2, rC = -2;
+    if (c.L) { rA = 0; a[0] = me[-1].mv[0]; a[1] = me[-1].mv[1]; }
+    if (c.T) { rB = 0; b[0] = me[-mw].mv[0]; b[1] = me[-mw].mv[1]; }
+    if (c.TR) { rC = 0; cc[0] = me[-mw + 1].mv[0]; cc[1] = me[-mw + 1].mv[1]; }
+    else if (c.T && c.L) { rC = 0; cc[0] = me[-mw - 1].mv[0]; cc[1] = me[-mw - 1].mv[1]; }
+    predict_mv_core(c.L, c.T, rA, a, rB, b, rC, cc, mvp, cand);
+    int ok = 0;
+    const bool c_is_me = cand[0] == mvx && cand[1] == mvy, z_is_me = mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
+    if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
+    if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
+    if (lane == 0) {
+        cc_pre p;
+        p.cbp = (uint8_t)cbp; p.skip_ok = (uint8_t)ok; p.nz_luma = (uint16_t)nzmask; p.cand[0] = (int16_t)cand[0]; p.cand[1] = (int16_t)cand[1];
+        p.sym_len = (uint16_t)off; p.pad = 0; p.est_intra = est;
+        k.pre[mb] = p;
     }
 }
 
@@ -688,27 +803,32 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_mb_encode(cc_kparams k)
     __shared__ WarpMem wm[MB_MAX_RPS];
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress[MB_MAX_RPS], progress2[MB_MAX_RPS];
-    CC_DYN_SMEM(dsm);
+    CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records {type | nz_luma << 16, mv} */
+    uint2 *nbline = (uint2 *)dsm;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool filt = wid >= k.rps;
     const int w = filt ? wid - k.rps : wid;
     const int row0 = blockIdx.x * k.rps, row = row0 + w;
     const bool valid = row < k.mb_h;
-    TopLines tl;
-    tl.sy = k.W + 32; tl.sc = (k.W >> 1) + 16;
-    tl.y = dsm; tl.c = dsm + (size_t)k.rps * tl.sy;
     if (lane == 0 && !filt) { progress[w] = 0; progress2[w] = 0; }
     __syncthreads();
     if (!valid) return;
     if (!filt) {
-        encode_row(k, &wm[w], tl, progress, w, row, row0, lane);
+        encode_row(k, &wm[w], nbline, progress, w, row, row0, lane);
     } else {
         for (int mbx = 0; mbx < k.mb_w; mbx++) {
+            const long long t0 = k.cyc ? clock64() : 0;
             wait_progress(progress + w, mbx + 1, lane);
+            const long long t1 = k.cyc ? clock64() : 0;
             if (w > 0) wait_progress(progress2 + w - 1, min(mbx + 2, k.mb_w), lane);
-            deblock_mb(k, &dbm[w], lane, mbx, row, mbx > 0, w > 0);
+            const long long t2 = k.cyc ? clock64() : 0;
+            deblock_mb(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
             __threadfence_block();
             if (lane == 0) progress2[w] = mbx + 1;
+            if (k.cyc && lane == 0) {
+                unsigned long long *cy = k.cyc + (size_t)row * 16 + 8;
+                cy[0] += (unsigned long long)(t1 - t0); cy[1] += (unsigned long long)(t2 - t1); cy[2] += (unsigned long long)(clock64() - t2);
+            }
         }
     }
 }
@@ -731,24 +851,39 @@ __global__ void k_pack(cc_kparams k) {
     const int row = blockIdx.x;
     unsigned offs = 0;
     for (int r = 0; r < row; r++) offs += (k.rowhdr[r].bytes + 15u) & ~15u;
-    const unsigned n16 = (k.rowhdr[row].bytes + 15u) >> 4;
-    if (hdr_bytes + mbh_bytes + offs + n16 * 16 > k.out_cap) return;
-    uint4 *dst = (uint4 *)(k.out_host_dev + hdr_bytes + mbh_bytes + offs);
-    const uint4 *src = (const uint4 *)(k.rowbuf + (size_t)row * k.mb_w * CC_ROW_PAYLOAD_PER_MB);
-    for (unsigned i = tid; i < n16; i += nt) dst[i] = src[i];
+    if (hdr_bytes + mbh_bytes + offs + ((k.rowhdr[row].bytes + 15u) & ~15u) > k.out_cap) return;
+    /* exclusive prefix of the row's per-MB symbol lengths (32-bit words), by warp 0 */
+    __shared__ unsigned mboff[513];
+    if (tid < 32) {
+        unsigned run = 0;
+        for (int base = 0; base < k.mb_w; base += 32) {
+            const int i = base + tid;
+            const unsigned len = i < k.mb_w ? (unsigned)(k.symlen[row * k.mb_w + i] >> 1) : 0u;
+            unsigned inc = len;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(FULL, inc, d); if (tid >= d) inc += t; }
+            if (i < k.mb_w) mboff[i] = run + inc - len;
+            run += __shfl_sync(FULL, inc, 31);
+        }
+    }
+    __syncthreads();
+    uint32_t *dst = (uint32_t *)(k.out_host_dev + hdr_bytes + mbh_bytes + offs);
+    const int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+    for (int i = wid; i < k.mb_w; i += nw) {
+        const unsigned n = (unsigned)(k.symlen[row * k.mb_w + i] >> 1);
+        const uint32_t *src = (const uint32_t *)(k.rowbuf + (size_t)(row * k.mb_w + i) * CC_ROW_PAYLOAD_PER_MB);
+        for (unsigned j = lane; j < n; j += 32) dst[mboff[i] + j] = src[j];
+    }
 }
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    const size_t smem = (size_t)k->rps * (2 * (size_t)k->W + 64);
-#ifndef CC_EMU
-    static size_t smem_set = 0; /* opt in above the 48 KB default once (wide pictures with many rows per slice) */
-    if (smem > smem_set) {
-        if (cudaFuncSetAttribute(k_mb_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
-        smem_set = smem;
-    }
-#endif
-    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), smem, st, *k);
+    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), (size_t)k->rps * k->mb_w * sizeof(uint2), st, *k);
+    return 1;
+}
+extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {
+    const int nmb = k->mb_w * k->mb_h;
+    CC_LAUNCH(k_p_code, dim3((unsigned)((nmb + PC_WARPS - 1) / PC_WARPS)), dim3(PC_WARPS * 32), st, *k);
     return 1;
 }
 extern "C" int cck_pack(const cc_kparams *k, cudaStream_t st) {

@@ -99,10 +99,12 @@ static int analyse_i4(struct ref_enc *e, int mbx, int mby, int16_t coef[16][16],
     return cost;
 }
 
-static int analyse_i16(struct ref_enc *e, int mbx, int mby, int *mode_out) {
+/* nb: the plane the neighbour samples come from — the reconstruction (real analysis) or the source picture
+ * (the P-frame intra gate: a neighbour-independent estimate, so it can be computed for all MBs in parallel) */
+static int analyse_i16(struct ref_enc *e, int mbx, int mby, int *mode_out, const uint8_t *nb) {
     const int sy = e->sy, lambda = ref_lambda[e->qp];
     const int L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
-    const uint8_t *rec = e->rec[0] + mby * 16 * sy + mbx * 16, *cur = e->cur[0] + mby * 16 * sy + mbx * 16;
+    const uint8_t *rec = nb + mby * 16 * sy + mbx * 16, *cur = e->cur[0] + mby * 16 * sy + mbx * 16;
     uint8_t pred[256];
     int best = 1 << 30;
     for (int m = 0; m < 4; m++) {
@@ -280,9 +282,19 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         mi->cbp = 0;
         cost_inter = mi->me_satd + lambda * (ref_mv_bits(mi->me_mv[0] - mvp[0]) + ref_mv_bits(mi->me_mv[1] - mvp[1]));
     }
-    cost_i16 = analyse_i16(e, mbx, mby, &mode16);
-    if (e->is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(e, mbx, mby, c4, m4, n4);
-    if (!e->is_idr) { cost_i16 += 8 * lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * lambda; } /* intra mb_type/chroma-mode overhead in P slices */
+    /* P frames: intra is analysed for real only when a source-based Intra16x16 estimate comes within 25 % of the inter
+     * cost [EXT: x264 makes the same kind of early-out in x264_mb_analyse_intra / fast_intra] */
+    int gate = 1;
+    if (!e->is_idr) {
+        int dummy;
+        gate = analyse_i16(e, mbx, mby, &dummy, e->cur[0]) * 4 <= cost_inter * 5;
+    }
+    cost_i16 = 1 << 30;
+    if (gate) {
+        cost_i16 = analyse_i16(e, mbx, mby, &mode16, e->rec[0]);
+        if (e->is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(e, mbx, mby, c4, m4, n4);
+        if (!e->is_idr) { cost_i16 += 8 * lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * lambda; } /* intra mb_type/chroma-mode overhead in P slices */
+    }
 
     int type;
     if (!e->is_idr && cost_inter <= cost_i16 && cost_inter <= cost_i4) type = REF_MB_P16;

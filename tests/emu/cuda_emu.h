@@ -84,6 +84,7 @@ void __syncthreads();
 static inline void __threadfence() {}
 static inline void __threadfence_block() {}
 static inline void __nanosleep(unsigned) { emu::yield(); }
+static inline long long clock64() { return 0; }
 
 template <typename T> static inline T emu_xchg(unsigned m, T v, int src_lane, bool valid) {
     static_assert(sizeof(T) <= 8, "shfl: type too wide");
