@@ -31,3 +31,10 @@ clean:
 	rm -rf build tests/emu/_build $(LIB)
 	$(MAKE) -C oracle clean
 .PHONY: all lib oracle emu clean
+
+# GStreamer element (outer boundary). Built only where GStreamer development files exist.
+gst:
+	@pkg-config --exists gstreamer-video-1.0 || { echo "gstreamer-video-1.0 not found: cudah264enc is compile-gated (see INTEGRATION.md)"; exit 0; }; \
+	$(CC) -O2 -fPIC -shared -std=gnu11 -Wall $$(pkg-config --cflags gstreamer-video-1.0) ceracoder_b200/gst/gstcudah264enc.c -o ceracoder_b200/gst/libgstcudah264enc.so \
+	  -Lceracoder_b200 -lceracuda -Wl,-rpath,'$$ORIGIN/..' $$(pkg-config --libs gstreamer-video-1.0)
+.PHONY: gst

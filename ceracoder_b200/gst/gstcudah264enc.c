@@ -1,0 +1,213 @@
+/*
+ * gstcudah264enc.c — GStreamer element `cudah264enc`: the outer drop-in boundary (SURVEY.md §8b, B-outer).
+ *
+ * It stands where ceracoder's pipeline files name `x264enc`
+ * (/root/reference/pipeline/generic/x264_veryfast_v4l_mjpeg_1080p30:6: "x264enc speed-preset=3 key-int-max=60
+ * name=venc_kbps"), is instantiated by gst_parse_launch (/root/reference/src/io/pipeline_loader.c:59), found by
+ * NAME (/root/reference/src/gst/encoder_control.c:29-32) and driven by g_object_set(element, "bps", ...)
+ * (/root/reference/src/gst/encoder_control.c:53) from the 20 ms balancer tick (/root/reference/src/ceracoder.c:263).
+ * Downstream is `h264parse config-interval=-1 ! queue ! mpegtsmux` (same file, lines 6-10), so byte-stream access
+ * units with SPS/PPS in-band at every IDR are what it must produce.
+ *
+ * All codec work is in libceracuda.so (include/ceracuda.h); this file is glue: caps, properties, buffers.
+ * Built only where GStreamer development files exist (`make gst`, gated on pkg-config gstreamer-video-1.0);
+ * neither this container nor the GPU box has them, so it is compile-gated and exercised through the ctypes mirror
+ * (ceracoder_b200/encoder.py), which implements the same property semantics.
+ */
+#include <gst/gst.h>
+#include <gst/video/video.h>
+#include <gst/video/gstvideoencoder.h>
+#include <string.h>
+#include "../../include/ceracuda.h"
+
+#define GST_TYPE_CUDA_H264_ENC (gst_cuda_h264_enc_get_type())
+G_DECLARE_FINAL_TYPE(GstCudaH264Enc, gst_cuda_h264_enc, GST, CUDA_H264_ENC, GstVideoEncoder)
+
+struct _GstCudaH264Enc {
+    GstVideoEncoder parent;
+    cc_enc *enc;                 /* NULL until set_format */
+    GstVideoCodecState *input_state;
+    /* properties; `bitrate_bps` is written from the GLib main-loop thread while handle_frame runs on a streaming thread */
+    volatile gint bitrate_bps;
+    guint key_int_max, speed_preset, tune, threads, rows_per_slice;
+    gint device;
+    gboolean byte_stream;
+};
+
+G_DEFINE_TYPE(GstCudaH264Enc, gst_cuda_h264_enc, GST_TYPE_VIDEO_ENCODER)
+GST_DEBUG_CATEGORY_STATIC(cudah264enc_debug);
+#define GST_CAT_DEFAULT cudah264enc_debug
+
+enum { PROP_0, PROP_BITRATE, PROP_BPS, PROP_SPEED_PRESET, PROP_KEY_INT_MAX, PROP_TUNE, PROP_BYTE_STREAM, PROP_THREADS, PROP_DEVICE, PROP_ROWS_PER_SLICE };
+
+static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
+    GST_STATIC_CAPS("video/x-raw, format=(string){ I420, NV12 }, width=(int)[16,8192], height=(int)[16,8192], framerate=(fraction)[0/1,MAX]"));
+static GstStaticPadTemplate src_tmpl = GST_STATIC_PAD_TEMPLATE("src", GST_PAD_SRC, GST_PAD_ALWAYS,
+    GST_STATIC_CAPS("video/x-h264, stream-format=(string)byte-stream, alignment=(string)au, profile=(string)constrained-baseline"));
+
+/* The reference writes `bitrate_bps / div` to "bps": kbit/s when the element is named venc_kbps, bit/s when named
+ * venc_bps (/root/reference/src/gst/encoder_control.c:29-32,53).  Disambiguate by our own object name, with the
+ * magnitude fallback of SURVEY §8b (legal range 300 k..30 M bps, /root/reference/src/core/bitrate_control.h:30-31). */
+static gint bps_from_property(GstCudaH264Enc *self, gint v) {
+    gchar *name = gst_object_get_name(GST_OBJECT(self));
+    gboolean kbps = name && g_str_has_prefix(name, "venc_kbps");
+    gboolean bps = name && g_str_has_prefix(name, "venc_bps");
+    g_free(name);
+    if (kbps || (!bps && v <= 30000)) return v * 1000;
+    return v;
+}
+
+static void set_bitrate(GstCudaH264Enc *self, gint bps) {
+    g_atomic_int_set(&self->bitrate_bps, bps);
+    if (self->enc) cc_enc_set_bitrate(self->enc, bps); /* wait-free atomic latch; applied at the next frame boundary */
+}
+
+static void gst_cuda_h264_enc_set_property(GObject *obj, guint id, const GValue *val, GParamSpec *ps) {
+    GstCudaH264Enc *self = GST_CUDA_H264_ENC(obj);
+    switch (id) {
+    case PROP_BITRATE: set_bitrate(self, (gint)g_value_get_uint(val) * 1000); break; /* x264enc-compatible: kbit/s */
+    case PROP_BPS: set_bitrate(self, bps_from_property(self, g_value_get_int(val))); break;
+    case PROP_SPEED_PRESET: self->speed_preset = g_value_get_uint(val); break; /* accepted for pipeline-text compatibility */
+    case PROP_KEY_INT_MAX: self->key_int_max = g_value_get_uint(val); break;
+    case PROP_TUNE: self->tune = g_value_get_uint(val); break;
+    case PROP_BYTE_STREAM: self->byte_stream = g_value_get_boolean(val); break;
+    case PROP_THREADS: self->threads = g_value_get_uint(val); break;
+    case PROP_DEVICE: self->device = g_value_get_int(val); break;
+    case PROP_ROWS_PER_SLICE: self->rows_per_slice = g_value_get_uint(val); break;
+    default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
+    }
+}
+static void gst_cuda_h264_enc_get_property(GObject *obj, guint id, GValue *val, GParamSpec *ps) {
+    GstCudaH264Enc *self = GST_CUDA_H264_ENC(obj);
+    gint bps = g_atomic_int_get(&self->bitrate_bps);
+    switch (id) {
+    case PROP_BITRATE: g_value_set_uint(val, (guint)(bps / 1000)); break;
+    case PROP_BPS: {
+        gchar *name = gst_object_get_name(GST_OBJECT(self));
+        g_value_set_int(val, (name && g_str_has_prefix(name, "venc_bps")) ? bps : bps / 1000);
+        g_free(name);
+        break;
+    }
+    case PROP_SPEED_PRESET: g_value_set_uint(val, self->speed_preset); break;
+    case PROP_KEY_INT_MAX: g_value_set_uint(val, self->key_int_max); break;
+    case PROP_TUNE: g_value_set_uint(val, self->tune); break;
+    case PROP_BYTE_STREAM: g_value_set_boolean(val, self->byte_stream); break;
+    case PROP_THREADS: g_value_set_uint(val, self->threads); break;
+    case PROP_DEVICE: g_value_set_int(val, self->device); break;
+    case PROP_ROWS_PER_SLICE: g_value_set_uint(val, self->rows_per_slice); break;
+    default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
+    }
+}
+
+static void close_codec(GstCudaH264Enc *self) {
+    if (self->enc) { cc_enc_close(self->enc); self->enc = NULL; }
+    if (self->input_state) { gst_video_codec_state_unref(self->input_state); self->input_state = NULL; }
+}
+static gboolean gst_cuda_h264_enc_stop(GstVideoEncoder *venc) { close_codec(GST_CUDA_H264_ENC(venc)); return TRUE; }
+
+/* (re)open the codec for the negotiated format — x264enc does the same in its set_format [EXT] */
+static gboolean gst_cuda_h264_enc_set_format(GstVideoEncoder *venc, GstVideoCodecState *state) {
+    GstCudaH264Enc *self = GST_CUDA_H264_ENC(venc);
+    GstVideoInfo *info = &state->info;
+    cc_enc_params p;
+    close_codec(self);
+    cc_enc_params_default(&p);
+    p.device = self->device;
+    p.width = GST_VIDEO_INFO_WIDTH(info); p.height = GST_VIDEO_INFO_HEIGHT(info);
+    p.fps_n = GST_VIDEO_INFO_FPS_N(info) > 0 ? GST_VIDEO_INFO_FPS_N(info) : 30;
+    p.fps_d = GST_VIDEO_INFO_FPS_D(info) > 0 ? GST_VIDEO_INFO_FPS_D(info) : 1;
+    p.format = GST_VIDEO_INFO_FORMAT(info) == GST_VIDEO_FORMAT_NV12 ? CC_FMT_NV12 : CC_FMT_I420;
+    p.bitrate_bps = g_atomic_int_get(&self->bitrate_bps);
+    p.key_int_max = (int)self->key_int_max;
+    p.rows_per_slice = (int)self->rows_per_slice;
+    int rc = cc_enc_open(&self->enc, &p);
+    if (rc != CC_OK) {
+        GST_ELEMENT_ERROR(self, LIBRARY, INIT, ("cc_enc_open failed: %s", cc_strerror(rc)), ("there is no CPU fallback"));
+        return FALSE;
+    }
+    self->input_state = gst_video_codec_state_ref(state);
+    GstCaps *caps = gst_caps_new_simple("video/x-h264", "stream-format", G_TYPE_STRING, "byte-stream", "alignment", G_TYPE_STRING, "au",
+                                        "profile", G_TYPE_STRING, "constrained-baseline", NULL);
+    GstVideoCodecState *out = gst_video_encoder_set_output_state(venc, caps, state);
+    gst_video_codec_state_unref(out);
+    gst_video_encoder_set_latency(venc, 0, 0); /* one frame in, one access unit out, synchronously (zerolatency) */
+    return gst_video_encoder_negotiate(venc);
+}
+
+static GstFlowReturn gst_cuda_h264_enc_handle_frame(GstVideoEncoder *venc, GstVideoCodecFrame *frame) {
+    GstCudaH264Enc *self = GST_CUDA_H264_ENC(venc);
+    GstVideoFrame vf;
+    cc_frame in;
+    cc_packet pkt;
+    if (!self->enc || !self->input_state) { gst_video_encoder_finish_frame(venc, frame); return GST_FLOW_NOT_NEGOTIATED; }
+    if (!gst_video_frame_map(&vf, &self->input_state->info, frame->input_buffer, GST_MAP_READ)) {
+        GST_ELEMENT_ERROR(self, RESOURCE, READ, ("cannot map input buffer"), (NULL));
+        gst_video_codec_frame_unref(frame);
+        return GST_FLOW_ERROR;
+    }
+    memset(&in, 0, sizeof in);
+    for (guint i = 0; i < GST_VIDEO_FRAME_N_PLANES(&vf) && i < 3; i++) { /* GStreamer strides are not tight */
+        in.plane[i] = GST_VIDEO_FRAME_PLANE_DATA(&vf, i);
+        in.stride[i] = GST_VIDEO_FRAME_PLANE_STRIDE(&vf, i);
+    }
+    in.pts = (int64_t)frame->pts;
+    unsigned flags = GST_VIDEO_CODEC_FRAME_IS_FORCE_KEYFRAME(frame) ? CC_FORCE_IDR : 0; /* upstream force-key-unit */
+    int rc = cc_enc_encode(self->enc, &in, flags, &pkt);
+    gst_video_frame_unmap(&vf);
+    if (rc != CC_OK) {
+        GST_ELEMENT_ERROR(self, STREAM, ENCODE, ("cc_enc_encode failed: %s", cc_strerror(rc)), (NULL));
+        gst_video_codec_frame_unref(frame);
+        return GST_FLOW_ERROR; /* ceracoder turns any bus ERROR into stop() (/root/reference/src/ceracoder.c:425-430) */
+    }
+    frame->output_buffer = gst_buffer_new_allocate(NULL, (gsize)pkt.size, NULL);
+    gst_buffer_fill(frame->output_buffer, 0, pkt.data, (gsize)pkt.size); /* pkt.data is owned by the handle */
+    if (pkt.is_idr) GST_VIDEO_CODEC_FRAME_SET_SYNC_POINT(frame); else GST_VIDEO_CODEC_FRAME_UNSET_SYNC_POINT(frame);
+    frame->dts = frame->pts; /* no B frames */
+    return gst_video_encoder_finish_frame(venc, frame);
+}
+
+static void gst_cuda_h264_enc_finalize(GObject *obj) {
+    close_codec(GST_CUDA_H264_ENC(obj));
+    G_OBJECT_CLASS(gst_cuda_h264_enc_parent_class)->finalize(obj);
+}
+
+static void gst_cuda_h264_enc_class_init(GstCudaH264EncClass *klass) {
+    GObjectClass *oc = G_OBJECT_CLASS(klass);
+    GstElementClass *ec = GST_ELEMENT_CLASS(klass);
+    GstVideoEncoderClass *vc = GST_VIDEO_ENCODER_CLASS(klass);
+    const GParamFlags rw = (GParamFlags)(G_PARAM_READWRITE | G_PARAM_STATIC_STRINGS);
+    const GParamFlags rwp = (GParamFlags)(rw | GST_PARAM_MUTABLE_PLAYING);
+    oc->set_property = gst_cuda_h264_enc_set_property;
+    oc->get_property = gst_cuda_h264_enc_get_property;
+    oc->finalize = gst_cuda_h264_enc_finalize;
+    /* `bitrate`: what the docs promise (/root/reference/README.md:256) and x264enc exposes [EXT]; `bps`: what the code writes */
+    g_object_class_install_property(oc, PROP_BITRATE, g_param_spec_uint("bitrate", "Bitrate", "Target bitrate in kbit/s (runtime-writable)", 300, 30000, 6000, rwp));
+    g_object_class_install_property(oc, PROP_BPS, g_param_spec_int("bps", "Bitrate (ceracoder)", "Target bitrate as ceracoder's encoder_control writes it: kbit/s for an element named venc_kbps, bit/s for venc_bps", 1, G_MAXINT, 6000, rwp));
+    g_object_class_install_property(oc, PROP_SPEED_PRESET, g_param_spec_uint("speed-preset", "Speed preset", "x264enc speed-preset value (1..10), accepted for pipeline compatibility", 0, 10, 3, rw));
+    g_object_class_install_property(oc, PROP_KEY_INT_MAX, g_param_spec_uint("key-int-max", "Key-frame interval", "Maximum distance between IDR frames (0 = 60)", 0, G_MAXINT, 60, rw));
+    g_object_class_install_property(oc, PROP_TUNE, g_param_spec_uint("tune", "Tune", "x264enc tune flags, accepted for compatibility (zerolatency = 0x4 is always in effect)", 0, 0xff, 0x4, rw));
+    g_object_class_install_property(oc, PROP_BYTE_STREAM, g_param_spec_boolean("byte-stream", "Byte stream", "Always Annex-B byte-stream", TRUE, rw));
+    g_object_class_install_property(oc, PROP_THREADS, g_param_spec_uint("threads", "Threads", "Ignored (the work runs on the GPU)", 0, 1024, 0, rw));
+    g_object_class_install_property(oc, PROP_DEVICE, g_param_spec_int("device", "CUDA device", "CUDA device ordinal", 0, 63, 0, rw));
+    g_object_class_install_property(oc, PROP_ROWS_PER_SLICE, g_param_spec_uint("rows-per-slice", "MB rows per slice", "Macroblock rows per slice (0 = 4)", 0, 8, 0, rw));
+    gst_element_class_set_static_metadata(ec, "CUDA H.264 encoder (ceracuda)", "Codec/Encoder/Video/Hardware",
+                                          "H.264 encoder on sm_100a CUDA kernels; drop-in for x264enc in ceracoder pipelines", "ceracuda");
+    gst_element_class_add_static_pad_template(ec, &sink_tmpl);
+    gst_element_class_add_static_pad_template(ec, &src_tmpl);
+    vc->set_format = gst_cuda_h264_enc_set_format;
+    vc->handle_frame = gst_cuda_h264_enc_handle_frame;
+    vc->stop = gst_cuda_h264_enc_stop;
+}
+static void gst_cuda_h264_enc_init(GstCudaH264Enc *self) {
+    self->bitrate_bps = 6000000; /* /root/reference/src/core/bitrate_control.h:32 */
+    self->key_int_max = 60; self->speed_preset = 3; self->tune = 0x4; self->byte_stream = TRUE;
+}
+
+static gboolean plugin_init(GstPlugin *plugin) {
+    GST_DEBUG_CATEGORY_INIT(cudah264enc_debug, "cudah264enc", 0, "ceracuda H.264 encoder");
+    return gst_element_register(plugin, "cudah264enc", GST_RANK_NONE, GST_TYPE_CUDA_H264_ENC);
+}
+#ifndef PACKAGE
+#define PACKAGE "ceracuda"
+#endif
+GST_PLUGIN_DEFINE(GST_VERSION_MAJOR, GST_VERSION_MINOR, cudah264enc, "ceracuda H.264 encoder", plugin_init, "0.1", "LGPL", "ceracuda", "https://github.com/CERALIVE/ceracoder")

@@ -1,0 +1,97 @@
+"""Rate control under the reference balancer's bitrate schedule (BASELINE config 2: 2<->12 Mbps steps; target: mean
+bitrate error <= 5 %).  The schedule is produced by the reference's own src/core balancer (tests/golden/README.md)."""
+import csv
+import os
+import subprocess
+import numpy as np
+import pytest
+from oracle_lib import ROOT
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def load_schedule(name="balancer_2_12mbps.csv"):
+    with open(os.path.join(GOLD, name)) as f:
+        rows = list(csv.reader(f))[1:]
+    return [(int(t), int(b)) for t, b in rows]
+
+
+def bitrate_at(sched, t_ms):
+    b = sched[0][1]
+    for t, v in sched:
+        if t <= t_ms:
+            b = v
+        else:
+            break
+    return b
+
+
+def test_fixture_shape():
+    s = load_schedule()
+    assert s[0] == (0, 12000000)
+    assert min(b for _, b in s) == 2000000 and s[-1][1] == 12000000
+    ups = [(t1 - t0, b1 - b0) for (t0, b0), (t1, b1) in zip(s[2:], s[3:])]
+    assert all(dt == 520 for dt, _ in ups)                  # one increase per 500 ms cooldown at the 20 ms tick
+    assert all(100000 <= db <= 400000 for _, db in ups)     # +incr + cur/30, floored to 100 kbps
+    assert all(b % 100000 == 0 for _, b in s)
+
+
+def test_fixture_matches_reference_balancer():
+    if not os.path.isdir("/root/reference/src/core"):
+        pytest.skip("reference sources not present on this machine")
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "ref"], stdout=subprocess.DEVNULL)
+    for algo, name in (("adaptive", "balancer_2_12mbps.csv"), ("aimd", "balancer_aimd_2_12mbps.csv")):
+        out = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "balancer_trace"), algo, "2000", "12000", "40"], capture_output=True, text=True, check=True).stdout
+        assert out == open(os.path.join(GOLD, name)).read()
+
+
+def run_schedule(lib, w, h, fps, sched, seconds, scale=1.0, pool=24, source="pan"):
+    """Encode `seconds` of video while replaying the schedule through the element's bps property at every 20 ms tick
+    that precedes a frame.  Returns per-frame (target_bps, bits)."""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    src = make_source(source, w, h)
+    frames = [src.frame(i) for i in range(pool)]
+    enc = CudaH264Enc(w, h, fps=(fps, 1), bitrate=int(sched[0][1] * scale) // 1000, name="venc_kbps", lib=lib)
+    out = []
+    n = int(seconds * fps)
+    for i in range(n):
+        t_ms = 1000.0 * i / fps
+        bps = int(bitrate_at(sched, t_ms) * scale)
+        enc.set_property("bps", bps // 1000)   # what encoder_control.c:53 writes for a venc_kbps element
+        p = i % (2 * pool - 2)
+        y, u, v = frames[p if p < pool else 2 * pool - 2 - p]
+        au = enc.encode(y, u, v)
+        out.append((enc.get_property("bitrate") * 1000, len(au) * 8))
+    enc.close()
+    return np.array(out, dtype=np.float64)
+
+
+def window_errors(tb, fps):
+    """|bits_out - integral(target)| / integral(target) over 1 s sliding windows."""
+    w = int(fps)
+    tgt = np.convolve(tb[:, 0] / fps, np.ones(w), "valid")
+    got = np.convolve(tb[:, 1], np.ones(w), "valid")
+    return np.abs(got - tgt) / tgt
+
+
+def test_rate_control_follows_steps_emulated():
+    """Small picture on the CPU emulation build: the controller must move QP with the target and keep the long-run rate."""
+    from emu_lib import emu_library
+    sched = [(0, 1200000), (1000, 400000), (2000, 1200000)]
+    tb = run_schedule(emu_library(), 176, 144, 15, sched, 3.0, pool=8)
+    hi = tb[:15, 1].sum(); lo = tb[15:30, 1].sum()
+    assert lo < 0.7 * hi
+    assert abs(tb[:, 1].sum() - (tb[:, 0] / 15).sum()) / (tb[:, 0] / 15).sum() < 0.25
+
+
+@pytest.mark.gpu
+def test_1080p60_balancer_schedule_bitrate_error():
+    from ceracoder_b200 import load_library
+    sched = load_schedule()
+    tb = run_schedule(load_library(), 1920, 1080, 60, sched, 36.0, pool=40)
+    err = window_errors(tb, 60)
+    total = abs(tb[:, 1].sum() - (tb[:, 0] / 60).sum()) / (tb[:, 0] / 60).sum()
+    print(f"mean 1s-window error {err.mean():.3f}, p95 {np.percentile(err, 95):.3f}, whole-run error {total:.3f}")
+    assert err.mean() <= 0.05, f"mean bitrate error {err.mean():.3f} > 5 %"
+    assert total <= 0.03
