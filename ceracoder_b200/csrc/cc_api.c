@@ -217,6 +217,7 @@ static void set_quant(cc_kparams *k) {
     cc_quant_tables(k->qp, 0, k->qmf[1], k->qbias[1]);
     cc_quant_tables(chroma_qp[k->qp], 1, k->qmf[2], k->qbias[2]);
     cc_quant_tables(chroma_qp[k->qp], 0, k->qmf[3], k->qbias[3]);
+    cc_quant8_tables(k->qp, k->q8mf, k->q8bias);
 }
 
 int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {

@@ -23,10 +23,14 @@ size_t cc_write_sps(const cc_seq *s, uint8_t *rbsp, size_t cap) {
     cc_bw b;
     int crop_r = (s->mb_w * 16 - s->w) / 2, crop_b = (s->mb_h * 16 - s->h) / 2;
     cc_bw_init(&b, rbsp, cap);
-    cc_bw_put(&b, 8, 66);   /* profile_idc: Baseline */
-    cc_bw_put(&b, 8, 0xC0); /* constraint_set0/1: Constrained Baseline */
+    cc_bw_put(&b, 8, 100);  /* profile_idc: High (8x8 transform; entropy coding stays CAVLC) */
+    cc_bw_put(&b, 8, 0);    /* constraint_set flags */
     cc_bw_put(&b, 8, (uint32_t)cc_level_idc(s));
     cc_bw_ue(&b, 0);        /* seq_parameter_set_id */
+    cc_bw_ue(&b, 1);        /* chroma_format_idc: 4:2:0 */
+    cc_bw_ue(&b, 0); cc_bw_ue(&b, 0); /* bit_depth_luma/chroma_minus8 */
+    cc_bw_put(&b, 1, 0);    /* qpprime_y_zero_transform_bypass_flag */
+    cc_bw_put(&b, 1, 0);    /* seq_scaling_matrix_present_flag */
     cc_bw_ue(&b, 0);        /* log2_max_frame_num_minus4 */
     cc_bw_ue(&b, 2);        /* pic_order_cnt_type: output order = decoding order */
     cc_bw_ue(&b, 1);        /* max_num_ref_frames */
@@ -70,6 +74,9 @@ size_t cc_write_pps(uint8_t *rbsp, size_t cap) {
     cc_bw_put(&b, 1, 1);    /* deblocking_filter_control_present_flag */
     cc_bw_put(&b, 1, 0);    /* constrained_intra_pred_flag */
     cc_bw_put(&b, 1, 0);    /* redundant_pic_cnt_present_flag */
+    cc_bw_put(&b, 1, 1);    /* transform_8x8_mode_flag */
+    cc_bw_put(&b, 1, 0);    /* pic_scaling_matrix_present_flag */
+    cc_bw_se(&b, 0);        /* second_chroma_qp_index_offset */
     size_t n = cc_bw_finish(&b);
     return b.overflow ? 0 : n;
 }
@@ -115,6 +122,22 @@ void cc_quant_tables(int qp, int intra, uint16_t mf[3], uint16_t bias[3]) {
     for (int c = 0; c < 3; c++) {
         int m = MF[qp % 6][c];
         int j = sh <= 0 ? m << -sh : (m + (1 << (sh - 1))) >> sh;
+        int b = ((dz << 10) + (j >> 1)) / j, lim = (1 << 15) / j;
+        mf[c] = (uint16_t)j;
+        bias[c] = (uint16_t)(b < lim ? b : lim);
+    }
+}
+
+/* 8x8 transform quantiser (inter): mf[6], bias[6] per position class of H.264 8.5.9 (normAdjust8x8 classes);
+ * level = sign * ((|c| + bias) * mf >> 16) [EXT: x264 quant_8x8, flat matrix, inter dead zone 11/64] */
+void cc_quant8_tables(int qp, uint16_t mf[6], uint16_t bias[6]) {
+    static const uint16_t MF8[6][6] = {{13107, 11428, 20972, 12222, 16777, 15481}, {11916, 10826, 19174, 11058, 14980, 14290},
+                                       {10082, 8943, 15978, 9675, 12710, 11985},   {9362, 8228, 14913, 8931, 11984, 11259},
+                                       {8192, 7346, 13159, 7740, 10486, 9777},     {7282, 6428, 11570, 6830, 9118, 8640}};
+    const int dz = 11, sh = qp / 6;
+    for (int c = 0; c < 6; c++) {
+        int m = MF8[qp % 6][c];
+        int j = sh <= 0 ? m : (m + (1 << (sh - 1))) >> sh;
         int b = ((dz << 10) + (j >> 1)) / j, lim = (1 << 15) / j;
         mf[c] = (uint16_t)j;
         bias[c] = (uint16_t)(b < lim ? b : lim);

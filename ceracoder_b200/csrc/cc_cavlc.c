@@ -100,6 +100,7 @@ int cc_cavlc_write_slice(cc_cavlc_ctx *c, cc_bw *b, int is_idr, int row0, int ro
                 cc_bw_se(b, m->mvd[0]); cc_bw_se(b, m->mvd[1]);
             } else if (m->type == CC_MB_I4) {
                 cc_bw_ue(b, P ? 5 : 0);
+                cc_bw_put(b, 1, 0); /* transform_size_8x8_flag: Intra4x4 (the PPS enables transform_8x8_mode) */
                 if (pay + 8 > pay_end) return -1;
                 for (int i = 0; i < 16; i++) { /* nibble: 8 = prev_intra4x4_pred_mode_flag, else rem_intra4x4_pred_mode */
                     int nib = (pay[i >> 1] >> (4 * (i & 1))) & 15;
@@ -111,6 +112,7 @@ int cc_cavlc_write_slice(cc_cavlc_ctx *c, cc_bw *b, int is_idr, int row0, int ro
             } else return -1;
             if (m->type >= CC_MB_I16) cc_bw_ue(b, (unsigned)(m->modes >> 2) & 3);
             if (!i16) cc_bw_ue(b, cc_vlc_cbp_code[m->type == CC_MB_I4 ? 0 : 1][m->cbp]);
+            if (m->type == CC_MB_P16 && cl) cc_bw_put(b, 1, m->t8 & 1); /* transform_size_8x8_flag */
             if (!i16 && !m->cbp) continue;
             cc_bw_se(b, 0); /* mb_qp_delta */
 #define NEXT_BLOCK(mask_, lv_)                                              \

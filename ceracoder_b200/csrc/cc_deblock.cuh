@@ -121,6 +121,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
         const int pe = ed ? ed - 1 : 3;
         bsv[ed] = (ed == 0 && !L) ? 0 : db_bs(ed == 0 ? nl.x : q0, ed == 0 ? nl.y : q1, db_blk(blk_row + pe), q0, q1, db_blk(blk_row + ed), ed == 0);
         bsh[ed] = (ed == 0 && !T) ? 0 : db_bs(ed == 0 ? nt.x : q0, ed == 0 ? nt.y : q1, db_blk(pe * 4 + g), q0, q1, db_blk(ed * 4 + g), ed == 0);
+        if ((ed & 1) && ((q0 >> 8) & 1u)) bsv[ed] = bsh[ed] = 0; /* transform_size_8x8_flag: edges 1 and 3 are not transform edges */
         any |= bsv[ed] | bsh[ed];
     }
     if (!__any_sync(FULL, any)) return;

@@ -82,4 +82,5 @@ void cc_rc_update(cc_rc *rc, int is_idr, int qp, long bits);
 
 /* quantiser tables for one qp: mf[3], bias[3] per class (0 even-even, 1 odd-odd, 2 mixed) */
 void cc_quant_tables(int qp, int intra, uint16_t mf[3], uint16_t bias[3]);
+void cc_quant8_tables(int qp, uint16_t mf[6], uint16_t bias[6]);
 #endif

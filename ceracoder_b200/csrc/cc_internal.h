@@ -45,7 +45,7 @@ typedef struct {
 
 /* host-side macroblock record (what the CAVLC writer needs besides the coefficient payload) */
 typedef struct {
-    uint8_t type, modes /* i16_mode | chroma_mode<<2 */, cbp, pad;
+    uint8_t type, modes /* i16_mode | chroma_mode<<2 */, cbp, t8 /* transform_size_8x8_flag */;
     int16_t mvd[2];
 } cc_mbhost; /* 8 bytes */
 
@@ -58,7 +58,8 @@ typedef struct {
     uint16_t nz_luma;
     int16_t cand[2];    /* P_Skip vector predicted from the neighbours' search vectors */
     uint16_t sym_len;   /* int16 units used in the MB's symbol slot */
-    uint16_t pad;
+    uint8_t t8;         /* coded with the 8x8 transform */
+    uint8_t pad;
     int32_t est_intra;  /* Intra16x16 SATD cost with SOURCE neighbours: gate of the real intra analysis */
 } cc_pre; /* 16 bytes */
 
@@ -94,6 +95,7 @@ typedef struct {
     cc_rowhdr *rowhdr; /* device */
     int qp, is_idr;
     uint16_t qmf[4][3], qbias[4][3]; /* quantiser: 0 luma intra, 1 luma inter, 2 chroma intra, 3 chroma inter; class-indexed */
+    uint16_t q8mf[6], q8bias[6];     /* 8x8 transform, luma inter; class-indexed (H.264 8.5.9) */
     /* packed output in mapped pinned host memory: [cc_rowhdr * mb_h][cc_mbhost * nmb][payload rows, 16-byte aligned] */
     uint8_t *out_host_dev; /* device pointer of that mapping */
     uint32_t out_cap;

@@ -19,7 +19,7 @@
  * 8.5 (transform), 8.7 (deblocking); decision rules follow the oracle (oracle/ref_mb.c), which is pinned
  * by libavcodec's decoder.
  */
-#include "cc_xform.cuh"
+#include "cc_xform8.cuh"
 #include "cc_deblock.cuh"
 
 #define MB_MAX_RPS 8
@@ -618,7 +618,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
         int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
         unsigned off = 0;
         cc_me me = {{0, 0}, {0, 0}, 0};
-        cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0};
+        cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
         if (!k.is_idr) { me = k.me[c.mb]; pre = k.pre[c.mb]; } /* independent of the neighbours: issued before the wait */
         stage_cur(k, c);
         const long long t0 = k.cyc ? clock64() : 0;
@@ -626,7 +626,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
         const long long t1 = k.cyc ? clock64() : 0;
         int path = 0; /* 0 fast, 1 skip probe, 2 intra analysis */
 
-        int type = CC_MB_P16, mode16 = 2, chroma_mode = 0, cbp = 0, mvx = 0, mvy = 0, mvdx = 0, mvdy = 0;
+        int type = CC_MB_P16, mode16 = 2, chroma_mode = 0, cbp = 0, mvx = 0, mvy = 0, mvdx = 0, mvdy = 0, t8 = 0;
         unsigned nzmask = 0;
         int mvp[2] = {0, 0}, skipmv[2] = {0, 0};
         int cost_inter = 1 << 30, cost_i4 = 1 << 30;
@@ -674,7 +674,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
 
             if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec */
                 mvx = me.mv[0]; mvy = me.mv[1]; mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1];
-                cbp = pre.cbp; nzmask = pre.nz_luma; off = pre.sym_len;
+                cbp = pre.cbp; nzmask = pre.nz_luma; off = pre.sym_len; t8 = pre.t8;
             } else {
                 if (type == CC_MB_I4) {
                     if (lane < 16) {
@@ -710,17 +710,17 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
         }
         if (lane == 0) {
             cc_mbdev d;
-            d.type = (uint8_t)type; d.pad0 = 0; d.nz_luma = (uint16_t)(type == CC_MB_PSKIP ? 0 : nzmask);
+            d.type = (uint8_t)type; d.pad0 = (uint8_t)t8; d.nz_luma = (uint16_t)(type == CC_MB_PSKIP ? 0 : nzmask);
             d.mv[0] = (int16_t)mvx; d.mv[1] = (int16_t)mvy;
 #pragma unroll
             for (int i = 0; i < 16; i++) d.i4_mode[i] = type == CC_MB_I4 ? m->m4[i] : 2;
             k.mbd[c.mb] = d;
             cc_mbhost hh;
-            hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.pad = 0;
+            hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.t8 = (uint8_t)t8;
             hh.mvd[0] = (int16_t)mvdx; hh.mvd[1] = (int16_t)mvdy;
             k.mbh[c.mb] = hh;
             k.symlen[c.mb] = (uint16_t)off;
-            nbl[mbx] = make_uint2((unsigned)type | ((unsigned)d.nz_luma << 16), ((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
+            nbl[mbx] = make_uint2((unsigned)type | ((unsigned)t8 << 8) | ((unsigned)d.nz_luma << 16), ((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
         }
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
@@ -744,9 +744,12 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
 #define PC_WARPS 4
 __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     __shared__ WarpMem wm[PC_WARPS];
+    __shared__ X8Mem x8m[PC_WARPS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int mb = blockIdx.x * PC_WARPS + wid, mw = k.mb_w;
     if (mb >= mw * k.mb_h) return;
+    X8Mem *x8 = &x8m[wid];
+    x8->zz[lane] = c_zigzag8[lane]; x8->zz[lane + 32] = c_zigzag8[lane + 32];
     MbCtx c;
     c.lane = lane; c.mbx = mb % mw; c.mby = mb / mw; c.mb = mb; c.px = c.mbx * 16; c.py = c.mby * 16;
     c.qp = k.qp; c.qpc = c_chroma_qp[k.qp]; c.lambda = c_lambda[k.qp]; c.m = &wm[wid];
@@ -759,7 +762,10 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     mc_chroma8(k, c, mvx, mvy);
     __syncwarp();
     unsigned nzmask;
-    int cbp = inter_luma(k, c, false, &nzmask);
+    /* transform size [EXT: x264_mb_analyse_transform]: 8x8 when the residual's sa8d is below its 4x4 satd */
+    int t8 = sa8d_mb(x8, m->curY, m->predY, lane) < me->satd;
+    int cbp = t8 ? inter_luma8(k, x8, m->curY, m->predY, m->recY, m->coef, c.qp, lane, &nzmask) : inter_luma(k, c, false, &nzmask);
+    if (!cbp) t8 = 0; /* the flag is only transmitted with coded luma */
     cbp |= encode_chroma(k, c, false, false) << 4;
     __syncwarp();
     publish_pixels(k, c);
@@ -792,7 +798,7 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     if (lane == 0) {
         cc_pre p;
         p.cbp = (uint8_t)cbp; p.skip_ok = (uint8_t)ok; p.nz_luma = (uint16_t)nzmask; p.cand[0] = (int16_t)cand[0]; p.cand[1] = (int16_t)cand[1];
-        p.sym_len = (uint16_t)off; p.pad = 0; p.est_intra = est;
+        p.sym_len = (uint16_t)off; p.t8 = (uint8_t)t8; p.pad = 0; p.est_intra = est;
         k.pre[mb] = p;
     }
 }

@@ -163,8 +163,9 @@ static int level_idc(const ref_enc *e) {
 }
 static int write_sps(const ref_enc *e, uint8_t *o) {
     int bp = 0, cr = (e->mb_w * 16 - e->w) / 2, cb = (e->mb_h * 16 - e->h) / 2;
-    ref_put_bits(o, &bp, 8, 66); ref_put_bits(o, &bp, 8, 0xC0); ref_put_bits(o, &bp, 8, (uint32_t)level_idc(e));
-    ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 2); ref_put_ue(o, &bp, 1); ref_put_bits(o, &bp, 1, 0);
+    ref_put_bits(o, &bp, 8, 100); ref_put_bits(o, &bp, 8, 0); ref_put_bits(o, &bp, 8, (uint32_t)level_idc(e)); /* High profile */
+    ref_put_ue(o, &bp, 0);
+    ref_put_ue(o, &bp, 1); ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 0); ref_put_bits(o, &bp, 1, 0); ref_put_bits(o, &bp, 1, 0); /* 4:2:0, 8 bit, no bypass, no scaling matrices */ ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 2); ref_put_ue(o, &bp, 1); ref_put_bits(o, &bp, 1, 0);
     ref_put_ue(o, &bp, (unsigned)e->mb_w - 1); ref_put_ue(o, &bp, (unsigned)e->mb_h - 1);
     ref_put_bits(o, &bp, 1, 1); ref_put_bits(o, &bp, 1, 1);
     ref_put_bits(o, &bp, 1, (cr || cb));
@@ -189,6 +190,7 @@ static int write_pps(uint8_t *o) {
     ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 0); ref_put_ue(o, &bp, 0); ref_put_bits(o, &bp, 1, 0); ref_put_bits(o, &bp, 2, 0);
     ref_put_se(o, &bp, 0); ref_put_se(o, &bp, 0); ref_put_se(o, &bp, 0);
     ref_put_bits(o, &bp, 1, 1); ref_put_bits(o, &bp, 1, 0); ref_put_bits(o, &bp, 1, 0);
+    ref_put_bits(o, &bp, 1, 1); ref_put_bits(o, &bp, 1, 0); ref_put_se(o, &bp, 0); /* transform_8x8_mode_flag, no scaling lists, second_chroma_qp_index_offset */
     ref_put_bits(o, &bp, 1, 1);
     while (bp & 7) ref_put_bits(o, &bp, 1, 0);
     return bp >> 3;

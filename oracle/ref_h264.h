@@ -42,6 +42,13 @@ void ref_dequant_4x4_dc(int16_t dct[16], int qp);
 void ref_dequant_2x2_dc(int16_t out[4], const int16_t in[4], int qp);
 void ref_add4x4_idct(uint8_t *dst, int sd, const uint8_t *pred, int sp, const int16_t dct[16]);
 int ref_decimate_score(const int16_t *zz, int n);
+/* 8x8 transform path (High profile) */
+void ref_sub8x8_dct8(int16_t dct[64], const uint8_t *cur, int sc, const uint8_t *pred, int sp);
+int ref_quant_8x8(int16_t dct[64], int qp, int intra);
+void ref_dequant_8x8(int16_t dct[64], int qp);
+void ref_add8x8_idct8(uint8_t *dst, int sd, const uint8_t *pred, int sp, const int16_t dct[64]);
+int ref_sa8d_8x8_raw(const uint8_t *a, int sa, const uint8_t *b, int sb);
+int ref_decimate_score64(const int16_t *zz);
 void ref_pred4x4(uint8_t dst[16], int mode, const uint8_t *top /*8, [-1]=topleft valid*/,
                  const uint8_t *left /*4*/, int has_top, int has_left);
 void ref_pred16x16(uint8_t *dst, int sd, int mode, const uint8_t *rec, int sr, int has_top,
@@ -72,6 +79,8 @@ typedef struct {
     int32_t me_satd;
     int16_t l1_mv[2];
     int32_t bits; /* bits this MB contributed to slice data */
+    uint8_t t8;   /* transform_size_8x8_flag (inter MBs only) */
+    uint8_t pad8[3];
 } ref_mb_info;
 
 typedef struct ref_enc ref_enc;

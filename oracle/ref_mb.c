@@ -150,6 +150,44 @@ static void encode_i16(struct ref_enc *e, int mbx, int mby, int mode, ref_mb_inf
     mi->i16_mode = (uint8_t)mode;
 }
 
+/* 8x8-transform variant (High profile, transform_size_8x8_flag = 1).  CAVLC carries an 8x8 block as four interleaved
+ * 4x4 blocks: block i of the 8x8 gets scan positions 4k+i (H.264 7.3.5.3.2 / 8.5.6), so coef/nnz keep the 4x4 layout. */
+static void encode_inter_luma8(struct ref_enc *e, int mbx, int mby, const uint8_t *pred, ref_mb_info *mi, int16_t *coef) {
+    const int sy = e->sy, qp = e->qp;
+    uint8_t *rec = e->rec[0] + mby * 16 * sy + mbx * 16;
+    const uint8_t *cur = e->cur[0] + mby * 16 * sy + mbx * 16;
+    int16_t d[4][64];
+    int score8[4], nz8[4], total = 0, cbp = 0;
+    for (int i8 = 0; i8 < 4; i8++) {
+        const int ox = (i8 & 1) * 8, oy = (i8 >> 1) * 8;
+        int16_t zz[64];
+        ref_sub8x8_dct8(d[i8], cur + oy * sy + ox, sy, pred + oy * 16 + ox, 16);
+        nz8[i8] = ref_quant_8x8(d[i8], qp, 0);
+        for (int k = 0; k < 64; k++) zz[k] = d[i8][ref_zigzag8x8[k]];
+        score8[i8] = ref_decimate_score64(zz);
+        total += score8[i8];
+        for (int k = 0; k < 64; k++) coef[(i8 * 4 + (k & 3)) * 16 + (k >> 2)] = zz[k];
+    }
+    for (int i8 = 0; i8 < 4; i8++) { /* [EXT] x264 luma decimation, same thresholds as the 4x4 path */
+        const int ox = (i8 & 1) * 8, oy = (i8 >> 1) * 8;
+        if (total < 6 || score8[i8] < 4) nz8[i8] = 0;
+        if (nz8[i8]) {
+            cbp |= 1 << i8;
+            ref_dequant_8x8(d[i8], qp);
+            ref_add8x8_idct8(rec + oy * sy + ox, sy, pred + oy * 16 + ox, 16, d[i8]);
+        } else {
+            memset(coef + i8 * 64, 0, 128);
+            copy_blk(rec + oy * sy + ox, sy, pred + oy * 16 + ox, 16, 8, 8);
+        }
+        for (int i4 = 0; i4 < 4; i4++) {
+            int n = 0;
+            for (int k = 0; k < 16; k++) n += coef[(i8 * 4 + i4) * 16 + k] != 0;
+            mi->nnz[i8 * 4 + i4] = (uint8_t)n;
+        }
+    }
+    mi->cbp = (uint8_t)((mi->cbp & 0x30) | cbp);
+}
+
 static void encode_inter_luma(struct ref_enc *e, int mbx, int mby, const uint8_t *pred, ref_mb_info *mi, int16_t *coef) {
     const int sy = e->sy, qp = e->qp;
     uint8_t *rec = e->rec[0] + mby * 16 * sy + mbx * 16;
@@ -247,6 +285,28 @@ static void predict_mv(struct ref_enc *e, int mbx, int mby, int mvp[2], int skip
 }
 
 /* ---- macroblock analysis + encode ---------------------------------------------- */
+/* the MB as P_L0_16x16 at its search vector: luma with the transform size chosen by
+ * [EXT] x264_mb_analyse_transform (sa8d of the residual < satd of the residual -> 8x8), then chroma */
+static void code_inter_at_me(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, int16_t *coef) {
+    const int sy = e->sy, sc = e->sc;
+    uint8_t predY[256], predC[2][64];
+    const uint8_t *cur = e->cur[0] + mby * 16 * sy + mbx * 16;
+    memset(coef, 0, COEF_PER_MB * sizeof(int16_t));
+    memset(mi->nnz, 0, sizeof mi->nnz);
+    mi->cbp = 0;
+    mi->mv[0] = mi->me_mv[0]; mi->mv[1] = mi->me_mv[1];
+    ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, mi->mv[0], mi->mv[1], 16, 16);
+    int s8 = 0;
+    for (int i8 = 0; i8 < 4; i8++) s8 += ref_sa8d_8x8_raw(cur + (i8 >> 1) * 8 * sy + (i8 & 1) * 8, sy, predY + (i8 >> 1) * 128 + (i8 & 1) * 8, 16);
+    mi->t8 = (uint8_t)(((s8 + 2) >> 2) < mi->me_satd);
+    if (mi->t8) encode_inter_luma8(e, mbx, mby, predY, mi, coef);
+    else encode_inter_luma(e, mbx, mby, predY, mi, coef);
+    if (!(mi->cbp & 15)) mi->t8 = 0; /* the flag is only transmitted with coded luma */
+    for (int pl = 0; pl < 2; pl++)
+        ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, mi->mv[0], mi->mv[1], 8, 8);
+    encode_chroma(e, mbx, mby, predC, 0, mi, coef);
+}
+
 void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     const int sy = e->sy, sc = e->sc, lambda = ref_lambda[e->qp];
     ref_mb_info *mi = MBI(e, mbx, mby);
@@ -263,23 +323,30 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     memset(mi->i4_mode, 2, 16);
     mi->cbp = 0; mi->mv[0] = mi->mv[1] = 0; mi->mvd[0] = mi->mvd[1] = 0; mi->i16_mode = 0; mi->chroma_mode = 0;
 
+    mi->t8 = 0;
     if (!e->is_idr) {
         predict_mv(e, mbx, mby, mvp, skipmv);
-        /* [EXT] x264 probe_skip: code the MB at the P_Skip vector; all-zero after decimation -> P_Skip */
-        ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, skipmv[0], skipmv[1], 16, 16);
-        encode_inter_luma(e, mbx, mby, predY, mi, coef);
-        if ((mi->cbp & 15) == 0) {
-            for (int pl = 0; pl < 2; pl++)
-                ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, skipmv[0], skipmv[1], 8, 8);
-            encode_chroma(e, mbx, mby, predC, 0, mi, coef);
-            if (mi->cbp == 0) {
-                mi->type = REF_MB_PSKIP; mi->mv[0] = (int16_t)skipmv[0]; mi->mv[1] = (int16_t)skipmv[1];
-                return;
-            }
+        /* [EXT] x264 probe_skip: would the MB coded at the P_Skip vector leave nothing after decimation?  When the skip
+         * vector IS the search vector the answer is the real coding at that vector (with its transform-size choice),
+         * otherwise a 4x4-transform probe. */
+        if (skipmv[0] == mi->me_mv[0] && skipmv[1] == mi->me_mv[1]) {
+            code_inter_at_me(e, mbx, mby, mi, coef);
+        } else {
+            ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, skipmv[0], skipmv[1], 16, 16);
+            encode_inter_luma(e, mbx, mby, predY, mi, coef);
+            if ((mi->cbp & 15) == 0) {
+                for (int pl = 0; pl < 2; pl++)
+                    ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, skipmv[0], skipmv[1], 8, 8);
+                encode_chroma(e, mbx, mby, predC, 0, mi, coef);
+            } else mi->cbp |= 0x10; /* not a skip; chroma not examined */
+        }
+        if (mi->cbp == 0) {
+            mi->type = REF_MB_PSKIP; mi->mv[0] = (int16_t)skipmv[0]; mi->mv[1] = (int16_t)skipmv[1]; mi->t8 = 0;
+            return;
         }
         memset(coef, 0, COEF_PER_MB * sizeof(int16_t));
         memset(mi->nnz, 0, sizeof mi->nnz);
-        mi->cbp = 0;
+        mi->cbp = 0; mi->t8 = 0;
         cost_inter = mi->me_satd + lambda * (ref_mv_bits(mi->me_mv[0] - mvp[0]) + ref_mv_bits(mi->me_mv[1] - mvp[1]));
     }
     /* P frames: intra is analysed for real only when a source-based Intra16x16 estimate comes within 25 % of the inter
@@ -311,9 +378,10 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     } else if (type == REF_MB_I16) {
         encode_i16(e, mbx, mby, mode16, mi, coef);
     } else {
-        mi->mv[0] = mi->me_mv[0]; mi->mv[1] = mi->me_mv[1];
-        ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, mi->mv[0], mi->mv[1], 16, 16);
-        encode_inter_luma(e, mbx, mby, predY, mi, coef);
+        code_inter_at_me(e, mbx, mby, mi, coef);
+        mi->mvd[0] = (int16_t)(mi->mv[0] - mvp[0]); mi->mvd[1] = (int16_t)(mi->mv[1] - mvp[1]);
+        if (mi->cbp == 0 && mi->mv[0] == skipmv[0] && mi->mv[1] == skipmv[1]) mi->type = REF_MB_PSKIP;
+        return;
     }
 
     if (type >= REF_MB_I16) { /* chroma intra mode by SATD over both planes */
@@ -330,12 +398,6 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         }
         mi->chroma_mode = (uint8_t)bm;
         encode_chroma(e, mbx, mby, predC, 1, mi, coef);
-    } else {
-        for (int pl = 0; pl < 2; pl++)
-            ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, mi->mv[0], mi->mv[1], 8, 8);
-        encode_chroma(e, mbx, mby, predC, 0, mi, coef);
-        mi->mvd[0] = (int16_t)(mi->mv[0] - mvp[0]); mi->mvd[1] = (int16_t)(mi->mv[1] - mvp[1]);
-        if (mi->cbp == 0 && mi->mv[0] == skipmv[0] && mi->mv[1] == skipmv[1]) mi->type = REF_MB_PSKIP;
     }
 }
 
@@ -385,7 +447,8 @@ static void filter_edge(uint8_t *pix, int xs, int ys, int n, const int *bS, int 
 static int edge_bs(const ref_mb_info *mp, int bp, const ref_mb_info *mq, int bq, int mb_edge) {
     int ip = mp->type >= REF_MB_I16, iq = mq->type >= REF_MB_I16;
     if (ip || iq) return mb_edge ? 4 : 3;
-    if (mp->nnz[bp] || mq->nnz[bq]) return 2;
+    /* 8x8-transform MBs: 'the 8x8 block containing the sample has non-zero coefficients' (8.7.2.1) */
+    if ((mp->t8 ? (mp->cbp >> (bp >> 2)) & 1 : mp->nnz[bp]) || (mq->t8 ? (mq->cbp >> (bq >> 2)) & 1 : mq->nnz[bq])) return 2;
     if (iabs(mp->mv[0] - mq->mv[0]) >= 4 || iabs(mp->mv[1] - mq->mv[1]) >= 4) return 1;
     return 0;
 }
@@ -409,8 +472,10 @@ void ref_mb_deblock(struct ref_enc *e, int mbx, int mby) {
                 any |= bS[k];
             }
             if (!any) continue;
-            if (dir == 0) filter_edge(Y + ed * 4, 1, sy, 16, bS, 0, qp);
-            else filter_edge(Y + ed * 4 * sy, sy, 1, 16, bS, 0, qp);
+            if (!(mq->t8 && (ed & 1))) { /* transform_size_8x8_flag: luma edges 1 and 3 are not transform edges */
+                if (dir == 0) filter_edge(Y + ed * 4, 1, sy, 16, bS, 0, qp);
+                else filter_edge(Y + ed * 4 * sy, sy, 1, 16, bS, 0, qp);
+            }
             if (!(ed & 1))
                 for (int pl = 1; pl < 3; pl++) {
                     uint8_t *C = e->rec[pl] + mby * 8 * sc + mbx * 8;
@@ -445,6 +510,7 @@ void ref_mb_write(struct ref_enc *e, int mbx, int mby, uint8_t *out, int *bp, in
         ref_put_se(out, bp, mi->mvd[0]); ref_put_se(out, bp, mi->mvd[1]);
     } else if (mi->type == REF_MB_I4) {
         ref_put_ue(out, bp, P ? 5 : 0);
+        ref_put_bits(out, bp, 1, 0); /* transform_size_8x8_flag (PPS transform_8x8_mode_flag = 1): Intra4x4, not Intra8x8 */
         for (int blk = 0; blk < 16; blk++) {
             int bx = ref_blk_x[blk], by = ref_blk_y[blk], mA, mB;
             if (bx > 0) mA = mi->i4_mode[blk_of[by][bx - 1]];
@@ -466,6 +532,7 @@ void ref_mb_write(struct ref_enc *e, int mbx, int mby, uint8_t *out, int *bp, in
         unsigned code = 0;
         while (tab[code] != mi->cbp) code++;
         ref_put_ue(out, bp, code);
+        if (mi->type == REF_MB_P16 && cl) ref_put_bits(out, bp, 1, mi->t8); /* transform_size_8x8_flag */
     }
     if (mi->type == REF_MB_I16 || mi->cbp) {
         ref_put_se(out, bp, 0); /* mb_qp_delta */

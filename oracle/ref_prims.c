@@ -391,3 +391,98 @@ int ref_median3(int a, int b, int c) {
     int mn = a < b ? a : b, mx = a < b ? b : a;
     return c < mn ? mn : (c > mx ? mx : c);
 }
+
+/* ---- 8x8 transform path (High profile: transform_size_8x8_flag) ----------------------------------- */
+/* [EXT] x264 sub8x8_dct8 1-D butterfly (the forward form matching H.264's 8x8 inverse) */
+static void dct8_1d(const int *s, int st, int *d, int dt) {
+    const int a0 = s[0] + s[7 * st], a1 = s[st] + s[6 * st], a2 = s[2 * st] + s[5 * st], a3 = s[3 * st] + s[4 * st];
+    const int a4 = s[0] - s[7 * st], a5 = s[st] - s[6 * st], a6 = s[2 * st] - s[5 * st], a7 = s[3 * st] - s[4 * st];
+    const int b0 = a0 + a3, b1 = a1 + a2, b2 = a0 - a3, b3 = a1 - a2;
+    const int b4 = a5 + a6 + ((a4 >> 1) + a4), b5 = a4 - a7 - ((a6 >> 1) + a6);
+    const int b6 = a4 + a7 - ((a5 >> 1) + a5), b7 = a5 - a6 + ((a7 >> 1) + a7);
+    d[0] = b0 + b1; d[dt] = b4 + (b7 >> 2); d[2 * dt] = b2 + (b3 >> 1); d[3 * dt] = b5 + (b6 >> 2);
+    d[4 * dt] = b0 - b1; d[5 * dt] = b6 - (b5 >> 2); d[6 * dt] = (b2 >> 1) - b3; d[7 * dt] = (b4 >> 2) - b7;
+}
+/* residual -> 8x8 forward transform: rows first, then columns; dct raster (y*8+x) */
+void ref_sub8x8_dct8(int16_t dct[64], const uint8_t *cur, int sc, const uint8_t *pred, int sp) {
+    int d[64], t[64];
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++) d[y * 8 + x] = cur[y * sc + x] - pred[y * sp + x];
+    for (int y = 0; y < 8; y++) dct8_1d(d + y * 8, 1, t + y * 8, 1);
+    for (int x = 0; x < 8; x++) dct8_1d(t + x, 8, d + x, 8);
+    for (int i = 0; i < 64; i++) dct[i] = (int16_t)d[i];
+}
+/* quantise in place (raster); level = sign * ((|c| + bias) * mf >> 16), mf = quant8_mf >> (qp/6) [EXT: x264 quant_8x8] */
+int ref_quant_8x8(int16_t dct[64], int qp, int intra) {
+    const int dz = intra ? 21 : 11, s = qp / 6;
+    int nz = 0;
+    for (int i = 0; i < 64; i++) {
+        const int m = ref_quant8_mf[qp % 6][ref_cls8[((i >> 3) & 3) * 4 + (i & 3)]];
+        const int j = s <= 0 ? m : (m + (1 << (s - 1))) >> s;
+        int b = ((dz << 10) + (j >> 1)) / j;
+        const int cap = (1 << 15) / j;
+        if (b > cap) b = cap;
+        dct[i] = (int16_t)quant_one(dct[i], j, b);
+        nz |= dct[i];
+    }
+    return nz != 0;
+}
+/* H.264 8.5.13 (scaling of 8x8 blocks, flat matrix): d = (c * 16 * v) << (qp/6 - 6), rounded right shift below qp 36 */
+void ref_dequant_8x8(int16_t dct[64], int qp) {
+    const int qb = qp / 6 - 6;
+    for (int i = 0; i < 64; i++) {
+        const int ls = ref_dequant8_v[qp % 6][ref_cls8[((i >> 3) & 3) * 4 + (i & 3)]] * 16;
+        dct[i] = (int16_t)(qb >= 0 ? (dct[i] * ls) << qb : (dct[i] * ls + (1 << (-qb - 1))) >> -qb);
+    }
+}
+/* H.264 8.5.13 eq 8-338..8-354: one 1-D inverse pass */
+static void idct8_1d(const int *s, int st, int *d, int dt) {
+    const int a0 = s[0] + s[4 * st], a2 = s[0] - s[4 * st], a4 = (s[2 * st] >> 1) - s[6 * st], a6 = s[2 * st] + (s[6 * st] >> 1);
+    const int a1 = -s[3 * st] + s[5 * st] - s[7 * st] - (s[7 * st] >> 1), a3 = s[st] + s[7 * st] - s[3 * st] - (s[3 * st] >> 1);
+    const int a5 = -s[st] + s[7 * st] + s[5 * st] + (s[5 * st] >> 1), a7 = s[3 * st] + s[5 * st] + s[st] + (s[st] >> 1);
+    const int b0 = a0 + a6, b2 = a2 + a4, b4 = a2 - a4, b6 = a0 - a6;
+    const int b1 = a1 + (a7 >> 2), b3 = a3 + (a5 >> 2), b5 = (a3 >> 2) - a5, b7 = a7 - (a1 >> 2);
+    d[0] = b0 + b7; d[dt] = b2 + b5; d[2 * dt] = b4 + b3; d[3 * dt] = b6 + b1;
+    d[4 * dt] = b6 - b1; d[5 * dt] = b4 - b3; d[6 * dt] = b2 - b5; d[7 * dt] = b0 - b7;
+}
+void ref_add8x8_idct8(uint8_t *dst, int sd, const uint8_t *pred, int sp, const int16_t dct[64]) {
+    int d[64], t[64];
+    for (int i = 0; i < 64; i++) d[i] = dct[i];
+    for (int y = 0; y < 8; y++) idct8_1d(d + y * 8, 1, t + y * 8, 1); /* horizontal first (8.5.13) */
+    for (int x = 0; x < 8; x++) idct8_1d(t + x, 8, d + x, 8);
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++) dst[y * sd + x] = (uint8_t)clip255(pred[y * sp + x] + ((d[y * 8 + x] + 32) >> 6));
+}
+/* [EXT] x264 pixel_sa8d_8x8 without its final rounding: sum |8x8 Hadamard of the difference| */
+int ref_sa8d_8x8_raw(const uint8_t *a, int sa, const uint8_t *b, int sb) {
+    int d[64], t[64], s = 0;
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++) d[y * 8 + x] = a[y * sa + x] - b[y * sb + x];
+    for (int pass = 0; pass < 2; pass++) {
+        for (int r = 0; r < 8; r++) {
+            const int *p = pass ? t + r : d + r * 8;
+            const int st = pass ? 8 : 1;
+            int *o = pass ? d + r : t + r * 8;
+            const int a0 = p[0] + p[st], a1 = p[0] - p[st], a2 = p[2 * st] + p[3 * st], a3 = p[2 * st] - p[3 * st];
+            const int a4 = p[4 * st] + p[5 * st], a5 = p[4 * st] - p[5 * st], a6 = p[6 * st] + p[7 * st], a7 = p[6 * st] - p[7 * st];
+            const int b0 = a0 + a2, b1 = a1 + a3, b2 = a0 - a2, b3 = a1 - a3, b4 = a4 + a6, b5 = a5 + a7, b6 = a4 - a6, b7 = a5 - a7;
+            o[0] = b0 + b4; o[st] = b1 + b5; o[2 * st] = b2 + b6; o[3 * st] = b3 + b7;
+            o[4 * st] = b0 - b4; o[5 * st] = b1 - b5; o[6 * st] = b2 - b6; o[7 * st] = b3 - b7;
+        }
+    }
+    for (int i = 0; i < 64; i++) s += iabs(d[i]);
+    return s;
+}
+/* [EXT] x264_decimate_score64 over zigzag-ordered levels of one 8x8 block */
+int ref_decimate_score64(const int16_t *zz) {
+    static const uint8_t ds8[64] = {3, 3, 3, 3, 2, 2, 2, 2, 2, 2, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};
+    int idx = 63, score = 0;
+    while (idx >= 0 && zz[idx] == 0) idx--;
+    while (idx >= 0) {
+        int run = 0;
+        if (iabs(zz[idx--]) > 1) return 9;
+        while (idx >= 0 && zz[idx] == 0) { idx--; run++; }
+        score += ds8[run];
+    }
+    return score;
+}

@@ -11,7 +11,8 @@ _SO = os.path.join(ROOT, "oracle", "libceraoracle.so")
 class MbInfo(C.Structure):
     _fields_ = [("type", C.c_uint8), ("i16_mode", C.c_uint8), ("chroma_mode", C.c_uint8), ("cbp", C.c_uint8),
                 ("i4_mode", C.c_uint8 * 16), ("mv", C.c_int16 * 2), ("mvd", C.c_int16 * 2), ("nnz", C.c_uint8 * 28),
-                ("me_mv", C.c_int16 * 2), ("me_satd", C.c_int32), ("l1_mv", C.c_int16 * 2), ("bits", C.c_int32)]
+                ("me_mv", C.c_int16 * 2), ("me_satd", C.c_int32), ("l1_mv", C.c_int16 * 2), ("bits", C.c_int32),
+                ("t8", C.c_uint8), ("pad8", C.c_uint8 * 3)]
 
 
 def build():
