@@ -6,13 +6,14 @@
  * One thread = one block; host pointers in, host pointers out (device staging inside).
  */
 #include "../../include/ceracuda.h"
-#include "cc_xform.cuh"
+#include "cc_xform8.cuh"
 #include "cc_i4_table.h"
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 extern "C" void cc_quant_tables(int qp, int intra, uint16_t mf[3], uint16_t bias[3]);
+extern "C" void cc_quant8_tables(int qp, uint16_t mf[6], uint16_t bias[6]);
 
 struct QT { uint16_t mf[3], bias[3]; };
 
@@ -136,6 +137,43 @@ extern "C" int cc_prim_tq4x4(const uint8_t *cur, const uint8_t *pred, int n, int
     return tq_any(cur, pred, n, qp, intra, levels, recon, 0);
 }
 extern "C" int cc_prim_dct4x4(const uint8_t *cur, const uint8_t *pred, int n, int16_t *coef) { return tq_any(cur, pred, n, 0, 0, coef, nullptr, 1); }
+
+/* 8x8 transform chain of whole macroblocks (four 8x8 blocks each), one warp per macroblock, no decimation:
+ * levels [mb][blk8][64 raster], recon [mb][256]; sa8d: the macroblock-level transform-size metric */
+__global__ void kp_tq8(cc_kparams k, const uint8_t *cur, const uint8_t *pred, int n, int16_t *levels, uint8_t *recon, int32_t *sa8d) {
+    __shared__ X8Mem xm[4];
+    __shared__ uint32_t sc[4][64], sp[4][64], sr[4][64];
+    __shared__ int16_t coef[4][16][16];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, i = blockIdx.x * 4 + wid;
+    if (i >= n) return;
+    X8Mem *x = &xm[wid];
+    x->zz[lane] = c_zigzag8[lane]; x->zz[lane + 32] = c_zigzag8[lane + 32];
+    for (int j = lane; j < 64; j += 32) { sc[wid][j] = cc_ld32u(cur + (size_t)i * 256 + 4 * j); sp[wid][j] = cc_ld32u(pred + (size_t)i * 256 + 4 * j); }
+    __syncwarp();
+    const int s8 = sa8d_mb(x, sc[wid], sp[wid], lane);
+    if (lane == 0) sa8d[i] = s8;
+    unsigned nz;
+    inter_luma8(k, x, sc[wid], sp[wid], sr[wid], coef[wid], k.qp, lane, &nz, false);
+    __syncwarp();
+    for (int j = lane; j < 256; j += 32) levels[(size_t)i * 256 + j] = x->q[j >> 6][j & 63];
+    for (int j = lane; j < 64; j += 32) *(uint32_t *)(recon + (size_t)i * 256 + 4 * j) = sr[wid][j];
+}
+extern "C" int cc_prim_tq8x8(const uint8_t *cur, const uint8_t *pred, int n_mb, int qp, int16_t *levels, uint8_t *recon, int32_t *sa8d) {
+    if (!cur || !pred || !levels || !recon || !sa8d || n_mb <= 0 || qp < 0 || qp > 51) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+    cc_kparams k;
+    memset(&k, 0, sizeof k);
+    k.qp = qp;
+    cc_quant8_tables(qp, k.q8mf, k.q8bias);
+    DevBuf dc, dp, dl, dr, ds;
+    if (dc.alloc((size_t)n_mb * 256, cur) || dp.alloc((size_t)n_mb * 256, pred) || dl.alloc((size_t)n_mb * 512, nullptr) || dr.alloc((size_t)n_mb * 256, nullptr) ||
+        ds.alloc((size_t)n_mb * 4, nullptr)) return CC_ERR_NOMEM;
+    CC_LAUNCH(kp_tq8, dim3((unsigned)((n_mb + 3) / 4)), dim3(128), 0, k, (const uint8_t *)dc.p, (const uint8_t *)dp.p, n_mb, (int16_t *)dl.p, (uint8_t *)dr.p, (int32_t *)ds.p);
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
+    if (cudaMemcpy(levels, dl.p, (size_t)n_mb * 512, cudaMemcpyDeviceToHost) != cudaSuccess) return CC_ERR_CUDA;
+    if (cudaMemcpy(recon, dr.p, (size_t)n_mb * 256, cudaMemcpyDeviceToHost) != cudaSuccess) return CC_ERR_CUDA;
+    return cudaMemcpy(sa8d, ds.p, (size_t)n_mb * 4, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
 
 extern "C" int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out) {
     if (!edge || !out || n <= 0 || mode < 0 || mode > 8) return CC_ERR_PARAM;

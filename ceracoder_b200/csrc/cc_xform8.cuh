@@ -104,7 +104,7 @@ __device__ __forceinline__ int decimate_score64(unsigned long long nzm) {
  * reconstruction -> recY (64 words).  Returns the luma cbp in all lanes; *nzmask gets all four 4x4 bits of every coded
  * 8x8 block (what the boundary-strength rule needs for 8x8-transform macroblocks, H.264 8.7.2.1). */
 __device__ __forceinline__ int inter_luma8(const cc_kparams &k, X8Mem *x, const uint32_t *curY, const uint32_t *predY, uint32_t *recY,
-                                           int16_t (*coef)[16], int qp, int lane, unsigned *nzmask) {
+                                           int16_t (*coef)[16], int qp, int lane, unsigned *nzmask, bool decimate = true) {
     const int b = lane >> 3, l = lane & 7;
     int d[8];
     x8_residual(curY, predY, b, l, d);
@@ -135,7 +135,7 @@ __device__ __forceinline__ int inter_luma8(const cc_kparams &k, X8Mem *x, const 
     const int score = big ? 9 : decimate_score64(nzm);          /* identical in the 8 lanes of a block */
     int tot = score + __shfl_xor_sync(FULL, score, 8);
     tot += __shfl_xor_sync(FULL, tot, 16);
-    const bool coded = nzm != 0ull && !(tot < 6 || score < 4);  /* [EXT] x264 luma decimation thresholds */
+    const bool coded = nzm != 0ull && !(decimate && (tot < 6 || score < 4));  /* [EXT] x264 luma decimation thresholds */
     /* interleaved 4x4 layout: scan position p -> block (p & 3), index p >> 2 */
 #pragma unroll
     for (int j = 0; j < 8; j++) coef[b * 4 + (j & 3)][2 * l + (j >> 2)] = coded ? (int16_t)z[j] : (int16_t)0;

@@ -80,6 +80,7 @@ def load_library(path=None):
     L.cc_prim_satd16x16.argtypes = [vp, vp, ci, vp]
     L.cc_prim_tq4x4.argtypes = [vp, vp, ci, ci, ci, vp, vp]
     L.cc_prim_dct4x4.argtypes = [vp, vp, ci, vp]
+    L.cc_prim_tq8x8.argtypes = [vp, vp, ci, ci, vp, vp, vp]
     L.cc_prim_pred4x4.argtypes = [vp, ci, ci, vp]
     L.cc_prim_mc_luma.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     _libs[path] = L

@@ -130,6 +130,9 @@ int cc_prim_satd16x16(const uint8_t *a, const uint8_t *b, int n, int32_t *out);
  * levels: n*16 int16 raster order; recon: n*16 u8 */
 int cc_prim_tq4x4(const uint8_t *cur, const uint8_t *pred, int n, int qp, int intra, int16_t *levels, uint8_t *recon);
 int cc_prim_dct4x4(const uint8_t *cur, const uint8_t *pred, int n, int16_t *coef);
+/* 8x8 transform chain (sub8x8_dct8 -> quant_8x8 (inter dead zone) -> dequant_8x8 -> add8x8_idct8 [EXT]) over n_mb 16x16 blocks (tight 256 B each,
+ * four 8x8 blocks per macroblock): levels n_mb*4*64 int16 raster, recon n_mb*256, sa8d n_mb = (sum|Hadamard8x8| over the MB + 2) >> 2 */
+int cc_prim_tq8x8(const uint8_t *cur, const uint8_t *pred, int n_mb, int qp, int16_t *levels, uint8_t *recon, int32_t *sa8d);
 /* intra 4x4 predictors: edge = n*13 bytes {left3,left2,left1,left0,topleft,top0..top7}; out n*16 */
 int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out);
 /* quarter-pel luma interpolation of n 16x16 blocks taken at (x,y)[i] + mv[i] from one w*h plane (borders replicated) */

@@ -132,3 +132,55 @@ def test_mc_luma_all_fractions(L):
         base = ext.ctypes.data + (pad + int(xy[i, 1])) * s + pad + int(xy[i, 0])
         O.ref_mc_luma(_p(r), 16, C.c_void_p(base), s, int(mv[i, 0]), int(mv[i, 1]), 16, 16)
         assert (out[i] == r).all(), (i, mv[i])
+
+
+@pytest.mark.parametrize("qp", [10, 23, 30, 36, 44, 51])
+def test_transform_chain_8x8(L, qp):
+    """sub8x8_dct8 -> quant_8x8 -> dequant_8x8 -> add8x8_idct8 and the sa8d transform-size metric, per macroblock."""
+    O = oracle()
+    rng = np.random.default_rng(800 + qp)
+    n = 64
+    cur = rng.integers(0, 256, (n, 16, 16), dtype=np.uint8)
+    pred = np.clip(cur.astype(np.int32) + rng.integers(-40, 41, (n, 16, 16)) * (rng.random((n, 1, 1)) < 0.8), 0, 255).astype(np.uint8)
+    pred[0] = cur[0]; cur[1] = 255; pred[1] = 0            # zero residual; extreme residual
+    lev = np.zeros((n, 4, 64), np.int16); rec = np.zeros((n, 16, 16), np.uint8); sa = np.zeros(n, np.int32)
+    assert L.cc_prim_tq8x8(_p(cur), _p(pred), n, qp, _p(lev), _p(rec), _p(sa)) == 0
+    for i in range(n):
+        ref_rec = np.zeros((16, 16), np.uint8); s = 0
+        for b in range(4):
+            oy, ox = (b >> 1) * 8, (b & 1) * 8
+            c = np.ascontiguousarray(cur[i, oy:oy + 8, ox:ox + 8]); p = np.ascontiguousarray(pred[i, oy:oy + 8, ox:ox + 8])
+            d = np.zeros(64, np.int16)
+            O.ref_sub8x8_dct8(_p(d), _p(c), 8, _p(p), 8)
+            O.ref_quant_8x8(_p(d), qp, 0)
+            assert (d == lev[i, b]).all(), f"levels differ: mb {i} block {b} qp {qp}"
+            O.ref_dequant_8x8(_p(d), qp)
+            o = np.zeros((8, 8), np.uint8)
+            O.ref_add8x8_idct8(_p(o), 8, _p(p), 8, _p(d))
+            ref_rec[oy:oy + 8, ox:ox + 8] = o
+            s += O.ref_sa8d_8x8_raw(_p(c), 8, _p(p), 8)
+        assert (ref_rec == rec[i]).all(), f"reconstruction differs: mb {i} qp {qp}"
+        assert sa[i] == (s + 2) >> 2
+    assert (lev[0] == 0).all() and (rec[0] == cur[0]).all() and sa[0] == 0   # zero residual reproduces the prediction
+
+
+def test_oracle_8x8_known_answers():
+    """Definition-level pins of the 8x8 oracle primitives (the decoder pins dequant + inverse transform separately)."""
+    O = oracle()
+    c = np.full((8, 8), 130, np.uint8); p = np.full((8, 8), 120, np.uint8)
+    d = np.zeros(64, np.int16)
+    O.ref_sub8x8_dct8(_p(d), _p(c), 8, _p(p), 8)
+    assert d[0] == 64 * 10 and (d[1:] == 0).all()                      # constant residual -> DC only, gain 64
+    assert O.ref_sa8d_8x8_raw(_p(c), 8, _p(p), 8) == 64 * 10           # Hadamard DC = 64 * c
+    z = np.zeros(64, np.int16); z[0] = 1
+    assert O.ref_decimate_score64(_p(z)) == 3
+    z[0] = 0; z[20] = 1
+    assert O.ref_decimate_score64(_p(z)) == 1                          # run of 20 zeros before it
+    z[21] = -2
+    assert O.ref_decimate_score64(_p(z)) == 9                          # any |level| > 1
+    # round trip at a fine quantiser stays close to the source
+    rng = np.random.default_rng(3)
+    c = rng.integers(0, 256, (8, 8), dtype=np.uint8); p = rng.integers(0, 256, (8, 8), dtype=np.uint8)
+    O.ref_sub8x8_dct8(_p(d), _p(c), 8, _p(p), 8); O.ref_quant_8x8(_p(d), 10, 0); O.ref_dequant_8x8(_p(d), 10)
+    o = np.zeros((8, 8), np.uint8); O.ref_add8x8_idct8(_p(o), 8, _p(p), 8, _p(d))
+    assert np.abs(o.astype(int) - c.astype(int)).max() <= 3
