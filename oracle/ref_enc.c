@@ -151,6 +151,42 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
         }
     }
     mi->me_mv[0] = (int16_t)bx; mi->me_mv[1] = (int16_t)by; mi->me_satd = bsatd;
+    mi->me_cost16 = bcost;
+    /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"): every quadrant searches +-2 full-pel
+     * around the 16x16 integer vector by SAD, then the same half/quarter-pel SATD refinement.  P_8x8 is chosen when the
+     * summed cost plus 8 lambda (mb_type + four sub_mb_type code lengths over P_L0_16x16) beats the 16x16 cost. */
+    int cost8 = 8 * lambda;
+    for (int p = 0; p < 4; p++) {
+        const uint8_t *c8 = cur + (p >> 1) * 8 * sy + (p & 1) * 8, *r8 = ref + (p >> 1) * 8 * sy + (p & 1) * 8;
+        unsigned b8 = ~0u;
+        int fx = bmx, fy = bmy;
+        for (int i = 0; i < 25; i++) {
+            int mx = bmx + i % 5 - 2, my = bmy + i / 5 - 2;
+            unsigned c = (unsigned)ref_sad(c8, sy, r8 + my * sy + mx, sy, 8, 8) +
+                         (unsigned)(lambda * (ref_mv_bits(4 * (mx - pm[0])) + ref_mv_bits(4 * (my - pm[1]))));
+            unsigned key = (c << 5) | (unsigned)i;
+            if (key < b8) { b8 = key; fx = mx; fy = my; }
+        }
+        int qx = 4 * fx, qy = 4 * fy, qcost = 1 << 30, qsatd = 0;
+        uint8_t p8[64];
+        for (int step = 2; step >= 1; step--) {
+            int cx = qx, cy = qy;
+            for (int i = (step == 2 ? -1 : 0); i < 9; i++) {
+                int dx, dy;
+                if (i < 0) { dx = dy = 0; }
+                else { if (i == 4) continue; dx = (i % 3 - 1) * step; dy = (i / 3 - 1) * step; }
+                int mx = cx + dx, my = cy + dy;
+                ref_mc_luma(p8, 8, r8, sy, mx, my, 8, 8);
+                int satd = ref_satd(c8, sy, p8, 8, 8, 8);
+                int c = satd + lambda * (ref_mv_bits(mx - 4 * pm[0]) + ref_mv_bits(my - 4 * pm[1]));
+                if (c < qcost) { qcost = c; qsatd = satd; qx = mx; qy = my; }
+            }
+        }
+        mi->me_mv8[p][0] = (int16_t)qx; mi->me_mv8[p][1] = (int16_t)qy; mi->me_satd8[p] = qsatd;
+        cost8 += qcost;
+    }
+    mi->me_cost8 = cost8;
+    mi->me_part = (uint8_t)(cost8 < bcost);
 }
 
 /* ---- headers ------------------------------------------------------------------------ */

@@ -80,7 +80,13 @@ typedef struct {
     int16_t l1_mv[2];
     int32_t bits; /* bits this MB contributed to slice data */
     uint8_t t8;   /* transform_size_8x8_flag (inter MBs only) */
-    uint8_t pad8[3];
+    uint8_t part; /* 0: one 16x16 partition, 1: P_8x8 (four 8x8 sub-macroblocks, sub_mb_type P_L0_8x8) */
+    uint8_t me_part; /* partitioning chosen by the motion search */
+    uint8_t pad8;
+    int16_t mv4[4][2], mvd4[4][2]; /* final vector / mvd per 8x8 quadrant (all equal for 16x16 and P_Skip) */
+    int16_t me_mv8[4][2];          /* 8x8 search vectors, quarter-pel */
+    int32_t me_satd8[4];
+    int32_t me_cost16, me_cost8;   /* search costs (SATD + lambda * approximate mvd bits [+ partition overhead]) */
 } ref_mb_info;
 
 typedef struct ref_enc ref_enc;

@@ -255,33 +255,68 @@ static void encode_chroma(struct ref_enc *e, int mbx, int mby, uint8_t pred[2][6
     mi->cbp = (uint8_t)((mi->cbp & 15) | ((any_ac ? 2 : (any_dc ? 1 : 0)) << 4));
 }
 
-/* ---- motion vector prediction, H.264 8.4.1.3 (one 16x16 partition per MB, one reference) */
-static void nb_mv(struct ref_enc *e, int x, int y, int avail, int *ref, int mv[2]) {
+/* ---- motion vector prediction, H.264 8.4.1.3 (16x16 or four 8x8 partitions per MB, one reference) */
+/* neighbour = 8x8 quadrant `part` of MB (x,y): ref -2 unavailable, -1 intra, 0 inter */
+static void nb_mv(struct ref_enc *e, int x, int y, int avail, int part, int *ref, int mv[2]) {
     mv[0] = mv[1] = 0;
     if (!avail) { *ref = -2; return; }
     ref_mb_info *n = MBI(e, x, y);
     if (n->type >= REF_MB_I16) { *ref = -1; return; }
-    *ref = 0; mv[0] = n->mv[0]; mv[1] = n->mv[1];
+    *ref = 0; mv[0] = n->mv4[part][0]; mv[1] = n->mv4[part][1];
 }
-static void predict_mv(struct ref_enc *e, int mbx, int mby, int mvp[2], int skip[2]) {
-    int rA, rB, rC, a[2], b[2], c[2];
-    int L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
-    nb_mv(e, mbx - 1, mby, L, &rA, a);
-    nb_mv(e, mbx, mby - 1, T, &rB, b);
-    nb_mv(e, mbx + 1, mby - 1, av_topright(e, mbx, mby), &rC, c);
-    if (rC == -2) nb_mv(e, mbx - 1, mby - 1, T && L, &rC, c);
+static void median_pred(int rA, const int *a, int rB, const int *b0, int rC, const int *c0, int mvp[2]) {
+    int b[2] = {b0[0], b0[1]}, c[2] = {c0[0], c0[1]};
     if (rB == -2 && rC == -2 && rA != -2) { rB = rC = rA; b[0] = c[0] = a[0]; b[1] = c[1] = a[1]; }
     int n = (rA == 0) + (rB == 0) + (rC == 0);
     if (n == 1) {
         const int *s = rA == 0 ? a : (rB == 0 ? b : c);
         mvp[0] = s[0]; mvp[1] = s[1];
     } else { mvp[0] = ref_median3(a[0], b[0], c[0]); mvp[1] = ref_median3(a[1], b[1], c[1]); }
+}
+/* 16x16 partition: A = left MB quadrant 1, B = top MB quadrant 2, C = top-right MB quadrant 2 (else D = top-left MB
+ * quadrant 3) — the quadrants that contain the neighbouring luma locations of 6.4.11.7 */
+static void predict_mv(struct ref_enc *e, int mbx, int mby, int mvp[2], int skip[2]) {
+    int rA, rB, rC, a[2], b[2], c[2];
+    int L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
+    nb_mv(e, mbx - 1, mby, L, 1, &rA, a);
+    nb_mv(e, mbx, mby - 1, T, 2, &rB, b);
+    nb_mv(e, mbx + 1, mby - 1, av_topright(e, mbx, mby), 2, &rC, c);
+    if (rC == -2) nb_mv(e, mbx - 1, mby - 1, T && L, 3, &rC, c);
+    median_pred(rA, a, rB, b, rC, c, mvp);
     /* P_Skip, 8.4.1.1 */
-    int rA0, rB0, a0[2], b0[2];
-    nb_mv(e, mbx - 1, mby, L, &rA0, a0);
-    nb_mv(e, mbx, mby - 1, T, &rB0, b0);
-    if (!L || !T || (rA0 == 0 && a0[0] == 0 && a0[1] == 0) || (rB0 == 0 && b0[0] == 0 && b0[1] == 0)) skip[0] = skip[1] = 0;
+    if (!L || !T || (rA == 0 && a[0] == 0 && a[1] == 0) || (rB == 0 && b[0] == 0 && b[1] == 0)) skip[0] = skip[1] = 0;
     else { skip[0] = mvp[0]; skip[1] = mvp[1]; }
+}
+/* 8x8 quadrant p of a P_8x8 MB; mv4 = vectors of the quadrants already decided (decoding order 0..3) */
+static void predict_mv8(struct ref_enc *e, int mbx, int mby, int p, int16_t (*mv4)[2], int *mvp) {
+    int rA, rB, rC, a[2], b[2], c[2];
+    int L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
+#define OWN(q, r, v) do { r = 0; v[0] = mv4[q][0]; v[1] = mv4[q][1]; } while (0)
+    if (p == 0) {
+        nb_mv(e, mbx - 1, mby, L, 1, &rA, a);
+        nb_mv(e, mbx, mby - 1, T, 2, &rB, b);
+        nb_mv(e, mbx, mby - 1, T, 3, &rC, c);
+        if (rC == -2) nb_mv(e, mbx - 1, mby - 1, T && L, 3, &rC, c);
+    } else if (p == 1) {
+        OWN(0, rA, a);
+        nb_mv(e, mbx, mby - 1, T, 3, &rB, b);
+        nb_mv(e, mbx + 1, mby - 1, av_topright(e, mbx, mby), 2, &rC, c);
+        if (rC == -2) nb_mv(e, mbx, mby - 1, T, 2, &rC, c);
+    } else if (p == 2) {
+        nb_mv(e, mbx - 1, mby, L, 3, &rA, a);
+        OWN(0, rB, b);
+        OWN(1, rC, c);
+    } else {
+        OWN(2, rA, a);
+        OWN(1, rB, b);
+        OWN(0, rC, c); /* C (the MB to the right) is not yet decoded -> D = quadrant 0 */
+    }
+#undef OWN
+    median_pred(rA, a, rB, b, rC, c, mvp);
+}
+static void set_mv_all(ref_mb_info *mi, int mx, int my) {
+    for (int p = 0; p < 4; p++) { mi->mv4[p][0] = (int16_t)mx; mi->mv4[p][1] = (int16_t)my; }
+    mi->mv[0] = (int16_t)mx; mi->mv[1] = (int16_t)my;
 }
 
 /* ---- macroblock analysis + encode ---------------------------------------------- */
@@ -294,16 +329,32 @@ static void code_inter_at_me(struct ref_enc *e, int mbx, int mby, ref_mb_info *m
     memset(coef, 0, COEF_PER_MB * sizeof(int16_t));
     memset(mi->nnz, 0, sizeof mi->nnz);
     mi->cbp = 0;
-    mi->mv[0] = mi->me_mv[0]; mi->mv[1] = mi->me_mv[1];
-    ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, mi->mv[0], mi->mv[1], 16, 16);
+    mi->part = mi->me_part;
+    int satd4 = mi->me_satd;
+    if (mi->part) { /* P_8x8: each quadrant predicted with its own vector (chroma: the 4x4 block it covers) */
+        satd4 = 0;
+        for (int p = 0; p < 4; p++) {
+            const int ox = (p & 1) * 8, oy = (p >> 1) * 8;
+            mi->mv4[p][0] = mi->me_mv8[p][0]; mi->mv4[p][1] = mi->me_mv8[p][1];
+            ref_mc_luma(predY + oy * 16 + ox, 16, e->ref[0] + (mby * 16 + oy) * sy + mbx * 16 + ox, sy, mi->mv4[p][0], mi->mv4[p][1], 8, 8);
+            for (int pl = 0; pl < 2; pl++)
+                ref_mc_chroma(predC[pl] + (oy / 2) * 8 + ox / 2, 8, e->ref[1 + pl] + (mby * 8 + oy / 2) * sc + mbx * 8 + ox / 2, sc,
+                              mi->mv4[p][0], mi->mv4[p][1], 4, 4);
+            satd4 += mi->me_satd8[p];
+        }
+        mi->mv[0] = mi->mv4[0][0]; mi->mv[1] = mi->mv4[0][1];
+    } else {
+        set_mv_all(mi, mi->me_mv[0], mi->me_mv[1]);
+        ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, mi->mv[0], mi->mv[1], 16, 16);
+        for (int pl = 0; pl < 2; pl++)
+            ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, mi->mv[0], mi->mv[1], 8, 8);
+    }
     int s8 = 0;
     for (int i8 = 0; i8 < 4; i8++) s8 += ref_sa8d_8x8_raw(cur + (i8 >> 1) * 8 * sy + (i8 & 1) * 8, sy, predY + (i8 >> 1) * 128 + (i8 & 1) * 8, 16);
-    mi->t8 = (uint8_t)(((s8 + 2) >> 2) < mi->me_satd);
+    mi->t8 = (uint8_t)(((s8 + 2) >> 2) < satd4);
     if (mi->t8) encode_inter_luma8(e, mbx, mby, predY, mi, coef);
     else encode_inter_luma(e, mbx, mby, predY, mi, coef);
     if (!(mi->cbp & 15)) mi->t8 = 0; /* the flag is only transmitted with coded luma */
-    for (int pl = 0; pl < 2; pl++)
-        ref_mc_chroma(predC[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, mi->mv[0], mi->mv[1], 8, 8);
     encode_chroma(e, mbx, mby, predC, 0, mi, coef);
 }
 
@@ -321,7 +372,9 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     memset(coef, 0, COEF_PER_MB * sizeof(int16_t));
     memset(mi->nnz, 0, sizeof mi->nnz);
     memset(mi->i4_mode, 2, 16);
-    mi->cbp = 0; mi->mv[0] = mi->mv[1] = 0; mi->mvd[0] = mi->mvd[1] = 0; mi->i16_mode = 0; mi->chroma_mode = 0;
+    mi->cbp = 0; mi->mvd[0] = mi->mvd[1] = 0; mi->i16_mode = 0; mi->chroma_mode = 0; mi->part = 0;
+    set_mv_all(mi, 0, 0);
+    memset(mi->mvd4, 0, sizeof mi->mvd4);
 
     mi->t8 = 0;
     if (!e->is_idr) {
@@ -329,7 +382,7 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         /* [EXT] x264 probe_skip: would the MB coded at the P_Skip vector leave nothing after decimation?  When the skip
          * vector IS the search vector the answer is the real coding at that vector (with its transform-size choice),
          * otherwise a 4x4-transform probe. */
-        if (skipmv[0] == mi->me_mv[0] && skipmv[1] == mi->me_mv[1]) {
+        if (!mi->me_part && skipmv[0] == mi->me_mv[0] && skipmv[1] == mi->me_mv[1]) {
             code_inter_at_me(e, mbx, mby, mi, coef);
         } else {
             ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, skipmv[0], skipmv[1], 16, 16);
@@ -341,12 +394,20 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
             } else mi->cbp |= 0x10; /* not a skip; chroma not examined */
         }
         if (mi->cbp == 0) {
-            mi->type = REF_MB_PSKIP; mi->mv[0] = (int16_t)skipmv[0]; mi->mv[1] = (int16_t)skipmv[1]; mi->t8 = 0;
+            mi->type = REF_MB_PSKIP; set_mv_all(mi, skipmv[0], skipmv[1]); mi->t8 = 0; mi->part = 0;
             return;
         }
         memset(coef, 0, COEF_PER_MB * sizeof(int16_t));
         memset(mi->nnz, 0, sizeof mi->nnz);
-        mi->cbp = 0; mi->t8 = 0;
+        mi->cbp = 0; mi->t8 = 0; mi->part = 0;
+        if (mi->me_part) { /* exact cost of the P_8x8 coding: per-quadrant SATD + mvd bits against the real predictors */
+            cost_inter = 8 * lambda;
+            for (int p = 0; p < 4; p++) {
+                int mp[2];
+                predict_mv8(e, mbx, mby, p, mi->me_mv8, mp);
+                cost_inter += mi->me_satd8[p] + lambda * (ref_mv_bits(mi->me_mv8[p][0] - mp[0]) + ref_mv_bits(mi->me_mv8[p][1] - mp[1]));
+            }
+        } else
         cost_inter = mi->me_satd + lambda * (ref_mv_bits(mi->me_mv[0] - mvp[0]) + ref_mv_bits(mi->me_mv[1] - mvp[1]));
     }
     /* P frames: intra is analysed for real only when a source-based Intra16x16 estimate comes within 25 % of the inter
@@ -379,6 +440,15 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         encode_i16(e, mbx, mby, mode16, mi, coef);
     } else {
         code_inter_at_me(e, mbx, mby, mi, coef);
+        if (mi->part) {
+            for (int p = 0; p < 4; p++) {
+                int mp[2];
+                predict_mv8(e, mbx, mby, p, mi->mv4, mp);
+                mi->mvd4[p][0] = (int16_t)(mi->mv4[p][0] - mp[0]); mi->mvd4[p][1] = (int16_t)(mi->mv4[p][1] - mp[1]);
+            }
+            mi->mvd[0] = mi->mvd4[0][0]; mi->mvd[1] = mi->mvd4[0][1];
+            return;
+        }
         mi->mvd[0] = (int16_t)(mi->mv[0] - mvp[0]); mi->mvd[1] = (int16_t)(mi->mv[1] - mvp[1]);
         if (mi->cbp == 0 && mi->mv[0] == skipmv[0] && mi->mv[1] == skipmv[1]) mi->type = REF_MB_PSKIP;
         return;
@@ -449,7 +519,7 @@ static int edge_bs(const ref_mb_info *mp, int bp, const ref_mb_info *mq, int bq,
     if (ip || iq) return mb_edge ? 4 : 3;
     /* 8x8-transform MBs: 'the 8x8 block containing the sample has non-zero coefficients' (8.7.2.1) */
     if ((mp->t8 ? (mp->cbp >> (bp >> 2)) & 1 : mp->nnz[bp]) || (mq->t8 ? (mq->cbp >> (bq >> 2)) & 1 : mq->nnz[bq])) return 2;
-    if (iabs(mp->mv[0] - mq->mv[0]) >= 4 || iabs(mp->mv[1] - mq->mv[1]) >= 4) return 1;
+    if (iabs(mp->mv4[bp >> 2][0] - mq->mv4[bq >> 2][0]) >= 4 || iabs(mp->mv4[bp >> 2][1] - mq->mv4[bq >> 2][1]) >= 4) return 1;
     return 0;
 }
 void ref_mb_deblock(struct ref_enc *e, int mbx, int mby) {
@@ -505,7 +575,11 @@ void ref_mb_write(struct ref_enc *e, int mbx, int mby, uint8_t *out, int *bp, in
     if (mi->type == REF_MB_PSKIP) { (*skip_run)++; mi->bits = 0; return; }
     if (P) { ref_put_ue(out, bp, (unsigned)*skip_run); *skip_run = 0; }
     int cl = mi->cbp & 15, cc = mi->cbp >> 4;
-    if (mi->type == REF_MB_P16) {
+    if (mi->type == REF_MB_P16 && mi->part) { /* P_8x8: mb_type 3, four sub_mb_type P_L0_8x8 (0), no ref_idx (one reference), four mvd */
+        ref_put_ue(out, bp, 3);
+        for (int p = 0; p < 4; p++) ref_put_ue(out, bp, 0);
+        for (int p = 0; p < 4; p++) { ref_put_se(out, bp, mi->mvd4[p][0]); ref_put_se(out, bp, mi->mvd4[p][1]); }
+    } else if (mi->type == REF_MB_P16) {
         ref_put_ue(out, bp, 0);
         ref_put_se(out, bp, mi->mvd[0]); ref_put_se(out, bp, mi->mvd[1]);
     } else if (mi->type == REF_MB_I4) {

@@ -12,7 +12,9 @@ class MbInfo(C.Structure):
     _fields_ = [("type", C.c_uint8), ("i16_mode", C.c_uint8), ("chroma_mode", C.c_uint8), ("cbp", C.c_uint8),
                 ("i4_mode", C.c_uint8 * 16), ("mv", C.c_int16 * 2), ("mvd", C.c_int16 * 2), ("nnz", C.c_uint8 * 28),
                 ("me_mv", C.c_int16 * 2), ("me_satd", C.c_int32), ("l1_mv", C.c_int16 * 2), ("bits", C.c_int32),
-                ("t8", C.c_uint8), ("pad8", C.c_uint8 * 3)]
+                ("t8", C.c_uint8), ("part", C.c_uint8), ("me_part", C.c_uint8), ("pad8", C.c_uint8),
+                ("mv4", C.c_int16 * 8), ("mvd4", C.c_int16 * 8), ("me_mv8", C.c_int16 * 8), ("me_satd8", C.c_int32 * 4),
+                ("me_cost16", C.c_int32), ("me_cost8", C.c_int32)]
 
 
 def build():
