@@ -49,6 +49,7 @@ void ref_enc_close(ref_enc *e) {
     free(e->l1alloc[0]); free(e->l1alloc[1]); free(e->mb); free(e->coef); free(e->slice_buf); free(e->slice_bits);
     free(e);
 }
+void ref_enc_set_partitions(ref_enc *e, int on) { e->part8 = on != 0; }
 int ref_enc_mb_w(const ref_enc *e) { return e->mb_w; }
 int ref_enc_mb_h(const ref_enc *e) { return e->mb_h; }
 const ref_mb_info *ref_enc_mb_info(const ref_enc *e) { return e->mb; }
@@ -151,7 +152,8 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
         }
     }
     mi->me_mv[0] = (int16_t)bx; mi->me_mv[1] = (int16_t)by; mi->me_satd = bsatd;
-    mi->me_cost16 = bcost;
+    mi->me_cost16 = bcost; mi->me_cost8 = 0; mi->me_part = 0;
+    if (!e->part8) return;
     /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"): every quadrant searches +-2 full-pel
      * around the 16x16 integer vector by SAD, then the same half/quarter-pel SATD refinement.  P_8x8 is chosen when the
      * summed cost plus 8 lambda (mb_type + four sub_mb_type code lengths over P_L0_16x16) beats the 16x16 cost. */

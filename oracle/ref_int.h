@@ -20,6 +20,7 @@ struct ref_enc {
     uint8_t *slice_buf;         /* per-slice RBSP scratch, slice_cap bytes each */
     int slice_cap;
     int *slice_bits;
+    int part8;                  /* 1: the motion search may choose P_8x8 (four 8x8 partitions) */
 };
 
 /* ref_mb.c */

@@ -36,6 +36,7 @@ def lib():
         L.ref_enc_open.restype = C.c_void_p
         L.ref_enc_open.argtypes = [C.c_int] * 5
         L.ref_enc_close.argtypes = [C.c_void_p]
+        L.ref_enc_set_partitions.argtypes = [C.c_void_p, C.c_int]
         L.ref_enc_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.ref_enc_get_recon.argtypes = [C.c_void_p] * 4
         L.ref_enc_mb_info.restype = C.POINTER(MbInfo)
@@ -46,10 +47,11 @@ def lib():
 
 
 class OracleEncoder:
-    def __init__(self, w, h, fps=30, rows_per_slice=4):
+    def __init__(self, w, h, fps=30, rows_per_slice=4, partitions=False):
         self.L = lib()
         self.h_ = self.L.ref_enc_open(w, h, fps, 1, rows_per_slice)
         assert self.h_
+        self.L.ref_enc_set_partitions(self.h_, int(partitions))
         self.w, self.h = w, h
         self.mb_w, self.mb_h = self.L.ref_enc_mb_w(self.h_), self.L.ref_enc_mb_h(self.h_)
         self.out = np.zeros(self.mb_w * self.mb_h * 1024 + 4096, np.uint8)

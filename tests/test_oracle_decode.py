@@ -7,8 +7,8 @@ from h264_decode import decode_aus, split_aus
 from oracle_lib import OracleEncoder
 
 
-def _run(src, w, h, qps, rps, gop=60):
-    enc = OracleEncoder(w, h, 30, rps)
+def _run(src, w, h, qps, rps, gop=60, partitions=False):
+    enc = OracleEncoder(w, h, 30, rps, partitions=partitions)
     aus, recs = [], []
     for i, qp in enumerate(qps):
         y, u, v = src.frame(i)
@@ -24,9 +24,10 @@ def _run(src, w, h, qps, rps, gop=60):
     ("testsrc", 160, 96, 6, [28, 28, 28]),
     ("ball", 128, 80, 1, [35, 30, 25, 20]),
 ])
-def test_decoder_equals_recon(name, w, h, rps, qps):
+@pytest.mark.parametrize("partitions", [False, True])
+def test_decoder_equals_recon(name, w, h, rps, qps, partitions):
     src = make_source(name, w, h)
-    aus, recs = _run(src, w, h, qps, rps, gop=4)
+    aus, recs = _run(src, w, h, qps, rps, gop=4, partitions=partitions)
     frames = decode_aus(aus)
     assert len(frames) == len(aus)
     for (y, u, v), (ry, ru, rv) in zip(frames, recs):
