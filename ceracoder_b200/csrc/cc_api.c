@@ -68,7 +68,7 @@ const char *cc_strerror(int c) {
 void cc_enc_params_default(cc_enc_params *p) {
     memset(p, 0, sizeof *p);
     p->fps_n = 30; p->fps_d = 1; p->format = CC_FMT_I420; p->bitrate_bps = 6000000; /* reference default max, bitrate_control.h:32 */
-    p->key_int_max = 60; p->rows_per_slice = 4; p->qp_min = 10; p->qp_max = 51;
+    p->key_int_max = 60; p->rows_per_slice = 4; p->qp_min = 10; p->qp_max = 51; p->partitions = 1;
 }
 
 static int dev_alloc(cc_enc *e, void **p, size_t n) {
@@ -124,6 +124,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     }
     if (rc == CC_OK && p->format == CC_FMT_NV12) rc = dev_alloc(e, (void **)&k->uvstage, (size_t)k->sy * (k->H / 2 + 1));
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me, sizeof(cc_me) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me8, sizeof(cc_me8) * nmb);
+    k->part8 = e->p.partitions != 0;
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);
@@ -135,7 +137,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->uright, (size_t)nmb * 32);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowhdr, sizeof(cc_rowhdr) * k->mb_h);
     if (rc == CC_OK && getenv("CC_DEBUG_CYCLES")) { rc = dev_alloc(e, (void **)&k->cyc, (size_t)k->mb_h * 16 * 8); if (rc == CC_OK) cudaMemset(k->cyc, 0, (size_t)k->mb_h * 16 * 8); }
-    if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
+    if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->me8, 0, sizeof(cc_me8) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
     /* packed symbol buffer: headers + per-MB records + payload (worst case) */
     e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(cc_mbhost) * nmb, 16) + (size_t)nmb * CC_ROW_PAYLOAD_PER_MB + 16 * k->mb_h);
     if (rc == CC_OK && cudaHostAlloc((void **)&e->out_host, e->out_cap, cudaHostAllocMapped) != cudaSuccess) rc = CC_ERR_NOMEM;
@@ -373,6 +375,20 @@ int cc_enc_get_me(cc_enc *e, int16_t *mv4, int32_t *satd) {
         satd[i] = tmp[i].satd;
     }
     free(tmp);
+    return er == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+int cc_enc_get_me8(cc_enc *e, int16_t *mv8, int32_t *satd4, uint8_t *part) {
+    if (!e || !mv8 || !satd4 || !part || e->inflight) return CC_ERR_PARAM;
+    const int nmb = e->k.mb_w * e->k.mb_h;
+    cc_me *t16 = (cc_me *)malloc(sizeof(cc_me) * nmb);
+    cc_me8 *t8 = (cc_me8 *)malloc(sizeof(cc_me8) * nmb);
+    cudaError_t er = (t16 && t8) ? cudaMemcpy(t16, e->k.me, sizeof(cc_me) * nmb, cudaMemcpyDeviceToHost) : cudaErrorMemoryAllocation;
+    if (er == cudaSuccess) er = cudaMemcpy(t8, e->k.me8, sizeof(cc_me8) * nmb, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < nmb && er == cudaSuccess; i++) {
+        memcpy(mv8 + 8 * i, t8[i].mv, 16); memcpy(satd4 + 4 * i, t8[i].satd, 16);
+        part[i] = (uint8_t)t16[i].part;
+    }
+    free(t16); free(t8);
     return er == cudaSuccess ? CC_OK : CC_ERR_CUDA;
 }
 int cc_enc_get_mbinfo(cc_enc *e, uint8_t *dst8) {

@@ -94,7 +94,13 @@ int cc_cavlc_write_slice(cc_cavlc_ctx *c, cc_bw *b, int is_idr, int row0, int ro
             if (P) { cc_bw_ue(b, skip_run); skip_run = 0; }
             pay = row_payload[mby] + (((size_t)(pay - row_payload[mby]) + 3) & ~(size_t)3); /* every MB's symbols start 4-byte aligned */
             const int cl = m->cbp & 15, cc = m->cbp >> 4, i16 = m->type == CC_MB_I16;
-            if (m->type == CC_MB_P16) {
+            if (m->type == CC_MB_P16 && (m->t8 & 2)) { /* P_8x8: mb_type 3, four sub_mb_type P_L0_8x8 (ue 0), no ref_idx (one reference), four mvd */
+                if (!P || pay + 16 > pay_end) return -1;
+                cc_bw_ue(b, 3);
+                cc_bw_put(b, 4, 15);
+                for (int i = 0; i < 8; i++) cc_bw_se(b, ((const int16_t *)pay)[i]);
+                pay += 16;
+            } else if (m->type == CC_MB_P16) {
                 if (!P) return -1;
                 cc_bw_ue(b, 0);
                 cc_bw_se(b, m->mvd[0]); cc_bw_se(b, m->mvd[1]);

@@ -19,10 +19,19 @@ struct __align__(16) DbMem {
     uint8_t C[2][12][16]; /* C[pl][r + 4][c + 4], r,c in -4..7 */
 };
 
-/* boundary strength between 4x4 blocks bp (of the record p) and bq (of q), H.264 8.7.2.1, single reference picture */
-__device__ __forceinline__ int db_bs(uint32_t p0, uint32_t p1, int bp, uint32_t q0, uint32_t q1, int bq, int mb_edge) {
+/* neighbour record of one macroblock as the slice keeps it in shared memory (written by the encode warp, read by MV
+ * prediction and by the filter): x = type | transform_size_8x8_flag << 8 | nz_luma << 16, mv[q] = vector of 8x8 quadrant q
+ * (x | y << 16; four equal words unless the macroblock is P_8x8) */
+struct NbRec { uint32_t x, mv[4]; };
+
+/* boundary strength between 4x4 blocks bp (decoding order, of the record p) and bq (of q), H.264 8.7.2.1, single reference picture */
+__device__ __forceinline__ int db_bs(const NbRec &p, int bp, const NbRec &q, int bq, int mb_edge) {
+    const uint32_t p0 = p.x, q0 = q.x;
     if ((p0 & 255u) >= CC_MB_I16 || (q0 & 255u) >= CC_MB_I16) return mb_edge ? 4 : 3;
     if (((p0 >> (16 + bp)) | (q0 >> (16 + bq))) & 1u) return 2;
+    const int ip = bp >> 2, iq = bq >> 2; /* selects, not indexing: the records live in registers */
+    const uint32_t p1 = ip == 0 ? p.mv[0] : (ip == 1 ? p.mv[1] : (ip == 2 ? p.mv[2] : p.mv[3]));
+    const uint32_t q1 = iq == 0 ? q.mv[0] : (iq == 1 ? q.mv[1] : (iq == 2 ? q.mv[2] : q.mv[3]));
     const int dx = (int)(int16_t)(p1 & 0xffffu) - (int)(int16_t)(q1 & 0xffffu);
     const int dy = (int)(int16_t)(p1 >> 16) - (int)(int16_t)(q1 >> 16);
     return (cc_iabs(dx) >= 4 || cc_iabs(dy) >= 4) ? 1 : 0;
@@ -92,7 +101,7 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
 }
 
 /* One macroblock.  L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const uint2 *nbl, int lane, int mbx, int mby, int L, int T) {
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
@@ -101,7 +110,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
     const int g = luma ? li >> 2 : (li & 7) >> 1;
     const int cpl = li >> 3, ci = li & 7;
     /* ---- boundary strengths first: most macroblocks of a P frame have nothing to filter ---- */
-    const uint2 nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
+    const NbRec nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
     uint32_t ly[4], lc[3];
 #pragma unroll
     for (int it = 0; it < 4; it++) {
@@ -113,14 +122,14 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
         const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
         lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
     }
-    const uint32_t q0 = nq.x, q1 = nq.y;
+    const uint32_t q0 = nq.x;
     int bsv[4], bsh[4], any = 0;
     const int blk_row = g * 4; /* raster index of the first 4x4 block of this lane's block row / column */
 #pragma unroll
     for (int ed = 0; ed < 4; ed++) {
         const int pe = ed ? ed - 1 : 3;
-        bsv[ed] = (ed == 0 && !L) ? 0 : db_bs(ed == 0 ? nl.x : q0, ed == 0 ? nl.y : q1, db_blk(blk_row + pe), q0, q1, db_blk(blk_row + ed), ed == 0);
-        bsh[ed] = (ed == 0 && !T) ? 0 : db_bs(ed == 0 ? nt.x : q0, ed == 0 ? nt.y : q1, db_blk(pe * 4 + g), q0, q1, db_blk(ed * 4 + g), ed == 0);
+        bsv[ed] = (ed == 0 && !L) ? 0 : db_bs(ed == 0 ? nl : nq, db_blk(blk_row + pe), nq, db_blk(blk_row + ed), ed == 0);
+        bsh[ed] = (ed == 0 && !T) ? 0 : db_bs(ed == 0 ? nt : nq, db_blk(pe * 4 + g), nq, db_blk(ed * 4 + g), ed == 0);
         if ((ed & 1) && ((q0 >> 8) & 1u)) bsv[ed] = bsh[ed] = 0; /* transform_size_8x8_flag: edges 1 and 3 are not transform edges */
         any |= bsv[ed] | bsh[ed];
     }

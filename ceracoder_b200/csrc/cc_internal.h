@@ -33,7 +33,14 @@ typedef struct {
     int16_t l1_mv[2]; /* coarse vector, half-res pixels */
     int16_t mv[2];    /* refined vector, quarter-pel */
     int32_t satd;     /* SATD of the 16x16 prediction at mv */
-} cc_me;
+    int32_t part;     /* 1: four 8x8 partitions (cc_me8) cost less than the 16x16 partition -> P_8x8 */
+} cc_me; /* 16 bytes */
+
+/* 8x8-partition search result per macroblock (quadrants in decoding order: 0 top-left, 1 top-right, 2 bottom-left, 3 bottom-right) */
+typedef struct {
+    int16_t mv[4][2]; /* quarter-pel */
+    int32_t satd[4];
+} cc_me8; /* 32 bytes */
 
 /* device-side macroblock record: neighbour context for prediction and deblocking */
 typedef struct {
@@ -45,8 +52,8 @@ typedef struct {
 
 /* host-side macroblock record (what the CAVLC writer needs besides the coefficient payload) */
 typedef struct {
-    uint8_t type, modes /* i16_mode | chroma_mode<<2 */, cbp, t8 /* transform_size_8x8_flag */;
-    int16_t mvd[2];
+    uint8_t type, modes /* i16_mode | chroma_mode<<2 */, cbp, t8 /* bit 0: transform_size_8x8_flag, bit 1: P_8x8 */;
+    int16_t mvd[2]; /* P_8x8: the four quadrants' mvd are the first 8 int16 of the macroblock's symbol slot */
 } cc_mbhost; /* 8 bytes */
 
 /* result of the parallel P-frame pre-pass (k_p_code) for one macroblock: the MB coded as P_L0_16x16 at the motion
@@ -59,7 +66,7 @@ typedef struct {
     int16_t cand[2];    /* P_Skip vector predicted from the neighbours' search vectors */
     uint16_t sym_len;   /* int16 units used in the MB's symbol slot */
     uint8_t t8;         /* coded with the 8x8 transform */
-    uint8_t pad;
+    uint8_t part;       /* coded as P_8x8 (levels start 8 int16 into the slot, leaving room for the four mvd) */
     int32_t est_intra;  /* Intra16x16 SATD cost with SOURCE neighbours: gate of the real intra analysis */
 } cc_pre; /* 16 bytes */
 
@@ -85,6 +92,8 @@ typedef struct {
     uint8_t *l1cur, *l1ref;
     uint8_t *uvstage;  /* NV12 interleaved chroma staging (pitch sy), or NULL */
     cc_me *me;
+    cc_me8 *me8;
+    int part8;         /* 1: the motion search may choose P_8x8 */
     cc_mbdev *mbd;
     cc_mbhost *mbh;    /* device copy */
     cc_pre *pre;

@@ -70,6 +70,12 @@ __device__ __forceinline__ void mc_luma16(const cc_kparams &k, const MbCtx &c, i
     c.m->predY[row * 4 + half * 2] = __vavgu4(a0, b0);
     c.m->predY[row * 4 + half * 2 + 1] = __vavgu4(a1, b1);
 }
+/* P_8x8: the lane mappings of mc_luma16 (row, 8-pixel half) and mc_chroma8 (plane, row, 4-pixel half) never straddle an 8x8
+ * quadrant (4x4 in chroma), so a P_8x8 macroblock is predicted by the same two functions with each lane passing the vector
+ * of the quadrant it lies in. */
+__device__ __forceinline__ int luma_lane_quad(int lane) { return ((lane >> 4) << 1) | (lane & 1); }
+__device__ __forceinline__ int chroma_lane_quad(int lane) { return (((lane >> 3) & 1) << 1) | (lane & 1); }
+__device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8);
 /* 8x8 chroma predictors (both planes), H.264 8.4.2.2.2; lane = (plane, row, half) */
 __device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
     const int pl = c.lane >> 4, row = (c.lane >> 1) & 7, half = c.lane & 1, fx = mvx & 7, fy = mvy & 7;
@@ -84,6 +90,18 @@ __device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, 
         a = a1; b = b1;
     }
     c.m->predC[pl][row * 2 + half] = w;
+}
+
+__device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8) {
+    const int ql = luma_lane_quad(c.lane), qc = chroma_lane_quad(c.lane);
+    int lx = m8.mv[0][0], ly = m8.mv[0][1], cx = lx, cy = ly;
+#pragma unroll
+    for (int q = 1; q < 4; q++) {
+        if (ql == q) { lx = m8.mv[q][0]; ly = m8.mv[q][1]; }
+        if (qc == q) { cx = m8.mv[q][0]; cy = m8.mv[q][1]; }
+    }
+    mc_luma16(k, c, lx, ly);
+    mc_chroma8(k, c, cx, cy);
 }
 
 /* ---- inter luma residual ------------------------------------------------------------------------------ */
@@ -417,22 +435,50 @@ __device__ __forceinline__ void predict_mv_core(int L, int T, int rA, int a[2], 
     if (!L || !T || (rA0 == 0 && a0x == 0 && a0y == 0) || (rB0 == 0 && b0x == 0 && b0y == 0)) skip[0] = skip[1] = 0;
     else { skip[0] = mvp[0]; skip[1] = mvp[1]; }
 }
-/* neighbour record as the slice keeps it in shared memory: x = type | nz_luma << 16, y = mv (x | y << 16) */
-__device__ __forceinline__ void nb_mv2(uint2 n, int avail, int &ref, int mv[2]) {
+/* quadrant q of a neighbour record (NbRec, cc_deblock.cuh) */
+__device__ __forceinline__ void nb_mv2(const NbRec *n, int q, int avail, int &ref, int mv[2]) {
     mv[0] = mv[1] = 0;
     if (!avail) { ref = -2; return; }
-    if ((n.x & 255u) >= CC_MB_I16) { ref = -1; return; }
-    ref = 0; mv[0] = (int)(int16_t)(n.y & 0xffffu); mv[1] = (int)(int16_t)(n.y >> 16);
+    if ((n->x & 255u) >= CC_MB_I16) { ref = -1; return; }
+    const uint32_t v = n->mv[q];
+    ref = 0; mv[0] = (int)(int16_t)(v & 0xffffu); mv[1] = (int)(int16_t)(v >> 16);
 }
-/* nbl: this row's line, nbu: the line of the row above (valid where c.T) */
-__device__ __forceinline__ void predict_mv(const MbCtx &c, const uint2 *nbl, const uint2 *nbu, int mvp[2], int skip[2]) {
+/* 16x16 partition: A = left MB quadrant 1, B = top MB quadrant 2, C = top-right MB quadrant 2, else D = top-left MB quadrant 3
+ * (the quadrants that contain the neighbouring luma locations of 6.4.11.7).  nbl: this row's line, nbu: the line of the row
+ * above (valid where c.T) */
+__device__ __forceinline__ void predict_mv(const MbCtx &c, const NbRec *nbl, const NbRec *nbu, int mvp[2], int skip[2]) {
     int rA, rB, rC, a[2], b[2], cc[2];
-    const uint2 z = make_uint2(0u, 0u);
-    nb_mv2(c.L ? nbl[c.mbx - 1] : z, c.L, rA, a);
-    nb_mv2(c.T ? nbu[c.mbx] : z, c.T, rB, b);
-    nb_mv2(c.TR ? nbu[c.mbx + 1] : z, c.TR, rC, cc);
-    if (rC == -2) nb_mv2((c.T && c.L) ? nbu[c.mbx - 1] : z, c.T && c.L, rC, cc);
+    nb_mv2(nbl + c.mbx - 1, 1, c.L, rA, a);
+    nb_mv2(nbu + c.mbx, 2, c.T, rB, b);
+    nb_mv2(nbu + c.mbx + 1, 2, c.TR, rC, cc);
+    if (rC == -2) nb_mv2(nbu + c.mbx - 1, 3, c.T && c.L, rC, cc);
     predict_mv_core(c.L, c.T, rA, a, rB, b, rC, cc, mvp, skip);
+}
+/* quadrant p of a P_8x8 macroblock; own = the macroblock's four vectors (quadrants before p are decided).  oracle/ref_mb.c predict_mv8 */
+__device__ __forceinline__ void predict_mv8(const MbCtx &c, const NbRec *nbl, const NbRec *nbu, int p, const cc_me8 &own, int mvp[2]) {
+    int rA, rB, rC, a[2], b[2], cc[2], dummy[2];
+#define OWN(q, r, v) do { r = 0; v[0] = own.mv[q][0]; v[1] = own.mv[q][1]; } while (0)
+    if (p == 0) {
+        nb_mv2(nbl + c.mbx - 1, 1, c.L, rA, a);
+        nb_mv2(nbu + c.mbx, 2, c.T, rB, b);
+        nb_mv2(nbu + c.mbx, 3, c.T, rC, cc);
+        if (rC == -2) nb_mv2(nbu + c.mbx - 1, 3, c.T && c.L, rC, cc);
+    } else if (p == 1) {
+        OWN(0, rA, a);
+        nb_mv2(nbu + c.mbx, 3, c.T, rB, b);
+        nb_mv2(nbu + c.mbx + 1, 2, c.TR, rC, cc);
+        if (rC == -2) nb_mv2(nbu + c.mbx, 2, c.T, rC, cc);
+    } else if (p == 2) {
+        nb_mv2(nbl + c.mbx - 1, 3, c.L, rA, a);
+        OWN(0, rB, b);
+        OWN(1, rC, cc);
+    } else {
+        OWN(2, rA, a);
+        OWN(1, rB, b);
+        OWN(0, rC, cc); /* C (the macroblock to the right) is not decoded yet -> D = quadrant 0 */
+    }
+#undef OWN
+    predict_mv_core(1, 1, rA, a, rB, b, rC, cc, mvp, dummy);
 }
 
 /* ---- intra chroma ------------------------------------------------------------------------------------------------ */
@@ -605,21 +651,26 @@ __device__ __forceinline__ void stage_neighbours(const cc_kparams &k, const MbCt
     if (lane < 16) m->edgeC[lane >> 3][9 + (lane & 7)] = c.L ? ur[16 + lane] : 0;
 }
 
-__device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volatile int *progress, int w, int row, int row0, int lane) {
+__device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volatile int *progress, int w, int row, int row0, int lane) {
     const int mw = k.mb_w, qp = k.qp;
     MbCtx c;
     c.lane = lane; c.mby = row; c.py = row * 16; c.qp = qp; c.qpc = c_chroma_qp[qp]; c.lambda = c_lambda[qp]; c.m = m;
     c.T = row > row0;
     unsigned total = 0, n_skip = 0, n_inter = 0, n_intra = 0, n_gate = 0, n_probe = 0;
-    uint2 *nbl = nbline + w * mw;
-    const uint2 *nbu = nbl - mw;
+    NbRec *nbl = nbline + w * mw;
+    const NbRec *nbu = nbl - mw;
     for (int mbx = 0; mbx < mw; mbx++) {
         c.mbx = mbx; c.px = mbx * 16; c.mb = row * mw + mbx; c.L = mbx > 0; c.TR = c.T && mbx + 1 < mw;
         int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
         unsigned off = 0;
-        cc_me me = {{0, 0}, {0, 0}, 0};
+        cc_me me = {{0, 0}, {0, 0}, 0, 0};
+        cc_me8 me8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}};
         cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
-        if (!k.is_idr) { me = k.me[c.mb]; pre = k.pre[c.mb]; } /* independent of the neighbours: issued before the wait */
+        if (!k.is_idr) { /* independent of the neighbours: issued before the wait */
+            me = k.me[c.mb]; pre = k.pre[c.mb];
+            if (me.part) me8 = k.me8[c.mb];
+        }
+        const int part = me.part;
         stage_cur(k, c);
         const long long t0 = k.cyc ? clock64() : 0;
         if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
@@ -629,6 +680,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
         int type = CC_MB_P16, mode16 = 2, chroma_mode = 0, cbp = 0, mvx = 0, mvy = 0, mvdx = 0, mvdy = 0, t8 = 0;
         unsigned nzmask = 0;
         int mvp[2] = {0, 0}, skipmv[2] = {0, 0};
+        int mvp8[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
         int cost_inter = 1 << 30, cost_i4 = 1 << 30;
         bool done = false;
 
@@ -637,13 +689,13 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
             /* [EXT] x264 probe_skip: would the MB coded at the P_Skip vector leave nothing after decimation?  The
              * pre-pass answered that for its search vector and for the two likeliest skip vectors. */
             bool zero;
-            if (skipmv[0] == me.mv[0] && skipmv[1] == me.mv[1]) zero = pre.cbp == 0;
+            if (!part && skipmv[0] == me.mv[0] && skipmv[1] == me.mv[1]) zero = pre.cbp == 0;
             else if (skipmv[0] == pre.cand[0] && skipmv[1] == pre.cand[1]) zero = pre.skip_ok & 1;
             else if (skipmv[0] == 0 && skipmv[1] == 0) zero = (pre.skip_ok >> 1) & 1;
             else { n_probe++; path = 1; zero = probe_zero(k, c, skipmv[0], skipmv[1]); }
             if (zero) {
                 type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
-                if (mvx != me.mv[0] || mvy != me.mv[1]) { /* reconstruction = prediction at the skip vector */
+                if (part || mvx != me.mv[0] || mvy != me.mv[1]) { /* reconstruction = prediction at the skip vector */
                     mc_luma16(k, c, mvx, mvy);
                     mc_chroma8(k, c, mvx, mvy);
                     __syncwarp();
@@ -653,6 +705,13 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
                     publish_pixels(k, c);
                 }
                 done = true;
+            } else if (part) { /* exact cost of the P_8x8 coding: per-quadrant SATD + mvd bits against the real predictors */
+                cost_inter = 8 * c.lambda;
+#pragma unroll
+                for (int p = 0; p < 4; p++) {
+                    predict_mv8(c, nbl, nbu, p, me8, mvp8[p]);
+                    cost_inter += me8.satd[p] + c.lambda * (cc_se_bits(me8.mv[p][0] - mvp8[p][0]) + cc_se_bits(me8.mv[p][1] - mvp8[p][1]));
+                }
             } else cost_inter = me.satd + c.lambda * (cc_se_bits(me.mv[0] - mvp[0]) + cc_se_bits(me.mv[1] - mvp[1]));
         }
         if (!done) {
@@ -673,7 +732,15 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
             else type = cost_i16 <= cost_i4 ? CC_MB_I16 : CC_MB_I4;
 
             if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec */
-                mvx = me.mv[0]; mvy = me.mv[1]; mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1];
+                if (part) { /* the four mvd go to the 8 int16 the pre-pass left free at the head of the slot */
+                    mvx = me8.mv[0][0]; mvy = me8.mv[0][1]; mvdx = mvx - mvp8[0][0]; mvdy = mvy - mvp8[0][1];
+                    if (lane < 8) {
+                        int v = 0;
+#pragma unroll
+                        for (int i = 0; i < 8; i++) if (lane == i) v = me8.mv[i >> 1][i & 1] - mvp8[i >> 1][i & 1];
+                        out[lane] = (int16_t)v;
+                    }
+                } else { mvx = me.mv[0]; mvy = me.mv[1]; mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1]; }
                 cbp = pre.cbp; nzmask = pre.nz_luma; off = pre.sym_len; t8 = pre.t8;
             } else {
                 if (type == CC_MB_I4) {
@@ -716,11 +783,17 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
             for (int i = 0; i < 16; i++) d.i4_mode[i] = type == CC_MB_I4 ? m->m4[i] : 2;
             k.mbd[c.mb] = d;
             cc_mbhost hh;
-            hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.t8 = (uint8_t)t8;
+            const int p8 = type == CC_MB_P16 && part;
+            hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.t8 = (uint8_t)(t8 | (p8 << 1));
             hh.mvd[0] = (int16_t)mvdx; hh.mvd[1] = (int16_t)mvdy;
             k.mbh[c.mb] = hh;
             k.symlen[c.mb] = (uint16_t)off;
-            nbl[mbx] = make_uint2((unsigned)type | ((unsigned)t8 << 8) | ((unsigned)d.nz_luma << 16), ((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
+            NbRec nr;
+            nr.x = (unsigned)type | ((unsigned)t8 << 8) | ((unsigned)d.nz_luma << 16);
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                nr.mv[q] = p8 ? (((unsigned)me8.mv[q][0] & 0xffffu) | ((unsigned)me8.mv[q][1] << 16)) : (((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
+            nbl[mbx] = nr;
         }
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
@@ -740,6 +813,12 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, uint2 *nbline, volat
     }
 }
 
+/* search vector of quadrant q of macroblock n (its 16x16 vector unless the search chose P_8x8) */
+__device__ __forceinline__ void search_mv(const cc_kparams &k, int n, int q, int mv[2]) {
+    if (k.me[n].part) { mv[0] = k.me8[n].mv[q][0]; mv[1] = k.me8[n].mv[q][1]; }
+    else { mv[0] = k.me[n].mv[0]; mv[1] = k.me[n].mv[1]; }
+}
+
 /* ---- P-frame pre-pass: every macroblock coded as P_L0_16x16 at its search vector, fully parallel ------------------------ */
 #define PC_WARPS 4
 __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
@@ -756,21 +835,28 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     c.L = c.mbx > 0; c.T = c.mby > (c.mby / k.rps) * k.rps; c.TR = c.T && c.mbx + 1 < mw;
     WarpMem *m = c.m;
     const cc_me *me = k.me + mb;
-    const int mvx = me->mv[0], mvy = me->mv[1];
+    const int mvx = me->mv[0], mvy = me->mv[1], part = me->part;
+    int satd4 = me->satd;
     stage_cur(k, c);
-    mc_luma16(k, c, mvx, mvy);
-    mc_chroma8(k, c, mvx, mvy);
+    if (part) { /* P_8x8: each quadrant predicted with its own vector (chroma: the 4x4 block it covers) */
+        const cc_me8 m8 = k.me8[mb];
+        mc_mb8(k, c, m8);
+        satd4 = m8.satd[0] + m8.satd[1] + m8.satd[2] + m8.satd[3];
+    } else {
+        mc_luma16(k, c, mvx, mvy);
+        mc_chroma8(k, c, mvx, mvy);
+    }
     __syncwarp();
     unsigned nzmask;
     /* transform size [EXT: x264_mb_analyse_transform]: 8x8 when the residual's sa8d is below its 4x4 satd */
-    int t8 = sa8d_mb(x8, m->curY, m->predY, lane) < me->satd;
+    int t8 = sa8d_mb(x8, m->curY, m->predY, lane) < satd4;
     int cbp = t8 ? inter_luma8(k, x8, m->curY, m->predY, m->recY, m->coef, c.qp, lane, &nzmask) : inter_luma(k, c, false, &nzmask);
     if (!cbp) t8 = 0; /* the flag is only transmitted with coded luma */
     cbp |= encode_chroma(k, c, false, false) << 4;
     __syncwarp();
     publish_pixels(k, c);
     int16_t *out = (int16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
-    const unsigned off = emit_mb(c, out, 0, CC_MB_P16, cbp);
+    const unsigned off = emit_mb(c, out, part ? 8 : 0, CC_MB_P16, cbp); /* P_8x8: 8 int16 left free for the four mvd */
     /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
     int est;
     {
@@ -786,19 +872,20 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     /* likeliest P_Skip vector: 8.4.1.1 applied to the neighbours' search vectors */
     int cand[2], mvp[2], a[2] = {0, 0}, b[2] = {0, 0}, cc[2] = {0, 0};
     int rA = -2, rB = -2, rC = -2;
-    if (c.L) { rA = 0; a[0] = me[-1].mv[0]; a[1] = me[-1].mv[1]; }
-    if (c.T) { rB = 0; b[0] = me[-mw].mv[0]; b[1] = me[-mw].mv[1]; }
-    if (c.TR) { rC = 0; cc[0] = me[-mw + 1].mv[0]; cc[1] = me[-mw + 1].mv[1]; }
-    else if (c.T && c.L) { rC = 0; cc[0] = me[-mw - 1].mv[0]; cc[1] = me[-mw - 1].mv[1]; }
+    if (c.L) { rA = 0; search_mv(k, mb - 1, 1, a); }
+    if (c.T) { rB = 0; search_mv(k, mb - mw, 2, b); }
+    if (c.TR) { rC = 0; search_mv(k, mb - mw + 1, 2, cc); }
+    else if (c.T && c.L) { rC = 0; search_mv(k, mb - mw - 1, 3, cc); }
     predict_mv_core(c.L, c.T, rA, a, rB, b, rC, cc, mvp, cand);
     int ok = 0;
-    const bool c_is_me = cand[0] == mvx && cand[1] == mvy, z_is_me = mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
+    /* a P_8x8 search result says nothing about the 16x16 coding at one vector: both probes run for real */
+    const bool c_is_me = !part && cand[0] == mvx && cand[1] == mvy, z_is_me = !part && mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
     if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
     if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
     if (lane == 0) {
         cc_pre p;
         p.cbp = (uint8_t)cbp; p.skip_ok = (uint8_t)ok; p.nz_luma = (uint16_t)nzmask; p.cand[0] = (int16_t)cand[0]; p.cand[1] = (int16_t)cand[1];
-        p.sym_len = (uint16_t)off; p.t8 = (uint8_t)t8; p.pad = 0; p.est_intra = est;
+        p.sym_len = (uint16_t)off; p.t8 = (uint8_t)t8; p.part = (uint8_t)part; p.est_intra = est;
         k.pre[mb] = p;
     }
 }
@@ -809,8 +896,8 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_mb_encode(cc_kparams k)
     __shared__ WarpMem wm[MB_MAX_RPS];
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress[MB_MAX_RPS], progress2[MB_MAX_RPS];
-    CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records {type | nz_luma << 16, mv} */
-    uint2 *nbline = (uint2 *)dsm;
+    CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records (NbRec) */
+    NbRec *nbline = (NbRec *)dsm;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool filt = wid >= k.rps;
     const int w = filt ? wid - k.rps : wid;
@@ -884,7 +971,7 @@ __global__ void k_pack(cc_kparams k) {
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), (size_t)k->rps * k->mb_w * sizeof(uint2), st, *k);
+    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), (size_t)k->rps * k->mb_w * sizeof(NbRec), st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

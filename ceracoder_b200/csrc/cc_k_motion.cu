@@ -72,6 +72,82 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy), cc_ld32u(B + (ptrdiff_t)r * k.sy));
 }
 
+/* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"; oracle/ref_enc.c me_l0, second half).
+ * Every quadrant searches +-2 full-pel around the macroblock's best full-pel vector by SAD (lane = candidate, the four
+ * quadrant SADs of a candidate come out of one pass over the 16 rows), then refines to half and quarter-pel by SATD
+ * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks.
+ * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
+__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, int mb, int px, int py, int fbx, int fby, const int pm[2], int lambda, int lane) {
+    unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    if (lane < 25) {
+        const int mx = fbx + lane % 5 - 2, my = fby + lane / 5 - 2;
+        const uint8_t *r = k.ref[0] + (ptrdiff_t)(py + my) * k.sy + px + mx;
+        unsigned s4[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int hy = 0; hy < 2; hy++)
+            for (int y = hy * 8; y < hy * 8 + 8; y++) {
+                uint32_t a, b, c, d;
+                cc_ld64u(r + (ptrdiff_t)y * k.sy, a, b);
+                cc_ld64u(r + (ptrdiff_t)y * k.sy + 8, c, d);
+                s4[hy * 2] += __vsadu4(a, sc[y * 4]) + __vsadu4(b, sc[y * 4 + 1]);
+                s4[hy * 2 + 1] += __vsadu4(c, sc[y * 4 + 2]) + __vsadu4(d, sc[y * 4 + 3]);
+            }
+        const unsigned bits = (unsigned)(lambda * (cc_se_bits(4 * (mx - pm[0])) + cc_se_bits(4 * (my - pm[1]))));
+#pragma unroll
+        for (int p = 0; p < 4; p++) key4[p] = ((s4[p] + bits) << 5) | (unsigned)lane;
+    }
+    const int p = lane >> 3, slot = (lane >> 2) & 1, b4 = lane & 3;
+    int fi = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int i = (int)(__reduce_min_sync(FULL, key4[q]) & 31u);
+        if (q == p) fi = i;
+    }
+    int qx = 4 * (fbx + fi % 5 - 2), qy = 4 * (fby + fi / 5 - 2);
+    const int ox = (p & 1) * 8 + (b4 & 1) * 4, oy = (p >> 1) * 8 + (b4 >> 1) * 4;
+    uint32_t cw[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) cw[r] = sc[(oy + r) * 4 + (ox >> 2)];
+    unsigned bestkey = 0xffffffffu;
+    int bestsatd = 0, bestx = qx, besty = qy;
+    for (int step = 2; step >= 1; step--) {
+        const int cx = qx, cy = qy;
+        const int npass = step == 2 ? 5 : 4;
+        for (int ps = 0; ps < npass; ps++) {
+            const int o = 2 * ps + slot + (step == 2 ? 0 : 1);
+            const bool valid = o <= 8;
+            int dx = 0, dy = 0;
+            if (o >= 1) { int i = o <= 4 ? o - 1 : o; dx = (i % 3 - 1) * step; dy = (i / 3 - 1) * step; }
+            int satd = 0;
+            if (valid) {
+                uint32_t pw[4];
+                cc_qpel4x4(k, px + ox, py + oy, cx + dx, cy + dy, pw);
+                satd = cc_satd4x4_words(cw, pw);
+            }
+            satd += __shfl_xor_sync(FULL, satd, 1);
+            satd += __shfl_xor_sync(FULL, satd, 2);
+            if (valid) {
+                const int mvx = cx + dx, mvy = cy + dy;
+                const unsigned cost = (unsigned)(satd + lambda * (cc_se_bits(mvx - 4 * pm[0]) + cc_se_bits(mvy - 4 * pm[1])));
+                const unsigned kk = (cost << 5) | (unsigned)o;
+                if (kk < bestkey) { bestkey = kk; bestsatd = satd; bestx = mvx; besty = mvy; }
+            }
+        }
+        const unsigned other = __shfl_xor_sync(FULL, bestkey, 4);
+        const int osatd = __shfl_xor_sync(FULL, bestsatd, 4), oxv = __shfl_xor_sync(FULL, bestx, 4), oyv = __shfl_xor_sync(FULL, besty, 4);
+        if (other < bestkey) { bestkey = other; bestsatd = osatd; bestx = oxv; besty = oyv; }
+        qx = bestx; qy = besty;
+        bestkey &= ~31u;
+    }
+    if ((lane & 7) == 0) {
+        k.me8[mb].mv[p][0] = (int16_t)qx; k.me8[mb].mv[p][1] = (int16_t)qy; k.me8[mb].satd[p] = bestsatd;
+    }
+    int cost8 = (int)(bestkey >> 5);
+    cost8 += __shfl_xor_sync(FULL, cost8, 8);
+    cost8 += __shfl_xor_sync(FULL, cost8, 16);
+    return cost8 + 8 * lambda;
+}
+
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     __shared__ uint32_t scur[ME_WARPS][64]; /* current MB, 16 rows x 4 words */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -117,7 +193,8 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     }
     unsigned bk = __reduce_min_sync(FULL, key);
     int bl = (int)(bk & 31u);
-    int bx = 4 * __shfl_sync(FULL, mx, bl), by = 4 * __shfl_sync(FULL, my, bl);
+    const int fbx = __shfl_sync(FULL, mx, bl), fby = __shfl_sync(FULL, my, bl); /* best full-pel vector: centre of the 8x8 searches */
+    int bx = 4 * fbx, by = 4 * fby;
 
     /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */
     const int blk = lane & 15, half = lane >> 4, ox = (blk & 3) * 4, oy = (blk >> 2) * 4;
@@ -157,8 +234,11 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
         bx = bestx; by = besty;
         bestkey &= ~31u; /* the winner becomes the incumbent (order 0) of the next step */
     }
+    const int cost16 = (int)(bestkey >> 5);
+    int part = 0;
+    if (k.part8) part = me_8x8(k, sc, mb, px, py, fbx, fby, pm, lambda, lane) < cost16;
     if (lane == 0) {
-        k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd;
+        k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd; k.me[mb].part = part;
     }
 }
 

@@ -20,7 +20,7 @@ class CeraCudaError(RuntimeError):
 
 class Params(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("device", "width", "height", "fps_n", "fps_d", "format", "bitrate_bps", "key_int_max",
-                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max")]
+                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max", "partitions")]
 
 
 class Frame(C.Structure):
@@ -61,6 +61,7 @@ def load_library(path=None):
     L.cc_enc_mb_w.argtypes = [vp]
     L.cc_enc_mb_h.argtypes = [vp]
     L.cc_enc_get_me.argtypes = [vp, vp, vp]
+    L.cc_enc_get_me8.argtypes = [vp, vp, vp, vp]
     L.cc_enc_get_mbinfo.argtypes = [vp, vp]
     L.cc_enc_device_bytes.argtypes = [vp]
     L.cc_enc_device_bytes.restype = C.c_size_t
@@ -100,7 +101,7 @@ class CudaH264Enc:
     """The `cudah264enc` element as a Python object: same properties as the pipeline line that names x264enc."""
 
     def __init__(self, width, height, fps=(30, 1), bitrate=6000, key_int_max=60, speed_preset=3, tune=0, name="venc_kbps",
-                 fmt="I420", device=0, rows_per_slice=4, qp_fixed=0, lib=None, byte_stream=True, threads=0):
+                 fmt="I420", device=0, rows_per_slice=4, qp_fixed=0, lib=None, byte_stream=True, threads=0, partitions=True):
         if isinstance(speed_preset, str):
             if speed_preset not in _SPEED_PRESETS:
                 raise ValueError(f"unknown speed-preset {speed_preset!r}")
@@ -120,6 +121,7 @@ class CudaH264Enc:
         p.format = {"I420": CC_FMT_I420, "NV12": CC_FMT_NV12}[fmt]
         p.bitrate_bps = int(bitrate) * 1000
         p.key_int_max, p.rows_per_slice, p.qp_fixed = key_int_max, rows_per_slice, qp_fixed
+        p.partitions = int(bool(partitions))
         self.fmt = fmt
         self._h = C.c_void_p()
         _check(self.L, self.L.cc_enc_open(C.byref(self._h), C.byref(p)), "cc_enc_open")
@@ -193,6 +195,13 @@ class CudaH264Enc:
         mv = np.zeros((n, 4), np.int16); satd = np.zeros(n, np.int32)
         _check(self.L, self.L.cc_enc_get_me(self._h, mv.ctypes.data, satd.ctypes.data), "cc_enc_get_me")
         return mv, satd
+
+    def motion8(self):
+        """8x8-partition search results of the last P frame: (mv[n,4,2] quarter-pel, satd[n,4], part[n])."""
+        n = self.mb_w * self.mb_h
+        mv = np.zeros((n, 4, 2), np.int16); satd = np.zeros((n, 4), np.int32); part = np.zeros(n, np.uint8)
+        _check(self.L, self.L.cc_enc_get_me8(self._h, mv.ctypes.data, satd.ctypes.data, part.ctypes.data), "cc_enc_get_me8")
+        return mv, satd, part
 
     def mbinfo(self):
         a = np.zeros((self.mb_w * self.mb_h, 8), np.uint8)

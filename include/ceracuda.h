@@ -50,6 +50,7 @@ typedef struct {
     int rows_per_slice;  /* macroblock rows per slice; 0 -> 4 */
     int qp_fixed;        /* > 0: constant-QP mode (rate control off); used by parity tests */
     int qp_min, qp_max;  /* 0 -> 10 / 51 */
+    int partitions;      /* 1: the motion search may split a macroblock into four 8x8 partitions (P_8x8); cc_enc_params_default sets 1 */
 } cc_enc_params;
 
 typedef struct {
@@ -97,7 +98,11 @@ int cc_enc_mb_h(const cc_enc *h);
 /* per-macroblock motion-search results of the last P frame: 4 int16 per MB (coarse mv x,y in half-res px;
  * final mv x,y in quarter-pel) and one int32 SATD per MB */
 int cc_enc_get_me(cc_enc *h, int16_t *mv4, int32_t *satd);
-/* per-macroblock decisions of the last frame: 8 bytes per MB {type, i16_mode, chroma_mode, cbp, mvd_x(2), mvd_y(2)} */
+/* 8x8-partition search results of the last P frame: per MB 8 int16 (quarter-pel mv x,y of quadrants 0..3), 4 int32 SATD and
+ * one byte: 1 = the search prefers P_8x8 */
+int cc_enc_get_me8(cc_enc *h, int16_t *mv8, int32_t *satd4, uint8_t *part);
+/* per-macroblock decisions of the last frame: 8 bytes per MB {type, i16_mode | chroma_mode << 2, cbp, transform_size_8x8_flag | P_8x8 << 1,
+ * mvd_x(2), mvd_y(2)} */
 int cc_enc_get_mbinfo(cc_enc *h, uint8_t *dst8);
 size_t cc_enc_device_bytes(const cc_enc *h);
 /* per-stage device timing with CUDA events on the encoder's own stream (bench.py's roofline figures) */

@@ -25,7 +25,7 @@ ref_enc *ref_enc_open(int width, int height, int fps_n, int fps_d, int rows_per_
     if (width < 16 || height < 16 || (width & 1) || (height & 1) || rows_per_slice < 1) return 0;
     ref_enc *e = (ref_enc *)calloc(1, sizeof *e);
     e->w = width; e->h = height; e->mb_w = (width + 15) / 16; e->mb_h = (height + 15) / 16;
-    e->rps = rows_per_slice; e->fps_n = fps_n; e->fps_d = fps_d;
+    e->rps = rows_per_slice; e->fps_n = fps_n; e->fps_d = fps_d; e->part8 = 1;
     int W = e->mb_w * 16, H = e->mb_h * 16, k = 0;
     for (int s = 0; s < 3; s++) { /* cur, rec, ref */
         uint8_t **dst = s == 0 ? e->cur : (s == 1 ? e->rec : e->ref);

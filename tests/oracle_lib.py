@@ -47,7 +47,7 @@ def lib():
 
 
 class OracleEncoder:
-    def __init__(self, w, h, fps=30, rows_per_slice=4, partitions=False):
+    def __init__(self, w, h, fps=30, rows_per_slice=4, partitions=True):
         self.L = lib()
         self.h_ = self.L.ref_enc_open(w, h, fps, 1, rows_per_slice)
         assert self.h_

@@ -11,17 +11,26 @@ def oracle_mb_table(orc):
     rows = []
     for j in range(n):
         o = orc.mb_struct(j)
-        rows.append((o.type, o.i16_mode, o.chroma_mode, o.cbp, o.l1_mv[0], o.l1_mv[1], o.me_mv[0], o.me_mv[1], o.me_satd))
+        rows.append((o.type, o.i16_mode, o.chroma_mode, o.cbp, o.l1_mv[0], o.l1_mv[1], o.me_mv[0], o.me_mv[1], o.me_satd, o.me_part, o.part, o.t8))
     return np.array(rows, dtype=np.int64)
 
 
-def run_parity(lib, source, w, h, qps, rps=4, gop=60, fmt="I420", check_decode=True, frames=None):
+def oracle_me8_table(orc):
+    n = orc.mb_w * orc.mb_h
+    mv = np.zeros((n, 4, 2), np.int64); satd = np.zeros((n, 4), np.int64)
+    for j in range(n):
+        o = orc.mb_struct(j)
+        mv[j] = np.array(o.me_mv8[:]).reshape(4, 2); satd[j] = o.me_satd8[:]
+    return mv, satd
+
+
+def run_parity(lib, source, w, h, qps, rps=4, gop=60, fmt="I420", check_decode=True, frames=None, partitions=True):
     """Encode the same frames at the same per-frame QP with libceracuda and with the CPU oracle; assert that the
     access units are byte-identical, the reconstructions identical, and (optionally) that libavcodec decodes the
     stream to exactly that reconstruction. Returns the list of access units."""
     src = make_source(source, w, h) if isinstance(source, str) else source
-    enc = CudaH264Enc(w, h, fps=(30, 1), rows_per_slice=rps, key_int_max=gop, lib=lib, fmt=fmt)
-    orc = OracleEncoder(w, h, 30, rps)
+    enc = CudaH264Enc(w, h, fps=(30, 1), rows_per_slice=rps, key_int_max=gop, lib=lib, fmt=fmt, partitions=partitions)
+    orc = OracleEncoder(w, h, 30, rps, partitions=partitions)
     aus, recs = [], []
     try:
         for i, qp in enumerate(qps):
@@ -40,10 +49,17 @@ def run_parity(lib, source, w, h, qps, rps=4, gop=60, fmt="I420", check_decode=T
                 assert (mv[:, :2] == t[:, 4:6]).all(), f"frame {i}: coarse motion vectors differ"
                 assert (mv[:, 2:] == t[:, 6:8]).all(), f"frame {i}: refined motion vectors differ"
                 assert (satd == t[:, 8]).all(), f"frame {i}: motion SATD differs"
+                mv8, satd8, part = enc.motion8()
+                assert (part == t[:, 9]).all(), f"frame {i}: partition choice of the search differs at {np.argwhere(part != t[:, 9])[:4].ravel()}"
+                if partitions:
+                    omv8, osatd8 = oracle_me8_table(orc)
+                    assert (mv8 == omv8).all(), f"frame {i}: 8x8 search vectors differ at {np.argwhere(mv8 != omv8)[:3]}"
+                    assert (satd8 == osatd8).all(), f"frame {i}: 8x8 search SATD differs"
             info = enc.mbinfo()
             t = oracle_mb_table(orc)
             assert (info[:, 0] == t[:, 0]).all(), f"frame {i}: macroblock types differ at {np.argwhere(info[:, 0] != t[:, 0])[:4].ravel()}"
             assert (info[:, 2] == t[:, 3]).all(), f"frame {i}: cbp differs"
+            assert (info[:, 3] == (t[:, 11] | ((t[:, 10] & (t[:, 0] == 1)) << 1))).all(), f"frame {i}: transform size / P_8x8 flags differ"
             assert (ry == oy).all(), f"frame {i}: luma reconstruction differs at {np.argwhere(ry != oy)[:3]}"
             assert (ru == ou).all() and (rv == ov).all(), f"frame {i}: chroma reconstruction differs"
             assert a == b, f"frame {i}: access units differ ({len(a)} vs {len(b)} bytes)"

@@ -29,6 +29,11 @@ def test_gop_restart_and_nv12(lib):
     run_parity(lib, "pan", 112, 80, [27, 28, 29], rps=3, fmt="NV12")
 
 
+def test_partitions_off(lib):
+    """cc_enc_params.partitions = 0: the search never chooses P_8x8 (16x16 partitions only)."""
+    run_parity(lib, "pan", 176, 144, [26, 27, 28], rps=4, partitions=False)
+
+
 def test_random_noise_frames(lib):
     rng = np.random.default_rng(5)
     w, h = 64, 64

@@ -31,6 +31,11 @@ def test_bitstream_identical_to_oracle(lib, name, w, h, rps, qps):
 def test_gop_restart_nv12_noise(lib):
     run_parity(lib, "pan", 80, 64, [30, 30, 30, 30, 30], rps=2, gop=2)
     run_parity(lib, "pan", 112, 80, [27, 28, 29], rps=3, fmt="NV12")
+
+
+def test_partitions_off(lib):
+    """cc_enc_params.partitions = 0: the search never chooses P_8x8 (16x16 partitions only)."""
+    run_parity(lib, "pan", 176, 144, [26, 27, 28], rps=4, partitions=False)
     rng = np.random.default_rng(5)
     w, h = 64, 64
     frames = [(rng.integers(0, 256, (h, w), dtype=np.uint8), rng.integers(0, 256, (h // 2, w // 2), dtype=np.uint8),

@@ -7,7 +7,7 @@ from h264_decode import decode_aus, split_aus
 from oracle_lib import OracleEncoder
 
 
-def _run(src, w, h, qps, rps, gop=60, partitions=False):
+def _run(src, w, h, qps, rps, gop=60, partitions=True):
     enc = OracleEncoder(w, h, 30, rps, partitions=partitions)
     aus, recs = [], []
     for i, qp in enumerate(qps):
