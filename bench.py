@@ -110,14 +110,14 @@ class ClockSampler:
 
 def run_streams(encs, frames_of, n_frames, start_idx, device_frames):
     """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes)."""
-    tot = [0, 0, 0, 0, 0, 0, 0, 0]
+    tot = [0, 0, 0, 0, 0, 0, 0, 0, 0.0, 0.0, 0.0, 0.0]
     lock = threading.Lock()
     errs = []
 
     def work(k, e):
         try:
             nb = ns = 0
-            st = [0, 0, 0, 0, 0]
+            st = [0, 0, 0, 0, 0, 0.0, 0.0, 0.0, 0.0]
             for i in range(n_frames):
                 fi = start_idx + i
                 e.set_property("bitrate", schedule_kbps(fi + 37 * k))
@@ -125,11 +125,11 @@ def run_streams(encs, frames_of, n_frames, start_idx, device_frames):
                 e.submit(y, u, v, pts=fi, device_frame=device_frames)
                 nb += e.collect(copy=False); ns += e.last.sym_bytes
                 L = e.last
-                for j, v in enumerate((L.n_skip, L.n_inter, L.n_intra, L.n_intra_analysed, L.n_skip_probed)):
+                for j, v in enumerate((L.n_skip, L.n_inter, L.n_intra, L.n_intra_analysed, L.n_skip_probed, L.submit_ms, L.wait_ms, L.host_ms, L.gpu_ms)):
                     st[j] += v
             with lock:
                 tot[0] += n_frames; tot[1] += nb; tot[2] += ns
-                for j in range(5):
+                for j in range(9):
                     tot[3 + j] += st[j]
         except Exception as ex:  # noqa: BLE001
             errs.append(ex)
@@ -199,6 +199,8 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--streams", type=int, default=STREAMS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rows-per-slice", type=int, default=4, help="macroblock rows per slice (experiments; the reported workload uses 4)")
+    ap.add_argument("--partitions", type=int, default=1, help="0: 16x16 partitions only (experiments)")
     ap.add_argument("--frames-per-step", type=int, default=FRAMES_PER_STEP, help="frames each stream encodes per step (shorten for ncu runs)")
     args = ap.parse_args()
     FRAMES_PER_STEP = args.frames_per_step
@@ -230,7 +232,8 @@ def main():
         return (p, W), (p + W * H, W // 2), (p + W * H * 5 // 4, W // 2)
 
     def make_encs():
-        return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L) for _ in range(S)]
+        return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L,
+                            rows_per_slice=args.rows_per_slice, partitions=bool(args.partitions)) for _ in range(S)]
 
     def timed(device_frames, steps, warmup, profile=False):
         encs = make_encs()
@@ -305,13 +308,14 @@ def main():
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
             "data": "synthetic S2 pan-sprites 1080p (SURVEY.md §8d), 40-frame pool played ping-pong",
             "config": {"workload": f"{S} concurrent 1080p60 cudah264enc streams per GPU, balancer-shaped 12->2->12 Mbps schedule (configs[1] x8, north_star target shape)",
-                       "width": W, "height": H, "fps": FPS, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": 4, "key_int_max": 60,
+                       "width": W, "height": H, "fps": FPS, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60,
                        "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
-            "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"]])),
+            "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"][:5]])),
+            "host_ms_per_frame": dict(zip(("submit_api", "wait_device", "cavlc_nal", "device_frame_latency"), [round(v / max(r_e2e["frames"], 1), 4) for v in r_e2e["mbstats"][5:9]])),
             "wall_ms": {"value_leg": r_dev["wall_ms"], "e2e_leg": r_e2e["wall_ms"]}}
     print(json.dumps(line))
     if world > 1:

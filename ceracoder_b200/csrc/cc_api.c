@@ -46,6 +46,8 @@ struct cc_enc {
     double stage_ms[CC_N_STAGES];
     long stage_n[CC_N_STAGES];
     uint32_t sym_bytes;
+    float submit_ms;
+    int tail_pending;            /* profile: the stages after ev1 (reference finishing) of the previous frame are not read yet */
 };
 
 static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
@@ -173,6 +175,8 @@ void cc_enc_close(cc_enc *e) {
             double f = 1.0 / ((double)e->frame_idx * e->k.mb_h);
             fprintf(stderr, "ceracuda cycles per MB row per frame: encode wait %.0f fast %.0f (n %.1f) probe %.0f (n %.1f) intra %.0f (n %.1f) | filter wait-enc %.0f wait-up %.0f work %.0f\n",
                     s[0] * f, s[1] * f, s[4] * f, s[2] * f, s[5] * f, s[3] * f, s[6] * f, s[8] * f, s[9] * f, s[10] * f);
+            fprintf(stderr, "ceracuda intra path, cycles per MB row per frame: neighbours+i16 analysis %.0f, i4 analysis %.0f (n %.1f), encode+chroma+publish %.0f, emit %.0f\n",
+                    s[11] * f, s[12] * f, s[13] * f, s[14] * f, s[15] * f);
         }
         free(h);
     }
@@ -225,6 +229,7 @@ static void set_quant(cc_kparams *k) {
 int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (!e || !in || !in->plane[0] || !in->plane[1]) return CC_ERR_PARAM;
     if (e->inflight) return CC_ERR_STATE;
+    const double t_submit = now_ms();
     cc_kparams *k = &e->k;
     const int nv12 = e->p.format == CC_FMT_NV12;
     if (!nv12 && !in->plane[2]) return CC_ERR_PARAM;
@@ -241,6 +246,13 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->cur_is_idr = is_idr; e->cur_qp = qp; e->cur_pts = in->pts;
 
     enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (e->tail_pending) { /* stages that ran behind the previous collect; skipped if they are still running */
+        for (int i = CC_STAGE_BORDER; i < CC_N_STAGES; i++) {
+            float ms = 0;
+            if (e->pev_used[i] && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
+        }
+        e->tail_pending = 0;
+    }
     CUCHECK(cudaEventRecord(e->ev0, e->st));
     if (e->profile) { cudaEventRecord(e->pev[CC_STAGE_UPLOAD], e->st); }
     CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
@@ -262,23 +274,27 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (!is_idr) e->launches += cck_p_code(k, e->st);
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
+    STAGE(CC_STAGE_PACK);
+    e->launches += cck_pack(k, e->st);
     STAGE(CC_STAGE_BORDER);
+    /* the access unit's symbols are in host memory here: cc_enc_collect waits for ev1 only, and the kernels that turn the
+     * reconstruction into the next frame's reference run while the host writes the bitstream */
+    CUCHECK(cudaEventRecord(e->ev1, e->st));
     e->launches += cck_border(k, e->st);
     STAGE(CC_STAGE_HPEL);
     e->launches += cck_hpel(k, e->st);
     STAGE(CC_STAGE_L1REF);
     e->launches += cck_l1ref(k, e->st);
-    STAGE(CC_STAGE_PACK);
-    e->launches += cck_pack(k, e->st);
     STAGE(CC_N_STAGES);
 #undef STAGE
-    CUCHECK(cudaEventRecord(e->ev1, e->st));
+    e->tail_pending = e->profile;
     CUCHECK(cudaGetLastError());
     /* the new reconstruction becomes the reference of the next frame */
     for (int i = 0; i < 3; i++) { uint8_t *t = k->rec[i]; k->rec[i] = k->ref[i]; k->ref[i] = t; }
     e->have_ref = 1;
     e->last_was_p = !is_idr;
     e->inflight = 1;
+    e->submit_ms = (float)(now_ms() - t_submit);
     return CC_OK;
 }
 
@@ -288,12 +304,14 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     if (!e || !out) return CC_ERR_PARAM;
     if (!e->inflight) return CC_ERR_STATE;
     cc_kparams *k = &e->k;
+    const double t_wait = now_ms();
     CUCHECK(cudaEventSynchronize(e->ev1));
+    out->wait_ms = (float)(now_ms() - t_wait); out->submit_ms = e->submit_ms;
     e->inflight = 0;
     float gpu_ms = 0;
     cudaEventElapsedTime(&gpu_ms, e->ev0, e->ev1);
     if (e->profile)
-        for (int i = 0; i < CC_N_STAGES; i++) {
+        for (int i = 0; i < CC_STAGE_BORDER; i++) {
             float ms = 0;
             if ((i == CC_STAGE_UPLOAD || e->pev_used[i]) && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) {
                 if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }

@@ -36,7 +36,8 @@ struct __align__(16) WarpMem {
     int16_t coef[27][16];  /* final levels in scan order: 0-15 luma, 16-23 chroma AC, 24 luma DC, 25/26 chroma DC */
     int16_t c4[16][16];    /* intra-4x4 candidate levels */
     int16_t dc[16];
-    uint8_t E[16];         /* intra-4x4 edge of the current block: left3..left0, top-left, top0..7, DC */
+    uint8_t S[48];         /* intra-4x4 source array of the current block (raw edge, DC, 3-tap and 2-tap filtered edge; tools/gen_i4_table.py) */
+    uint8_t nbm[8];        /* Intra4x4PredMode of the left MB's column-3 blocks [0..3] and the top MB's row-3 blocks [4..7]; 255 = unavailable */
     uint8_t m4[16];        /* intra-4x4 candidate modes */
     uint8_t m4code[16];    /* syntax nibble per block: 8 = predicted mode, else rem_intra4x4_pred_mode */
     uint8_t n4[16];
@@ -326,39 +327,60 @@ __device__ __forceinline__ int encode_i16(const cc_kparams &k, const MbCtx &c, c
 /* ---- intra 4x4 ---------------------------------------------------------------------------------------------- */
 /* analyses and codes the 16 blocks in decoding order; reconstruction goes into m->tile, levels into m->c4,
  * modes into m->m4 / m->m4code / m->n4.  Returns the cost (SATD + lambda*bits) in all lanes. */
-__device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c) {
+/* thresh: Intra4x4 can only be chosen with a cost below it, and the running cost never decreases, so the analysis stops as
+ * soon as it is reached ([EXT] x264_mb_analyse_intra's i_satd_thresh early termination).  The decision is the same as
+ * without the early exit; only the work differs.  Returns 1 << 30 when abandoned. */
+__device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, int thresh) {
     WarpMem *m = c.m;
     const int lane = c.lane;
-    const cc_mbdev *nl = k.mbd + c.mb - 1, *nt = k.mbd + c.mb - k.mb_w;
+    /* neighbour macroblocks' modes (global memory): one round trip for the whole macroblock, before the block loop */
+    if (lane < 8) {
+        const int top = lane >> 2, i = lane & 3;
+        int v = 255;
+        if (top ? c.T : c.L) {
+            const cc_mbdev *n = k.mbd + c.mb - (top ? k.mb_w : 1);
+            v = n->type == CC_MB_I4 ? n->i4_mode[c_blk_of[top ? 12 + i : i * 4 + 3]] : 2;
+        }
+        m->nbm[lane] = (uint8_t)v;
+    }
+    /* this lane's mode as 16 source-array indices (lanes 9..31 never use theirs) */
+    uint32_t sx[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) sx[r] = g_i4idx[lane & 15][r];
+    const int md = lane < 9 ? lane : 2;
     int cost = 24 * c.lambda;
+    __syncwarp();
     for (int blk = 0; blk < 16; blk++) {
         const int bx = c_blk_x[blk], by = c_blk_y[blk];
         const int has_top = by > 0 || c.T, has_left = bx > 0 || c.L;
         int has_tr;
         if (by == 0) has_tr = bx < 3 ? c.T : c.TR;
         else has_tr = !(bx == 3 || blk == 3 || blk == 11 || blk == 7 || blk == 13 || blk == 15);
-        /* edge array */
+        /* edge sample of this lane (E index = lane: left3..left0, top-left, top0..7), its filtered forms, the DC value */
+        int e = 0;
         if (lane < 13) {
-            int v;
-            if (lane < 4) v = m->tile[1 + by * 4 + (3 - lane)][3 + bx * 4];
-            else if (lane == 4) v = m->tile[by * 4][3 + bx * 4];
-            else { int i = lane - 5; v = (i < 4 || has_tr) ? m->tile[by * 4][4 + bx * 4 + i] : m->tile[by * 4][4 + bx * 4 + 3]; }
-            m->E[lane] = (uint8_t)v;
+            if (lane < 4) e = m->tile[1 + by * 4 + (3 - lane)][3 + bx * 4];
+            else if (lane == 4) e = m->tile[by * 4][3 + bx * 4];
+            else { const int i = lane - 5; e = m->tile[by * 4][4 + bx * 4 + ((i < 4 || has_tr) ? i : 3)]; }
         }
-        __syncwarp();
         {
-            int st = m->E[5] + m->E[6] + m->E[7] + m->E[8], sl = m->E[0] + m->E[1] + m->E[2] + m->E[3];
-            int dcv = (has_top && has_left) ? (st + sl + 4) >> 3 : (has_top ? (st + 2) >> 2 : (has_left ? (sl + 2) >> 2 : 128));
-            if (lane == 13) m->E[13] = (uint8_t)dcv;
+            int a = __shfl_up_sync(FULL, e, 1), cdn = __shfl_down_sync(FULL, e, 1);
+            if (lane == 0) a = e;
+            if (lane == 12) cdn = e;
+            const int sl = __reduce_add_sync(FULL, lane < 4 ? e : 0), st = __reduce_add_sync(FULL, (lane >= 5 && lane < 9) ? e : 0);
+            if (lane < 13) {
+                m->S[lane] = (uint8_t)e;
+                m->S[16 + lane] = (uint8_t)((a + 2 * e + cdn + 2) >> 2);
+                if (lane < 12) m->S[32 + lane] = (uint8_t)((e + cdn + 1) >> 1);
+            } else if (lane == 13)
+                m->S[13] = (uint8_t)((has_top && has_left) ? (st + sl + 4) >> 3 : (has_top ? (st + 2) >> 2 : (has_left ? (sl + 2) >> 2 : 128)));
         }
         /* predicted mode, H.264 8.3.1.1 */
         int mA, mB;
         if (bx > 0) mA = m->m4[c_blk_of[by * 4 + bx - 1]];
-        else if (c.L) mA = nl->type == CC_MB_I4 ? nl->i4_mode[c_blk_of[by * 4 + 3]] : 2;
-        else mA = -1;
+        else { mA = m->nbm[by]; if (mA == 255) mA = -1; }
         if (by > 0) mB = m->m4[c_blk_of[(by - 1) * 4 + bx]];
-        else if (c.T) mB = nt->type == CC_MB_I4 ? nt->i4_mode[c_blk_of[12 + bx]] : 2;
-        else mB = -1;
+        else { mB = m->nbm[4 + bx]; if (mB == 255) mB = -1; }
         const int pm = (mA < 0 || mB < 0) ? 2 : min(mA, mB);
         __syncwarp();
         uint32_t cw[4], pw[4] = {0, 0, 0, 0};
@@ -366,21 +388,13 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c) {
         for (int r = 0; r < 4; r++) cw[r] = m->curY[(by * 4 + r) * 4 + bx];
         unsigned key = 0xffffffffu;
         {
-            const int md = lane < 9 ? lane : 2;
             const bool ok = lane < 9 && (md == 2 || ((md == 0 || md == 3 || md == 7) && has_top) || ((md == 1 || md == 8) && has_left) ||
                                          ((md == 4 || md == 5 || md == 6) && has_top && has_left));
             if (ok) {
 #pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    uint32_t w = 0;
-#pragma unroll
-                    for (int x = 0; x < 4; x++) {
-                        unsigned t = c_i4tab[md][r * 4 + x];
-                        int v = (m->E[t & 15] + 2 * m->E[(t >> 4) & 15] + m->E[(t >> 8) & 15] + 2) >> 2;
-                        w |= (uint32_t)v << (8 * x);
-                    }
-                    pw[r] = w;
-                }
+                for (int r = 0; r < 4; r++)
+                    pw[r] = (uint32_t)m->S[sx[r] & 255u] | ((uint32_t)m->S[(sx[r] >> 8) & 255u] << 8) | ((uint32_t)m->S[(sx[r] >> 16) & 255u] << 16) |
+                            ((uint32_t)m->S[sx[r] >> 24] << 24);
                 int satd = cc_satd4x4_words(cw, pw);
                 key = ((unsigned)(satd + c.lambda * (md == pm ? 1 : 4)) << 4) | (unsigned)md;
             }
@@ -388,6 +402,7 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c) {
         const unsigned bk = __reduce_min_sync(FULL, key);
         const int bm = (int)(bk & 15u);
         cost += (int)(bk >> 4);
+        if (cost >= thresh) return 1 << 30; /* uniform across the warp */
 #pragma unroll
         for (int r = 0; r < 4; r++) pw[r] = __shfl_sync(FULL, pw[r], bm);
         /* every lane runs the block's transform chain on identical data; lane 0 publishes */
@@ -688,17 +703,19 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             predict_mv(c, nbl, nbu, mvp, skipmv);
             /* [EXT] x264 probe_skip: would the MB coded at the P_Skip vector leave nothing after decimation?  The
              * pre-pass answered that for its search vector and for the two likeliest skip vectors. */
-            bool zero;
+            bool zero, pred_ready = false;
             if (!part && skipmv[0] == me.mv[0] && skipmv[1] == me.mv[1]) zero = pre.cbp == 0;
             else if (skipmv[0] == pre.cand[0] && skipmv[1] == pre.cand[1]) zero = pre.skip_ok & 1;
             else if (skipmv[0] == 0 && skipmv[1] == 0) zero = (pre.skip_ok >> 1) & 1;
-            else { n_probe++; path = 1; zero = probe_zero(k, c, skipmv[0], skipmv[1]); }
+            else { n_probe++; path = 1; zero = probe_zero(k, c, skipmv[0], skipmv[1]); pred_ready = true; /* predY / predC hold the prediction at skipmv */ }
             if (zero) {
                 type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
                 if (part || mvx != me.mv[0] || mvy != me.mv[1]) { /* reconstruction = prediction at the skip vector */
-                    mc_luma16(k, c, mvx, mvy);
-                    mc_chroma8(k, c, mvx, mvy);
-                    __syncwarp();
+                    if (!pred_ready) {
+                        mc_luma16(k, c, mvx, mvy);
+                        mc_chroma8(k, c, mvx, mvy);
+                        __syncwarp();
+                    }
                     m->recY[lane] = m->predY[lane]; m->recY[lane + 32] = m->predY[lane + 32];
                     m->recC[lane >> 4][lane & 15] = m->predC[lane >> 4][lane & 15];
                     __syncwarp();
@@ -721,11 +738,18 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             int cost_i16 = 1 << 30;
             if (gate) {
                 n_gate++; path = 2;
+                const long long ta = k.cyc ? clock64() : 0;
                 stage_neighbours(k, c);
                 __syncwarp();
                 i16_params(c, ip);
                 cost_i16 = analyse_i16(c, ip, &mode16);
-                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c);
+                const long long tb = k.cyc ? clock64() : 0;
+                /* Intra4x4 wins only if cost_i4 < cost_i16 and (P frames) cost_i4 + 8 lambda < cost_inter */
+                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda));
+                if (k.cyc && lane == 0) {
+                    unsigned long long *cy = k.cyc + (size_t)row * 16;
+                    cy[11] += (unsigned long long)(tb - ta); cy[12] += (unsigned long long)(clock64() - tb); cy[13] += cost_i4 < (1 << 30);
+                }
                 if (!k.is_idr) { cost_i16 += 8 * c.lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * c.lambda; }
             }
             if (!k.is_idr && cost_inter <= cost_i16 && cost_inter <= cost_i4) type = CC_MB_P16;
@@ -743,6 +767,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 } else { mvx = me.mv[0]; mvy = me.mv[1]; mvdx = mvx - mvp[0]; mvdy = mvy - mvp[1]; }
                 cbp = pre.cbp; nzmask = pre.nz_luma; off = pre.sym_len; t8 = pre.t8;
             } else {
+                const long long tc = k.cyc ? clock64() : 0;
                 if (type == CC_MB_I4) {
                     if (lane < 16) {
                         const uint32_t *s = (const uint32_t *)m->c4[lane];
@@ -772,7 +797,12 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                     }
                     off += 4;
                 }
+                const long long td = k.cyc ? clock64() : 0;
                 off = emit_mb(c, out, off, type, cbp);
+                if (k.cyc && lane == 0) {
+                    unsigned long long *cy = k.cyc + (size_t)row * 16;
+                    cy[14] += (unsigned long long)(td - tc); cy[15] += (unsigned long long)(clock64() - td);
+                }
             }
         }
         if (lane == 0) {
@@ -971,7 +1001,12 @@ __global__ void k_pack(cc_kparams k) {
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), (size_t)k->rps * k->mb_w * sizeof(NbRec), st, *k);
+    const size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
+#ifndef CC_EMU_BUILD
+    /* static (31.5 KB) + dynamic shared memory passes the default 48 KB limit from ~3300-pixel-wide pictures on: opt in */
+    if (dyn > 16 * 1024) cudaFuncSetAttribute(k_mb_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); /* per device; cheap */
+#endif
+    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

@@ -30,7 +30,7 @@ class Frame(C.Structure):
 class Packet(C.Structure):
     _fields_ = [("data", C.POINTER(C.c_uint8)), ("size", C.c_int), ("is_idr", C.c_int), ("qp", C.c_int), ("pts", C.c_int64),
                 ("n_skip", C.c_int), ("n_inter", C.c_int), ("n_intra", C.c_int), ("sym_bytes", C.c_int), ("gpu_ms", C.c_float), ("host_ms", C.c_float),
-                ("n_intra_analysed", C.c_int), ("n_skip_probed", C.c_int)]
+                ("n_intra_analysed", C.c_int), ("n_skip_probed", C.c_int), ("submit_ms", C.c_float), ("wait_ms", C.c_float)]
 
 
 _libs = {}
@@ -208,7 +208,7 @@ class CudaH264Enc:
         _check(self.L, self.L.cc_enc_get_mbinfo(self._h, a.ctypes.data), "cc_enc_get_mbinfo")
         return a
 
-    STAGES = ("upload", "ingest", "me_coarse", "me_fine", "p_code", "mb_encode", "border", "hpel", "l1ref", "pack")
+    STAGES = ("upload", "ingest", "me_coarse", "me_fine", "p_code", "mb_encode", "pack", "border", "hpel", "l1ref")
 
     def set_profile(self, on=True):
         _check(self.L, self.L.cc_enc_set_profile(self._h, int(on)), "cc_enc_set_profile")

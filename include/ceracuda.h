@@ -70,6 +70,8 @@ typedef struct {
     float gpu_ms;        /* device time of the frame's kernels (CUDA events) */
     float host_ms;       /* host entropy coding + packaging time */
     int n_intra_analysed, n_skip_probed; /* P frames: MBs that took the slow paths of the wavefront kernel */
+    float submit_ms;     /* host time spent inside cc_enc_submit issuing the frame's copies and launches */
+    float wait_ms;       /* host time cc_enc_collect spent waiting for the device */
 } cc_packet;
 
 const char *cc_version(void);
@@ -106,8 +108,8 @@ int cc_enc_get_me8(cc_enc *h, int16_t *mv8, int32_t *satd4, uint8_t *part);
 int cc_enc_get_mbinfo(cc_enc *h, uint8_t *dst8);
 size_t cc_enc_device_bytes(const cc_enc *h);
 /* per-stage device timing with CUDA events on the encoder's own stream (bench.py's roofline figures) */
-enum { CC_STAGE_UPLOAD = 0, CC_STAGE_INGEST, CC_STAGE_ME_COARSE, CC_STAGE_ME_FINE, CC_STAGE_P_CODE, CC_STAGE_MB_ENCODE, CC_STAGE_BORDER,
-       CC_STAGE_HPEL, CC_STAGE_L1REF, CC_STAGE_PACK, CC_STAGE_COUNT };
+enum { CC_STAGE_UPLOAD = 0, CC_STAGE_INGEST, CC_STAGE_ME_COARSE, CC_STAGE_ME_FINE, CC_STAGE_P_CODE, CC_STAGE_MB_ENCODE, CC_STAGE_PACK,
+       CC_STAGE_BORDER, CC_STAGE_HPEL, CC_STAGE_L1REF, CC_STAGE_COUNT }; /* in execution order */
 int cc_enc_set_profile(cc_enc *h, int on);
 int cc_enc_get_stage_ms(const cc_enc *h, double *ms_sum /*[CC_STAGE_COUNT]*/, long *count /*[CC_STAGE_COUNT]*/);
 /* number of kernel launches issued by this handle since open */

@@ -28,6 +28,9 @@ def test_i4_tap_table_matches_oracle_predictors():
                 L.ref_pred4x4(out, mode, C.c_void_p(top.ctypes.data + 1), C.c_void_p(left.ctypes.data), ht, hl)
                 mine = [(E[t & 15] + 2 * E[(t >> 4) & 15] + E[(t >> 8) & 15] + 2) >> 2 for t in tab[mode]]
                 assert mine == list(out), (mode, ht, hl)
+                S = gen_i4_table.build_S(E)   # the one-lookup-per-pixel form used by the wavefront kernel
+                st = gen_i4_table.sidx_table()[mode]
+                assert [S[(st[i >> 2] >> (8 * (i & 3))) & 255] for i in range(16)] == list(out), (mode, ht, hl)
 
 
 def test_generated_headers_are_current():
@@ -35,3 +38,5 @@ def test_generated_headers_are_current():
     txt = open(os.path.join(ROOT, "ceracoder_b200", "csrc", "cc_i4_table.h")).read()
     for r in gen_i4_table.table():
         assert ", ".join("0x%03x" % v for v in r) in txt
+    for r in gen_i4_table.sidx_table():
+        assert ", ".join("0x%08xu" % v for v in r) in txt
