@@ -11,7 +11,10 @@
 #define CC_LAUNCH(kern, grid, block, stream, ...) kern<<<grid, block, 0, stream>>>(__VA_ARGS__)
 #define CC_LAUNCH_SMEM(kern, grid, block, smem, stream, ...) kern<<<grid, block, smem, stream>>>(__VA_ARGS__)
 #define CC_DYN_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
-#define CC_SPIN_PAUSE() __nanosleep(20)
+#ifndef CC_SPIN_NS
+#define CC_SPIN_NS 20
+#endif
+#define CC_SPIN_PAUSE() __nanosleep(CC_SPIN_NS)
 #else
 #define CC_LAUNCH(kern, grid, block, stream, ...) emu::launch(grid, block, 0, [&] { kern(__VA_ARGS__); })
 #define CC_LAUNCH_SMEM(kern, grid, block, smem, stream, ...) emu::launch(grid, block, smem, [&] { kern(__VA_ARGS__); })
@@ -99,17 +102,46 @@ __device__ __forceinline__ void cc_ld64u(const uint8_t *p, uint32_t &lo, uint32_
     lo = __funnelshift_r(w0, w1, sh);
     hi = __funnelshift_r(w1, w2, sh);
 }
+/* acc + sum of |a.b[i] - b.b[i]| over the four bytes: one VABSDIFF4.U8.ACC (the __vsadu4 intrinsic leaves the add separate) */
+__device__ __forceinline__ uint32_t cc_sad4_acc(uint32_t a, uint32_t b, uint32_t acc) {
+#ifdef CC_EMU_BUILD
+    return acc + __vsadu4(a, b);
+#else
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+    return d;
+#endif
+}
 __device__ __forceinline__ int cc_byte(uint32_t w, int i) { return (int)((w >> (8 * i)) & 255u); }
 
-/* one 4x4 SATD (Hadamard of the difference, sum|.| >> 1) from packed rows: c[r], p[r] = 4 pixels each */
+/* c + sum over the four bytes of (unsigned byte of a) * (signed byte of b): one IDP.4A.U8.S8 */
+__device__ __forceinline__ int cc_dp4a_us(uint32_t a, uint32_t b, int c) {
+#ifdef CC_EMU_BUILD
+    for (int i = 0; i < 4; i++) c += (int)((a >> (8 * i)) & 255u) * (int)(int8_t)((b >> (8 * i)) & 255u);
+    return c;
+#else
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#endif
+}
+/* rows of the 4-point Hadamard matrix and their negatives as packed signed bytes (pixel 0 = low byte) */
+#define CC_H0 0x01010101u /* + + + + */
+#define CC_H1 0xffff0101u /* + + - - */
+#define CC_H2 0x01ffff01u /* + - - + */
+#define CC_H3 0xff01ff01u /* + - + - */
+#define CC_NEG4(h) ((~(h) & 0xfefefefeu) | 0x01010101u) /* bytes are +1 (0x01) or -1 (0xff): negation swaps them */
+
+/* one 4x4 SATD (Hadamard of the difference, sum|.| >> 1) from packed rows: c[r], p[r] = 4 pixels each.  The horizontal
+ * transform of the difference comes straight off the packed bytes as dot products with +-1 rows (2 IDP.4A per coefficient). */
 __device__ __forceinline__ int cc_satd4x4_words(const uint32_t c[4], const uint32_t p[4]) {
     int t[16];
 #pragma unroll
     for (int r = 0; r < 4; r++) {
-        int d0 = cc_byte(c[r], 0) - cc_byte(p[r], 0), d1 = cc_byte(c[r], 1) - cc_byte(p[r], 1);
-        int d2 = cc_byte(c[r], 2) - cc_byte(p[r], 2), d3 = cc_byte(c[r], 3) - cc_byte(p[r], 3);
-        int s01 = d0 + d1, m01 = d0 - d1, s23 = d2 + d3, m23 = d2 - d3;
-        t[r * 4 + 0] = s01 + s23; t[r * 4 + 1] = s01 - s23; t[r * 4 + 2] = m01 - m23; t[r * 4 + 3] = m01 + m23;
+        t[r * 4 + 0] = cc_dp4a_us(c[r], CC_H0, cc_dp4a_us(p[r], CC_NEG4(CC_H0), 0));
+        t[r * 4 + 1] = cc_dp4a_us(c[r], CC_H1, cc_dp4a_us(p[r], CC_NEG4(CC_H1), 0));
+        t[r * 4 + 2] = cc_dp4a_us(c[r], CC_H2, cc_dp4a_us(p[r], CC_NEG4(CC_H2), 0));
+        t[r * 4 + 3] = cc_dp4a_us(c[r], CC_H3, cc_dp4a_us(p[r], CC_NEG4(CC_H3), 0));
     }
     int s = 0;
 #pragma unroll

@@ -14,24 +14,25 @@
 #include "cc_dev.cuh"
 
 #define L1_WIN 40          /* 8 + 2*16 */
-#define L1_PITCH 44        /* bytes per staged row: 11 words (odd word count spreads rows over banks) */
+#define L1_PITCHW 12       /* words per staged row: 10 of window + 2 of padding read by the last candidate group */
 #define ME_WARPS 4
 
+/* Work item = (dy, group of 4 consecutive dx): the 4 candidates share the same three aligned words of every window row, so a
+ * row costs 3 LDS + 6 funnel shifts + 8 VABSDIFF4.ACC for 4 candidates (algorithmic integer ops, SURVEY.md 8d: 16 per candidate). */
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
-    __shared__ __align__(16) uint8_t win[ME_WARPS][L1_WIN * L1_PITCH + 8];
+    __shared__ __align__(16) uint32_t win[ME_WARPS][L1_WIN * L1_PITCHW];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
     if (mb >= nmb) return; /* whole warp exits together */
     const int mbx = mb % k.mb_w, mby = mb / k.mb_w;
     const uint8_t *cur = k.l1cur + (size_t)(mby * 8) * k.sc + mbx * 8;
-    const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx * 8 - CC_L1R);
-    uint8_t *w = win[wid];
-    for (int i = lane; i < L1_WIN * 10; i += 32) { /* 10 words per row */
-        int r = i / 10, c = i % 10;
-        *(uint32_t *)(w + r * L1_PITCH + 4 * c) = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
+    const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx * 8 - CC_L1R); /* 4-byte aligned */
+    uint32_t *w = win[wid];
+    for (int i = lane; i < L1_WIN * 10; i += 32) {
+        const int r = i / 10, c = i - r * 10;
+        w[r * L1_PITCHW + c] = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
     }
-    if (lane < L1_WIN) *(uint32_t *)(w + lane * L1_PITCH + 40) = 0; /* pad word read by the funnel shift */
-    if (lane < 2) *(uint32_t *)(w + L1_WIN * L1_PITCH + 4 * lane) = 0;
+    for (int r = lane; r < L1_WIN; r += 32) { w[r * L1_PITCHW + 10] = 0; w[r * L1_PITCHW + 11] = 0; }
     uint32_t c0[8], c1[8];
 #pragma unroll
     for (int r = 0; r < 8; r++) {
@@ -40,18 +41,26 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
     }
     __syncwarp();
     unsigned best = 0xffffffffu;
-    for (int c = lane; c < 33 * 33; c += 32) {
-        int dy = c / 33, dx = c - dy * 33; /* window coordinates 0..32 */
-        const uint8_t *p = w + dy * L1_PITCH + dx;
-        unsigned sad = 0;
+    for (int item = lane; item < 33 * 9; item += 32) {
+        const int dy = item / 9, g = item - dy * 9; /* window coordinates: dy 0..32, dx = 4g .. 4g+3 */
+        const uint32_t *p = w + dy * L1_PITCHW + g;
+        uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0;
 #pragma unroll
         for (int r = 0; r < 8; r++) {
-            uint32_t lo, hi;
-            cc_ld64u(p + r * L1_PITCH, lo, hi);
-            sad += __vsadu4(lo, c0[r]) + __vsadu4(hi, c1[r]);
+            const uint32_t w0 = p[r * L1_PITCHW], w1 = p[r * L1_PITCHW + 1], w2 = p[r * L1_PITCHW + 2];
+            s0 = cc_sad4_acc(w0, c0[r], cc_sad4_acc(w1, c1[r], s0));
+            s1 = cc_sad4_acc(__funnelshift_r(w0, w1, 8), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 8), c1[r], s1));
+            s2 = cc_sad4_acc(__funnelshift_r(w0, w1, 16), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 16), c1[r], s2));
+            s3 = cc_sad4_acc(__funnelshift_r(w0, w1, 24), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 24), c1[r], s3));
         }
-        unsigned key = ((4u * sad + (unsigned)(cc_iabs(dx - 16) + cc_iabs(dy - 16))) << 11) | (unsigned)c;
-        best = min(best, key);
+        const unsigned ady = (unsigned)cc_iabs(dy - 16), idx = (unsigned)(dy * 33 + 4 * g);
+        const int dx = 4 * g - 16;
+        best = min(best, ((4u * s0 + (unsigned)cc_iabs(dx) + ady) << 11) | idx);
+        if (g < 8) { /* dx = 32 is the only candidate of the last group */
+            best = min(best, ((4u * s1 + (unsigned)cc_iabs(dx + 1) + ady) << 11) | (idx + 1));
+            best = min(best, ((4u * s2 + (unsigned)cc_iabs(dx + 2) + ady) << 11) | (idx + 2));
+            best = min(best, ((4u * s3 + (unsigned)cc_iabs(dx + 3) + ady) << 11) | (idx + 3));
+        }
     }
     best = __reduce_min_sync(FULL, best);
     if (lane == 0) {

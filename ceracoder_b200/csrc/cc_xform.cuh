@@ -10,14 +10,23 @@
 #include "cc_dev.cuh"
 
 /* ---- transform chain (one 4x4 block per lane) ------------------------------------------------------- */
+/* rows of the forward core transform Cf = [1 1 1 1; 2 1 -1 -2; 1 -1 -1 1; 1 -2 2 -1] as packed signed bytes, and their negatives */
+#define CC_CF0 0x01010101u
+#define CC_CF1 0xfeff0102u
+#define CC_CF2 0x01ffff01u
+#define CC_CF3 0xff02fe01u
+#define CC_CF0N 0xffffffffu
+#define CC_CF1N 0x0201fffeu
+#define CC_CF2N 0xff0101ffu
+#define CC_CF3N 0x01fe02ffu
 __device__ __forceinline__ void dct4x4_res(const uint32_t c[4], const uint32_t p[4], int d[16]) {
     int t[16];
 #pragma unroll
-    for (int r = 0; r < 4; r++) {
-        int d0 = cc_byte(c[r], 0) - cc_byte(p[r], 0), d1 = cc_byte(c[r], 1) - cc_byte(p[r], 1);
-        int d2 = cc_byte(c[r], 2) - cc_byte(p[r], 2), d3 = cc_byte(c[r], 3) - cc_byte(p[r], 3);
-        int s03 = d0 + d3, s12 = d1 + d2, m03 = d0 - d3, m12 = d1 - d2;
-        t[r * 4 + 0] = s03 + s12; t[r * 4 + 1] = 2 * m03 + m12; t[r * 4 + 2] = s03 - s12; t[r * 4 + 3] = m03 - 2 * m12;
+    for (int r = 0; r < 4; r++) { /* horizontal pass on the packed bytes: Cf_k . cur - Cf_k . pred */
+        t[r * 4 + 0] = cc_dp4a_us(c[r], CC_CF0, cc_dp4a_us(p[r], CC_CF0N, 0));
+        t[r * 4 + 1] = cc_dp4a_us(c[r], CC_CF1, cc_dp4a_us(p[r], CC_CF1N, 0));
+        t[r * 4 + 2] = cc_dp4a_us(c[r], CC_CF2, cc_dp4a_us(p[r], CC_CF2N, 0));
+        t[r * 4 + 3] = cc_dp4a_us(c[r], CC_CF3, cc_dp4a_us(p[r], CC_CF3N, 0));
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) {

@@ -38,7 +38,7 @@ _libs = {}
 
 def load_library(path=None):
     """Load libceracuda.so (built in-tree by `make lib` / __graft_entry__.build()). Fails loudly if missing."""
-    path = path or LIB_PATH
+    path = path or os.environ.get("CERACUDA_LIB") or LIB_PATH   # CERACUDA_LIB: an alternative build of the same library (kernel experiments)
     if path in _libs:
         return _libs[path]
     if not os.path.exists(path):
