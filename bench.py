@@ -148,6 +148,26 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture
+    (profiles/traffic.json, written by tools/summarize_profiles.py); None if no capture is committed."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)[kernel]
+        return t["dram_bytes_read"] + t["dram_bytes_write"]
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def int_peaks(L):
+    out = {}
+    for kind, name in enumerate(("vabsdiff4_acc", "iadd", "lop3", "idp4a")):
+        g = C.c_double()
+        if L.cc_bench_int_peak(kind, C.byref(g)) == 0:
+            out[name] = g.value
+    return out
+
+
 def cpu_baseline(pool, n_frames, rps=4):
     """The oracle (CPU port of the same algorithm, OpenMP over slices/MBs) timed on this box's host cores."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -289,13 +309,25 @@ def main():
         avg_ms = st[dom][0] / max(st[dom][1], 1)
         ach = ALG_BYTES_PER_FRAME / (avg_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": {"mb_encode": "k_mb_encode", "me_coarse": "k_me_l1", "me_fine": "k_me_l0", "hpel": "k_hpel"}.get(dom, dom),
-                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": ncu_traffic({"mb_encode": "k_mb_encode", "me_coarse": "k_me_l1", "me_fine": "k_me_l0", "p_code": "k_p_code"}.get(dom, dom)),
                 "avg_launch_ms": avg_ms, "launches_timed": st[dom][1], "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ALG_BYTES_PER_FRAME,
                 "note": "one launch = one 1080p frame of one stream; 8 streams' launches overlap on the GPU, so the per-launch duration includes sharing; "
                         "aggregate_achieved = value * 4.5*W*H",
                 "aggregate_achieved": value * ALG_BYTES_PER_FRAME / 1e9,
                 "stage_ms_per_frame": {s: st[s][0] / max(st[s][1], 1) for s in st}}
+    # integer roofline: algorithmic 4-pixel abs-diff-accumulate ops of the exhaustive coarse search
+    # (33*33 candidates x 16 ops per macroblock) over k_me_l1's CUDA-event time, against the VABSDIFF4 peak measured here
+    introof = None
+    if st and "me_coarse" in st and st["me_coarse"][1]:
+        pk = int_peaks(L)
+        ops = (W // 16) * ((H + 15) // 16) * 33 * 33 * 16
+        ms_l1 = st["me_coarse"][0] / st["me_coarse"][1]
+        a = ops / (ms_l1 * 1e-3) / 1e9
+        introof = {"kernel": "k_me_l1", "op": "4-pixel abs-diff-accumulate (VABSDIFF4.U8.ACC)", "algorithmic_ops_per_launch": ops, "avg_launch_ms": ms_l1,
+                   "achieved": a, "peak": pk.get("vabsdiff4_acc"), "unit": "Gop/s (thread-level)", "frac": a / pk["vabsdiff4_acc"] if pk.get("vabsdiff4_acc") else None,
+                   "measured_peaks_gops": pk, "note": "launches of 8 streams overlap on the GPU; the kernel alone (ncu, profiles/) runs faster"}
     cpu = None
     if not args.no_cpu_baseline:
         t0 = time.perf_counter()
@@ -312,7 +344,7 @@ def main():
                        "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
             "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"][:5]])),
             "host_ms_per_frame": dict(zip(("submit_api", "wait_device", "cavlc_nal", "device_frame_latency"), [round(v / max(r_e2e["frames"], 1), 4) for v in r_e2e["mbstats"][5:9]])),

@@ -98,6 +98,63 @@ struct DevBuf {
 };
 static dim3 grid_for(int n) { return dim3((unsigned)((n + 127) / 128)); }
 
+/* ---- integer-pipe peak ("the peak must be measured on the box") ---------------------------------------
+ * Register-resident loops of independent operations, every SM filled (8 CTAs x 256 threads per SM), timed with CUDA
+ * events, best of 10.  kind 0: VABSDIFF4.U8.ACC (the __vsadu4-class op of the SAD searches), 1: IADD, 2: LOP3, 3: IDP.4A. */
+#define KP_PEAK_ILP 8
+#define KP_PEAK_ITERS 4096
+template <int KIND> __global__ void __launch_bounds__(256) kp_int_peak(uint32_t seed, uint32_t *sink) {
+    uint32_t v[KP_PEAK_ILP], b = seed + threadIdx.x, c = seed ^ 0x5bd1e995u;
+#pragma unroll
+    for (int i = 0; i < KP_PEAK_ILP; i++) v[i] = seed * (i + 1) + threadIdx.x;
+    for (int it = 0; it < KP_PEAK_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < KP_PEAK_ILP; i++) {
+            if (KIND == 0) v[i] = cc_sad4_acc(v[i], b, c);
+            else if (KIND == 1) asm volatile("add.u32 %0, %0, %1;" : "+r"(v[i]) : "r"(b)); /* volatile: a plain sum would be strength-reduced */
+            else if (KIND == 2) v[i] = (v[i] & b) ^ c;
+            else v[i] = (uint32_t)cc_dp4a_us(v[i], b, (int)c);
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < KP_PEAK_ILP; i++) r ^= v[i];
+    if (r == 0x12345678u) sink[0] = r; /* keeps the loop alive; practically never true */
+}
+extern "C" int cc_bench_int_peak(int kind, double *gops) {
+    if (!gops || kind < 0 || kind > 3) return CC_ERR_PARAM;
+    if (!have_device()) return CC_ERR_CUDA;
+#ifdef CC_EMU_BUILD
+    *gops = 0; return CC_ERR_CUDA;
+#else
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    DevBuf sink;
+    if (sink.alloc(16, nullptr)) return CC_ERR_NOMEM;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const dim3 grid((unsigned)sms * 8), block(256);
+    float best = 1e30f;
+    for (int rep = 0; rep < 11; rep++) {
+        cudaEventRecord(e0, 0);
+        if (kind == 0) kp_int_peak<0><<<grid, block>>>(12345u + rep, (uint32_t *)sink.p);
+        else if (kind == 1) kp_int_peak<1><<<grid, block>>>(12345u + rep, (uint32_t *)sink.p);
+        else if (kind == 2) kp_int_peak<2><<<grid, block>>>(12345u + rep, (uint32_t *)sink.p);
+        else kp_int_peak<3><<<grid, block>>>(12345u + rep, (uint32_t *)sink.p);
+        cudaEventRecord(e1, 0);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return CC_ERR_CUDA; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0 && ms < best) best = ms; /* first launch warms up */
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    const double ops = (double)sms * 8 * 256 * KP_PEAK_ILP * KP_PEAK_ITERS; /* thread-level operations */
+    *gops = ops / (best * 1e-3) / 1e9;
+    return CC_OK;
+#endif
+}
+
 extern "C" int cc_prim_sad(const uint8_t *a, const uint8_t *b, int w, int h, int n, int32_t *out) {
     if (!a || !b || !out || n <= 0 || w <= 0 || h <= 0 || (w * h) % 4) return CC_ERR_PARAM;
     if (!have_device()) return CC_ERR_CUDA;

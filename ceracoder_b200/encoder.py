@@ -84,6 +84,7 @@ def load_library(path=None):
     L.cc_prim_tq8x8.argtypes = [vp, vp, ci, ci, vp, vp, vp]
     L.cc_prim_pred4x4.argtypes = [vp, ci, ci, vp]
     L.cc_prim_mc_luma.argtypes = [vp, ci, ci, vp, vp, ci, vp]
+    L.cc_bench_int_peak.argtypes = [ci, C.POINTER(C.c_double)]
     _libs[path] = L
     return L
 

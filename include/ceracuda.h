@@ -145,6 +145,11 @@ int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out);
 /* quarter-pel luma interpolation of n 16x16 blocks taken at (x,y)[i] + mv[i] from one w*h plane (borders replicated) */
 int cc_prim_mc_luma(const uint8_t *plane, int w, int h, const int16_t *xy, const int16_t *mv, int n, uint8_t *out);
 
+/* Integer-pipe peak of the device, measured: thread-level G-ops/s of a register-resident loop of independent
+ * operations on every SM.  kind 0: VABSDIFF4.U8.ACC (4-pixel abs-diff-accumulate, the SAD searches' op), 1: IADD, 2: LOP3,
+ * 3: IDP.4A (the SATD / DCT row dot products).  Used by bench.py for the integer roofline. */
+int cc_bench_int_peak(int kind, double *gops);
+
 #ifdef __cplusplus
 }
 #endif
