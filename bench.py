@@ -21,6 +21,9 @@ import time
 
 import numpy as np
 
+# more than 8 streams per process need more hardware queues than the default 8, or they serialise pairwise
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
