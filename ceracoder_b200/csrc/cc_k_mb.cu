@@ -58,7 +58,8 @@ struct MbCtx {
 
 /* ---- motion compensation ----------------------------------------------------------------------------- */
 /* 16x16 luma predictor at quarter-pel mv into m->predY; lane = (row, half) */
-__device__ __forceinline__ void mc_luma16(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
+__device__ __forceinline__ void mc_luma16(const cc_kparams &k, const MbCtx &c, int mvx, int mvy, uint32_t *dstY = nullptr) {
+    if (!dstY) dstY = c.m->predY;
     const int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
     const int row = c.lane >> 1, half = c.lane & 1;
     const ptrdiff_t base = (ptrdiff_t)(c.py + row + (mvy >> 2)) * k.sy + c.px + half * 8 + (mvx >> 2);
@@ -68,8 +69,8 @@ __device__ __forceinline__ void mc_luma16(const cc_kparams &k, const MbCtx &c, i
     uint32_t a0, a1, b0, b1;
     cc_ld64u(A, a0, a1);
     cc_ld64u(B, b0, b1);
-    c.m->predY[row * 4 + half * 2] = __vavgu4(a0, b0);
-    c.m->predY[row * 4 + half * 2 + 1] = __vavgu4(a1, b1);
+    dstY[row * 4 + half * 2] = __vavgu4(a0, b0);
+    dstY[row * 4 + half * 2 + 1] = __vavgu4(a1, b1);
 }
 /* P_8x8: the lane mappings of mc_luma16 (row, 8-pixel half) and mc_chroma8 (plane, row, 4-pixel half) never straddle an 8x8
  * quadrant (4x4 in chroma), so a P_8x8 macroblock is predicted by the same two functions with each lane passing the vector
@@ -78,7 +79,8 @@ __device__ __forceinline__ int luma_lane_quad(int lane) { return ((lane >> 4) <<
 __device__ __forceinline__ int chroma_lane_quad(int lane) { return (((lane >> 3) & 1) << 1) | (lane & 1); }
 __device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8);
 /* 8x8 chroma predictors (both planes), H.264 8.4.2.2.2; lane = (plane, row, half) */
-__device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
+__device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, int mvx, int mvy, uint32_t (*dstC)[16] = nullptr) {
+    if (!dstC) dstC = c.m->predC;
     const int pl = c.lane >> 4, row = (c.lane >> 1) & 7, half = c.lane & 1, fx = mvx & 7, fy = mvy & 7;
     const uint8_t *p = k.ref[1 + pl] + (ptrdiff_t)(c.mby * 8 + row + (mvy >> 3)) * k.sc + c.mbx * 8 + half * 4 + (mvx >> 3);
     uint32_t w = 0;
@@ -90,7 +92,7 @@ __device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, 
         w |= (uint32_t)v << (8 * x);
         a = a1; b = b1;
     }
-    c.m->predC[pl][row * 2 + half] = w;
+    dstC[pl][row * 2 + half] = w;
 }
 
 __device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8) {
@@ -613,6 +615,66 @@ __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, 
     return zl && zc;
 }
 
+/* Two P_Skip tests in one pass (the pre-pass probes its two likeliest skip vectors): prediction A in predY / predC, prediction B
+ * in recY / recC (free at that point); lanes 0-15 run the luma blocks of A and lanes 16-31 those of B, lanes 0-7 / 8-15 the chroma
+ * blocks.  Same arithmetic as inter_luma / encode_chroma in probe mode.  Returns bit 0: nothing survives at A, bit 1: at B. */
+__device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, int ax, int ay, int bx2, int by2) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
+    mc_luma16(k, c, ax, ay);
+    mc_chroma8(k, c, ax, ay);
+    mc_luma16(k, c, bx2, by2, m->recY);
+    mc_chroma8(k, c, bx2, by2, m->recC);
+    __syncwarp();
+    unsigned nzl;
+    { /* luma */
+        const int b = lane & 15, bx = c_blk_x[b], by = c_blk_y[b];
+        const uint32_t *pred = lane < 16 ? m->predY : m->recY;
+        uint32_t cw[4], pw[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) { cw[r] = m->curY[(by * 4 + r) * 4 + bx]; pw[r] = pred[(by * 4 + r) * 4 + bx]; }
+        int d[16], z[16];
+        dct4x4_res(cw, pw, d);
+        int nnz = quant4x4(d, k.qmf[1], k.qbias[1], false);
+        to_scan(d, z, false);
+        const int score = decimate_score(z);
+        int s8 = score + __shfl_xor_sync(FULL, score, 1);
+        s8 += __shfl_xor_sync(FULL, s8, 2);
+        int tot = s8 + __shfl_xor_sync(FULL, s8, 4);
+        tot += __shfl_xor_sync(FULL, tot, 8); /* sum over the 16 lanes of this half */
+        if (tot < 6 || s8 < 4) nnz = 0;
+        nzl = __ballot_sync(FULL, nnz > 0);
+    }
+    unsigned nzc;
+    { /* chroma: lanes 0-15 = (probe, plane, block) */
+        const int sel = (lane >> 3) & 1, pl = (lane >> 2) & 1, b = lane & 3, bx = b & 1, by = b >> 1;
+        const uint32_t *pred = sel ? m->recC[pl] : m->predC[pl];
+        const uint16_t *mf = k.qmf[3], *bias = k.qbias[3];
+        uint32_t cw[4], pw[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) { cw[r] = m->curC[pl][(by * 4 + r) * 2 + bx]; pw[r] = pred[(by * 4 + r) * 2 + bx]; }
+        int d[16], z[16];
+        dct4x4_res(cw, pw, d);
+        const int dc = d[0];
+        int nnz = quant4x4(d, mf, bias, true);
+        to_scan(d, z, true);
+        int score = decimate_score(z);
+        score += __shfl_xor_sync(FULL, score, 1);
+        score += __shfl_xor_sync(FULL, score, 2);
+        int nac = nnz > 0;
+        nac |= __shfl_xor_sync(FULL, nac, 1);
+        nac |= __shfl_xor_sync(FULL, nac, 2);
+        if (score < 7) nac = 0;
+        const int d0 = __shfl_sync(FULL, dc, 0, 4), d1 = __shfl_sync(FULL, dc, 1, 4), d2 = __shfl_sync(FULL, dc, 2, 4), d3 = __shfl_sync(FULL, dc, 3, 4);
+        const int a = d0 + d1, bb = d0 - d1, cc = d2 + d3, e = d2 - d3;
+        const int ndc = (quant_one(a + cc, mf[0] >> 1, bias[0] << 1) != 0) | (quant_one(bb + e, mf[0] >> 1, bias[0] << 1) != 0) |
+                        (quant_one(a - cc, mf[0] >> 1, bias[0] << 1) != 0) | (quant_one(bb - e, mf[0] >> 1, bias[0] << 1) != 0);
+        nzc = __ballot_sync(FULL, lane < 16 && (nac || ndc));
+    }
+    __syncwarp();
+    return (((nzl & 0xffffu) | (nzc & 0xffu)) == 0 ? 1 : 0) | (((nzl >> 16) | (nzc & 0xff00u)) == 0 ? 2 : 0);
+}
+
 /* Unfiltered neighbour samples.  Intra prediction uses the reconstruction BEFORE deblocking (H.264 8.3), while the
  * filter warps of the same slice modify k.rec a few macroblocks behind the encode warps, and in P frames most
  * macroblocks are reconstructed by the parallel pre-pass, not by this warp.  So whoever reconstructs a macroblock
@@ -910,8 +972,11 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     int ok = 0;
     /* a P_8x8 search result says nothing about the 16x16 coding at one vector: both probes run for real */
     const bool c_is_me = !part && cand[0] == mvx && cand[1] == mvy, z_is_me = !part && mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
-    if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
-    if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
+    if (!c_is_me && !z_is_me && !z_is_c) ok = probe_zero2(k, c, cand[0], cand[1], 0, 0); /* publish_pixels is done: recY / recC are free */
+    else {
+        if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
+        if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
+    }
     if (lane == 0) {
         cc_pre p;
         p.cbp = (uint8_t)cbp; p.skip_ok = (uint8_t)ok; p.nz_luma = (uint16_t)nzmask; p.cand[0] = (int16_t)cand[0]; p.cand[1] = (int16_t)cand[1];

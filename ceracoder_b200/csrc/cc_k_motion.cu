@@ -84,9 +84,10 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
 /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"; oracle/ref_enc.c me_l0, second half).
  * Every quadrant searches +-2 full-pel around the macroblock's best full-pel vector by SAD (lane = candidate, the four
  * quadrant SADs of a candidate come out of one pass over the 16 rows), then refines to half and quarter-pel by SATD
- * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks.
+ * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks
+ * (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
  * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
-__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, int mb, int px, int py, int fbx, int fby, const int pm[2], int lambda, int lane) {
+__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
     unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
     if (lane < 25) {
         const int mx = fbx + lane % 5 - 2, my = fby + lane / 5 - 2;
@@ -107,12 +108,21 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, i
     }
     const int p = lane >> 3, slot = (lane >> 2) & 1, b4 = lane & 3;
     int fi = 0;
+    unsigned full8 = (unsigned)(8 * lambda);
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-        const int i = (int)(__reduce_min_sync(FULL, key4[q]) & 31u);
-        if (q == p) fi = i;
+        const unsigned bq = __reduce_min_sync(FULL, key4[q]);
+        full8 += bq >> 5;
+        if (q == p) fi = (int)(bq & 31u);
     }
     int qx = 4 * (fbx + fi % 5 - 2), qy = 4 * (fby + fi / 5 - 2);
+    /* partitions pay only where parts of the macroblock move differently: unless the four full-pel quadrant costs plus the
+     * partition overhead already beat the full-pel 16x16 cost, the sub-pel refinement is not run and the macroblock stays one
+     * partition */
+    if (full8 >= full16) {
+        if (lane < 8) { ((uint32_t *)k.me8[mb].mv)[lane & 3] = 0u; ((uint32_t *)k.me8[mb].satd)[lane & 3] = 0u; }
+        return 1 << 30;
+    }
     const int ox = (p & 1) * 8 + (b4 & 1) * 4, oy = (p >> 1) * 8 + (b4 >> 1) * 4;
     uint32_t cw[4];
 #pragma unroll
@@ -245,7 +255,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     }
     const int cost16 = (int)(bestkey >> 5);
     int part = 0;
-    if (k.part8) part = me_8x8(k, sc, mb, px, py, fbx, fby, pm, lambda, lane) < cost16;
+    if (k.part8) part = me_8x8(k, sc, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
     if (lane == 0) {
         k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd; k.me[mb].part = part;
     }

@@ -157,7 +157,8 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
     /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"): every quadrant searches +-2 full-pel
      * around the 16x16 integer vector by SAD, then the same half/quarter-pel SATD refinement.  P_8x8 is chosen when the
      * summed cost plus 8 lambda (mb_type + four sub_mb_type code lengths over P_L0_16x16) beats the 16x16 cost. */
-    int cost8 = 8 * lambda;
+    int cost8 = 8 * lambda, f8[4][2];
+    unsigned full8 = (unsigned)(8 * lambda);
     for (int p = 0; p < 4; p++) {
         const uint8_t *c8 = cur + (p >> 1) * 8 * sy + (p & 1) * 8, *r8 = ref + (p >> 1) * 8 * sy + (p & 1) * 8;
         unsigned b8 = ~0u;
@@ -169,6 +170,17 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
             unsigned key = (c << 5) | (unsigned)i;
             if (key < b8) { b8 = key; fx = mx; fy = my; }
         }
+        f8[p][0] = fx; f8[p][1] = fy;
+        full8 += b8 >> 5;
+    }
+    /* partitions pay only where parts of the macroblock move differently: unless the four full-pel quadrant costs plus the
+     * partition overhead already beat the full-pel 16x16 cost, the sub-pel refinement of the quadrants is not run and the
+     * macroblock stays one partition */
+    memset(mi->me_mv8, 0, sizeof mi->me_mv8); memset(mi->me_satd8, 0, sizeof mi->me_satd8);
+    if (full8 >= (best >> 5)) return;
+    for (int p = 0; p < 4; p++) {
+        const uint8_t *c8 = cur + (p >> 1) * 8 * sy + (p & 1) * 8, *r8 = ref + (p >> 1) * 8 * sy + (p & 1) * 8;
+        const int fx = f8[p][0], fy = f8[p][1];
         int qx = 4 * fx, qy = 4 * fy, qcost = 1 << 30, qsatd = 0;
         uint8_t p8[64];
         for (int step = 2; step >= 1; step--) {
