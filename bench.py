@@ -118,22 +118,14 @@ def run_streams(encs, frames_of, n_frames, start_idx, device_frames):
     errs = []
 
     def work(k, e):
-        try:
-            nb = ns = 0
-            st = [0, 0, 0, 0, 0, 0.0, 0.0, 0.0, 0.0]
-            for i in range(n_frames):
-                fi = start_idx + i
-                e.set_property("bitrate", schedule_kbps(fi + 37 * k))
-                y, u, v = frames_of(k, fi)
-                e.submit(y, u, v, pts=fi, device_frame=device_frames)
-                nb += e.collect(copy=False); ns += e.last.sym_bytes
-                L = e.last
-                for j, v in enumerate((L.n_skip, L.n_inter, L.n_intra, L.n_intra_analysed, L.n_skip_probed, L.submit_ms, L.wait_ms, L.host_ms, L.gpu_ms)):
-                    st[j] += v
+        try:  # one C call per stream per run_streams(): the frame loop itself runs in C (cc_enc_encode_sequence), off the interpreter lock
+            frames = [frames_of(k, start_idx + i) for i in range(n_frames)]
+            rates = [schedule_kbps(start_idx + i + 37 * k) for i in range(n_frames)]
+            s = e.encode_sequence(frames, rates, device_frame=device_frames)
             with lock:
-                tot[0] += n_frames; tot[1] += nb; tot[2] += ns
-                for j in range(9):
-                    tot[3 + j] += st[j]
+                tot[0] += s.frames; tot[1] += s.au_bytes; tot[2] += s.sym_bytes
+                for j, v in enumerate((s.n_skip, s.n_inter, s.n_intra, s.n_intra_analysed, s.n_skip_probed, s.submit_ms, s.wait_ms, s.host_ms, s.gpu_ms)):
+                    tot[3 + j] += v
         except Exception as ex:  # noqa: BLE001
             errs.append(ex)
     th = [threading.Thread(target=work, args=(k, e)) for k, e in enumerate(encs)]

@@ -372,6 +372,25 @@ int cc_enc_encode(cc_enc *e, const cc_frame *in, unsigned flags, cc_packet *out)
     return rc != CC_OK ? rc : cc_enc_collect(e, out);
 }
 
+int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate_bps, int n, unsigned flags, cc_seq_stats *acc, cc_packet *last) {
+    if (!e || !frames || !acc || n < 0) return CC_ERR_PARAM;
+    cc_packet pkt;
+    memset(&pkt, 0, sizeof pkt);
+    for (int i = 0; i < n; i++) {
+        if (bitrate_bps && bitrate_bps[i] != cc_enc_get_bitrate(e)) cc_enc_set_bitrate(e, bitrate_bps[i]);
+        int rc = cc_enc_submit(e, &frames[i], flags);
+        if (rc == CC_OK) rc = cc_enc_collect(e, &pkt);
+        if (rc != CC_OK) return rc;
+        acc->frames++; acc->au_bytes += pkt.size; acc->sym_bytes += pkt.sym_bytes;
+        acc->n_skip += pkt.n_skip; acc->n_inter += pkt.n_inter; acc->n_intra += pkt.n_intra;
+        acc->n_intra_analysed += pkt.n_intra_analysed; acc->n_skip_probed += pkt.n_skip_probed;
+        acc->submit_ms += pkt.submit_ms; acc->wait_ms += pkt.wait_ms; acc->host_ms += pkt.host_ms; acc->gpu_ms += pkt.gpu_ms;
+        acc->last_qp = pkt.qp;
+    }
+    if (last) *last = pkt;
+    return CC_OK;
+}
+
 /* ---- test hooks ----------------------------------------------------------------------------------- */
 int cc_enc_get_recon(cc_enc *e, uint8_t *y, uint8_t *u, uint8_t *v) {
     if (!e || !y || !u || !v || e->inflight) return CC_ERR_PARAM;

@@ -28,8 +28,10 @@ extern "C" {
 
 enum { CC_MB_PSKIP = 0, CC_MB_P16 = 1, CC_MB_I16 = 2, CC_MB_I4 = 3 };
 
+#define CC_ALIGN16 __attribute__((aligned(16))) /* lets the kernels fetch a record with one 128-bit load */
+
 /* motion-search result per macroblock */
-typedef struct {
+typedef struct CC_ALIGN16 {
     int16_t l1_mv[2]; /* coarse vector, half-res pixels */
     int16_t mv[2];    /* refined vector, quarter-pel */
     int32_t satd;     /* SATD of the 16x16 prediction at mv */
@@ -37,7 +39,7 @@ typedef struct {
 } cc_me; /* 16 bytes */
 
 /* 8x8-partition search result per macroblock (quadrants in decoding order: 0 top-left, 1 top-right, 2 bottom-left, 3 bottom-right) */
-typedef struct {
+typedef struct CC_ALIGN16 {
     int16_t mv[4][2]; /* quarter-pel */
     int32_t satd[4];
 } cc_me8; /* 32 bytes */
@@ -59,7 +61,7 @@ typedef struct {
 /* result of the parallel P-frame pre-pass (k_p_code) for one macroblock: the MB coded as P_L0_16x16 at the motion
  * search vector (levels in the MB's symbol slot, reconstruction in k.rec), plus skip probes at the two most likely
  * P_Skip vectors.  The wavefront kernel only decides; it recomputes nothing for macroblocks that stay inter. */
-typedef struct {
+typedef struct CC_ALIGN16 {
     uint8_t cbp;        /* luma 8x8 bits | chroma << 4, coded at me.mv */
     uint8_t skip_ok;    /* bit 0: nothing survives at cand[] ; bit 1: nothing survives at (0,0) */
     uint16_t nz_luma;

@@ -19,6 +19,7 @@
  * 8.5 (transform), 8.7 (deblocking); decision rules follow the oracle (oracle/ref_mb.c), which is pinned
  * by libavcodec's decoder.
  */
+#include <stdlib.h>
 #include "cc_xform8.cuh"
 #include "cc_deblock.cuh"
 
@@ -736,19 +737,32 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
     unsigned total = 0, n_skip = 0, n_inter = 0, n_intra = 0, n_gate = 0, n_probe = 0;
     NbRec *nbl = nbline + w * mw;
     const NbRec *nbu = nbl - mw;
+    /* Software pipeline: everything a macroblock needs from global memory that does not depend on its neighbours (search
+     * result, pre-pass record, source pixels) is loaded one macroblock ahead, so its latency (HBM when 8 streams share the
+     * L2) overlaps the previous macroblock's work instead of heading the serial chain. */
+    cc_me nme = {{0, 0}, {0, 0}, 0, 0};
+    cc_pre npre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
+    uint32_t ncur[3] = {0, 0, 0};
+    auto fetch = [&](int x) {
+        const int mb = row * mw + x;
+        if (!k.is_idr) { nme = k.me[mb]; npre = k.pre[mb]; }
+        const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + x * 16;
+        ncur[0] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
+        ncur[1] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
+        ncur[2] = *(const uint32_t *)(k.cur[1 + (lane >> 4)] + (size_t)(row * 8 + ((lane >> 1) & 7)) * k.sc + x * 8 + 4 * (lane & 1));
+    };
+    fetch(0);
     for (int mbx = 0; mbx < mw; mbx++) {
         c.mbx = mbx; c.px = mbx * 16; c.mb = row * mw + mbx; c.L = mbx > 0; c.TR = c.T && mbx + 1 < mw;
         int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
         unsigned off = 0;
-        cc_me me = {{0, 0}, {0, 0}, 0, 0};
+        const cc_me me = nme;
+        const cc_pre pre = npre;
         cc_me8 me8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}};
-        cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
-        if (!k.is_idr) { /* independent of the neighbours: issued before the wait */
-            me = k.me[c.mb]; pre = k.pre[c.mb];
-            if (me.part) me8 = k.me8[c.mb];
-        }
+        if (me.part) me8 = k.me8[c.mb];
         const int part = me.part;
-        stage_cur(k, c);
+        m->curY[lane] = ncur[0]; m->curY[lane + 32] = ncur[1]; m->curC[lane >> 4][lane & 15] = ncur[2]; /* = stage_cur */
+        if (mbx + 1 < mw) fetch(mbx + 1);
         const long long t0 = k.cyc ? clock64() : 0;
         if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
         const long long t1 = k.cyc ? clock64() : 0;
@@ -987,10 +1001,19 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
 
 /* CTA = one slice.  Warps [0, rps) encode one macroblock row each; warps [rps, 2*rps) run the in-loop filter over the
  * same rows, each a few macroblocks behind its encode warp and 2 macroblocks behind the filter warp of the row above. */
-__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_mb_encode(cc_kparams k) {
-    __shared__ WarpMem wm[MB_MAX_RPS];
-    __shared__ DbMem dbm[MB_MAX_RPS];
-    __shared__ volatile int progress[MB_MAX_RPS], progress2[MB_MAX_RPS];
+#ifndef CC_MB_MAXNREG
+#define CC_MB_MAXNREG 0
+#endif
+#if CC_MB_MAXNREG > 0 && !defined(CC_EMU_BUILD) /* experiments: an explicit register cap instead of the launch bound */
+#define CC_MB_BOUNDS(rps) __maxnreg__(CC_MB_MAXNREG)
+#else
+#define CC_MB_BOUNDS(rps) __launch_bounds__(2 * (rps) * 32)
+#endif
+template <int RPS> /* RPS = most rows per slice this instance serves: 4 (256 threads, no 128-register cap) or MB_MAX_RPS */
+__global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
+    __shared__ WarpMem wm[RPS];
+    __shared__ DbMem dbm[RPS];
+    __shared__ volatile int progress[RPS], progress2[RPS];
     CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records (NbRec) */
     NbRec *nbline = (NbRec *)dsm;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1066,12 +1089,22 @@ __global__ void k_pack(cc_kparams k) {
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    const size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
+    size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
 #ifndef CC_EMU_BUILD
+    { /* experiment knob: pad the request so fewer foreign CTAs share the SM with a wavefront CTA (CC_WAVEFRONT_SMEM_KB) */
+        static int pad_kb = -1;
+        if (pad_kb < 0) { const char *v = getenv("CC_WAVEFRONT_SMEM_KB"); pad_kb = v ? atoi(v) : 0; }
+        if (pad_kb > 0 && dyn < (size_t)pad_kb * 1024) dyn = (size_t)pad_kb * 1024;
+        if (dyn > 190 * 1024) dyn = 190 * 1024;
+    }
     /* static (31.5 KB) + dynamic shared memory passes the default 48 KB limit from ~3300-pixel-wide pictures on: opt in */
-    if (dyn > 16 * 1024) cudaFuncSetAttribute(k_mb_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); /* per device; cheap */
+    if (dyn > 16 * 1024) { /* per device; cheap */
+        if (k->rps <= 4) cudaFuncSetAttribute(k_mb_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
+        else cudaFuncSetAttribute(k_mb_encode<MB_MAX_RPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
+    }
 #endif
-    CC_LAUNCH_SMEM(k_mb_encode, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
+    if (k->rps <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
+    else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

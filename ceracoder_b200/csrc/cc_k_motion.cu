@@ -73,10 +73,10 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
 /* predicted 4x4 block (4 rows of 4 pixels) at quarter-pel vector (mvx,mvy) relative to pixel (px,py) */
 __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, int mvx, int mvy, uint32_t out[4]) {
     int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
-    const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
-    ptrdiff_t base = (ptrdiff_t)(py + (mvy >> 2)) * k.sy + px + (mvx >> 2);
-    const uint8_t *A = pl[e & 3] + base + ((e >> 2) & 1) + (ptrdiff_t)((e >> 3) & 1) * k.sy;
-    const uint8_t *B = pl[(e >> 4) & 3] + base + ((e >> 6) & 1) + (ptrdiff_t)((e >> 7) & 1) * k.sy;
+    const int pa = e & 3, pb = (e >> 4) & 3; /* plane selects, not an indexed pointer array (that would live on the stack) */
+    const int base = (py + (mvy >> 2)) * k.sy + px + (mvx >> 2);
+    const uint8_t *A = (pa == 0 ? k.ref[0] : (pa == 1 ? k.hb : (pa == 2 ? k.hh : k.hj))) + (base + ((e >> 2) & 1) + ((e >> 3) & 1) * k.sy);
+    const uint8_t *B = (pb == 0 ? k.ref[0] : (pb == 1 ? k.hb : (pb == 2 ? k.hh : k.hj))) + (base + ((e >> 6) & 1) + ((e >> 7) & 1) * k.sy);
 #pragma unroll
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy), cc_ld32u(B + (ptrdiff_t)r * k.sy));
 }

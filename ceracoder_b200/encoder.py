@@ -33,6 +33,11 @@ class Packet(C.Structure):
                 ("n_intra_analysed", C.c_int), ("n_skip_probed", C.c_int), ("submit_ms", C.c_float), ("wait_ms", C.c_float)]
 
 
+class SeqStats(C.Structure):
+    _fields_ = [(n, C.c_long) for n in ("frames", "au_bytes", "sym_bytes", "n_skip", "n_inter", "n_intra", "n_intra_analysed", "n_skip_probed")] + \
+               [(n, C.c_double) for n in ("submit_ms", "wait_ms", "host_ms", "gpu_ms")] + [("last_qp", C.c_int)]
+
+
 _libs = {}
 
 
@@ -56,6 +61,7 @@ def load_library(path=None):
     L.cc_enc_encode.argtypes = [vp, C.POINTER(Frame), C.c_uint, C.POINTER(Packet)]
     L.cc_enc_submit.argtypes = [vp, C.POINTER(Frame), C.c_uint]
     L.cc_enc_collect.argtypes = [vp, C.POINTER(Packet)]
+    L.cc_enc_encode_sequence.argtypes = [vp, C.POINTER(Frame), C.POINTER(ci), ci, C.c_uint, C.POINTER(SeqStats), C.POINTER(Packet)]
     L.cc_enc_set_next_qp.argtypes = [vp, ci]
     L.cc_enc_get_recon.argtypes = [vp, vp, vp, vp]
     L.cc_enc_mb_w.argtypes = [vp]
@@ -174,6 +180,20 @@ class CudaH264Enc:
         f = self._frame(y, u, v, pts)
         flags = (CC_FORCE_IDR if force_idr else 0) | (CC_FRAME_DEVICE if device_frame else 0)
         _check(self.L, self.L.cc_enc_submit(self._h, C.byref(f), flags), "cc_enc_submit")
+
+    def encode_sequence(self, frames, bitrates_kbps, device_frame=False, stats=None):
+        """Consecutive frames in one C call (cc_enc_encode_sequence): frames = [(y, u, v)] as for encode(); bitrates in kbit/s
+        (the `bitrate` property, written only when it changes). Returns the accumulated SeqStats."""
+        n = len(frames)
+        arr = (Frame * n)()
+        for i, (y, u, v) in enumerate(frames):
+            f = self._frame(y, u, v, i)
+            arr[i].plane, arr[i].stride, arr[i].pts = f.plane, f.stride, f.pts
+        br = (C.c_int * n)(*[int(b) * 1000 for b in bitrates_kbps])
+        stats = stats if stats is not None else SeqStats()
+        _check(self.L, self.L.cc_enc_encode_sequence(self._h, arr, br, n, CC_FRAME_DEVICE if device_frame else 0, C.byref(stats), C.byref(self._pkt)),
+               "cc_enc_encode_sequence")
+        return stats
 
     def collect(self, copy=True):
         _check(self.L, self.L.cc_enc_collect(self._h, C.byref(self._pkt)), "cc_enc_collect")

@@ -92,6 +92,18 @@ int cc_enc_encode(cc_enc *h, const cc_frame *in, unsigned flags, cc_packet *out)
 int cc_enc_submit(cc_enc *h, const cc_frame *in, unsigned flags);
 int cc_enc_collect(cc_enc *h, cc_packet *out);
 
+/* Consecutive frames of one stream in one call: for i in [0, n): cc_enc_set_bitrate(h, bitrate_bps[i]) if it changed (what
+ * src/gst/encoder_control.c:51-53 does), then cc_enc_encode(frames[i]) — the loop the element's streaming thread runs, so a
+ * Python harness can drive many streams without serialising on the interpreter lock.  Sums over the n access units are added
+ * to *acc (zero it first); the last access unit stays readable through `last` (may be NULL). */
+typedef struct {
+    long frames, au_bytes, sym_bytes;
+    long n_skip, n_inter, n_intra, n_intra_analysed, n_skip_probed;
+    double submit_ms, wait_ms, host_ms, gpu_ms;
+    int last_qp;
+} cc_seq_stats;
+int cc_enc_encode_sequence(cc_enc *h, const cc_frame *frames, const int *bitrate_bps, int n, unsigned flags, cc_seq_stats *acc, cc_packet *last);
+
 /* Test hooks. */
 int cc_enc_set_next_qp(cc_enc *h, int qp); /* overrides rate control for the next submitted frame only */
 int cc_enc_get_recon(cc_enc *h, uint8_t *y, uint8_t *u, uint8_t *v); /* coded size (MB multiple), tight rows */

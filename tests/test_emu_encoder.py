@@ -56,3 +56,25 @@ def test_strided_input(lib):
     orc = OracleEncoder(w, h, 30, 4)
     assert a == orc.encode(y, u, v, True, 30)
     enc.close()
+
+
+def test_encode_sequence_equals_frame_by_frame(lib):
+    """cc_enc_encode_sequence (the streaming-thread loop in C) = set_property + encode per frame, under rate control."""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    w, h = 96, 64
+    src = make_source("pan", w, h)
+    frames = [src.frame(i) for i in range(5)]
+    rates = [6000, 6000, 2000, 2000, 9000]
+    a = CudaH264Enc(w, h, fps=(60, 1), lib=lib)
+    st = a.encode_sequence(frames, rates)
+    b = CudaH264Enc(w, h, fps=(60, 1), lib=lib)
+    sizes = []
+    for (y, u, v), r in zip(frames, rates):
+        b.set_property("bitrate", r)
+        sizes.append(len(b.encode(y, u, v)))
+    assert st.frames == 5 and st.au_bytes == sum(sizes) and st.last_qp == b.last.qp
+    assert a.last.size == sizes[-1] and a.get_property("bitrate") == 9000
+    (ya, ua, va), (yb, ub, vb) = a.recon(), b.recon()
+    assert (ya == yb).all() and (ua == ub).all() and (va == vb).all()
+    a.close(); b.close()
