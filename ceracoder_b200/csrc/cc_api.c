@@ -129,6 +129,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me8, sizeof(cc_me8) * nmb);
     k->part8 = e->p.partitions != 0;
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->nbrec, (size_t)20 * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->pre, sizeof(cc_pre) * nmb);
@@ -247,7 +248,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
 
     enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     if (e->tail_pending) { /* stages that ran behind the previous collect; skipped if they are still running */
-        for (int i = CC_STAGE_BORDER; i < CC_N_STAGES; i++) {
+        for (int i = CC_STAGE_DEBLOCK; i < CC_N_STAGES; i++) {
             float ms = 0;
             if (e->pev_used[i] && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
         }
@@ -276,10 +277,12 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->launches += cck_encode(k, e->st);
     STAGE(CC_STAGE_PACK);
     e->launches += cck_pack(k, e->st);
-    STAGE(CC_STAGE_BORDER);
+    STAGE(CC_STAGE_DEBLOCK);
     /* the access unit's symbols are in host memory here: cc_enc_collect waits for ev1 only, and the kernels that turn the
      * reconstruction into the next frame's reference run while the host writes the bitstream */
     CUCHECK(cudaEventRecord(e->ev1, e->st));
+    e->launches += cck_deblock(k, e->st);
+    STAGE(CC_STAGE_BORDER);
     e->launches += cck_border(k, e->st);
     STAGE(CC_STAGE_HPEL);
     e->launches += cck_hpel(k, e->st);
@@ -311,7 +314,7 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     float gpu_ms = 0;
     cudaEventElapsedTime(&gpu_ms, e->ev0, e->ev1);
     if (e->profile)
-        for (int i = 0; i < CC_STAGE_BORDER; i++) {
+        for (int i = 0; i < CC_STAGE_DEBLOCK; i++) {
             float ms = 0;
             if ((i == CC_STAGE_UPLOAD || e->pev_used[i]) && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) {
                 if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }

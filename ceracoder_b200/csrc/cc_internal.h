@@ -97,6 +97,7 @@ typedef struct {
     cc_me8 *me8;
     int part8;         /* 1: the motion search may choose P_8x8 */
     cc_mbdev *mbd;
+    uint32_t *nbrec;   /* per MB 5 words {type | t8 << 8 | nz_luma << 16, mv of quadrants 0..3}: what k_deblock needs from k_mb_encode */
     cc_mbhost *mbh;    /* device copy */
     cc_pre *pre;
     uint16_t *symlen;  /* per MB: int16 units used in its symbol slot (even; 0 for P_Skip) */
@@ -124,6 +125,7 @@ int cck_me_l0(const cc_kparams *k, cudaStream_t st);
 int cck_motion(const cc_kparams *k, cudaStream_t st);
 int cck_p_code(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);
+int cck_deblock(const cc_kparams *k, cudaStream_t st);
 int cck_pack(const cc_kparams *k, cudaStream_t st);
 
 #ifdef __cplusplus

@@ -900,6 +900,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             for (int q = 0; q < 4; q++)
                 nr.mv[q] = p8 ? (((unsigned)me8.mv[q][0] & 0xffffu) | ((unsigned)me8.mv[q][1] << 16)) : (((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
             nbl[mbx] = nr;
+            ((NbRec *)k.nbrec)[c.mb] = nr; /* for k_deblock */
         }
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
@@ -999,47 +1000,59 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     }
 }
 
-/* CTA = one slice.  Warps [0, rps) encode one macroblock row each; warps [rps, 2*rps) run the in-loop filter over the
- * same rows, each a few macroblocks behind its encode warp and 2 macroblocks behind the filter warp of the row above. */
+/* CTA = one slice, one warp per macroblock row (2-MB-lag wavefront).  The in-loop filter is a second kernel (k_deblock, same
+ * shape) launched after k_pack: nothing in the access unit depends on it, so the host writes the bitstream while the filter and
+ * the reference-finishing kernels run. */
 #ifndef CC_MB_MAXNREG
 #define CC_MB_MAXNREG 0
 #endif
 #if CC_MB_MAXNREG > 0 && !defined(CC_EMU_BUILD) /* experiments: an explicit register cap instead of the launch bound */
 #define CC_MB_BOUNDS(rps) __maxnreg__(CC_MB_MAXNREG)
 #else
-#define CC_MB_BOUNDS(rps) __launch_bounds__(2 * (rps) * 32)
+#define CC_MB_BOUNDS(rps) __launch_bounds__((rps) * 32)
 #endif
 template <int RPS> /* RPS = most rows per slice this instance serves: 4 (256 threads, no 128-register cap) or MB_MAX_RPS */
 __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
     __shared__ WarpMem wm[RPS];
-    __shared__ DbMem dbm[RPS];
-    __shared__ volatile int progress[RPS], progress2[RPS];
+    __shared__ volatile int progress[RPS];
     CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records (NbRec) */
     NbRec *nbline = (NbRec *)dsm;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const bool filt = wid >= k.rps;
-    const int w = filt ? wid - k.rps : wid;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int row0 = blockIdx.x * k.rps, row = row0 + w;
-    const bool valid = row < k.mb_h;
-    if (lane == 0 && !filt) { progress[w] = 0; progress2[w] = 0; }
+    if (lane == 0) progress[w] = 0;
     __syncthreads();
-    if (!valid) return;
-    if (!filt) {
-        encode_row(k, &wm[w], nbline, progress, w, row, row0, lane);
-    } else {
-        for (int mbx = 0; mbx < k.mb_w; mbx++) {
-            const long long t0 = k.cyc ? clock64() : 0;
-            wait_progress(progress + w, mbx + 1, lane);
-            const long long t1 = k.cyc ? clock64() : 0;
-            if (w > 0) wait_progress(progress2 + w - 1, min(mbx + 2, k.mb_w), lane);
-            const long long t2 = k.cyc ? clock64() : 0;
-            deblock_mb(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
-            __threadfence_block();
-            if (lane == 0) progress2[w] = mbx + 1;
-            if (k.cyc && lane == 0) {
-                unsigned long long *cy = k.cyc + (size_t)row * 16 + 8;
-                cy[0] += (unsigned long long)(t1 - t0); cy[1] += (unsigned long long)(t2 - t1); cy[2] += (unsigned long long)(clock64() - t2);
-            }
+    if (row >= k.mb_h) return;
+    encode_row(k, &wm[w], nbline, progress, w, row, row0, lane);
+}
+
+/* In-loop filter: CTA = one slice, one warp per macroblock row, 2 macroblocks behind the warp of the row above (H.264 8.7 is
+ * raster-ordered).  The neighbour records the encode kernel left in global memory are staged into shared memory first. */
+__global__ void __launch_bounds__(MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
+    __shared__ DbMem dbm[MB_MAX_RPS];
+    __shared__ volatile int progress2[MB_MAX_RPS];
+    CC_DYN_SMEM(dsm);
+    NbRec *nbline = (NbRec *)dsm;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int row0 = blockIdx.x * k.rps, row = row0 + w;
+    const int rows = min(k.rps, k.mb_h - row0);
+    {
+        const uint32_t *src = (const uint32_t *)k.nbrec + (size_t)row0 * k.mb_w * 5;
+        uint32_t *dst = (uint32_t *)nbline;
+        for (int i = threadIdx.x; i < rows * k.mb_w * 5; i += blockDim.x) dst[i] = src[i];
+    }
+    if (lane == 0) progress2[w] = 0;
+    __syncthreads();
+    if (row >= k.mb_h) return;
+    for (int mbx = 0; mbx < k.mb_w; mbx++) {
+        const long long t1 = k.cyc ? clock64() : 0;
+        if (w > 0) wait_progress(progress2 + w - 1, min(mbx + 2, k.mb_w), lane);
+        const long long t2 = k.cyc ? clock64() : 0;
+        deblock_mb(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
+        __threadfence_block();
+        if (lane == 0) progress2[w] = mbx + 1;
+        if (k.cyc && lane == 0) {
+            unsigned long long *cy = k.cyc + (size_t)row * 16 + 8;
+            cy[1] += (unsigned long long)(t2 - t1); cy[2] += (unsigned long long)(clock64() - t2);
         }
     }
 }
@@ -1103,8 +1116,17 @@ extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
         else cudaFuncSetAttribute(k_mb_encode<MB_MAX_RPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
     }
 #endif
-    if (k->rps <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
-    else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
+    if (k->rps <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
+    else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
+    return 1;
+}
+extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
+    const int ns = (k->mb_h + k->rps - 1) / k->rps;
+    const size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
+#ifndef CC_EMU_BUILD
+    if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
+#endif
+    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {
