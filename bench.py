@@ -111,16 +111,20 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def run_streams(encs, frames_of, n_frames, start_idx, device_frames):
-    """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes)."""
+def run_streams(encs, frames_of, n_frames, start_idx, device_frames, phase=0, warm=False):
+    """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes, ...).
+    phase: stream k runs phase*k frames ahead of stream 0 (its warm-up is that much longer), so that independent streams do
+    not sit on the same GOP phase (eight live streams do not emit their IDR frames in the same instant)."""
     tot = [0, 0, 0, 0, 0, 0, 0, 0, 0.0, 0.0, 0.0, 0.0]
     lock = threading.Lock()
     errs = []
 
     def work(k, e):
         try:  # one C call per stream per run_streams(): the frame loop itself runs in C (cc_enc_encode_sequence), off the interpreter lock
-            frames = [frames_of(k, start_idx + i) for i in range(n_frames)]
-            rates = [schedule_kbps(start_idx + i + 37 * k) for i in range(n_frames)]
+            n = n_frames + (phase * k if warm else 0)
+            first = start_idx + (0 if warm else phase * k)
+            frames = [frames_of(k, first + i) for i in range(n)]
+            rates = [schedule_kbps(first + i + 37 * k) for i in range(n)]
             s = e.encode_sequence(frames, rates, device_frame=device_frames)
             with lock:
                 tot[0] += s.frames; tot[1] += s.au_bytes; tot[2] += s.sym_bytes
@@ -254,7 +258,7 @@ def main():
         encs = make_encs()
         base = dbase if device_frames else hbase
         fo = lambda k, fi: planes(base, k, fi)  # noqa: E731
-        run_streams(encs, fo, FRAMES_PER_STEP * max(warmup, 1), 0, device_frames)  # warm-up steps (IDR + RC settle)
+        run_streams(encs, fo, FRAMES_PER_STEP * max(warmup, 1), 0, device_frames, phase=7, warm=True)  # warm-up steps (IDR + RC settle), GOP phases spread
         if profile:
             [e.set_profile(True) for e in encs]
         launches0 = sum(e.kernel_launches() for e in encs)
@@ -263,7 +267,7 @@ def main():
             dist.barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter(); ev0.record()
-        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), device_frames)
+        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), device_frames, phase=7)
         torch.cuda.synchronize(); ev1.record(); torch.cuda.synchronize()
         wall_ms = 1e3 * (time.perf_counter() - t0)
         ms = max(ev0.elapsed_time(ev1), 1e-3)

@@ -37,7 +37,7 @@ struct __align__(16) WarpMem {
     int16_t coef[27][16];  /* final levels in scan order: 0-15 luma, 16-23 chroma AC, 24 luma DC, 25/26 chroma DC */
     int16_t c4[16][16];    /* intra-4x4 candidate levels */
     int16_t dc[16];
-    uint8_t S[48];         /* intra-4x4 source array of the current block (raw edge, DC, 3-tap and 2-tap filtered edge; tools/gen_i4_table.py) */
+    uint8_t S[2][48];      /* intra-4x4 source arrays of the two blocks in flight (raw edge, DC, 3-tap and 2-tap filtered edge; tools/gen_i4_table.py) */
     uint8_t nbm[8];        /* Intra4x4PredMode of the left MB's column-3 blocks [0..3] and the top MB's row-3 blocks [4..7]; 255 = unavailable */
     uint8_t m4[16];        /* intra-4x4 candidate modes */
     uint8_t m4code[16];    /* syntax nibble per block: 8 = predicted mode, else rem_intra4x4_pred_mode */
@@ -335,7 +335,7 @@ __device__ __forceinline__ int encode_i16(const cc_kparams &k, const MbCtx &c, c
  * without the early exit; only the work differs.  Returns 1 << 30 when abandoned. */
 __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, int thresh) {
     WarpMem *m = c.m;
-    const int lane = c.lane;
+    const int lane = c.lane, half = lane >> 4, l = lane & 15;
     /* neighbour macroblocks' modes (global memory): one round trip for the whole macroblock, before the block loop */
     if (lane < 8) {
         const int top = lane >> 2, i = lane & 3;
@@ -346,69 +346,86 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
         }
         m->nbm[lane] = (uint8_t)v;
     }
-    /* this lane's mode as 16 source-array indices (lanes 9..31 never use theirs) */
+    /* this lane's mode as 16 source-array indices (lanes 9..15 of a half never use theirs) */
     uint32_t sx[4];
 #pragma unroll
-    for (int r = 0; r < 4; r++) sx[r] = g_i4idx[lane & 15][r];
-    const int md = lane < 9 ? lane : 2;
+    for (int r = 0; r < 4; r++) sx[r] = g_i4idx[l][r];
+    const int md = l < 9 ? l : 2;
+    uint8_t *S = m->S[half];
     int cost = 24 * c.lambda;
     __syncwarp();
-    for (int blk = 0; blk < 16; blk++) {
-        const int bx = c_blk_x[blk], by = c_blk_y[blk];
-        const int has_top = by > 0 || c.T, has_left = bx > 0 || c.L;
+    /* The sixteen blocks depend on their left, top, top-left and top-right neighbours only, so blocks with equal bx + 2*by are
+     * independent: 10 steps instead of 16, the two half-warps taking one block each (the predictors available to a block still
+     * follow decoding order, H.264 6.4.11.4).  Costs add up in a different order; their sum and every decision are the same. */
+    for (int t = 0; t < 10; t++) {
+        /* half 0: the block of the step with the smaller by; half 1: the one a block row further down, if any */
+        const int by0 = t >= 2 ? (t - 2) >> 1 : 0; /* smallest by with 0 <= t - 2*by <= 3 */
+        const int by = by0 + half, bx = t - 2 * by;
+        const bool act = by < 4 && bx >= 0 && bx < 4;
+        const int bxs = act ? bx : 0, bys = act ? by : 0; /* safe coordinates for the idle half */
+        const int blk = c_blk_of[bys * 4 + bxs];
+        const int has_top = bys > 0 || c.T, has_left = bxs > 0 || c.L;
         int has_tr;
-        if (by == 0) has_tr = bx < 3 ? c.T : c.TR;
-        else has_tr = !(bx == 3 || blk == 3 || blk == 11 || blk == 7 || blk == 13 || blk == 15);
-        /* edge sample of this lane (E index = lane: left3..left0, top-left, top0..7), its filtered forms, the DC value */
+        if (bys == 0) has_tr = bxs < 3 ? c.T : c.TR;
+        else has_tr = !(bxs == 3 || blk == 3 || blk == 11 || blk == 7 || blk == 13 || blk == 15);
+        /* edge sample of this lane (E index = l: left3..left0, top-left, top0..7), its filtered forms, the DC value */
         int e = 0;
-        if (lane < 13) {
-            if (lane < 4) e = m->tile[1 + by * 4 + (3 - lane)][3 + bx * 4];
-            else if (lane == 4) e = m->tile[by * 4][3 + bx * 4];
-            else { const int i = lane - 5; e = m->tile[by * 4][4 + bx * 4 + ((i < 4 || has_tr) ? i : 3)]; }
+        if (l < 13) {
+            if (l < 4) e = m->tile[1 + bys * 4 + (3 - l)][3 + bxs * 4];
+            else if (l == 4) e = m->tile[bys * 4][3 + bxs * 4];
+            else { const int i = l - 5; e = m->tile[bys * 4][4 + bxs * 4 + ((i < 4 || has_tr) ? i : 3)]; }
         }
         {
-            int a = __shfl_up_sync(FULL, e, 1), cdn = __shfl_down_sync(FULL, e, 1);
-            if (lane == 0) a = e;
-            if (lane == 12) cdn = e;
-            const int sl = __reduce_add_sync(FULL, lane < 4 ? e : 0), st = __reduce_add_sync(FULL, (lane >= 5 && lane < 9) ? e : 0);
-            if (lane < 13) {
-                m->S[lane] = (uint8_t)e;
-                m->S[16 + lane] = (uint8_t)((a + 2 * e + cdn + 2) >> 2);
-                if (lane < 12) m->S[32 + lane] = (uint8_t)((e + cdn + 1) >> 1);
-            } else if (lane == 13)
-                m->S[13] = (uint8_t)((has_top && has_left) ? (st + sl + 4) >> 3 : (has_top ? (st + 2) >> 2 : (has_left ? (sl + 2) >> 2 : 128)));
+            int a = __shfl_up_sync(FULL, e, 1, 16), cdn = __shfl_down_sync(FULL, e, 1, 16);
+            if (l == 0) a = e;
+            if (l == 12) cdn = e;
+            int sums = (l < 4 ? e : 0) | ((l >= 5 && l < 9 ? e : 0) << 16); /* left sum | top sum << 16, over the half-warp */
+#pragma unroll
+            for (int sft = 1; sft < 16; sft <<= 1) sums += __shfl_xor_sync(FULL, sums, sft);
+            const int sl = sums & 0xffff, st = sums >> 16;
+            if (l < 13) {
+                S[l] = (uint8_t)e;
+                S[16 + l] = (uint8_t)((a + 2 * e + cdn + 2) >> 2);
+                if (l < 12) S[32 + l] = (uint8_t)((e + cdn + 1) >> 1);
+            } else if (l == 13)
+                S[13] = (uint8_t)((has_top && has_left) ? (st + sl + 4) >> 3 : (has_top ? (st + 2) >> 2 : (has_left ? (sl + 2) >> 2 : 128)));
         }
         /* predicted mode, H.264 8.3.1.1 */
         int mA, mB;
-        if (bx > 0) mA = m->m4[c_blk_of[by * 4 + bx - 1]];
-        else { mA = m->nbm[by]; if (mA == 255) mA = -1; }
-        if (by > 0) mB = m->m4[c_blk_of[(by - 1) * 4 + bx]];
-        else { mB = m->nbm[4 + bx]; if (mB == 255) mB = -1; }
+        if (bxs > 0) mA = m->m4[c_blk_of[bys * 4 + bxs - 1]];
+        else { mA = m->nbm[bys]; if (mA == 255) mA = -1; }
+        if (bys > 0) mB = m->m4[c_blk_of[(bys - 1) * 4 + bxs]];
+        else { mB = m->nbm[4 + bxs]; if (mB == 255) mB = -1; }
         const int pm = (mA < 0 || mB < 0) ? 2 : min(mA, mB);
         __syncwarp();
         uint32_t cw[4], pw[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int r = 0; r < 4; r++) cw[r] = m->curY[(by * 4 + r) * 4 + bx];
+        for (int r = 0; r < 4; r++) cw[r] = m->curY[(bys * 4 + r) * 4 + bxs];
         unsigned key = 0xffffffffu;
         {
-            const bool ok = lane < 9 && (md == 2 || ((md == 0 || md == 3 || md == 7) && has_top) || ((md == 1 || md == 8) && has_left) ||
-                                         ((md == 4 || md == 5 || md == 6) && has_top && has_left));
+            const bool ok = l < 9 && (md == 2 || ((md == 0 || md == 3 || md == 7) && has_top) || ((md == 1 || md == 8) && has_left) ||
+                                      ((md == 4 || md == 5 || md == 6) && has_top && has_left));
             if (ok) {
 #pragma unroll
                 for (int r = 0; r < 4; r++)
-                    pw[r] = (uint32_t)m->S[sx[r] & 255u] | ((uint32_t)m->S[(sx[r] >> 8) & 255u] << 8) | ((uint32_t)m->S[(sx[r] >> 16) & 255u] << 16) |
-                            ((uint32_t)m->S[sx[r] >> 24] << 24);
+                    pw[r] = (uint32_t)S[sx[r] & 255u] | ((uint32_t)S[(sx[r] >> 8) & 255u] << 8) | ((uint32_t)S[(sx[r] >> 16) & 255u] << 16) |
+                            ((uint32_t)S[sx[r] >> 24] << 24);
                 int satd = cc_satd4x4_words(cw, pw);
                 key = ((unsigned)(satd + c.lambda * (md == pm ? 1 : 4)) << 4) | (unsigned)md;
             }
         }
-        const unsigned bk = __reduce_min_sync(FULL, key);
+        unsigned bk = key; /* minimum over the half-warp */
+#pragma unroll
+        for (int sft = 1; sft < 16; sft <<= 1) bk = min(bk, __shfl_xor_sync(FULL, bk, sft));
         const int bm = (int)(bk & 15u);
-        cost += (int)(bk >> 4);
+        {
+            const int mine = act ? (int)(bk >> 4) : 0;
+            cost += mine + __shfl_xor_sync(FULL, mine, 16);
+        }
         if (cost >= thresh) return 1 << 30; /* uniform across the warp */
 #pragma unroll
-        for (int r = 0; r < 4; r++) pw[r] = __shfl_sync(FULL, pw[r], bm);
-        /* every lane runs the block's transform chain on identical data; lane 0 publishes */
+        for (int r = 0; r < 4; r++) pw[r] = __shfl_sync(FULL, pw[r], bm, 16);
+        /* every lane of the half runs the block's transform chain on identical data; its lane 0 publishes */
         int d[16], z[16];
         dct4x4_res(cw, pw, d);
         const int nnz = quant4x4(d, k.qmf[0], k.qbias[0], false);
@@ -419,7 +436,7 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
 #pragma unroll
             for (int r = 0; r < 4; r++) ow[r] = pw[r];
         }
-        if (lane == 0) {
+        if (l == 0 && act) {
             store_levels(m->c4[blk], z);
 #pragma unroll
             for (int r = 0; r < 4; r++) *(uint32_t *)&m->tile[1 + by * 4 + r][4 + bx * 4] = ow[r];
