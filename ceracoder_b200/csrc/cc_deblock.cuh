@@ -100,27 +100,33 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
     }
 }
 
-/* One macroblock.  L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
+/* One macroblock, one colour component group per warp: PL = 0 luma, PL = 1 both chroma planes (the two run in different warps
+ * of the slice's CTA as independent wavefronts — in one warp their different code paths would be serialised).
+ * L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
+template <int PL>
 __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
-    const bool luma = lane < 16;
+    const bool luma = PL == 0, act = lane < 16; /* lanes 16-31 only help with loads and stores */
     const int li = lane & 15;                 /* luma line, or chroma: plane = li >> 3, line = li & 7 */
     const int g = luma ? li >> 2 : (li & 7) >> 1;
     const int cpl = li >> 3, ci = li & 7;
     /* ---- boundary strengths first: most macroblocks of a P frame have nothing to filter ---- */
     const NbRec nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
-    uint32_t ly[4], lc[3];
+    uint32_t ly[4] = {0, 0, 0, 0}, lc[3] = {0, 0, 0};
+    if (luma) {
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
-        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-        ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
-    }
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
+        }
+    } else {
 #pragma unroll
-    for (int it = 0; it < 3; it++) {
-        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-        lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+        }
     }
     const uint32_t q0 = nq.x;
     int bsv[4], bsh[4], any = 0;
@@ -131,19 +137,22 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
         bsv[ed] = (ed == 0 && !L) ? 0 : db_bs(ed == 0 ? nl : nq, db_blk(blk_row + pe), nq, db_blk(blk_row + ed), ed == 0);
         bsh[ed] = (ed == 0 && !T) ? 0 : db_bs(ed == 0 ? nt : nq, db_blk(pe * 4 + g), nq, db_blk(ed * 4 + g), ed == 0);
         if ((ed & 1) && ((q0 >> 8) & 1u)) bsv[ed] = bsh[ed] = 0; /* transform_size_8x8_flag: edges 1 and 3 are not transform edges */
-        any |= bsv[ed] | bsh[ed];
+        if (luma || !(ed & 1)) any |= bsv[ed] | bsh[ed]; /* chroma filters on the strengths of luma edges 0 and 2 only */
     }
-    if (!__any_sync(FULL, any)) return;
+    if (!__any_sync(FULL, act && any)) return;
     /* ---- stage ---- */
+    if (luma) {
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
-        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-        if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
-    }
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
+        }
+    } else {
 #pragma unroll
-    for (int it = 0; it < 3; it++) {
-        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-        if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
+        }
     }
     __syncwarp();
     const int alpha = c_alpha[luma ? qp : qpc], beta = c_beta[luma ? qp : qpc];
@@ -152,7 +161,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
     for (int i = 0; i < 3; i++) tc0[i] = c_tc0[luma ? qp : qpc][i];
 
     /* ---- vertical edges: one lane = one pixel row ---- */
-    {
+    if (act) {
         const int *bs = bsv;
         const int first = L ? 0 : 1;
         if (luma) {
@@ -181,7 +190,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
     }
     __syncwarp();
     /* ---- horizontal edges: one lane = one pixel column ---- */
-    {
+    if (act) {
         const int *bs = bsh;
         const int first = T ? 0 : 1;
         if (luma) {
@@ -202,17 +211,20 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
     }
     __syncwarp();
     /* ---- store: own macroblock, the 4 columns left of it (if L), the 4 rows above it (if T) ---- */
+    if (luma) {
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
-        const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-        const bool ok = idx < 100 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
-        if (ok) *(uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) = *(const uint32_t *)&db->Y[r][4 * cw];
-    }
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            const bool ok = idx < 100 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
+            if (ok) *(uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) = *(const uint32_t *)&db->Y[r][4 * cw];
+        }
+    } else {
 #pragma unroll
-    for (int it = 0; it < 3; it++) {
-        const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-        const bool ok = idx < 72 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
-        if (ok) *(uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) = *(const uint32_t *)&db->C[pl][r][4 * cw];
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            const bool ok = idx < 72 && (r >= 4 ? (cw > 0 || L) : (T && cw > 0));
+            if (ok) *(uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) = *(const uint32_t *)&db->C[pl][r][4 * cw];
+        }
     }
     __syncwarp();
 }

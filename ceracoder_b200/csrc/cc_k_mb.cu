@@ -1042,14 +1042,16 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
     encode_row(k, &wm[w], nbline, progress, w, row, row0, lane);
 }
 
-/* In-loop filter: CTA = one slice, one warp per macroblock row, 2 macroblocks behind the warp of the row above (H.264 8.7 is
- * raster-ordered).  The neighbour records the encode kernel left in global memory are staged into shared memory first. */
-__global__ void __launch_bounds__(MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
+/* In-loop filter: CTA = one slice; per macroblock row one luma warp and one chroma warp, each 2 macroblocks behind the warp of
+ * the same kind in the row above (H.264 8.7 is raster-ordered; luma and chroma are independent wavefronts).  The neighbour
+ * records the encode kernel left in global memory are staged into shared memory first. */
+__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
-    __shared__ volatile int progress2[MB_MAX_RPS];
+    __shared__ volatile int progress2[2][MB_MAX_RPS];
     CC_DYN_SMEM(dsm);
     NbRec *nbline = (NbRec *)dsm;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int pl = wid >= k.rps, w = pl ? wid - k.rps : wid; /* warps [0, rps): luma rows, [rps, 2 rps): chroma rows */
     const int row0 = blockIdx.x * k.rps, row = row0 + w;
     const int rows = min(k.rps, k.mb_h - row0);
     {
@@ -1057,17 +1059,19 @@ __global__ void __launch_bounds__(MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
         uint32_t *dst = (uint32_t *)nbline;
         for (int i = threadIdx.x; i < rows * k.mb_w * 5; i += blockDim.x) dst[i] = src[i];
     }
-    if (lane == 0) progress2[w] = 0;
+    if (lane == 0) progress2[pl][w] = 0;
     __syncthreads();
     if (row >= k.mb_h) return;
+    volatile int *prog = progress2[pl];
     for (int mbx = 0; mbx < k.mb_w; mbx++) {
         const long long t1 = k.cyc ? clock64() : 0;
-        if (w > 0) wait_progress(progress2 + w - 1, min(mbx + 2, k.mb_w), lane);
+        if (w > 0) wait_progress(prog + w - 1, min(mbx + 2, k.mb_w), lane);
         const long long t2 = k.cyc ? clock64() : 0;
-        deblock_mb(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
+        if (pl) deblock_mb<1>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
+        else deblock_mb<0>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
         __threadfence_block();
-        if (lane == 0) progress2[w] = mbx + 1;
-        if (k.cyc && lane == 0) {
+        if (lane == 0) prog[w] = mbx + 1;
+        if (k.cyc && lane == 0 && !pl) {
             unsigned long long *cy = k.cyc + (size_t)row * 16 + 8;
             cy[1] += (unsigned long long)(t2 - t1); cy[2] += (unsigned long long)(clock64() - t2);
         }
@@ -1143,7 +1147,7 @@ extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
 #ifndef CC_EMU_BUILD
     if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
 #endif
-    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
+    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {
