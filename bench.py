@@ -189,7 +189,7 @@ def main_reference(args, rank, world):
     from ceracoder_b200.synth import make_source
     src = make_source("pan", W, H)
     pool = [src.frame(i) for i in range(8)]
-    sample = 3  # P frames per step
+    sample = FRAMES_PER_STEP  # P frames per step: one stream's share of a step of the CUDA arm
     for _ in range(args.warmup):
         cpu_baseline(pool, 1)
     t0 = time.perf_counter()
@@ -289,6 +289,33 @@ def main():
     clocks = sampler.stop()
     r_e2e = timed(False, args.steps, args.warmup)
 
+    def quality_leg(n_frames=360):
+        """One 1080p60 stream, frame by frame through the public call, under a 12 -> 2 -> 12 Mbps square wave (2 s per level):
+        Y-PSNR of the reconstruction against the source (the decoder reproduces the reconstruction bit-exactly — parity
+        tests) and the bitrate error over 1 s windows.  Untimed."""
+        enc = CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, device=local, lib=L, partitions=bool(args.partitions))
+        bits, targ, psnr = [], [], []
+        for i in range(n_frames):
+            kb = 12000 if (i // (2 * FPS)) % 2 == 0 else 2000
+            enc.set_property("bitrate", kb)
+            y, u, v = pool[pingpong(i, POOL)]
+            au = enc.encode(y, u, v)
+            bits.append(8 * len(au)); targ.append(kb * 1000.0 / FPS)
+            if i % 12 == 11:
+                ry = enc.recon()[0][:H, :W]
+                mse = float(((ry.astype(np.float32) - y.astype(np.float32)) ** 2).mean())
+                psnr.append((kb, 10 * np.log10(255.0 ** 2 / max(mse, 1e-9))))
+        enc.close()
+        b, t = np.array(bits, float), np.array(targ, float)
+        err = [abs(b[i:i + FPS].sum() - t[i:i + FPS].sum()) / t[i:i + FPS].sum() for i in range(0, n_frames - FPS + 1, FPS // 4)]
+        return {"frames": n_frames, "schedule": "square wave 12 <-> 2 Mbps, 2 s per level, 1080p60, one stream",
+                "achieved_kbps": float(b.sum() / (n_frames / FPS) / 1e3), "target_kbps": float(t.sum() / (n_frames / FPS) / 1e3),
+                "bitrate_error_1s_windows": {"mean": float(np.mean(err)), "p95": float(np.percentile(err, 95))},
+                "y_psnr_db": {"at_12mbps": float(np.mean([p for k, p in psnr if k == 12000])), "at_2mbps": float(np.mean([p for k, p in psnr if k == 2000]))},
+                "vs_x264enc": None, "note": "x264enc / libx264 are not installed on this box: the PSNR delta against x264 veryfast was not measured"}
+
+    quality = quality_leg() if rank == 0 and not args.no_cpu_baseline else None
+
     dev = torch.device("cuda", local)
     f_dev, ms_dev = aggregate(r_dev["frames"], r_dev["ms"], world, device=dev)
     f_e2e, ms_e2e = aggregate(r_e2e["frames"], r_e2e["ms"], world, device=dev)
@@ -330,7 +357,7 @@ def main():
     cpu = None
     if not args.no_cpu_baseline:
         t0 = time.perf_counter()
-        n = 4
+        n = 160  # ~10 s of host work
         fps_cpu = cpu_baseline(pool, n)
         cpu = {"value": fps_cpu, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
                "sample": f"{n} P frames of one 1080p stream at QP 30 with the oracle (OpenMP, all host threads), {time.perf_counter() - t0:.1f} s"}
@@ -343,7 +370,7 @@ def main():
                        "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu, "quality": quality,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
             "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"][:5]])),
             "host_ms_per_frame": dict(zip(("submit_api", "wait_device", "cavlc_nal", "device_frame_latency"), [round(v / max(r_e2e["frames"], 1), 4) for v in r_e2e["mbstats"][5:9]])),
