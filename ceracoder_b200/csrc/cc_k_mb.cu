@@ -622,15 +622,55 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
 }
 
 /* does the macroblock coded at (mvx,mvy) leave nothing after quantisation + decimation?  (P_Skip test) */
+/* One pass: lanes 0-15 take the luma blocks, lanes 16-23 the chroma blocks (same arithmetic as inter_luma / encode_chroma in
+ * probe mode; the two only differ in quantiser tables, the DC handling of chroma and the decimation rule). */
 __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
     mc_luma16(k, c, mvx, mvy);
     mc_chroma8(k, c, mvx, mvy);
     __syncwarp();
-    unsigned nz;
-    const bool zl = inter_luma(k, c, true, &nz) == 0;
-    const bool zc = encode_chroma(k, c, false, true) == 0;
+    const bool chroma = lane >= 16;
+    const int pl = (lane >> 2) & 1, b = chroma ? (lane & 3) : lane;
+    const int bx = chroma ? (b & 1) : c_blk_x[b], by = chroma ? (b >> 1) : c_blk_y[b];
+    uint32_t cw[4], pw[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        cw[r] = chroma ? m->curC[pl][(by * 4 + r) * 2 + bx] : m->curY[(by * 4 + r) * 4 + bx];
+        pw[r] = chroma ? m->predC[pl][(by * 4 + r) * 2 + bx] : m->predY[(by * 4 + r) * 4 + bx];
+    }
+    uint16_t mf[3], bias[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) { mf[i] = chroma ? k.qmf[3][i] : k.qmf[1][i]; bias[i] = chroma ? k.qbias[3][i] : k.qbias[1][i]; }
+    int d[16], sc[17], z[16];
+    dct4x4_res(cw, pw, d);
+    const int dc = d[0];
+    int nnz = quant4x4(d, mf, bias, false);
+    if (chroma) { nnz -= d[0] != 0; d[0] = 0; } /* chroma AC blocks: the DC goes through the 2x2 transform below */
+    to_scan(d, sc, false);
+    sc[16] = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) z[i] = chroma ? sc[i + 1] : sc[i]; /* AC-only scan for chroma: the run lengths start at position 1 */
+    const int score = decimate_score(z);
+    int s8 = score + __shfl_xor_sync(FULL, score, 1);
+    s8 += __shfl_xor_sync(FULL, s8, 2);              /* luma: the 8x8 block's score; chroma: the plane's */
+    int tot = s8 + __shfl_xor_sync(FULL, s8, 4);
+    tot += __shfl_xor_sync(FULL, tot, 8);            /* luma: the macroblock's score (lanes 0-15) */
+    int nac = nnz > 0;
+    nac |= __shfl_xor_sync(FULL, nac, 1);
+    nac |= __shfl_xor_sync(FULL, nac, 2);
+    const int d0 = __shfl_sync(FULL, dc, 0, 4), d1 = __shfl_sync(FULL, dc, 1, 4), d2 = __shfl_sync(FULL, dc, 2, 4), d3 = __shfl_sync(FULL, dc, 3, 4);
+    bool nz;
+    if (!chroma) nz = nnz > 0 && !(tot < 6 || s8 < 4);
+    else {
+        const int a = d0 + d1, bb = d0 - d1, cc = d2 + d3, e = d2 - d3;
+        const int ndc = (quant_one(a + cc, mf[0] >> 1, bias[0] << 1) != 0) | (quant_one(bb + e, mf[0] >> 1, bias[0] << 1) != 0) |
+                        (quant_one(a - cc, mf[0] >> 1, bias[0] << 1) != 0) | (quant_one(bb - e, mf[0] >> 1, bias[0] << 1) != 0);
+        nz = (nac && s8 >= 7) || ndc;
+    }
+    const bool any = __ballot_sync(FULL, lane < 24 && nz) != 0;
     __syncwarp();
-    return zl && zc;
+    return !any;
 }
 
 /* Two P_Skip tests in one pass (the pre-pass probes its two likeliest skip vectors): prediction A in predY / predC, prediction B
@@ -898,26 +938,29 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 }
             }
         }
-        if (lane == 0) {
-            cc_mbdev d;
-            d.type = (uint8_t)type; d.pad0 = (uint8_t)t8; d.nz_luma = (uint16_t)(type == CC_MB_PSKIP ? 0 : nzmask);
-            d.mv[0] = (int16_t)mvx; d.mv[1] = (int16_t)mvy;
-#pragma unroll
-            for (int i = 0; i < 16; i++) d.i4_mode[i] = type == CC_MB_I4 ? m->m4[i] : 2;
-            k.mbd[c.mb] = d;
-            cc_mbhost hh;
+        { /* publish the macroblock's records: every value is warp-uniform, lane i stores word i of the list below in one go */
             const int p8 = type == CC_MB_P16 && part;
-            hh.type = (uint8_t)type; hh.modes = (uint8_t)(mode16 | (chroma_mode << 2)); hh.cbp = (uint8_t)cbp; hh.t8 = (uint8_t)(t8 | (p8 << 1));
-            hh.mvd[0] = (int16_t)mvdx; hh.mvd[1] = (int16_t)mvdy;
-            k.mbh[c.mb] = hh;
-            k.symlen[c.mb] = (uint16_t)off;
-            NbRec nr;
-            nr.x = (unsigned)type | ((unsigned)t8 << 8) | ((unsigned)d.nz_luma << 16);
+            const uint32_t nz16 = type == CC_MB_PSKIP ? 0u : (nzmask & 0xffffu);
+            const uint32_t w_hdr = (uint32_t)type | ((uint32_t)t8 << 8) | (nz16 << 16);
+            const uint32_t w_mv = ((uint32_t)mvx & 0xffffu) | ((uint32_t)mvy << 16);
+            uint32_t *mbd = (uint32_t *)(k.mbd + c.mb), *nbg = k.nbrec + (size_t)c.mb * 5, *nbs = (uint32_t *)(nbl + mbx);
+            if (lane < 2) {        /* cc_mbdev words 0,1: type | t8 | nz_luma, mv */
+                mbd[lane] = lane ? w_mv : w_hdr;
+            } else if (lane < 6) { /* cc_mbdev words 2..5: Intra4x4PredMode of the 16 blocks (DC for every other type) */
+                mbd[lane] = type == CC_MB_I4 ? *(const uint32_t *)&m->m4[4 * (lane - 2)] : 0x02020202u;
+            } else if (lane < 16) { /* NbRec {hdr, mv of quadrants 0..3}: global copy for k_deblock (6..10), shared-memory line (11..15) */
+                const int i = lane < 11 ? lane - 6 : lane - 11;
+                uint32_t v = w_hdr;
+                if (i > 0) {
+                    v = w_mv;
 #pragma unroll
-            for (int q = 0; q < 4; q++)
-                nr.mv[q] = p8 ? (((unsigned)me8.mv[q][0] & 0xffffu) | ((unsigned)me8.mv[q][1] << 16)) : (((unsigned)mvx & 0xffffu) | ((unsigned)mvy << 16));
-            nbl[mbx] = nr;
-            ((NbRec *)k.nbrec)[c.mb] = nr; /* for k_deblock */
+                    for (int q = 0; q < 4; q++) if (p8 && i == q + 1) v = ((uint32_t)me8.mv[q][0] & 0xffffu) | ((uint32_t)me8.mv[q][1] << 16);
+                }
+                (lane < 11 ? nbg : nbs)[i] = v;
+            } else if (lane == 16) { /* cc_mbhost */
+                const uint32_t h0 = (uint32_t)type | ((uint32_t)(mode16 | (chroma_mode << 2)) << 8) | ((uint32_t)cbp << 16) | ((uint32_t)(t8 | (p8 << 1)) << 24);
+                *(uint2 *)(k.mbh + c.mb) = make_uint2(h0, ((uint32_t)mvdx & 0xffffu) | ((uint32_t)mvdy << 16));
+            } else if (lane == 17) k.symlen[c.mb] = (uint16_t)off;
         }
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
