@@ -94,7 +94,7 @@ if __name__ == "__main__":
     os.makedirs(P, exist_ok=True)
     launches()
     traffic = {}
-    for kn in ("k_mb_encode", "k_p_code", "k_me_l1", "k_me_l0"):
+    for kn in ("k_mb_encode", "k_deblock", "k_p_code", "k_me_l1", "k_me_l0"):
         kernel(kn, traffic)
     json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
     for f in (f"{tag}_cycles.err",):
