@@ -170,7 +170,8 @@ def int_peaks(L):
 def cpu_baseline(pool, n_frames, rps=4):
     """The oracle (CPU port of the same algorithm, OpenMP over slices/MBs) timed on this box's host cores."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from oracle_lib import OracleEncoder
+    from oracle_lib import OracleEncoder, lib as oracle_lib_handle
+    oracle_lib_handle().ref_set_threads(os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1; the baseline uses every host thread
     enc = OracleEncoder(W, H, FPS, rps)
     y, u, v = pool[0]
     enc.encode(y, u, v, True, 30)  # IDR outside the timed sample, like a warm stream

@@ -165,8 +165,13 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     return CC_OK;
 }
 
+/* every entry point may be called from a thread whose current device is another GPU (one process driving several devices,
+ * or worker threads created after cc_enc_open): bind the handle's device first */
+static int bind_device(const cc_enc *e) { return cudaSetDevice(e->p.device) == cudaSuccess ? CC_OK : CC_ERR_CUDA; }
+
 void cc_enc_close(cc_enc *e) {
     if (!e) return;
+    bind_device(e);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->k.cyc && e->frame_idx > 0) { /* CC_DEBUG_CYCLES=1: where the wavefront kernel's warps spent their cycles */
         size_t n = (size_t)e->k.mb_h * 16;
@@ -230,6 +235,7 @@ static void set_quant(cc_kparams *k) {
 int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (!e || !in || !in->plane[0] || !in->plane[1]) return CC_ERR_PARAM;
     if (e->inflight) return CC_ERR_STATE;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     const double t_submit = now_ms();
     cc_kparams *k = &e->k;
     const int nv12 = e->p.format == CC_FMT_NV12;
@@ -306,6 +312,7 @@ static int is_idr_prof(const cc_enc *e) { return e->cur_is_idr; }
 int cc_enc_collect(cc_enc *e, cc_packet *out) {
     if (!e || !out) return CC_ERR_PARAM;
     if (!e->inflight) return CC_ERR_STATE;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     cc_kparams *k = &e->k;
     const double t_wait = now_ms();
     CUCHECK(cudaEventSynchronize(e->ev1));
@@ -397,6 +404,7 @@ int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate
 /* ---- test hooks ----------------------------------------------------------------------------------- */
 int cc_enc_get_recon(cc_enc *e, uint8_t *y, uint8_t *u, uint8_t *v) {
     if (!e || !y || !u || !v || e->inflight) return CC_ERR_PARAM;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     cc_kparams *k = &e->k; /* after submit the newest reconstruction is k->ref */
     CUCHECK(cudaStreamSynchronize(e->st));
     CUCHECK(cudaMemcpy2D(y, (size_t)k->W, k->ref[0], (size_t)k->sy, (size_t)k->W, (size_t)k->H, cudaMemcpyDeviceToHost));
@@ -406,6 +414,7 @@ int cc_enc_get_recon(cc_enc *e, uint8_t *y, uint8_t *u, uint8_t *v) {
 }
 int cc_enc_get_me(cc_enc *e, int16_t *mv4, int32_t *satd) {
     if (!e || !mv4 || !satd || e->inflight) return CC_ERR_PARAM;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     const int nmb = e->k.mb_w * e->k.mb_h;
     cc_me *tmp = (cc_me *)malloc(sizeof(cc_me) * nmb);
     if (!tmp) return CC_ERR_NOMEM;
@@ -419,6 +428,7 @@ int cc_enc_get_me(cc_enc *e, int16_t *mv4, int32_t *satd) {
 }
 int cc_enc_get_me8(cc_enc *e, int16_t *mv8, int32_t *satd4, uint8_t *part) {
     if (!e || !mv8 || !satd4 || !part || e->inflight) return CC_ERR_PARAM;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     const int nmb = e->k.mb_w * e->k.mb_h;
     cc_me *t16 = (cc_me *)malloc(sizeof(cc_me) * nmb);
     cc_me8 *t8 = (cc_me8 *)malloc(sizeof(cc_me8) * nmb);
@@ -433,6 +443,7 @@ int cc_enc_get_me8(cc_enc *e, int16_t *mv8, int32_t *satd4, uint8_t *part) {
 }
 int cc_enc_get_mbinfo(cc_enc *e, uint8_t *dst8) {
     if (!e || !dst8 || e->inflight) return CC_ERR_PARAM;
+    if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     CUCHECK(cudaMemcpy(dst8, e->k.mbh, sizeof(cc_mbhost) * e->k.mb_w * e->k.mb_h, cudaMemcpyDeviceToHost));
     return CC_OK;
 }

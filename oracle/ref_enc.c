@@ -50,6 +50,12 @@ void ref_enc_close(ref_enc *e) {
     free(e);
 }
 void ref_enc_set_partitions(ref_enc *e, int on) { e->part8 = on != 0; }
+#ifdef _OPENMP
+#include <omp.h>
+void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); } /* launchers such as torchrun export OMP_NUM_THREADS=1 */
+#else
+void ref_set_threads(int n) { (void)n; }
+#endif
 int ref_enc_mb_w(const ref_enc *e) { return e->mb_w; }
 int ref_enc_mb_h(const ref_enc *e) { return e->mb_h; }
 const ref_mb_info *ref_enc_mb_info(const ref_enc *e) { return e->mb; }

@@ -95,6 +95,8 @@ ref_enc *ref_enc_open(int width, int height, int fps_n, int fps_d, int rows_per_
 void ref_enc_close(ref_enc *e);
 /* enable (1) / disable (0) P_8x8 partitions; ref_enc_open leaves them on.  Mirrors cc_enc_params.partitions of the product. */
 void ref_enc_set_partitions(ref_enc *e, int on);
+/* OpenMP threads the slice / macroblock loops use (0 = leave as is) */
+void ref_set_threads(int n);
 /* encode one frame (I420, arbitrary strides). is_idr: 1 = IDR, 0 = P. qp 10..51.
  * returns AU size in bytes (Annex-B, SPS/PPS prepended on IDR), <0 on error */
 int ref_enc_encode(ref_enc *e, const uint8_t *y, int sy, const uint8_t *u, int su,

@@ -37,6 +37,7 @@ def lib():
         L.ref_enc_open.argtypes = [C.c_int] * 5
         L.ref_enc_close.argtypes = [C.c_void_p]
         L.ref_enc_set_partitions.argtypes = [C.c_void_p, C.c_int]
+        L.ref_set_threads.argtypes = [C.c_int]
         L.ref_enc_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.ref_enc_get_recon.argtypes = [C.c_void_p] * 4
         L.ref_enc_mb_info.restype = C.POINTER(MbInfo)
