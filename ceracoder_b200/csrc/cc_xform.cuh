@@ -34,9 +34,11 @@ __device__ __forceinline__ void dct4x4_res(const uint32_t c[4], const uint32_t p
         d[i] = s03 + s12; d[4 + i] = 2 * m03 + m12; d[8 + i] = s03 - s12; d[12 + i] = m03 - 2 * m12;
     }
 }
+/* [EXT] x264 quant: sign(c) * min(((f + |c|) * mf) >> 16, 2047) — branch-free: magnitude once, sign restored by xor / subtract */
 __device__ __forceinline__ int quant_one(int c, int mf, int f) {
-    int l = c > 0 ? ((f + c) * mf) >> 16 : -(((f - c) * mf) >> 16);
-    return l > 2047 ? 2047 : (l < -2047 ? -2047 : l);
+    const int s = c >> 31;                       /* 0 or -1 */
+    const int l = min(((f + cc_iabs(c)) * mf) >> 16, 2047);
+    return (l ^ s) - s;
 }
 /* quantise raster coefficients in place; returns number of non-zero levels (skipping position 0 if ac_only) */
 __device__ __forceinline__ int quant4x4(int d[16], const uint16_t mf[3], const uint16_t bias[3], bool ac_only) {
@@ -53,12 +55,21 @@ __device__ __forceinline__ int quant4x4(int d[16], const uint16_t mf[3], const u
 /* H.264 8.5.12.1: level scaling with a flat matrix, in place */
 __device__ __forceinline__ void dequant4x4(int d[16], int qp) {
     const int qb = qp / 6 - 4, r = qp % 6;
-    const int v0 = c_dequant_v[r][0] * 16, v1 = c_dequant_v[r][1] * 16, v2 = c_dequant_v[r][2] * 16;
+    int v0 = c_dequant_v[r][0] * 16, v1 = c_dequant_v[r][1] * 16, v2 = c_dequant_v[r][2] * 16;
+    if (qb >= 0) { /* qp >= 24 (uniform): the shift folds into the scale, one multiply per coefficient */
+        v0 <<= qb; v1 <<= qb; v2 <<= qb;
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const int cls = ((i & 1) && ((i >> 2) & 1)) ? 1 : (((i & 1) || ((i >> 2) & 1)) ? 2 : 0);
-        const int ls = cls == 0 ? v0 : (cls == 1 ? v1 : v2);
-        d[i] = qb >= 0 ? (d[i] * ls) << qb : (d[i] * ls + (1 << (-qb - 1))) >> -qb;
+        for (int i = 0; i < 16; i++) {
+            const int cls = ((i & 1) && ((i >> 2) & 1)) ? 1 : (((i & 1) || ((i >> 2) & 1)) ? 2 : 0);
+            d[i] *= cls == 0 ? v0 : (cls == 1 ? v1 : v2);
+        }
+    } else {
+        const int sh = -qb, rnd = 1 << (sh - 1);
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int cls = ((i & 1) && ((i >> 2) & 1)) ? 1 : (((i & 1) || ((i >> 2) & 1)) ? 2 : 0);
+            d[i] = (d[i] * (cls == 0 ? v0 : (cls == 1 ? v1 : v2)) + rnd) >> sh;
+        }
     }
 }
 /* H.264 8.5.12.2 + 8.5.14: inverse transform, add prediction, clip */
