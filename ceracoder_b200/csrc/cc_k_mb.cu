@@ -1137,8 +1137,18 @@ __global__ void k_pack(cc_kparams k) {
         return;
     }
     const int row = blockIdx.x;
-    unsigned offs = 0;
-    for (int r = 0; r < row; r++) offs += (k.rowhdr[r].bytes + 15u) & ~15u;
+    /* byte offset of this row's payload = sum of the padded sizes of the rows before it: loaded in parallel, reduced per warp
+     * (a serial loop would chain up to mb_h dependent global loads) */
+    __shared__ unsigned part[4];
+    {
+        unsigned v = 0;
+        for (int r = tid; r < row; r += nt) v += (k.rowhdr[r].bytes + 15u) & ~15u;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+        if ((tid & 31) == 0) part[tid >> 5] = v;
+    }
+    __syncthreads();
+    const unsigned offs = part[0] + part[1] + part[2] + part[3];
     if (hdr_bytes + mbh_bytes + offs + ((k.rowhdr[row].bytes + 15u) & ~15u) > k.out_cap) return;
     /* exclusive prefix of the row's per-MB symbol lengths (32-bit words), by warp 0 */
     __shared__ unsigned mboff[513];

@@ -78,3 +78,39 @@ def test_encode_sequence_equals_frame_by_frame(lib):
     (ya, ua, va), (yb, ub, vb) = a.recon(), b.recon()
     assert (ya == yb).all() and (ua == ub).all() and (va == vb).all()
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("w,h,rps", [(16, 16, 4), (18, 16, 1), (32, 18, 2), (48, 16, 8)])
+def test_minimum_and_odd_sizes(lib, w, h, rps):
+    """smallest legal pictures (even, >= 16), sizes that are not macroblock multiples, a single macroblock"""
+    run_parity(lib, "pan", w, h, [30, 31, 22], rps=rps)
+
+
+def test_force_idr_flag_and_pts(lib):
+    """CC_FORCE_IDR (upstream force-key-unit) restarts the GOP; pts passes through; SPS/PPS precede every IDR."""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    from h264_decode import decode_aus
+    w, h = 64, 48
+    src = make_source("pan", w, h)
+    e = CudaH264Enc(w, h, lib=lib, qp_fixed=30)
+    aus = []
+    for i in range(5):
+        y, u, v = src.frame(i)
+        aus.append(e.encode(y, u, v, pts=1000 + i, force_idr=(i == 3)))
+        assert e.last.pts == 1000 + i
+        assert e.last.is_idr == (i in (0, 3))
+        assert (aus[-1][:5] == b"\x00\x00\x00\x01\x67") == bool(e.last.is_idr)
+    assert len(decode_aus(aus)) == 5
+    e.close()
+
+
+def test_bitrate_property_is_clamped_to_the_reference_range(lib):
+    """/root/reference/src/core/bitrate_control.h:30-31: 300 kbps .. 30 Mbps"""
+    from ceracoder_b200 import CudaH264Enc
+    e = CudaH264Enc(64, 48, lib=lib)
+    e.set_property("bitrate", 1)
+    assert e.get_property("bitrate") == 300
+    e.set_property("bitrate", 10 ** 6)
+    assert e.get_property("bitrate") == 30000
+    e.close()
