@@ -81,6 +81,35 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy), cc_ld32u(B + (ptrdiff_t)r * k.sy));
 }
 
+/* Full-pel SADs of five horizontally adjacent candidates at once.  A lane takes four source rows (4 g .. 4 g + 3) of one
+ * candidate row: it loads the 24-byte strip of the reference row once (six aligned words, realigned with five funnel shifts) and
+ * slides the 16-pixel window over it in registers — a quarter of the loads of "lane = candidate", and every load is used by five
+ * candidates.  r points at the pixel of candidate dx = 0 in the first of the lane's rows; acc[dx][h] += SAD of the left (h = 0) /
+ * right (h = 1) 8 columns. */
+__device__ __forceinline__ void sad_strip5(const uint8_t *r, int sy, const uint32_t *sc4, unsigned acc[5][2]) {
+    const uintptr_t a = (uintptr_t)r;
+    const unsigned sh = (unsigned)(a & 3) * 8u;
+    const uint32_t *q = (const uint32_t *)(a & ~(uintptr_t)3);
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+        const uint32_t *w = (const uint32_t *)((const uint8_t *)q + (ptrdiff_t)y * sy);
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4], w5 = w[5];
+        uint32_t v[6];
+        v[0] = __funnelshift_r(w0, w1, sh); v[1] = __funnelshift_r(w1, w2, sh); v[2] = __funnelshift_r(w2, w3, sh);
+        v[3] = __funnelshift_r(w3, w4, sh); v[4] = __funnelshift_r(w4, w5, sh); v[5] = 0;
+        const uint32_t c0 = sc4[y * 4], c1 = sc4[y * 4 + 1], c2 = sc4[y * 4 + 2], c3 = sc4[y * 4 + 3];
+#pragma unroll
+        for (int dx = 0; dx < 5; dx++) {
+            const int j = dx >> 2;
+            const unsigned s8 = (unsigned)(dx & 3) * 8u;
+            const uint32_t p0 = s8 ? __funnelshift_r(v[j], v[j + 1], s8) : v[j], p1 = s8 ? __funnelshift_r(v[j + 1], v[j + 2], s8) : v[j + 1];
+            const uint32_t p2 = s8 ? __funnelshift_r(v[j + 2], v[j + 3], s8) : v[j + 2], p3 = s8 ? __funnelshift_r(v[j + 3], v[j + 4], s8) : v[j + 3];
+            acc[dx][0] = cc_sad4_acc(p1, c1, cc_sad4_acc(p0, c0, acc[dx][0]));
+            acc[dx][1] = cc_sad4_acc(p3, c3, cc_sad4_acc(p2, c2, acc[dx][1]));
+        }
+    }
+}
+
 /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"; oracle/ref_enc.c me_l0, second half).
  * Every quadrant searches +-2 full-pel around the macroblock's best full-pel vector by SAD (lane = candidate, the four
  * quadrant SADs of a candidate come out of one pass over the 16 rows), then refines to half and quarter-pel by SATD
@@ -88,23 +117,30 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
  * (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
  * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
 __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
+    /* lanes 0..19 = (candidate row dy = lane >> 2, source rows 4 g .. 4 g + 3 with g = lane & 3): rows of g < 2 belong to the top
+     * quadrants, the others to the bottom ones */
     unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-    if (lane < 25) {
-        const int mx = fbx + lane % 5 - 2, my = fby + lane / 5 - 2;
-        const uint8_t *r = k.ref[0] + (ptrdiff_t)(py + my) * k.sy + px + mx;
-        unsigned s4[4] = {0, 0, 0, 0};
+    {
+        const int dyi = lane >> 2, g = lane & 3;
+        unsigned acc[5][2];
 #pragma unroll
-        for (int hy = 0; hy < 2; hy++)
-            for (int y = hy * 8; y < hy * 8 + 8; y++) {
-                uint32_t a, b, c, d;
-                cc_ld64u(r + (ptrdiff_t)y * k.sy, a, b);
-                cc_ld64u(r + (ptrdiff_t)y * k.sy + 8, c, d);
-                s4[hy * 2] += __vsadu4(a, sc[y * 4]) + __vsadu4(b, sc[y * 4 + 1]);
-                s4[hy * 2 + 1] += __vsadu4(c, sc[y * 4 + 2]) + __vsadu4(d, sc[y * 4 + 3]);
-            }
-        const unsigned bits = (unsigned)(lambda * (cc_se_bits(4 * (mx - pm[0])) + cc_se_bits(4 * (my - pm[1]))));
+        for (int dx = 0; dx < 5; dx++) acc[dx][0] = acc[dx][1] = 0;
+        if (lane < 20) sad_strip5(k.ref[0] + (ptrdiff_t)(py + fby + dyi - 2 + 4 * g) * k.sy + px + fbx - 2, k.sy, sc + 16 * g, acc);
+        unsigned kl = 0xffffffffu, kr = 0xffffffffu;
+        const int my = fby + dyi - 2;
+        const int bits_y = cc_se_bits(4 * (my - pm[1]));
 #pragma unroll
-        for (int p = 0; p < 4; p++) key4[p] = ((s4[p] + bits) << 5) | (unsigned)lane;
+        for (int dx = 0; dx < 5; dx++) {
+            const unsigned sl = acc[dx][0] + __shfl_xor_sync(FULL, acc[dx][0], 1), sr = acc[dx][1] + __shfl_xor_sync(FULL, acc[dx][1], 1);
+            const unsigned bits = (unsigned)(lambda * (cc_se_bits(4 * (fbx + dx - 2 - pm[0])) + bits_y));
+            const unsigned cand = (unsigned)(dyi * 5 + dx);
+            kl = min(kl, ((sl + bits) << 5) | cand);
+            kr = min(kr, ((sr + bits) << 5) | cand);
+        }
+        if (lane < 20) {
+            if (g < 2) { key4[0] = kl; key4[1] = kr; }
+            else { key4[2] = kl; key4[3] = kr; }
+        }
     }
     const int p = lane >> 3, slot = (lane >> 2) & 1, b4 = lane & 3;
     int fi = 0;
@@ -193,26 +229,35 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     __syncwarp();
     const uint32_t *sc = scur[wid];
 
-    /* full-pel: lane = candidate */
+    /* full-pel, 27 candidates: the predictor (0), the zero vector (1), 5 x 5 around the coarse vector (2 + 5 dy + dx).
+     * lanes 0..19 = (candidate row, four source rows) of the 5 x 5 window, five candidates each (sad_strip5);
+     * lanes 20..23 / 24..27 = the predictor / the zero vector as the centre of a strip of their own */
     unsigned key = 0xffffffffu;
-    int mx = 0, my = 0;
-    if (lane < 27) {
-        if (lane == 0) { mx = pm[0]; my = pm[1]; }
-        else if (lane >= 2) { mx = l1x + (lane - 2) % 5 - 2; my = l1y + (lane - 2) / 5 - 2; }
-        const uint8_t *r = k.ref[0] + (ptrdiff_t)(py + my) * k.sy + px + mx;
-        unsigned sad = 0;
-        for (int y = 0; y < 16; y++) {
-            uint32_t a, b, c, d;
-            cc_ld64u(r + (ptrdiff_t)y * k.sy, a, b);
-            cc_ld64u(r + (ptrdiff_t)y * k.sy + 8, c, d);
-            sad += __vsadu4(a, sc[y * 4]) + __vsadu4(b, sc[y * 4 + 1]) + __vsadu4(c, sc[y * 4 + 2]) + __vsadu4(d, sc[y * 4 + 3]);
+    {
+        const int g = lane & 3, dyi = lane >> 2;
+        int sx = l1x - 2, syy = l1y + dyi - 2;
+        if (lane >= 24) { sx = -2; syy = 0; }
+        else if (lane >= 20) { sx = pm[0] - 2; syy = pm[1]; }
+        unsigned acc[5][2];
+#pragma unroll
+        for (int dx = 0; dx < 5; dx++) acc[dx][0] = acc[dx][1] = 0;
+        if (lane < 28) sad_strip5(k.ref[0] + (ptrdiff_t)(py + syy + 4 * g) * k.sy + px + sx, k.sy, sc + 16 * g, acc);
+        const int bits_y = cc_se_bits(4 * (syy - pm[1]));
+#pragma unroll
+        for (int dx = 0; dx < 5; dx++) {
+            unsigned sad = acc[dx][0] + acc[dx][1];
+            sad += __shfl_xor_sync(FULL, sad, 1);
+            sad += __shfl_xor_sync(FULL, sad, 2);
+            const unsigned cost = sad + (unsigned)(lambda * (cc_se_bits(4 * (sx + dx - pm[0])) + bits_y));
+            const bool ok = lane < 20 || (lane < 28 && dx == 2);
+            const unsigned cand = lane < 20 ? (unsigned)(2 + dyi * 5 + dx) : (lane < 24 ? 0u : 1u);
+            if (ok) key = min(key, (cost << 5) | cand);
         }
-        unsigned cost = sad + (unsigned)(lambda * (cc_se_bits(4 * (mx - pm[0])) + cc_se_bits(4 * (my - pm[1]))));
-        key = (cost << 5) | (unsigned)lane;
     }
-    unsigned bk = __reduce_min_sync(FULL, key);
-    int bl = (int)(bk & 31u);
-    const int fbx = __shfl_sync(FULL, mx, bl), fby = __shfl_sync(FULL, my, bl); /* best full-pel vector: centre of the 8x8 searches */
+    const unsigned bk = __reduce_min_sync(FULL, key);
+    const int bl = (int)(bk & 31u);
+    /* best full-pel vector: centre of the 8x8 searches */
+    const int fbx = bl == 0 ? pm[0] : (bl == 1 ? 0 : l1x + (bl - 2) % 5 - 2), fby = bl == 0 ? pm[1] : (bl == 1 ? 0 : l1y + (bl - 2) / 5 - 2);
     int bx = 4 * fbx, by = 4 * fby;
 
     /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */

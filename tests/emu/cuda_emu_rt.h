@@ -50,6 +50,7 @@ static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned f) {
 static inline cudaError_t cudaEventDestroy(cudaEvent_t e) { free(e); return 0; }
 static inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s) { (void)s; e->t = emu_now_ms(); return 0; }
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t e) { (void)e; return 0; }
+static inline cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned f) { (void)s; (void)e; (void)f; return 0; } /* launches run to completion in order */
 static inline cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b) { *ms = (float)(b->t - a->t); return 0; }
 #ifdef __cplusplus
 }
