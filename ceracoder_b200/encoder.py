@@ -181,15 +181,22 @@ class CudaH264Enc:
         flags = (CC_FORCE_IDR if force_idr else 0) | (CC_FRAME_DEVICE if device_frame else 0)
         _check(self.L, self.L.cc_enc_submit(self._h, C.byref(f), flags), "cc_enc_submit")
 
-    def encode_sequence(self, frames, bitrates_kbps, device_frame=False, stats=None):
-        """Consecutive frames in one C call (cc_enc_encode_sequence): frames = [(y, u, v)] as for encode(); bitrates in kbit/s
-        (the `bitrate` property, written only when it changes). Returns the accumulated SeqStats."""
+    def prepare_sequence(self, frames, bitrates_kbps):
+        """Frame descriptors (cc_frame: plane pointers, strides, pts) and the per-frame bitrates of a sequence as C arrays.
+        Building them is interpreter work (it holds the GIL); callers that time encode_sequence() build them beforehand."""
         n = len(frames)
         arr = (Frame * n)()
         for i, (y, u, v) in enumerate(frames):
             f = self._frame(y, u, v, i)
             arr[i].plane, arr[i].stride, arr[i].pts = f.plane, f.stride, f.pts
         br = (C.c_int * n)(*[int(b) * 1000 for b in bitrates_kbps])
+        return arr, br, n, frames  # `frames` keeps the source arrays alive
+
+    def encode_sequence(self, frames, bitrates_kbps=None, device_frame=False, stats=None):
+        """Consecutive frames in one C call (cc_enc_encode_sequence): frames = [(y, u, v)] as for encode(), or the result of
+        prepare_sequence(); bitrates in kbit/s (the `bitrate` property, written only when it changes).
+        Returns the accumulated SeqStats."""
+        arr, br, n, _keep = frames if bitrates_kbps is None else self.prepare_sequence(frames, bitrates_kbps)
         stats = stats if stats is not None else SeqStats()
         _check(self.L, self.L.cc_enc_encode_sequence(self._h, arr, br, n, CC_FRAME_DEVICE if device_frame else 0, C.byref(stats), C.byref(self._pkt)),
                "cc_enc_encode_sequence")
