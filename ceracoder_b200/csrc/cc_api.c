@@ -47,6 +47,10 @@ struct cc_enc {
     long stage_n[CC_N_STAGES];
     uint32_t sym_bytes;
     float submit_ms;
+    double t_submit0;            /* host time at the start of the last cc_enc_submit */
+    float dev_ms_hist[4];        /* device latency (submit -> access unit ready) of the last frames: how long collect may sleep */
+    unsigned dev_ms_n;
+    int sleep_wait;              /* CERACUDA_WAIT=spin turns the sleep off */
     int tail_pending;            /* profile: the stages after ev1 (reference finishing) of the previous frame are not read yet */
 };
 
@@ -158,6 +162,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     for (int i = 0; i <= CC_N_STAGES && rc == CC_OK; i++) if (cudaEventCreate(&e->pev[i]) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
+    { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
     cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max);
     cudaStreamSynchronize(e->st);
     cudaDeviceSynchronize();
@@ -304,6 +309,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->last_was_p = !is_idr;
     e->inflight = 1;
     e->submit_ms = (float)(now_ms() - t_submit);
+    e->t_submit0 = t_submit;
     return CC_OK;
 }
 
@@ -315,11 +321,24 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
     if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     cc_kparams *k = &e->k;
     const double t_wait = now_ms();
+    /* The device needs ~2 ms per frame and the driver's wait spins: with one host thread per stream and several streams
+     * (or several GPUs' worth of streams) per box the spinning threads take the cores the other streams' bitstream
+     * writers need.  Sleep through 80 % of what is left of the shortest recent device latency, then let the driver spin. */
+    if (e->sleep_wait && e->dev_ms_n >= 4) {
+        float lo = e->dev_ms_hist[0];
+        for (int i = 1; i < 4; i++) if (e->dev_ms_hist[i] < lo) lo = e->dev_ms_hist[i];
+        const double left = (double)lo - (t_wait - e->t_submit0);
+        if (left > 0.3) {
+            struct timespec ts = {0, (long)(left * 0.8e6)};
+            nanosleep(&ts, NULL);
+        }
+    }
     CUCHECK(cudaEventSynchronize(e->ev1));
     out->wait_ms = (float)(now_ms() - t_wait); out->submit_ms = e->submit_ms;
     e->inflight = 0;
     float gpu_ms = 0;
     cudaEventElapsedTime(&gpu_ms, e->ev0, e->ev1);
+    e->dev_ms_hist[e->dev_ms_n++ & 3] = gpu_ms;
     if (e->profile)
         for (int i = 0; i < CC_STAGE_DEBLOCK; i++) {
             float ms = 0;
