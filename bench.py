@@ -229,6 +229,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows-per-slice", type=int, default=4, help="macroblock rows per slice (experiments; the reported workload uses 4)")
     ap.add_argument("--partitions", type=int, default=1, help="0: 16x16 partitions only (experiments)")
+    ap.add_argument("--input-format", default="I420", choices=["I420", "YUY2", "BGRx"],
+                    help="frame format handed to the encoder; packed formats are converted inside the ingest kernel (SURVEY 8f N2). "
+                         "The YUY2 pool carries exactly the I420 pool's pictures (chroma rows doubled), so the encoded workload is the same")
     ap.add_argument("--frames-per-step", type=int, default=FRAMES_PER_STEP, help="frames each stream encodes per step (shorten for ncu runs)")
     args = ap.parse_args()
     FRAMES_PER_STEP = args.frames_per_step
@@ -246,21 +249,34 @@ def main():
     L = load_library()
     S = args.streams
     pool = make_pool()
-    fsz = W * H * 3 // 2
+    FMT = args.input_format
+    fsz = W * H * {"I420": 3, "YUY2": 4, "BGRx": 8}[FMT] // 2
     # pinned host pool (e2e leg) and HBM-resident pool (value leg); both > 126 MB L2 together with the encoders' planes
     hbase = L.cc_host_alloc(fsz * POOL); dbase = L.cc_dev_alloc(fsz * POOL)
     assert hbase and dbase
     harr = np.ctypeslib.as_array(C.cast(hbase, C.POINTER(C.c_uint8)), shape=(POOL, fsz))
     for i, (y, u, v) in enumerate(pool):
-        harr[i, :W * H] = y.ravel(); harr[i, W * H:W * H * 5 // 4] = u.ravel(); harr[i, W * H * 5 // 4:] = v.ravel()
+        if FMT == "I420":
+            harr[i, :W * H] = y.ravel(); harr[i, W * H:W * H * 5 // 4] = u.ravel(); harr[i, W * H * 5 // 4:] = v.ravel()
+        elif FMT == "YUY2":
+            f = harr[i].reshape(H, 2 * W)
+            f[:, 0::2] = y; f[:, 1::4] = np.repeat(u, 2, axis=0); f[:, 3::4] = np.repeat(v, 2, axis=0)
+        else:  # BGRx from the same pictures (BT.709 limited range, float; the encoder converts back with its integer matrix)
+            yy = (y.astype(np.float32) - 16) * (255 / 219)
+            uu = np.repeat(np.repeat(u, 2, 0), 2, 1).astype(np.float32) - 128; vv = np.repeat(np.repeat(v, 2, 0), 2, 1).astype(np.float32) - 128
+            f = harr[i].reshape(H, W, 4)
+            f[..., 2] = np.clip(yy + 1.7927 * vv, 0, 255); f[..., 1] = np.clip(yy - 0.2132 * uu - 0.5329 * vv, 0, 255)
+            f[..., 0] = np.clip(yy + 2.1124 * uu, 0, 255); f[..., 3] = 255
     assert L.cc_dev_upload(dbase, hbase, fsz * POOL) == 0
 
     def planes(base, k, fi):
         p = base + pingpong(fi + 5 * k, POOL) * fsz
+        if FMT != "I420":
+            return (p, W * (2 if FMT == "YUY2" else 4)), None, None
         return (p, W), (p + W * H, W // 2), (p + W * H * 5 // 4, W // 2)
 
     def make_encs():
-        return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L,
+        return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L, fmt=FMT,
                             rows_per_slice=args.rows_per_slice, partitions=bool(args.partitions)) for _ in range(S)]
 
     def timed(device_frames, steps, warmup, profile=False):
@@ -376,7 +392,7 @@ def main():
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
             "data": "synthetic S2 pan-sprites 1080p (SURVEY.md §8d), 40-frame pool played ping-pong",
             "config": {"workload": f"{S} concurrent 1080p60 cudah264enc streams per GPU, balancer-shaped 12->2->12 Mbps schedule (configs[1] x8, north_star target shape)",
-                       "width": W, "height": H, "fps": FPS, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60,
+                       "width": W, "height": H, "fps": FPS, "input_format": FMT, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60,
                        "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},

@@ -90,7 +90,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!h || !p) return CC_ERR_PARAM;
     *h = NULL;
     if (p->width < 16 || p->height < 16 || (p->width & 1) || (p->height & 1) || p->width > 8192 || p->height > 8192) return CC_ERR_PARAM;
-    if (p->format != CC_FMT_I420 && p->format != CC_FMT_NV12) return CC_ERR_PARAM;
+    if (p->format < CC_FMT_I420 || p->format > CC_FMT_BGRX) return CC_ERR_PARAM;
     if (p->fps_n <= 0 || p->fps_d <= 0) return CC_ERR_PARAM;
     if (p->rows_per_slice < 0 || p->rows_per_slice > 8) return CC_ERR_PARAM; /* one warp per MB row, at most 8 rows (256 threads) per slice CTA */
     int ndev = 0;
@@ -129,6 +129,10 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
         k->ref[1] = chr[4] + co; k->ref[2] = chr[5] + co; k->l1cur = chr[6] + co; k->l1ref = chr[7] + co;
     }
     if (rc == CC_OK && p->format == CC_FMT_NV12) rc = dev_alloc(e, (void **)&k->uvstage, (size_t)k->sy * (k->H / 2 + 1));
+    if (rc == CC_OK && (p->format == CC_FMT_YUY2 || p->format == CC_FMT_BGRX)) {
+        k->pks = (int)roundup((size_t)k->w * (p->format == CC_FMT_YUY2 ? 2 : 4), 128);
+        rc = dev_alloc(e, (void **)&k->pkstage, (size_t)k->pks * k->h);
+    }
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me, sizeof(cc_me) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me8, sizeof(cc_me8) * nmb);
     k->part8 = e->p.partitions != 0;
@@ -238,14 +242,20 @@ static void set_quant(cc_kparams *k) {
 }
 
 int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
-    if (!e || !in || !in->plane[0] || !in->plane[1]) return CC_ERR_PARAM;
+    if (!e || !in) return CC_ERR_PARAM;
     if (e->inflight) return CC_ERR_STATE;
     if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     const double t_submit = now_ms();
     cc_kparams *k = &e->k;
-    const int nv12 = e->p.format == CC_FMT_NV12;
-    if (!nv12 && !in->plane[2]) return CC_ERR_PARAM;
-    if (in->stride[0] < k->w || in->stride[1] < (nv12 ? k->w : k->w / 2)) return CC_ERR_PARAM;
+    const int nv12 = e->p.format == CC_FMT_NV12, fmt = e->p.format;
+    const int packed = fmt == CC_FMT_YUY2 || fmt == CC_FMT_BGRX;
+    if (!in->plane[0]) return CC_ERR_PARAM;
+    if (packed) {
+        if (in->stride[0] < k->w * (fmt == CC_FMT_YUY2 ? 2 : 4)) return CC_ERR_PARAM;
+    } else {
+        if (!in->plane[1] || (!nv12 && !in->plane[2])) return CC_ERR_PARAM;
+        if (in->stride[0] < k->w || in->stride[1] < (nv12 ? k->w : k->w / 2)) return CC_ERR_PARAM;
+    }
     int is_idr = !e->have_ref || (flags & CC_FORCE_IDR) || e->gop_pos >= e->p.key_int_max;
     if (is_idr) { e->gop_pos = 0; e->frame_num = 0; }
     int bps = __atomic_load_n(&e->pending_bps, __ATOMIC_RELAXED);
@@ -267,17 +277,21 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     }
     CUCHECK(cudaEventRecord(e->ev0, e->st));
     if (e->profile) { cudaEventRecord(e->pev[CC_STAGE_UPLOAD], e->st); }
-    CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
-    if (nv12) {
-        CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, in->plane[1], (size_t)in->stride[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
+    if (packed) {
+        CUCHECK(cudaMemcpy2DAsync(k->pkstage, (size_t)k->pks, in->plane[0], (size_t)in->stride[0], (size_t)k->w * (fmt == CC_FMT_YUY2 ? 2 : 4), (size_t)k->h, kind, e->st));
     } else {
-        CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
-        CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+        CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
+        if (nv12) {
+            CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, in->plane[1], (size_t)in->stride[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
+        } else {
+            CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+            CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+        }
     }
 #define STAGE(i) do { if (e->profile) { cudaEventRecord(e->pev[i], e->st); e->pev_used[i] = 1; } } while (0)
     for (int i = 0; i <= CC_N_STAGES; i++) e->pev_used[i] = 0;
     STAGE(CC_STAGE_INGEST);
-    e->launches += cck_ingest(k, nv12, e->st);
+    e->launches += cck_ingest(k, fmt, e->st);
     STAGE(CC_STAGE_ME_COARSE);
     if (!is_idr) e->launches += cck_me_l1(k, e->st);
     STAGE(CC_STAGE_ME_FINE);

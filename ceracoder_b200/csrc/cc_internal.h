@@ -93,6 +93,8 @@ typedef struct {
     uint8_t *hb, *hh, *hj; /* half-pel planes of ref: horizontal, vertical, centre */
     uint8_t *l1cur, *l1ref;
     uint8_t *uvstage;  /* NV12 interleaved chroma staging (pitch sy), or NULL */
+    uint8_t *pkstage;  /* packed-input staging (YUY2: 2 bytes / pixel, BGRx: 4), pitch pks, or NULL */
+    int pks;
     cc_me *me;
     cc_me8 *me8;
     int part8;         /* 1: the motion search may choose P_8x8 */
@@ -115,7 +117,7 @@ typedef struct {
 } cc_kparams;
 
 /* kernel launch wrappers (cc_kernels.cu); each returns the number of kernels launched */
-int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st);
+int cck_ingest(const cc_kparams *k, int fmt, cudaStream_t st);
 int cck_finish_ref(const cc_kparams *k, cudaStream_t st); /* rec -> borders, half-pel planes, half-res plane */
 int cck_border(const cc_kparams *k, cudaStream_t st);
 int cck_hpel(const cc_kparams *k, cudaStream_t st);

@@ -42,6 +42,57 @@ __global__ void k_ingest(cc_kparams k, int nv12) {
     }
 }
 
+
+/* ---- k_ingest_packed: colour conversion fused into the ingest --------------------------------- */
+/* Packed input (YUY2 or BGRx, uploaded as is into k.pkstage) -> padded 4:2:0 planes + half-resolution luma in one pass: the
+ * `videoconvert` in front of the encoder in the reference's pipeline text.  One thread = one 2x2 luma block; interior blocks
+ * read one 32-bit (YUY2) or 64-bit (BGRx) word per row, blocks in the padding clamp their source coordinates.
+ * Arithmetic: oracle/ref_convert.c (bit-exact, tests/test_convert.py). */
+__constant__ int c_rgb2yuv[2][9] = {
+    {66, 129, 25, -38, -74, 112, 112, -94, -18},   /* BT.601, pictures of up to 576 lines */
+    {47, 157, 16, -26, -87, 112, 112, -102, -10},  /* BT.709 */
+};
+template <int FMT> /* 2 = YUY2, 3 = BGRx */
+__global__ void k_ingest_packed(cc_kparams k) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= (k.W >> 1)) return;
+    const int sx0 = min(2 * x, k.w - 2), sy0 = min(2 * y, k.h - 2); /* w, h are even: the block clamps as a whole ... */
+    const bool edge = 2 * x >= k.w || 2 * y >= k.h;              /* ... and replicates the last column / row in the padding */
+    const uint8_t *r0 = k.pkstage + (size_t)sy0 * k.pks, *r1 = r0 + k.pks;
+    int Y[4], U, V;
+    if (FMT == 2) {
+        const uint32_t a = *(const uint32_t *)(r0 + 2 * sx0), b = *(const uint32_t *)(r1 + 2 * sx0);
+        Y[0] = a & 255; Y[1] = (a >> 16) & 255; Y[2] = b & 255; Y[3] = (b >> 16) & 255;
+        U = (int)(((a >> 8) & 255) + ((b >> 8) & 255) + 1) >> 1;
+        V = (int)((a >> 24) + (b >> 24) + 1) >> 1;
+    } else {
+        const int *m = c_rgb2yuv[k.h > 576];
+        const uint2 a = *(const uint2 *)(r0 + 4 * sx0), b = *(const uint2 *)(r1 + 4 * sx0);
+        const uint32_t px[4] = {a.x, a.y, b.x, b.y};
+        int sr = 0, sg = 0, sb = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int B = px[i] & 255, G = (px[i] >> 8) & 255, R = (px[i] >> 16) & 255;
+            Y[i] = (m[0] * R + m[1] * G + m[2] * B + 4224) >> 8;
+            sr += R; sg += G; sb += B;
+        }
+        const int R = (sr + 2) >> 2, G = (sg + 2) >> 2, B = (sb + 2) >> 2;
+        U = (m[3] * R + m[4] * G + m[5] * B + 32896) >> 8;
+        V = (m[6] * R + m[7] * G + m[8] * B + 32896) >> 8;
+    }
+    if (edge) { /* padding: replicate the picture's last column / row (what k_ingest does for planar input) */
+        if (2 * x >= k.w) { Y[0] = Y[1]; Y[2] = Y[3]; }
+        if (2 * y >= k.h) { Y[0] = Y[2]; Y[1] = Y[3]; }
+        if (2 * x >= k.w && 2 * y >= k.h) Y[0] = Y[1] = Y[2] = Y[3];
+    }
+    uint8_t *dy = k.cur[0] + (size_t)(2 * y) * k.sy + 2 * x;
+    *(uint16_t *)dy = (uint16_t)(Y[0] | (Y[1] << 8));
+    *(uint16_t *)(dy + k.sy) = (uint16_t)(Y[2] | (Y[3] << 8));
+    k.l1cur[(size_t)y * k.sc + x] = (uint8_t)((Y[0] + Y[1] + Y[2] + Y[3] + 2) >> 2);
+    k.cur[1][(size_t)y * k.sc + x] = (uint8_t)U;
+    k.cur[2][(size_t)y * k.sc + x] = (uint8_t)V;
+}
+
 /* ---- k_border ---------------------------------------------------------------------------------------- */
 /* grid.y = plane (0 luma, 1 Cb, 2 Cr); one thread per border byte-quad */
 __global__ void k_border(cc_kparams k) {
@@ -139,9 +190,11 @@ __global__ void k_l1ref(cc_kparams k) {
 }
 
 /* ---- launch wrappers --------------------------------------------------------------------------------- */
-extern "C" int cck_ingest(const cc_kparams *k, int nv12, cudaStream_t st) {
+extern "C" int cck_ingest(const cc_kparams *k, int fmt, cudaStream_t st) { /* fmt: CC_FMT_* of include/ceracuda.h */
     dim3 grid((unsigned)((k->W / 2 + 127) / 128), (unsigned)(k->H / 2));
-    CC_LAUNCH(k_ingest, grid, dim3(128), st, *k, nv12);
+    if (fmt == 2) CC_LAUNCH(k_ingest_packed<2>, grid, dim3(128), st, *k);
+    else if (fmt == 3) CC_LAUNCH(k_ingest_packed<3>, grid, dim3(128), st, *k);
+    else CC_LAUNCH(k_ingest, grid, dim3(128), st, *k, fmt == 1);
     return 1;
 }
 extern "C" int cck_border(const cc_kparams *k, cudaStream_t st) {

@@ -11,7 +11,7 @@ import numpy as np
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libceracuda.so")
 CC_FORCE_IDR, CC_FRAME_DEVICE = 1, 2
-CC_FMT_I420, CC_FMT_NV12 = 0, 1
+CC_FMT_I420, CC_FMT_NV12, CC_FMT_YUY2, CC_FMT_BGRX = 0, 1, 2, 3
 
 
 class CeraCudaError(RuntimeError):
@@ -125,7 +125,7 @@ class CudaH264Enc:
         self.L.cc_enc_params_default(C.byref(p))
         p.device, p.width, p.height = device, self.width, self.height
         p.fps_n, p.fps_d = (fps if isinstance(fps, tuple) else (int(fps), 1))
-        p.format = {"I420": CC_FMT_I420, "NV12": CC_FMT_NV12}[fmt]
+        p.format = {"I420": CC_FMT_I420, "NV12": CC_FMT_NV12, "YUY2": CC_FMT_YUY2, "BGRx": CC_FMT_BGRX}[fmt]  # packed: one plane, converted on the device
         p.bitrate_bps = int(bitrate) * 1000
         p.key_int_max, p.rows_per_slice, p.qp_fixed = key_int_max, rows_per_slice, qp_fixed
         p.partitions = int(bool(partitions))
@@ -155,9 +155,9 @@ class CudaH264Enc:
         raise AttributeError(prop)
 
     # -- data path --
-    def _frame(self, y, u, v=None, pts=0):
+    def _frame(self, y, u=None, v=None, pts=0):
         f = Frame()
-        planes = [y, u] + ([v] if v is not None else [])
+        planes = [y] + ([u] if u is not None else []) + ([v] if v is not None else [])
         for i, pl in enumerate(planes):
             if isinstance(pl, tuple):  # (pointer, stride): device or pinned memory handed over raw
                 f.plane[i], f.stride[i] = pl
@@ -167,8 +167,9 @@ class CudaH264Enc:
         f.pts = pts
         return f
 
-    def encode(self, y, u, v=None, pts=0, force_idr=False, qp=None, device_frame=False):
-        """One frame in, one Annex-B access unit out (bytes). Frame planes: numpy uint8 arrays (any row stride)."""
+    def encode(self, y, u=None, v=None, pts=0, force_idr=False, qp=None, device_frame=False):
+        """One frame in, one Annex-B access unit out (bytes). Frame planes: numpy uint8 arrays (any row stride); packed formats
+        (YUY2, BGRx) pass their one plane as `y` (rows of 2 w or 4 w bytes)."""
         if qp is not None:
             _check(self.L, self.L.cc_enc_set_next_qp(self._h, int(qp)), "cc_enc_set_next_qp")
         f = self._frame(y, u, v, pts)
@@ -176,7 +177,7 @@ class CudaH264Enc:
         _check(self.L, self.L.cc_enc_encode(self._h, C.byref(f), flags, C.byref(self._pkt)), "cc_enc_encode")
         return C.string_at(self._pkt.data, self._pkt.size)
 
-    def submit(self, y, u, v=None, pts=0, force_idr=False, device_frame=False):
+    def submit(self, y, u=None, v=None, pts=0, force_idr=False, device_frame=False):
         f = self._frame(y, u, v, pts)
         flags = (CC_FORCE_IDR if force_idr else 0) | (CC_FRAME_DEVICE if device_frame else 0)
         _check(self.L, self.L.cc_enc_submit(self._h, C.byref(f), flags), "cc_enc_submit")

@@ -41,7 +41,7 @@ GST_DEBUG_CATEGORY_STATIC(cudah264enc_debug);
 enum { PROP_0, PROP_BITRATE, PROP_BPS, PROP_SPEED_PRESET, PROP_KEY_INT_MAX, PROP_TUNE, PROP_BYTE_STREAM, PROP_THREADS, PROP_DEVICE, PROP_ROWS_PER_SLICE };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
-    GST_STATIC_CAPS("video/x-raw, format=(string){ I420, NV12 }, width=(int)[16,8192], height=(int)[16,8192], framerate=(fraction)[0/1,MAX]"));
+    GST_STATIC_CAPS("video/x-raw, format=(string){ I420, NV12, YUY2, BGRx }, width=(int)[16,8192], height=(int)[16,8192], framerate=(fraction)[0/1,MAX]"));
 static GstStaticPadTemplate src_tmpl = GST_STATIC_PAD_TEMPLATE("src", GST_PAD_SRC, GST_PAD_ALWAYS,
     GST_STATIC_CAPS("video/x-h264, stream-format=(string)byte-stream, alignment=(string)au, profile=(string)constrained-baseline"));
 
@@ -116,7 +116,12 @@ static gboolean gst_cuda_h264_enc_set_format(GstVideoEncoder *venc, GstVideoCode
     p.width = GST_VIDEO_INFO_WIDTH(info); p.height = GST_VIDEO_INFO_HEIGHT(info);
     p.fps_n = GST_VIDEO_INFO_FPS_N(info) > 0 ? GST_VIDEO_INFO_FPS_N(info) : 30;
     p.fps_d = GST_VIDEO_INFO_FPS_D(info) > 0 ? GST_VIDEO_INFO_FPS_D(info) : 1;
-    p.format = GST_VIDEO_INFO_FORMAT(info) == GST_VIDEO_FORMAT_NV12 ? CC_FMT_NV12 : CC_FMT_I420;
+    switch (GST_VIDEO_INFO_FORMAT(info)) { /* packed formats are converted inside the ingest kernel: no videoconvert upstream */
+    case GST_VIDEO_FORMAT_NV12: p.format = CC_FMT_NV12; break;
+    case GST_VIDEO_FORMAT_YUY2: p.format = CC_FMT_YUY2; break;
+    case GST_VIDEO_FORMAT_BGRx: p.format = CC_FMT_BGRX; break;
+    default: p.format = CC_FMT_I420; break;
+    }
     p.bitrate_bps = g_atomic_int_get(&self->bitrate_bps);
     p.key_int_max = (int)self->key_int_max;
     p.rows_per_slice = (int)self->rows_per_slice;

@@ -35,7 +35,12 @@ extern "C" {
 #define CC_ERR_STATE (-4)  /* call order violated (collect without submit, ...) */
 #define CC_ERR_OVERFLOW (-5) /* access unit did not fit the internal output buffer */
 
-enum { CC_FMT_I420 = 0, CC_FMT_NV12 = 1 };
+/* CC_FMT_YUY2 / CC_FMT_BGRX: packed input (plane[0], stride[0] only), converted to 4:2:0 inside the ingest kernel — the
+ * `videoconvert` in front of x264enc in /root/reference/pipeline/generic/x264_veryfast_v4l_mjpeg_1080p30:3-5.
+ * YUY2: luma as is, chroma = rounded mean of the two rows.  BGRx: 8-bit limited-range matrix, BT.709 above 576 lines else
+ * BT.601 (GStreamer's default colorimetry for YUV video of that size), chroma from the rounded 2x2 mean of R, G, B.
+ * The exact integer arithmetic is stated in oracle/ref_convert.c. */
+enum { CC_FMT_I420 = 0, CC_FMT_NV12 = 1, CC_FMT_YUY2 = 2, CC_FMT_BGRX = 3 };
 enum { CC_FORCE_IDR = 1u, CC_FRAME_DEVICE = 2u /* plane pointers are device memory */ };
 
 typedef struct cc_enc cc_enc;

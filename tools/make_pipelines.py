@@ -35,9 +35,11 @@ def v4l_mjpeg(w, h, fps, preset):
             "videoconvert ! video/x-raw,format=I420 ! ", encoder(preset)] + TAIL + AUDIO_ALSA + MUX
 
 
-def camlink(preset):
+def camlink(preset, direct=False):
+    """direct: the capture format (YUY2) goes straight into the encoder, which converts it inside its ingest kernel
+     — no videoconvert pass on the CPU"""
     return ["v4l2src ! ", "identity name=v_delay signal-handoffs=TRUE ! ", "videorate ! video/x-raw,framerate=30000/1001 ! ", OVERLAY,
-            "videoconvert ! video/x-raw,format=NV12 ! ", encoder(preset)] + TAIL + AUDIO_ALSA + MUX
+            "video/x-raw,format=YUY2 ! " if direct else "videoconvert ! video/x-raw,format=NV12 ! ", encoder(preset)] + TAIL + AUDIO_ALSA + MUX
 
 
 def test_pattern(w, h, fps, preset):
@@ -51,6 +53,7 @@ FILES = {
     "cuda_h264_v4l_mjpeg_720p30": v4l_mjpeg(1280, 720, 30, 3),
     "cuda_h264_v4l_mjpeg_720p": v4l_mjpeg(1280, 720, 0, 3),
     "cuda_h264_camlink": camlink(3),
+    "cuda_h264_camlink_yuy2": camlink(3, direct=True),
     "cuda_h264_test_1080p30": test_pattern(1920, 1080, 30, 3),
     "cuda_h264_test_1080p60": test_pattern(1920, 1080, 60, 3),
     "cuda_h264_test_720p60": test_pattern(1280, 720, 60, 3),
