@@ -17,7 +17,7 @@ $(LIB): $(CU) $(CS) $(HDR)
 	mkdir -p build
 	for f in $(CS); do $(CC) -O2 -fPIC -std=gnu11 -Wall -I/usr/local/cuda/include -c $$f -o build/$$(basename $$f .c).o || exit 1; done
 	for f in $(CU); do $(NVCC) $(NVFLAGS) -c $$f -o build/$$(basename $$f .cu).o 2> build/$$(basename $$f .cu).ptxas.log || { cat build/$$(basename $$f .cu).ptxas.log; exit 1; }; done
-	$(NVCC) -shared -o $@ build/cc_api.o build/cc_bitstream.o build/cc_cavlc.o build/cc_rc.o build/cc_k_frame.o build/cc_k_motion.o build/cc_k_mb.o build/cc_k_prims.o -lm
+	$(NVCC) -shared -o $@ build/cc_api.o build/cc_bitstream.o build/cc_cavlc.o build/cc_rc.o build/cc_k_frame.o build/cc_k_motion.o build/cc_k_mb.o build/cc_k_prims.o -lm -lpthread
 oracle:
 	$(MAKE) -C oracle
 emu: $(EMU)
@@ -26,7 +26,7 @@ $(EMU): $(CU) $(CS) $(HDR) tests/emu/cuda_emu.h tests/emu/cuda_emu_rt.h tests/em
 	for f in $(CS); do $(CC) -O2 -g -fPIC -std=gnu11 -Wall -DCC_EMU_BUILD -Itests/emu -c $$f -o tests/emu/_build/$$(basename $$f .c).o || exit 1; done
 	for f in $(CU); do $(CXX) -O2 -g -fPIC -std=c++17 -Wall -Wno-unused-function -Wno-unknown-pragmas -DCC_EMU_BUILD -Itests/emu -include tests/emu/cuda_emu.h -x c++ -c $$f -o tests/emu/_build/$$(basename $$f .cu).o || exit 1; done
 	$(CXX) -O2 -g -fPIC -std=c++17 -Itests/emu -c tests/emu/cuda_emu.cpp -o tests/emu/_build/cuda_emu.o
-	$(CXX) -shared -o $@ tests/emu/_build/*.o -lm
+	$(CXX) -shared -o $@ tests/emu/_build/*.o -lm -lpthread
 clean:
 	rm -rf build tests/emu/_build $(LIB)
 	$(MAKE) -C oracle clean

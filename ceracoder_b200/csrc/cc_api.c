@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <pthread.h>
 
 #define CC_MIN_BPS 300000   /* /root/reference/src/core/bitrate_control.h:30 */
 #define CC_MAX_BPS 30000000 /* /root/reference/src/core/bitrate_control.h:31 */
@@ -46,6 +47,16 @@ struct cc_enc {
     double stage_ms[CC_N_STAGES];
     long stage_n[CC_N_STAGES];
     uint32_t sym_bytes;
+    /* slice-writer pool (cc_enc_params.threads > 1): workers + the collecting thread take slices off job_next */
+    int n_workers;               /* extra threads */
+    pthread_t workers[16];
+    pthread_mutex_t job_mu;
+    pthread_cond_t job_cv, done_cv;
+    unsigned job_gen;
+    int job_stop, job_next, job_left, job_ns, job_is_idr, job_err;
+    const cc_mbhost *job_mbh; const cc_rowhdr *job_rh; const uint8_t *const *job_rowp;
+    uint8_t **slice_out; size_t *slice_len; size_t slice_cap; /* per slice: its NAL unit */
+    uint8_t *worker_rbsp[17];    /* scratch RBSP per thread (index n_workers = the collecting thread) */
     float submit_ms;
     double t_submit0;            /* host time at the start of the last cc_enc_submit */
     float dev_ms_hist[4];        /* device latency (submit -> access unit ready) of the last frames: how long collect may sleep */
@@ -85,6 +96,81 @@ static int dev_alloc(cc_enc *e, void **p, size_t n) {
     return CC_OK;
 }
 static size_t roundup(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+/* ---- slice-writer pool ------------------------------------------------------------------------------ */
+/* Slices are independent (no prediction, no CAVLC context across slice borders; the per-MB total_coeff array is written
+ * by the slice that owns the macroblock), so their NAL units can be written concurrently and concatenated in order. */
+static int write_slice_nal(cc_enc *e, int s, uint8_t *rbsp, uint8_t *out, size_t cap, size_t *len) {
+    const cc_kparams *k = &e->k;
+    const int r0 = s * k->rps, r1 = r0 + k->rps < k->mb_h ? r0 + k->rps : k->mb_h, is_idr = e->job_is_idr;
+    cc_bw b;
+    cc_bw_init(&b, rbsp, e->rbsp_cap);
+    cc_write_slice_header(&b, r0 * k->mb_w, is_idr, e->frame_num, e->idr_pic_id, e->cur_qp);
+    if (cc_cavlc_write_slice(&e->cav, &b, is_idr, r0, r1, e->job_mbh, e->job_rh, e->job_rowp) != 0) return CC_ERR_STATE;
+    const size_t m = cc_bw_finish(&b);
+    if (b.overflow) return CC_ERR_OVERFLOW;
+    *len = cc_write_nal(out, cap, is_idr ? 0x65 : 0x41, rbsp, m);
+    return *len ? CC_OK : CC_ERR_OVERFLOW;
+}
+static void pool_take_slices(cc_enc *e, int tid) {
+    for (;;) {
+        const int s = __atomic_fetch_add(&e->job_next, 1, __ATOMIC_ACQUIRE);
+        if (s >= e->job_ns) return;
+        const int rc = write_slice_nal(e, s, e->worker_rbsp[tid], e->slice_out[s], e->slice_cap, &e->slice_len[s]);
+        if (rc != CC_OK) __atomic_store_n(&e->job_err, rc, __ATOMIC_RELAXED);
+        if (__atomic_sub_fetch(&e->job_left, 1, __ATOMIC_ACQ_REL) == 0) {
+            pthread_mutex_lock(&e->job_mu); pthread_cond_signal(&e->done_cv); pthread_mutex_unlock(&e->job_mu);
+        }
+    }
+}
+typedef struct { cc_enc *e; int tid; } pool_arg;
+static void *pool_main(void *a) {
+    cc_enc *e = ((pool_arg *)a)->e;
+    const int tid = ((pool_arg *)a)->tid;
+    free(a);
+    unsigned seen = 0;
+    for (;;) {
+        pthread_mutex_lock(&e->job_mu);
+        while (!e->job_stop && e->job_gen == seen) pthread_cond_wait(&e->job_cv, &e->job_mu);
+        seen = e->job_gen;
+        const int stop = e->job_stop;
+        pthread_mutex_unlock(&e->job_mu);
+        if (stop) return NULL;
+        pool_take_slices(e, tid);
+    }
+}
+static int pool_start(cc_enc *e, int threads) {
+    const int ns = (e->k.mb_h + e->k.rps - 1) / e->k.rps;
+    if (threads > 16) threads = 16;
+    if (threads > ns) threads = ns;
+    if (threads < 2) return CC_OK;
+    pthread_mutex_init(&e->job_mu, NULL); pthread_cond_init(&e->job_cv, NULL); pthread_cond_init(&e->done_cv, NULL);
+    e->slice_cap = e->rbsp_cap + e->rbsp_cap / 2 + 64;
+    e->slice_out = (uint8_t **)calloc((size_t)ns, sizeof *e->slice_out);
+    e->slice_len = (size_t *)calloc((size_t)ns, sizeof *e->slice_len);
+    if (!e->slice_out || !e->slice_len) return CC_ERR_NOMEM;
+    for (int s = 0; s < ns; s++) if (!(e->slice_out[s] = (uint8_t *)malloc(e->slice_cap))) return CC_ERR_NOMEM;
+    for (int t = 0; t < threads; t++) if (!(e->worker_rbsp[t] = (uint8_t *)malloc(e->rbsp_cap))) return CC_ERR_NOMEM;
+    for (int t = 0; t < threads - 1; t++) {
+        pool_arg *a = (pool_arg *)malloc(sizeof *a);
+        if (!a) return CC_ERR_NOMEM;
+        a->e = e; a->tid = t;
+        if (pthread_create(&e->workers[t], NULL, pool_main, a) != 0) { free(a); return CC_ERR_NOMEM; }
+        e->n_workers = t + 1;
+    }
+    return CC_OK;
+}
+static void pool_stop(cc_enc *e) {
+    if (e->n_workers) {
+        pthread_mutex_lock(&e->job_mu); e->job_stop = 1; pthread_cond_broadcast(&e->job_cv); pthread_mutex_unlock(&e->job_mu);
+        for (int t = 0; t < e->n_workers; t++) pthread_join(e->workers[t], NULL);
+        pthread_mutex_destroy(&e->job_mu); pthread_cond_destroy(&e->job_cv); pthread_cond_destroy(&e->done_cv);
+        e->n_workers = 0;
+    }
+    if (e->slice_out) { const int ns = (e->k.mb_h + e->k.rps - 1) / e->k.rps; for (int s = 0; s < ns; s++) free(e->slice_out[s]); }
+    free(e->slice_out); free(e->slice_len); e->slice_out = NULL; e->slice_len = NULL;
+    for (int t = 0; t < 17; t++) { free(e->worker_rbsp[t]); e->worker_rbsp[t] = NULL; }
+}
 
 int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!h || !p) return CC_ERR_PARAM;
@@ -161,6 +247,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     e->cav.mb_w = k->mb_w; e->cav.mb_h = k->mb_h; e->cav.rps = k->rps;
     e->cav.nnz = (uint8_t *)calloc((size_t)nmb, 24);
     if (!e->au || !e->rbsp || !e->cav.nnz) rc = CC_ERR_NOMEM;
+    if (rc == CC_OK) rc = pool_start(e, p->threads);
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
     for (int i = 0; i <= CC_N_STAGES && rc == CC_OK; i++) if (cudaEventCreate(&e->pev[i]) != cudaSuccess) rc = CC_ERR_CUDA;
@@ -196,6 +283,7 @@ void cc_enc_close(cc_enc *e) {
         free(h);
     }
     for (int i = 0; i < e->n_dev_alloc; i++) cudaFree(e->dev_alloc[i]);
+    pool_stop(e);
     if (e->out_host) cudaFreeHost(e->out_host);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
@@ -386,17 +474,31 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
         if (!m || !w) return CC_ERR_OVERFLOW;
         n += w;
     }
-    for (int r0 = 0; r0 < k->mb_h; r0 += k->rps) {
-        int r1 = r0 + k->rps < k->mb_h ? r0 + k->rps : k->mb_h;
-        cc_bw b;
-        cc_bw_init(&b, e->rbsp, e->rbsp_cap);
-        cc_write_slice_header(&b, r0 * k->mb_w, is_idr, e->frame_num, e->idr_pic_id, e->cur_qp);
-        if (cc_cavlc_write_slice(&e->cav, &b, is_idr, r0, r1, mbh, rh, rowp) != 0) { fprintf(stderr, "ceracuda: malformed symbol stream\n"); return CC_ERR_STATE; }
-        size_t m = cc_bw_finish(&b);
-        if (b.overflow) return CC_ERR_OVERFLOW;
-        size_t w = cc_write_nal(e->au + n, e->au_cap - n, is_idr ? 0x65 : 0x41, e->rbsp, m);
-        if (!w) return CC_ERR_OVERFLOW;
-        n += w;
+    e->job_is_idr = is_idr; e->job_mbh = mbh; e->job_rh = rh; e->job_rowp = rowp;
+    const int n_slices = (k->mb_h + k->rps - 1) / k->rps;
+    if (e->n_workers) { /* cc_enc_params.threads > 1: the slices are written concurrently, then joined in order */
+        pthread_mutex_lock(&e->job_mu);
+        e->job_ns = n_slices; e->job_left = n_slices; e->job_err = CC_OK; e->job_gen++;
+        __atomic_store_n(&e->job_next, 0, __ATOMIC_RELEASE); /* a worker still leaving the previous frame's loop may pick a slice up at once */
+        pthread_cond_broadcast(&e->job_cv);
+        pthread_mutex_unlock(&e->job_mu);
+        pool_take_slices(e, e->n_workers);
+        pthread_mutex_lock(&e->job_mu);
+        while (__atomic_load_n(&e->job_left, __ATOMIC_ACQUIRE) > 0) pthread_cond_wait(&e->done_cv, &e->job_mu);
+        pthread_mutex_unlock(&e->job_mu);
+        if (e->job_err != CC_OK) { if (e->job_err == CC_ERR_STATE) fprintf(stderr, "ceracuda: malformed symbol stream\n"); return e->job_err; }
+        for (int s = 0; s < n_slices; s++) {
+            if (n + e->slice_len[s] > e->au_cap) return CC_ERR_OVERFLOW;
+            memcpy(e->au + n, e->slice_out[s], e->slice_len[s]);
+            n += e->slice_len[s];
+        }
+    } else {
+        for (int s = 0; s < n_slices; s++) {
+            size_t w = 0;
+            const int rc = write_slice_nal(e, s, e->rbsp, e->au + n, e->au_cap - n, &w);
+            if (rc != CC_OK) { if (rc == CC_ERR_STATE) fprintf(stderr, "ceracuda: malformed symbol stream\n"); return rc; }
+            n += w;
+        }
     }
     cc_rc_update(&e->rc, is_idr, e->cur_qp, (long)n * 8);
     e->frame_num = (e->frame_num + 1) & 15;

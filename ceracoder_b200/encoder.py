@@ -20,7 +20,7 @@ class CeraCudaError(RuntimeError):
 
 class Params(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("device", "width", "height", "fps_n", "fps_d", "format", "bitrate_bps", "key_int_max",
-                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max", "partitions")]
+                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max", "partitions", "threads")]
 
 
 class Frame(C.Structure):
@@ -129,6 +129,7 @@ class CudaH264Enc:
         p.bitrate_bps = int(bitrate) * 1000
         p.key_int_max, p.rows_per_slice, p.qp_fixed = key_int_max, rows_per_slice, qp_fixed
         p.partitions = int(bool(partitions))
+        p.threads = int(threads)  # x264enc's `threads`: host threads writing the slices of one access unit
         self.fmt = fmt
         self._h = C.c_void_p()
         _check(self.L, self.L.cc_enc_open(C.byref(self._h), C.byref(p)), "cc_enc_open")

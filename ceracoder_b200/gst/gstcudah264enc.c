@@ -125,6 +125,7 @@ static gboolean gst_cuda_h264_enc_set_format(GstVideoEncoder *venc, GstVideoCode
     p.bitrate_bps = g_atomic_int_get(&self->bitrate_bps);
     p.key_int_max = (int)self->key_int_max;
     p.rows_per_slice = (int)self->rows_per_slice;
+    p.threads = (int)self->threads;
     int rc = cc_enc_open(&self->enc, &p);
     if (rc != CC_OK) {
         GST_ELEMENT_ERROR(self, LIBRARY, INIT, ("cc_enc_open failed: %s", cc_strerror(rc)), ("there is no CPU fallback"));
@@ -192,7 +193,7 @@ static void gst_cuda_h264_enc_class_init(GstCudaH264EncClass *klass) {
     g_object_class_install_property(oc, PROP_KEY_INT_MAX, g_param_spec_uint("key-int-max", "Key-frame interval", "Maximum distance between IDR frames (0 = 60)", 0, G_MAXINT, 60, rw));
     g_object_class_install_property(oc, PROP_TUNE, g_param_spec_uint("tune", "Tune", "x264enc tune flags, accepted for compatibility (zerolatency = 0x4 is always in effect)", 0, 0xff, 0x4, rw));
     g_object_class_install_property(oc, PROP_BYTE_STREAM, g_param_spec_boolean("byte-stream", "Byte stream", "Always Annex-B byte-stream", TRUE, rw));
-    g_object_class_install_property(oc, PROP_THREADS, g_param_spec_uint("threads", "Threads", "Ignored (the work runs on the GPU)", 0, 1024, 0, rw));
+    g_object_class_install_property(oc, PROP_THREADS, g_param_spec_uint("threads", "Threads", "Host threads writing the slices of one access unit (0 = the streaming thread alone)", 0, 1024, 0, rw));
     g_object_class_install_property(oc, PROP_DEVICE, g_param_spec_int("device", "CUDA device", "CUDA device ordinal", 0, 63, 0, rw));
     g_object_class_install_property(oc, PROP_ROWS_PER_SLICE, g_param_spec_uint("rows-per-slice", "MB rows per slice", "Macroblock rows per slice (0 = 4)", 0, 8, 0, rw));
     gst_element_class_set_static_metadata(ec, "CUDA H.264 encoder (ceracuda)", "Codec/Encoder/Video/Hardware",

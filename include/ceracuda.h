@@ -56,6 +56,10 @@ typedef struct {
     int qp_fixed;        /* > 0: constant-QP mode (rate control off); used by parity tests */
     int qp_min, qp_max;  /* 0 -> 10 / 51 */
     int partitions;      /* 1: the motion search may split a macroblock into four 8x8 partitions (P_8x8); cc_enc_params_default sets 1 */
+    int threads;         /* host threads that write the slices of one access unit (x264enc's `threads` property: its sliced-threads
+                          * under tune=zerolatency).  0 / 1: the calling thread alone — right when one thread per stream already keeps
+                          * the host busy; 2..16: a single large stream (2160p) whose bitstream writing would otherwise take longer
+                          * than its device work.  The access unit is the same bytes either way */
 } cc_enc_params;
 
 typedef struct {

@@ -114,3 +114,21 @@ def test_bitrate_property_is_clamped_to_the_reference_range(lib):
     e.set_property("bitrate", 10 ** 6)
     assert e.get_property("bitrate") == 30000
     e.close()
+
+
+def test_slice_writer_threads_give_the_same_access_units(lib):
+    """cc_enc_params.threads (x264enc's `threads`): the slices of an access unit written by a pool of host threads are the
+    bytes the calling thread alone writes."""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    w, h = 176, 144
+    src = make_source("pan", w, h)
+    a = CudaH264Enc(w, h, lib=lib, rows_per_slice=1, threads=0)
+    b = CudaH264Enc(w, h, lib=lib, rows_per_slice=1, threads=4)
+    c = CudaH264Enc(w, h, lib=lib, rows_per_slice=4, threads=16)  # more threads than slices: clamped
+    d = CudaH264Enc(w, h, lib=lib, rows_per_slice=4)
+    for i in range(8):
+        y, u, v = src.frame(i)
+        assert a.encode(y, u, v, qp=26 + i) == b.encode(y, u, v, qp=26 + i)
+        assert c.encode(y, u, v, qp=26 + i) == d.encode(y, u, v, qp=26 + i)
+    [e.close() for e in (a, b, c, d)]

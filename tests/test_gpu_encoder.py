@@ -113,3 +113,18 @@ def test_submit_collect_and_device_frames(lib):
     for d, _ in ptrs:
         L.cc_dev_free(d)
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+def test_slice_writer_threads_give_the_same_access_units(lib):
+    """cc_enc_params.threads: 1080p, 17 slices written by 6 host threads = the bytes of the single-threaded writer"""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    w, h = 1920, 1080
+    src = make_source("pan", w, h)
+    a = CudaH264Enc(w, h, lib=lib, bitrate=12000)
+    b = CudaH264Enc(w, h, lib=lib, bitrate=12000, threads=6)
+    for i in range(12):
+        y, u, v = src.frame(i)
+        assert a.encode(y, u, v) == b.encode(y, u, v)
+    a.close(); b.close()
