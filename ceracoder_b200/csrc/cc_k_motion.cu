@@ -17,10 +17,11 @@
 #define L1_PITCHW 12       /* words per staged row: 10 of window + 2 of padding read by the last candidate group */
 #define ME_WARPS 4
 
-/* Work item = (dy, group of 4 consecutive dx): the 4 candidates share the same three aligned words of every window row, so a
- * row costs 3 LDS + 6 funnel shifts + 8 VABSDIFF4.ACC for 4 candidates (algorithmic integer ops, SURVEY.md 8d: 16 per candidate). */
+/* Work item = (pair of consecutive dy, group of 4 consecutive dx) = 8 candidates.  The 4 dx share the same three aligned words
+ * of every window row and the two dy share 7 of their 8 rows, so the item reads 9 rows: 27 LDS + 54 funnel shifts for
+ * 128 VABSDIFF4.ACC (algorithmic integer ops, SURVEY.md 8d: 16 per candidate). */
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
-    __shared__ __align__(16) uint32_t win[ME_WARPS][L1_WIN * L1_PITCHW];
+    __shared__ __align__(16) uint32_t win[ME_WARPS][(L1_WIN + 1) * L1_PITCHW]; /* + 1 row read (and discarded) by the pair that starts at dy = 32 */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
     if (mb >= nmb) return; /* whole warp exits together */
@@ -33,6 +34,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
         w[r * L1_PITCHW + c] = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
     }
     for (int r = lane; r < L1_WIN; r += 32) { w[r * L1_PITCHW + 10] = 0; w[r * L1_PITCHW + 11] = 0; }
+    if (lane < L1_PITCHW) w[L1_WIN * L1_PITCHW + lane] = 0;
     uint32_t c0[8], c1[8];
 #pragma unroll
     for (int r = 0; r < 8; r++) {
@@ -41,25 +43,34 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
     }
     __syncwarp();
     unsigned best = 0xffffffffu;
-    for (int item = lane; item < 33 * 9; item += 32) {
-        const int dy = item / 9, g = item - dy * 9; /* window coordinates: dy 0..32, dx = 4g .. 4g+3 */
+    for (int item = lane; item < 17 * 9; item += 32) {
+        const int dyp = item / 9, g = item - dyp * 9, dy = 2 * dyp; /* window coordinates: dy, dy + 1 in 0..32, dx = 4g .. 4g+3 */
         const uint32_t *p = w + dy * L1_PITCHW + g;
-        uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+        uint32_t s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
 #pragma unroll
-        for (int r = 0; r < 8; r++) {
+        for (int r = 0; r < 9; r++) {
             const uint32_t w0 = p[r * L1_PITCHW], w1 = p[r * L1_PITCHW + 1], w2 = p[r * L1_PITCHW + 2];
-            s0 = cc_sad4_acc(w0, c0[r], cc_sad4_acc(w1, c1[r], s0));
-            s1 = cc_sad4_acc(__funnelshift_r(w0, w1, 8), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 8), c1[r], s1));
-            s2 = cc_sad4_acc(__funnelshift_r(w0, w1, 16), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 16), c1[r], s2));
-            s3 = cc_sad4_acc(__funnelshift_r(w0, w1, 24), c0[r], cc_sad4_acc(__funnelshift_r(w1, w2, 24), c1[r], s3));
+            uint32_t a[4], b[4];
+            a[0] = w0; b[0] = w1;
+#pragma unroll
+            for (int i = 1; i < 4; i++) { a[i] = __funnelshift_r(w0, w1, 8 * i); b[i] = __funnelshift_r(w1, w2, 8 * i); }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if (r < 8) s[0][i] = cc_sad4_acc(a[i], c0[r], cc_sad4_acc(b[i], c1[r], s[0][i]));
+                if (r >= 1) s[1][i] = cc_sad4_acc(a[i], c0[r - 1], cc_sad4_acc(b[i], c1[r - 1], s[1][i]));
+            }
         }
-        const unsigned ady = (unsigned)cc_iabs(dy - 16), idx = (unsigned)(dy * 33 + 4 * g);
         const int dx = 4 * g - 16;
-        best = min(best, ((4u * s0 + (unsigned)cc_iabs(dx) + ady) << 11) | idx);
-        if (g < 8) { /* dx = 32 is the only candidate of the last group */
-            best = min(best, ((4u * s1 + (unsigned)cc_iabs(dx + 1) + ady) << 11) | (idx + 1));
-            best = min(best, ((4u * s2 + (unsigned)cc_iabs(dx + 2) + ady) << 11) | (idx + 2));
-            best = min(best, ((4u * s3 + (unsigned)cc_iabs(dx + 3) + ady) << 11) | (idx + 3));
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            if (dy + j > 32) continue;
+            const unsigned ady = (unsigned)cc_iabs(dy + j - 16), idx = (unsigned)((dy + j) * 33 + 4 * g);
+            best = min(best, ((4u * s[j][0] + (unsigned)cc_iabs(dx) + ady) << 11) | idx);
+            if (g < 8) { /* dx = 32 is the only candidate of the last group */
+                best = min(best, ((4u * s[j][1] + (unsigned)cc_iabs(dx + 1) + ady) << 11) | (idx + 1));
+                best = min(best, ((4u * s[j][2] + (unsigned)cc_iabs(dx + 2) + ady) << 11) | (idx + 2));
+                best = min(best, ((4u * s[j][3] + (unsigned)cc_iabs(dx + 3) + ady) << 11) | (idx + 3));
+            }
         }
     }
     best = __reduce_min_sync(FULL, best);
