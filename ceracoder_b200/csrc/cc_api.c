@@ -223,6 +223,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->me8, sizeof(cc_me8) * nmb);
     k->part8 = e->p.partitions != 0;
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
+    if (rc == CC_OK) rc = cck_me_l1_prepare(k);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->nbrec, (size_t)20 * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);

@@ -92,6 +92,8 @@ typedef struct {
     uint8_t *ref[3];   /* previous reconstruction (deblocked, borders extended) */
     uint8_t *hb, *hh, *hj; /* half-pel planes of ref: horizontal, vertical, centre */
     uint8_t *l1cur, *l1ref;
+    unsigned long long tmap_l1[16]; /* CUtensorMap (128 B, opaque here) over the allocation of l1ref: k_me_l1 loads its search windows with TMA */
+    int tmap_l1_ok;
     uint8_t *uvstage;  /* NV12 interleaved chroma staging (pitch sy), or NULL */
     uint8_t *pkstage;  /* packed-input staging (YUY2: 2 bytes / pixel, BGRx: 4), pitch pks, or NULL */
     int pks;
@@ -122,6 +124,7 @@ int cck_finish_ref(const cc_kparams *k, cudaStream_t st); /* rec -> borders, hal
 int cck_border(const cc_kparams *k, cudaStream_t st);
 int cck_hpel(const cc_kparams *k, cudaStream_t st);
 int cck_l1ref(const cc_kparams *k, cudaStream_t st);
+int cck_me_l1_prepare(cc_kparams *k); /* builds k->tmap_l1 (after the planes are allocated); CC_OK or CC_ERR_CUDA */
 int cck_me_l1(const cc_kparams *k, cudaStream_t st);
 int cck_me_l0(const cc_kparams *k, cudaStream_t st);
 int cck_motion(const cc_kparams *k, cudaStream_t st);

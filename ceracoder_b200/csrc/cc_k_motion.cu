@@ -14,34 +14,70 @@
 #include "cc_dev.cuh"
 
 #define L1_WIN 40          /* 8 + 2*16 */
-#define L1_PITCHW 12       /* words per staged row: 10 of window + 2 of padding read by the last candidate group */
+#define L1_PITCHW 20       /* words per staged row: the CTA's four macroblocks share one 64-pixel-wide window (16 words) + the 2 words the
+                            * last candidate group reads past it; 20 keeps the rows of a warp's work items on different banks */
+#define L1_ROWS (L1_WIN + 1) /* + 1 row read (and discarded) by the candidate pair that starts at dy = 32 */
+#ifndef CC_EMU_BUILD
+#include <cuda.h>          /* CUtensorMap */
+#endif
 #define ME_WARPS 4
 
 /* Work item = (pair of consecutive dy, group of 4 consecutive dx) = 8 candidates.  The 4 dx share the same three aligned words
  * of every window row and the two dy share 7 of their 8 rows, so the item reads 9 rows: 27 LDS + 54 funnel shifts for
  * 128 VABSDIFF4.ACC (algorithmic integer ops, SURVEY.md 8d: 16 per candidate). */
+/* CTA = four horizontally adjacent macroblocks (grid = (mb_w / 4, mb_h)): their search windows overlap, so the CTA stages ONE
+ * 80-byte x 41-row tile of the half-resolution reference with a single TMA load (cp.async.bulk.tensor.2d into shared memory,
+ * completion on an mbarrier) instead of 4 x 400 per-lane word loads. */
+#ifndef CC_EMU_BUILD
+__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k, const __grid_constant__ CUtensorMap tmap) {
+#else
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
-    __shared__ __align__(16) uint32_t win[ME_WARPS][(L1_WIN + 1) * L1_PITCHW]; /* + 1 row read (and discarded) by the pair that starts at dy = 32 */
+#endif
+    __shared__ __align__(128) uint32_t win[L1_ROWS * L1_PITCHW];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
-    if (mb >= nmb) return; /* whole warp exits together */
-    const int mbx = mb % k.mb_w, mby = mb / k.mb_w;
-    const uint8_t *cur = k.l1cur + (size_t)(mby * 8) * k.sc + mbx * 8;
-    const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx * 8 - CC_L1R); /* 4-byte aligned */
-    uint32_t *w = win[wid];
-    for (int i = lane; i < L1_WIN * 10; i += 32) {
-        const int r = i / 10, c = i - r * 10;
-        w[r * L1_PITCHW + c] = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
+    const int mbx0 = blockIdx.x * ME_WARPS, mbx = mbx0 + wid, mby = blockIdx.y;
+#ifndef CC_EMU_BUILD
+    __shared__ __align__(8) unsigned long long mbar;
+    const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar), win_a = (uint32_t)__cvta_generic_to_shared(win);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int r = lane; r < L1_WIN; r += 32) { w[r * L1_PITCHW + 10] = 0; w[r * L1_PITCHW + 11] = 0; }
-    if (lane < L1_PITCHW) w[L1_WIN * L1_PITCHW + lane] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) { /* tile origin in allocation coordinates: the plane starts CC_PADC rows / columns into it */
+        const int tx = CC_PADC + mbx0 * 8 - CC_L1R, ty = CC_PADC + mby * 8 - CC_L1R;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_a), "r"(L1_ROWS * L1_PITCHW * 4) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     ::"r"(win_a), "l"((unsigned long long)&tmap), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+    }
+#else
+    {
+        const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx0 * 8 - CC_L1R); /* 4-byte aligned */
+        for (int i = threadIdx.x; i < L1_ROWS * L1_PITCHW; i += blockDim.x) {
+            const int r = i / L1_PITCHW, c = i - r * L1_PITCHW;
+            win[i] = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
+        }
+        __syncthreads();
+    }
+#endif
+    if (mbx >= k.mb_w) return; /* whole warp exits together (after the CTA-wide barrier above) */
+    const int mb = mby * k.mb_w + mbx;
+    const uint8_t *cur = k.l1cur + (size_t)(mby * 8) * k.sc + mbx * 8;
+    const uint32_t *w = win + 2 * wid; /* this macroblock's 40-pixel window starts 8 pixels per macroblock into the tile */
     uint32_t c0[8], c1[8];
 #pragma unroll
     for (int r = 0; r < 8; r++) {
         c0[r] = *(const uint32_t *)(cur + (size_t)r * k.sc);
         c1[r] = *(const uint32_t *)(cur + (size_t)r * k.sc + 4);
     }
-    __syncwarp();
+#ifndef CC_EMU_BUILD
+    { /* the tile has landed when the mbarrier's phase 0 completes */
+        uint32_t ok;
+        do {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a) : "memory");
+        } while (!ok);
+    }
+#endif
     unsigned best = 0xffffffffu;
     for (int item = lane; item < 17 * 9; item += 32) {
         const int dyp = item / 9, g = item - dyp * 9, dy = 2 * dyp; /* window coordinates: dy, dy + 1 in 0..32, dx = 4g .. 4g+3 */
@@ -318,9 +354,38 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
 }
 
 extern "C" int cck_me_l1(const cc_kparams *k, cudaStream_t st) {
-    int nmb = k->mb_w * k->mb_h;
-    CC_LAUNCH(k_me_l1, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k);
+    const dim3 grid((unsigned)((k->mb_w + ME_WARPS - 1) / ME_WARPS), (unsigned)k->mb_h);
+#ifndef CC_EMU_BUILD
+    CUtensorMap tm;
+    memcpy(&tm, k->tmap_l1, sizeof tm);
+    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k, tm);
+#else
+    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k);
+#endif
     return 1;
+}
+/* Tensor map over the whole allocation of the half-resolution reference plane (pitch sc, CC_PADC border rows / columns around
+ * the picture): box = one CTA's window tile.  cuTensorMapEncodeTiled comes from the driver through the runtime's entry-point
+ * query, so the library does not link libcuda. */
+extern "C" int cck_me_l1_prepare(cc_kparams *k) {
+#ifndef CC_EMU_BUILD
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void *fn = NULL;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) return -2; /* CC_ERR_CUDA */
+    static_assert(sizeof(CUtensorMap) <= sizeof(((cc_kparams *)0)->tmap_l1), "tensor map does not fit its slot");
+    CUtensorMap tm;
+    uint8_t *base = k->l1ref - ((size_t)CC_PADC * k->sc + CC_PADC);
+    const cuuint64_t dims[2] = {(cuuint64_t)k->sc, (cuuint64_t)(k->H / 2 + 2 * CC_PADC)};
+    const cuuint64_t strides[1] = {(cuuint64_t)k->sc};
+    const cuuint32_t box[2] = {L1_PITCHW * 4, L1_ROWS}, es[2] = {1, 1};
+    if (((encode_fn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -2; /* CC_ERR_CUDA */
+    memcpy(k->tmap_l1, &tm, sizeof tm);
+#endif
+    k->tmap_l1_ok = 1;
+    return 0;
 }
 extern "C" int cck_me_l0(const cc_kparams *k, cudaStream_t st) {
     int nmb = k->mb_w * k->mb_h;
