@@ -351,8 +351,25 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
 #pragma unroll
     for (int r = 0; r < 4; r++) sx[r] = g_i4idx[l][r];
     const int md = l < 9 ? l : 2;
+    /* neighbours this lane's mode predicts from (H.264 8.3.1.2): V, DDL, VL need the top row; H, HU the left column; DDR, VR, HD both */
+    const bool need_top = md == 0 || md == 3 || md == 7 || md == 4 || md == 5 || md == 6;
+    const bool need_left = md == 1 || md == 8 || md == 4 || md == 5 || md == 6;
     uint8_t *S = m->S[half];
     int cost = 24 * c.lambda;
+    /* The block's transform chain is split over its half-warp: lane l owns coefficient l (raster: vertical frequency l >> 2,
+     * horizontal l & 3) through forward transform, quantisation and level scaling; the sixteen scaled coefficients are then
+     * gathered by shuffles for the inverse transform.  Per-lane constants of that coefficient: */
+    const int fu = l & 3, fv = l >> 2;
+    const uint32_t cfu = fu == 0 ? CC_CF0 : (fu == 1 ? CC_CF1 : (fu == 2 ? CC_CF2 : CC_CF3));
+    const uint32_t cfun = fu == 0 ? CC_CF0N : (fu == 1 ? CC_CF1N : (fu == 2 ? CC_CF2N : CC_CF3N));
+    const int av0 = fv == 1 ? 2 : 1, av1 = fv == 0 ? 1 : (fv == 1 ? 1 : (fv == 2 ? -1 : -2)); /* column fv of Cf^T: Cf[fv][0..3] */
+    const int av2 = fv == 0 ? 1 : (fv == 1 ? -1 : (fv == 2 ? -1 : 2)), av3 = fv == 0 ? 1 : (fv == 1 ? -2 : (fv == 2 ? 1 : -1));
+    const int qcls = ((l & 1) && (fv & 1)) ? 1 : (((l & 1) || (fv & 1)) ? 2 : 0);
+    const int qmf = k.qmf[0][qcls], qbias = k.qbias[0][qcls];
+    const int dqb = c.qp / 6 - 4, dqsh = dqb < 0 ? -dqb : 0;
+    const int dqv = (c_dequant_v[c.qp % 6][qcls] * 16) << (dqb > 0 ? dqb : 0);
+    const int dqrnd = dqsh ? 1 << (dqsh - 1) : 0;
+    const int spos = (int)((0xfea9db83c7426510ull >> (4 * l)) & 15u); /* scan position of raster coefficient l (inverse zigzag) */
     __syncwarp();
     /* The sixteen blocks depend on their left, top, top-left and top-right neighbours only, so blocks with equal bx + 2*by are
      * independent: 10 steps instead of 16, the two half-warps taking one block each (the predictors available to a block still
@@ -403,8 +420,7 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
         for (int r = 0; r < 4; r++) cw[r] = m->curY[(bys * 4 + r) * 4 + bxs];
         unsigned key = 0xffffffffu;
         {
-            const bool ok = l < 9 && (md == 2 || ((md == 0 || md == 3 || md == 7) && has_top) || ((md == 1 || md == 8) && has_left) ||
-                                      ((md == 4 || md == 5 || md == 6) && has_top && has_left));
+            const bool ok = l < 9 && (has_top || !need_top) && (has_left || !need_left);
             if (ok) {
 #pragma unroll
                 for (int r = 0; r < 4; r++)
@@ -425,24 +441,40 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
         if (cost >= thresh) return 1 << 30; /* uniform across the warp */
 #pragma unroll
         for (int r = 0; r < 4; r++) pw[r] = __shfl_sync(FULL, pw[r], bm, 16);
-        /* every lane of the half runs the block's transform chain on identical data; its lane 0 publishes */
-        int d[16], z[16];
-        dct4x4_res(cw, pw, d);
-        const int nnz = quant4x4(d, k.qmf[0], k.qbias[0], false);
-        to_scan(d, z, false);
-        uint32_t ow[4];
-        if (nnz) { dequant4x4(d, c.qp); idct4x4_add(d, pw, ow); }
-        else {
+        /* forward transform of this lane's coefficient (horizontal pass as byte dot products, then its column of Cf^T),
+         * quantisation, level scaling */
+        int th[4];
 #pragma unroll
-            for (int r = 0; r < 4; r++) ow[r] = pw[r];
+        for (int r = 0; r < 4; r++) th[r] = cc_dp4a_us(cw[r], cfu, cc_dp4a_us(pw[r], cfun, 0));
+        const int coef = av0 * th[0] + av1 * th[1] + av2 * th[2] + av3 * th[3];
+        const int level = quant_one(coef, qmf, qbias);
+        const int nnz = __popc((__ballot_sync(FULL, level != 0) >> (16 * half)) & 0xffffu);
+        const int dq = (level * dqv + dqrnd) >> dqsh;
+        /* inverse transform, H.264 8.5.12.2, also split: row pass in lane (row fv, column fu) from the four scaled coefficients
+         * of its quad, column pass from the four row-pass values of its column (lanes fu, fu + 4, fu + 8, fu + 12); the lane
+         * ends up with the reconstructed sample (fu, fv).  All-zero levels give residual 0: no special case. */
+        int px;
+        {
+            const int q0 = l & ~3;
+            const int a0 = __shfl_sync(FULL, dq, q0, 16), a1 = __shfl_sync(FULL, dq, q0 + 1, 16);
+            const int a2 = __shfl_sync(FULL, dq, q0 + 2, 16), a3 = __shfl_sync(FULL, dq, q0 + 3, 16);
+            const int e0 = a0 + a2, e1 = a0 - a2, e2 = (a1 >> 1) - a3, e3 = a1 + (a3 >> 1);
+            const int t = fu == 0 ? e0 + e3 : (fu == 1 ? e1 + e2 : (fu == 2 ? e1 - e2 : e0 - e3));
+            const int b0 = __shfl_sync(FULL, t, fu, 16), b1 = __shfl_sync(FULL, t, fu + 4, 16);
+            const int b2 = __shfl_sync(FULL, t, fu + 8, 16), b3 = __shfl_sync(FULL, t, fu + 12, 16);
+            const int g0 = b0 + b2, g1 = b0 - b2, g2 = (b1 >> 1) - b3, g3 = b1 + (b3 >> 1);
+            const int o = fv == 0 ? g0 + g3 : (fv == 1 ? g1 + g2 : (fv == 2 ? g1 - g2 : g0 - g3));
+            const uint32_t prow = fv == 0 ? pw[0] : (fv == 1 ? pw[1] : (fv == 2 ? pw[2] : pw[3]));
+            px = cc_clip255((int)((prow >> (8 * fu)) & 255u) + ((o + 32) >> 6));
         }
-        if (l == 0 && act) {
-            store_levels(m->c4[blk], z);
-#pragma unroll
-            for (int r = 0; r < 4; r++) *(uint32_t *)&m->tile[1 + by * 4 + r][4 + bx * 4] = ow[r];
-            m->m4[blk] = (uint8_t)bm;
-            m->m4code[blk] = (uint8_t)(bm == pm ? 8 : (bm < pm ? bm : bm - 1));
-            m->n4[blk] = (uint8_t)nnz;
+        if (act) {
+            m->c4[blk][spos] = (int16_t)level;
+            m->tile[1 + by * 4 + fv][4 + bx * 4 + fu] = (uint8_t)px;
+            if (l == 0) {
+                m->m4[blk] = (uint8_t)bm;
+                m->m4code[blk] = (uint8_t)(bm == pm ? 8 : (bm < pm ? bm : bm - 1));
+                m->n4[blk] = (uint8_t)nnz;
+            }
         }
         __syncwarp();
     }
