@@ -831,10 +831,11 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
      * L2) overlaps the previous macroblock's work instead of heading the serial chain. */
     cc_me nme = {{0, 0}, {0, 0}, 0, 0};
     cc_pre npre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
+    cc_me8 nme8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}};
     uint32_t ncur[3] = {0, 0, 0};
     auto fetch = [&](int x) {
         const int mb = row * mw + x;
-        if (!k.is_idr) { nme = k.me[mb]; npre = k.pre[mb]; }
+        if (!k.is_idr) { nme = k.me[mb]; npre = k.pre[mb]; if (k.part8) nme8 = k.me8[mb]; }
         const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + x * 16;
         ncur[0] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
         ncur[1] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
@@ -847,8 +848,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
         unsigned off = 0;
         const cc_me me = nme;
         const cc_pre pre = npre;
-        cc_me8 me8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}};
-        if (me.part) me8 = k.me8[c.mb];
+        const cc_me8 me8 = nme8; /* zeros unless me.part (k_me_l0 clears the record of an unsplit macroblock) */
         const int part = me.part;
         m->curY[lane] = ncur[0]; m->curY[lane + 32] = ncur[1]; m->curC[lane >> 4][lane & 15] = ncur[2]; /* = stage_cur */
         if (mbx + 1 < mw) fetch(mbx + 1);
