@@ -328,6 +328,13 @@ static void set_quant(cc_kparams *k) {
     cc_quant_tables(chroma_qp[k->qp], 1, k->qmf[2], k->qbias[2]);
     cc_quant_tables(chroma_qp[k->qp], 0, k->qmf[3], k->qbias[3]);
     cc_quant8_tables(k->qp, k->q8mf, k->q8bias);
+    /* level = ((bias + |c|) * mf) >> 16 >= n  <=>  |c| >= ceil(n * 65536 / mf) - bias */
+    for (int t = 0; t < 4; t++)
+        for (int c = 0; c < 3; c++)
+            for (int n = 1; n <= 2; n++) {
+                const int mf = k->qmf[t][c], thr = (n * 65536 + mf - 1) / mf - k->qbias[t][c];
+                k->qthr[t][c][n - 1] = (uint16_t)(thr < 0 ? 0 : (thr > 65535 ? 65535 : thr));
+            }
 }
 
 int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {

@@ -111,6 +111,7 @@ typedef struct {
     cc_rowhdr *rowhdr; /* device */
     int qp, is_idr;
     uint16_t qmf[4][3], qbias[4][3]; /* quantiser: 0 luma intra, 1 luma inter, 2 chroma intra, 3 chroma inter; class-indexed */
+    uint16_t qthr[4][3][2];          /* smallest |coefficient| that quantises to a level of magnitude >= 1 / >= 2 (P_Skip probes only need that much) */
     uint16_t q8mf[6], q8bias[6];     /* 8x8 transform, luma inter; class-indexed (H.264 8.5.9) */
     /* packed output in mapped pinned host memory: [cc_rowhdr * mb_h][cc_mbhost * nmb][payload rows, 16-byte aligned] */
     uint8_t *out_host_dev; /* device pointer of that mapping */

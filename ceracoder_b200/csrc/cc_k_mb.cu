@@ -674,16 +674,18 @@ __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, 
     uint16_t mf[3], bias[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) { mf[i] = chroma ? k.qmf[3][i] : k.qmf[1][i]; bias[i] = chroma ? k.qbias[3][i] : k.qbias[1][i]; }
-    int d[16], sc[17], z[16];
+    int d[16];
     dct4x4_res(cw, pw, d);
     const int dc = d[0];
-    int nnz = quant4x4(d, mf, bias, false);
-    if (chroma) { nnz -= d[0] != 0; d[0] = 0; } /* chroma AC blocks: the DC goes through the 2x2 transform below */
-    to_scan(d, sc, false);
-    sc[16] = 0;
+    /* only the positions of the non-zero levels and whether any exceeds 1 matter here: threshold compares, no quantiser */
+    uint16_t thr[3][2];
 #pragma unroll
-    for (int i = 0; i < 16; i++) z[i] = chroma ? sc[i + 1] : sc[i]; /* AC-only scan for chroma: the run lengths start at position 1 */
-    const int score = decimate_score(z);
+    for (int i = 0; i < 3; i++) { thr[i][0] = chroma ? k.qthr[3][i][0] : k.qthr[1][i][0]; thr[i][1] = chroma ? k.qthr[3][i][1] : k.qthr[1][i][1]; }
+    unsigned nzm, big;
+    quant_masks(d, thr, nzm, big);
+    if (chroma) { nzm >>= 1; big >>= 1; } /* chroma AC blocks: the DC goes through the 2x2 transform below; run lengths start at position 1 */
+    const int nnz = __popc(nzm);
+    const int score = decimate_masks(nzm, big);
     int s8 = score + __shfl_xor_sync(FULL, score, 1);
     s8 += __shfl_xor_sync(FULL, s8, 2);              /* luma: the 8x8 block's score; chroma: the plane's */
     int tot = s8 + __shfl_xor_sync(FULL, s8, 4);
@@ -723,11 +725,12 @@ __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, 
         uint32_t cw[4], pw[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) { cw[r] = m->curY[(by * 4 + r) * 4 + bx]; pw[r] = pred[(by * 4 + r) * 4 + bx]; }
-        int d[16], z[16];
+        int d[16];
         dct4x4_res(cw, pw, d);
-        int nnz = quant4x4(d, k.qmf[1], k.qbias[1], false);
-        to_scan(d, z, false);
-        const int score = decimate_score(z);
+        unsigned nzm, big;
+        quant_masks(d, k.qthr[1], nzm, big);
+        int nnz = __popc(nzm);
+        const int score = decimate_masks(nzm, big);
         int s8 = score + __shfl_xor_sync(FULL, score, 1);
         s8 += __shfl_xor_sync(FULL, s8, 2);
         int tot = s8 + __shfl_xor_sync(FULL, s8, 4);
@@ -743,12 +746,14 @@ __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, 
         uint32_t cw[4], pw[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) { cw[r] = m->curC[pl][(by * 4 + r) * 2 + bx]; pw[r] = pred[(by * 4 + r) * 2 + bx]; }
-        int d[16], z[16];
+        int d[16];
         dct4x4_res(cw, pw, d);
         const int dc = d[0];
-        int nnz = quant4x4(d, mf, bias, true);
-        to_scan(d, z, true);
-        int score = decimate_score(z);
+        unsigned nzm, big;
+        quant_masks(d, k.qthr[3], nzm, big);
+        nzm >>= 1; big >>= 1; /* AC only */
+        const int nnz = __popc(nzm);
+        int score = decimate_masks(nzm, big);
         score += __shfl_xor_sync(FULL, score, 1);
         score += __shfl_xor_sync(FULL, score, 2);
         int nac = nnz > 0;

@@ -115,6 +115,33 @@ __device__ __forceinline__ void store_levels(int16_t *dst, const int z[16]) {
 #pragma unroll
     for (int i = 0; i < 8; i++) w[i] = ((uint32_t)z[2 * i] & 0xffffu) | ((uint32_t)z[2 * i + 1] << 16);
 }
+/* What a P_Skip probe needs of the quantiser: which scan positions hold a non-zero level (nzm) and which a level of magnitude
+ * above 1 (big) — two compares per coefficient against the thresholds of cc_kparams.qthr instead of the multiply / shift / clamp /
+ * sign of quant_one.  d: raster coefficients; bit k of the masks = scan position k. */
+__device__ __forceinline__ void quant_masks(const int d[16], const uint16_t thr[3][2], unsigned &nzm, unsigned &big) {
+    const int t1[3] = {thr[0][0], thr[1][0], thr[2][0]}, t2[3] = {thr[0][1], thr[1][1], thr[2][1]};
+    nzm = 0; big = 0;
+#pragma unroll
+    for (int kk = 0; kk < 16; kk++) {
+        const int i = (int)((0xfeb7adc963258410ull >> (4 * kk)) & 15u); /* raster index of scan position kk (zigzag) */
+        const int cls = ((i & 1) && ((i >> 2) & 1)) ? 1 : (((i & 1) || ((i >> 2) & 1)) ? 2 : 0);
+        const int a = cc_iabs(d[i]);
+        nzm |= (unsigned)(a >= t1[cls]) << kk;
+        big |= (unsigned)(a >= t2[cls]) << kk;
+    }
+}
+/* decimate_score from the masks of quant_masks */
+__device__ __forceinline__ int decimate_masks(unsigned nzm, unsigned big) {
+    if (big) return 9;
+    int score = 0;
+    while (nzm) {
+        int hi = 31 - __clz((int)nzm);
+        nzm &= ~(1u << hi);
+        int run = nzm ? hi - (31 - __clz((int)nzm)) - 1 : hi;
+        score += run == 0 ? 3 : (run <= 2 ? 2 : (run <= 5 ? 1 : 0));
+    }
+    return score;
+}
 /* [EXT] x264_decimate_score over scan-ordered levels */
 __device__ __forceinline__ int decimate_score(const int z[16]) {
     unsigned nzm = 0, big = 0;
