@@ -103,42 +103,40 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
 /* One macroblock, one colour component group per warp: PL = 0 luma, PL = 1 both chroma planes (the two run in different warps
  * of the slice's CTA as independent wavefronts — in one warp their different code paths would be serialised).
  * L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
-/* The macroblock's pixels with their 4-pixel left / top context, as the lanes hold them between fetch and staging:
- * luma 20 rows x 5 words (100 words, 4 per lane), chroma 2 planes x 12 rows x 3 words (72 words, 3 per lane). */
 template <int PL>
-__device__ __forceinline__ void db_fetch(const cc_kparams &k, int lane, int mbx, int mby, uint32_t px4[4]) {
-    const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
-    if (PL == 0) {
-#pragma unroll
-        for (int it = 0; it < 4; it++) {
-            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            px4[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
-        }
-    } else {
-#pragma unroll
-        for (int it = 0; it < 3; it++) {
-            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            px4[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
-        }
-        px4[3] = 0u;
-    }
-}
-
-/* px4: the macroblock as db_fetch returned it.  The fetch may have been issued BEFORE the left neighbour was filtered (the kernel
- * loads one macroblock ahead); prev_filtered says that the neighbour's filtered tile is still in db, and the left context
- * columns are then taken from its right edge instead.  Returns whether this macroblock was filtered (db holds its tile). */
-template <int PL>
-__device__ __forceinline__ bool deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T, const uint32_t px4[4],
-                                           bool prev_filtered) {
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
-    if (c_alpha[qp] == 0) return false; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
+    if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
     const bool luma = PL == 0, act = lane < 16; /* lanes 16-31 only help with loads and stores */
     const int li = lane & 15;                 /* luma line, or chroma: plane = li >> 3, line = li & 7 */
     const int g = luma ? li >> 2 : (li & 7) >> 1;
     const int cpl = li >> 3, ci = li & 7;
     /* ---- boundary strengths first: most macroblocks of a P frame have nothing to filter ---- */
     const NbRec nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
+    { /* The common P-frame case first (warp-uniform, ~20 instructions instead of the eight strength computations): the macroblock
+       * and its left / top neighbours are inter-coded without luma coefficients and all move with one vector — every boundary
+       * strength is 0 (8.7.2.1: no intra, no coefficients, equal vectors), nothing to filter, not even a pixel to load. */
+        const uint32_t v = nq.mv[0];
+        const bool flat = (nq.x & 0xffff00ffu) < CC_MB_I16 && nq.mv[1] == v && nq.mv[2] == v && nq.mv[3] == v &&
+                          (nl.x & 0xffff00ffu) < CC_MB_I16 && nl.mv[0] == v && nl.mv[1] == v && nl.mv[2] == v && nl.mv[3] == v &&
+                          (nt.x & 0xffff00ffu) < CC_MB_I16 && nt.mv[0] == v && nt.mv[1] == v && nt.mv[2] == v && nt.mv[3] == v;
+        if (flat) return;
+    }
+    uint32_t ly[4] = {0, 0, 0, 0}, lc[3] = {0, 0, 0};
+    if (luma) {
+#pragma unroll
+        for (int it = 0; it < 4; it++) {
+            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
+            ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
+        }
+    } else {
+#pragma unroll
+        for (int it = 0; it < 3; it++) {
+            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
+            lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+        }
+    }
     const uint32_t q0 = nq.x;
     int bsv[4], bsh[4], any = 0;
     const int blk_row = g * 4; /* raster index of the first 4x4 block of this lane's block row / column */
@@ -150,32 +148,19 @@ __device__ __forceinline__ bool deblock_mb(const cc_kparams &k, DbMem *db, const
         if ((ed & 1) && ((q0 >> 8) & 1u)) bsv[ed] = bsh[ed] = 0; /* transform_size_8x8_flag: edges 1 and 3 are not transform edges */
         if (luma || !(ed & 1)) any |= bsv[ed] | bsh[ed]; /* chroma filters on the strengths of luma edges 0 and 2 only */
     }
-    if (!__any_sync(FULL, act && any)) return false;
-    /* ---- stage (left context from the neighbour's tile if that was filtered after this macroblock's pixels were fetched) ---- */
-    uint32_t st[4];
+    if (!__any_sync(FULL, act && any)) return;
+    /* ---- stage ---- */
     if (luma) {
 #pragma unroll
         for (int it = 0; it < 4; it++) {
             const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            st[it] = (prev_filtered && idx < 100 && cw == 0) ? *(const uint32_t *)&db->Y[r][16] : px4[it];
-        }
-        __syncwarp();
-#pragma unroll
-        for (int it = 0; it < 4; it++) {
-            const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = st[it];
+            if (idx < 100) *(uint32_t *)&db->Y[r][4 * cw] = ly[it];
         }
     } else {
 #pragma unroll
         for (int it = 0; it < 3; it++) {
             const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            st[it] = (prev_filtered && idx < 72 && cw == 0) ? *(const uint32_t *)&db->C[pl][r][8] : px4[it];
-        }
-        __syncwarp();
-#pragma unroll
-        for (int it = 0; it < 3; it++) {
-            const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = st[it];
+            if (idx < 72) *(uint32_t *)&db->C[pl][r][4 * cw] = lc[it];
         }
     }
     __syncwarp();
@@ -251,6 +236,5 @@ __device__ __forceinline__ bool deblock_mb(const cc_kparams &k, DbMem *db, const
         }
     }
     __syncwarp();
-    return true;
 }
 #endif

@@ -1143,24 +1143,12 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
     __syncthreads();
     if (row >= k.mb_h) return;
     volatile int *prog = progress2[pl];
-    /* software pipeline: the pixels of macroblock x + 1 are requested before macroblock x is filtered, so their L2 latency
-     * hides behind the filter.  Its top context must be final by then: the row above has to be 3 macroblocks ahead instead
-     * of 2 (3 more steps per slice against ~20 % less time per step). */
-    uint32_t cur[4], nxt[4];
-    if (w > 0) wait_progress(prog + w - 1, min(2, k.mb_w), lane);
-    if (pl) db_fetch<1>(k, lane, 0, row, nxt); else db_fetch<0>(k, lane, 0, row, nxt);
-    bool prevf = false;
     for (int mbx = 0; mbx < k.mb_w; mbx++) {
         const long long t1 = k.cyc ? clock64() : 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++) cur[i] = nxt[i];
-        if (mbx + 1 < k.mb_w) {
-            if (w > 0) wait_progress(prog + w - 1, min(mbx + 3, k.mb_w), lane);
-            if (pl) db_fetch<1>(k, lane, mbx + 1, row, nxt); else db_fetch<0>(k, lane, mbx + 1, row, nxt);
-        }
+        if (w > 0) wait_progress(prog + w - 1, min(mbx + 2, k.mb_w), lane);
         const long long t2 = k.cyc ? clock64() : 0;
-        if (pl) prevf = deblock_mb<1>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0, cur, prevf);
-        else prevf = deblock_mb<0>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0, cur, prevf);
+        if (pl) deblock_mb<1>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
+        else deblock_mb<0>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
         __threadfence_block();
         if (lane == 0) prog[w] = mbx + 1;
         if (k.cyc && lane == 0 && !pl) {
