@@ -128,3 +128,11 @@ def test_slice_writer_threads_give_the_same_access_units(lib):
         y, u, v = src.frame(i)
         assert a.encode(y, u, v) == b.encode(y, u, v)
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,rps", [(16, 16, 4), (18, 16, 1), (32, 18, 2), (48, 16, 8), (8192 // 4, 16, 4)])
+def test_minimum_and_odd_sizes(lib, w, h, rps):
+    """smallest legal pictures, sizes that are not macroblock multiples, one very wide macroblock row: the TMA window tiles of the
+    coarse search hang over every edge of the padded plane here"""
+    run_parity(lib, "pan", w, h, [30, 31, 22], rps=rps)
