@@ -42,6 +42,7 @@ struct __align__(16) WarpMem {
     uint8_t m4[16];        /* intra-4x4 candidate modes */
     uint8_t m4code[16];    /* syntax nibble per block: 8 = predicted mode, else rem_intra4x4_pred_mode */
     uint8_t n4[16];
+    uint4 pf[4][4];        /* ring of prefetched per-macroblock records (cc_me, cc_pre, cc_me8 = 16 + 16 + 32 bytes), filled by cp.async */
 };
 
 /* intra 4x4 predictors as 3-tap filters over the edge array E (H.264 8.3.1.2):
@@ -831,29 +832,51 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
     unsigned total = 0, n_skip = 0, n_inter = 0, n_intra = 0, n_gate = 0, n_probe = 0;
     NbRec *nbl = nbline + w * mw;
     const NbRec *nbu = nbl - mw;
-    /* Software pipeline: everything a macroblock needs from global memory that does not depend on its neighbours (search
-     * result, pre-pass record, source pixels) is loaded one macroblock ahead, so its latency (HBM when 8 streams share the
-     * L2) overlaps the previous macroblock's work instead of heading the serial chain. */
-    cc_me nme = {{0, 0}, {0, 0}, 0, 0};
-    cc_pre npre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
-    cc_me8 nme8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}};
+    /* Software pipeline: everything a macroblock needs from global memory that does not depend on its neighbours is requested
+     * ahead of its turn, so the latency (HBM when 8 streams share the L2) overlaps earlier macroblocks' work instead of heading
+     * the serial chain: the search / pre-pass records three macroblocks ahead by cp.async into a shared-memory ring (no register
+     * waits on them until they are read), the source pixels one macroblock ahead in registers. */
     uint32_t ncur[3] = {0, 0, 0};
     auto fetch = [&](int x) {
-        const int mb = row * mw + x;
-        if (!k.is_idr) { nme = k.me[mb]; npre = k.pre[mb]; if (k.part8) nme8 = k.me8[mb]; }
         const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + x * 16;
         ncur[0] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
         ncur[1] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
         ncur[2] = *(const uint32_t *)(k.cur[1 + (lane >> 4)] + (size_t)(row * 8 + ((lane >> 1) & 7)) * k.sc + x * 8 + 4 * (lane & 1));
     };
+    auto fetch_rec = [&](int x) { /* one commit group per call, also when there is nothing left to request */
+        if (x < mw && lane < (k.part8 ? 4 : 2)) {
+            const int mb = row * mw + x;
+            const void *src = lane == 0 ? (const void *)(k.me + mb) : (lane == 1 ? (const void *)(k.pre + mb) : (const void *)((const uint4 *)(k.me8 + mb) + (lane - 2)));
+#ifndef CC_EMU_BUILD
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&m->pf[x & 3][lane])), "l"(src) : "memory");
+#else
+            m->pf[x & 3][lane] = *(const uint4 *)src;
+#endif
+        }
+#ifndef CC_EMU_BUILD
+        asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+    };
     fetch(0);
+    if (!k.is_idr) { fetch_rec(0); fetch_rec(1); fetch_rec(2); }
     for (int mbx = 0; mbx < mw; mbx++) {
         c.mbx = mbx; c.px = mbx * 16; c.mb = row * mw + mbx; c.L = mbx > 0; c.TR = c.T && mbx + 1 < mw;
         int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
         unsigned off = 0;
-        const cc_me me = nme;
-        const cc_pre pre = npre;
-        const cc_me8 me8 = nme8; /* zeros unless me.part (k_me_l0 clears the record of an unsplit macroblock) */
+        cc_me me = {{0, 0}, {0, 0}, 0, 0};
+        cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
+        cc_me8 me8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}}; /* zeros unless me.part (k_me_l0 clears the record of an unsplit macroblock) */
+        if (!k.is_idr) {
+            fetch_rec(mbx + 3);
+#ifndef CC_EMU_BUILD
+            asm volatile("cp.async.wait_group 3;" ::: "memory"); /* all but the three newest groups: this macroblock's records are in */
+#endif
+            __syncwarp();
+            const uint4 *pf = m->pf[mbx & 3];
+            *(uint4 *)&me = pf[0];
+            *(uint4 *)&pre = pf[1];
+            if (k.part8) { ((uint4 *)&me8)[0] = pf[2]; ((uint4 *)&me8)[1] = pf[3]; }
+        }
         const int part = me.part;
         m->curY[lane] = ncur[0]; m->curY[lane + 32] = ncur[1]; m->curC[lane >> 4][lane & 15] = ncur[2]; /* = stage_cur */
         if (mbx + 1 < mw) fetch(mbx + 1);
