@@ -6,7 +6,7 @@ B="python bench.py --steps 1 --warmup 1 --streams 2 --frames-per-step 6 --no-cpu
 $B > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || exit 1
 CC_DEBUG_CYCLES=1 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_cycles.json 2> gpurun_out/${TAG}_cycles.err
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $B > gpurun_out/${TAG}_ncu1.log 2>&1
-for kn in k_mb_encode k_deblock k_p_code k_me_l1 k_me_l0; do
+for kn in k_mb_encode k_deblock k_p_code k_me_l1 k_me_l0 k_hpel k_ingest k_border k_l1ref k_pack; do
   ncu --set full --clock-control none --import-source on -k regex:$kn -s 8 -c 2 -f -o gpurun_out/${TAG}_$kn $B > gpurun_out/${TAG}_ncu_$kn.log 2>&1
 done
 ls -la gpurun_out

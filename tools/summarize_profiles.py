@@ -22,7 +22,7 @@ CMD = "python bench.py --steps 1 --warmup 1 --streams 2 --frames-per-step 6 --no
 METRICS = [
     "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
     "launch__shared_mem_per_block_static", "launch__shared_mem_per_block_dynamic",
-    "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+    "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed", "dram__bytes.sum.per_second",
     "lts__t_bytes.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
     "smsp__inst_executed.sum", "sm__inst_executed_pipe_alu.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
@@ -94,7 +94,7 @@ if __name__ == "__main__":
     os.makedirs(P, exist_ok=True)
     launches()
     traffic = {}
-    for kn in ("k_mb_encode", "k_deblock", "k_p_code", "k_me_l1", "k_me_l0"):
+    for kn in ("k_mb_encode", "k_deblock", "k_p_code", "k_me_l1", "k_me_l0", "k_hpel", "k_ingest", "k_border", "k_l1ref", "k_pack"):
         kernel(kn, traffic)
     json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
     for f in (f"{tag}_cycles.err",):
