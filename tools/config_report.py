@@ -8,7 +8,8 @@ handle_frame does).  Prints one JSON object per config: achieved kbit/s, bitrate
 left out of the error: the rate control starts from its initial QP), Y-PSNR of the reconstruction against the source (the decoder
 reproduces the reconstruction bit for bit - tests/test_gpu_encoder.py), host milliseconds per frame.  Not a bench.py line
 (bench.py reports the 8-stream throughput workload and the 2 <-> 12 Mbps step response of config 2).
-usage (under gpurun): python tools/config_report.py [seconds]"""
+With a second argument, per-frame `frame,bits,qp,is_idr` lines of every config are written to that file (rate-control analysis).
+usage (under gpurun): python tools/config_report.py [seconds [frames.csv]]"""
 import json
 import os
 import sys
@@ -29,6 +30,7 @@ CASES = [("config1_1080p30_6mbps", "testsrc", 1920, 1080, 30, 6000),
 def main():
     secs = float(sys.argv[1]) if len(sys.argv) > 1 else 6.0
     L = load_library()
+    dump = open(sys.argv[2], "w") if len(sys.argv) > 2 else None
     for name, source, w, h, fps, kbps in CASES:
         src = make_source(source, w, h)
         n = int(secs * fps)
@@ -45,6 +47,8 @@ def main():
             au = enc.encode(y, u, v, pts=i)
             ms.append(1e3 * (time.perf_counter() - t0))
             bits.append(8 * len(au)); qps.append(int(enc.last.qp))
+            if dump:
+                dump.write(f"{name},{i},{8 * len(au)},{int(enc.last.qp)},{int(enc.last.is_idr)}\n")
             if i % 6 == 5:
                 ry = enc.recon()[0][:h, :w]
                 mse = float(((ry.astype(np.float32) - y.astype(np.float32)) ** 2).mean())
