@@ -179,6 +179,14 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (p->format < CC_FMT_I420 || p->format > CC_FMT_BGRX) return CC_ERR_PARAM;
     if (p->fps_n <= 0 || p->fps_d <= 0) return CC_ERR_PARAM;
     if (p->rows_per_slice < 0 || p->rows_per_slice > 8) return CC_ERR_PARAM; /* one warp per MB row, at most 8 rows (256 threads) per slice CTA */
+    { /* the SPS must be able to name a level that covers the stream: nothing beyond level 5.2 (Table A-1: 36 864 macroblocks per
+       * picture, 2 073 600 per second — 2160p60 fits, 8192 x 8192 does not) */
+        const long fs = (long)((p->width + 15) / 16) * ((p->height + 15) / 16);
+        if (!cc_level_idc_for(fs, (fs * p->fps_n + p->fps_d - 1) / p->fps_d)) {
+            fprintf(stderr, "ceracuda: %dx%d at %d/%d fps is beyond H.264 level 5.2\n", p->width, p->height, p->fps_n, p->fps_d);
+            return CC_ERR_PARAM;
+        }
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || p->device < 0 || p->device >= ndev) {
         fprintf(stderr, "ceracuda: no usable CUDA device (count %d, asked for %d); there is no CPU fallback\n", ndev, p->device);
@@ -425,10 +433,21 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
 
 static int is_idr_prof(const cc_enc *e) { return e->cur_is_idr; }
 
+static int collect_inner(cc_enc *e, cc_packet *out);
 int cc_enc_collect(cc_enc *e, cc_packet *out) {
     if (!e || !out) return CC_ERR_PARAM;
     if (!e->inflight) return CC_ERR_STATE;
     if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
+    const int rc = collect_inner(e, out);
+    if (rc != CC_OK) {
+        /* The frame's reconstruction already replaced the reference in cc_enc_submit, but no access unit leaves the encoder:
+         * a following P frame would predict from a picture the decoder never received.  Restart the stream with an IDR. */
+        e->inflight = 0;
+        e->have_ref = 0;
+    }
+    return rc;
+}
+static int collect_inner(cc_enc *e, cc_packet *out) {
     cc_kparams *k = &e->k;
     const double t_wait = now_ms();
     /* The device needs ~2 ms per frame and the driver's wait spins: with one host thread per stream and several streams

@@ -1,7 +1,8 @@
 /*
  * cc_bitstream.c — sequence/picture parameter sets, slice header and Annex-B NAL packaging
  * (ITU-T H.264 7.3.2.1, 7.3.2.2, 7.3.3, 7.4.1, Annex B).  Host C.
- * Stream shape: Constrained Baseline, one reference frame, POC type 2, CAVLC, slices of whole MB rows,
+ * Stream shape: High profile (profile_idc 100: transform_8x8_mode on, entropy coding CAVLC), one reference frame, POC type 2,
+ * slices of whole MB rows,
  * in-loop deblocking confined to the slice (disable_deblocking_filter_idc = 2) so that slices are
  * independent work units for the GPU.  Downstream in the reference pipeline is
  * `h264parse config-interval=-1 ! mpegtsmux` (/root/reference/pipeline/generic/x264_veryfast_v4l_mjpeg_1080p30:6-7),
@@ -9,14 +10,22 @@
  */
 #include "cc_host.h"
 
+/* Table A-1: {level_idc, MaxMBPS, MaxFS, MaxBR}; MaxBR in units of 1250 bit/s for High profile (cpbBrVclFactor, Table A-2).
+ * The bitrate the level must cover is the largest one the `bitrate` property can be set to at run time: 30 Mbit/s
+ * (/root/reference/src/core/bitrate_control.h:31), not the value the stream starts with. */
+static const int cc_levels[][4] = {{30, 40500, 1620, 10000},   {31, 108000, 3600, 14000},  {32, 216000, 5120, 20000},
+                                   {40, 245760, 8192, 20000},  {41, 245760, 8192, 50000},  {42, 522240, 8704, 50000},
+                                   {50, 589824, 22080, 135000}, {51, 983040, 36864, 240000}, {52, 2073600, 36864, 240000}};
+#define CC_LEVEL_MAX_BPS 30000000L
+int cc_level_idc_for(long fs, long mbps) {
+    for (int i = 0; i < 9; i++)
+        if (fs <= cc_levels[i][2] && mbps <= cc_levels[i][1] && CC_LEVEL_MAX_BPS <= 1250L * cc_levels[i][3]) return cc_levels[i][0];
+    return 0; /* beyond level 5.2 */
+}
 static int cc_level_idc(const cc_seq *s) {
-    /* Table A-1: {level, MaxMBPS, MaxFS} */
-    static const int t[][3] = {{30, 40500, 1620},  {31, 108000, 3600},  {32, 216000, 5120},  {40, 245760, 8192},
-                               {42, 522240, 8704}, {50, 589824, 22080}, {51, 983040, 36864}, {52, 2073600, 36864}};
-    long fs = (long)s->mb_w * s->mb_h, mbps = fs * s->fps_n / (s->fps_d ? s->fps_d : 1);
-    for (int i = 0; i < 8; i++)
-        if (fs <= t[i][2] && mbps <= t[i][1]) return t[i][0];
-    return 52;
+    long fs = (long)s->mb_w * s->mb_h, mbps = (fs * s->fps_n + (s->fps_d ? s->fps_d : 1) - 1) / (s->fps_d ? s->fps_d : 1);
+    int l = cc_level_idc_for(fs, mbps);
+    return l ? l : 52; /* cc_enc_open rejects such streams; kept total for callers that bypass it */
 }
 
 size_t cc_write_sps(const cc_seq *s, uint8_t *rbsp, size_t cap) {

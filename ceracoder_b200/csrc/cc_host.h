@@ -49,6 +49,8 @@ static inline size_t cc_bw_finish(cc_bw *b) {
 typedef struct {
     int w, h, mb_w, mb_h, fps_n, fps_d;
 } cc_seq;
+/* level_idc (Table A-1) that covers a picture of fs macroblocks at mbps macroblocks/s and 30 Mbit/s; 0 = beyond level 5.2 */
+int cc_level_idc_for(long fs, long mbps);
 size_t cc_write_sps(const cc_seq *s, uint8_t *rbsp, size_t cap);
 size_t cc_write_pps(uint8_t *rbsp, size_t cap);
 void cc_write_slice_header(cc_bw *b, int first_mb, int is_idr, int frame_num, int idr_pic_id, int qp);

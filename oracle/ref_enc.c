@@ -211,10 +211,14 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
 
 /* ---- headers ------------------------------------------------------------------------ */
 static int level_idc(const ref_enc *e) {
-    static const int tab[][3] = {{30, 40500, 1620},   {31, 108000, 3600},  {32, 216000, 5120},  {40, 245760, 8192},
-                                 {42, 522240, 8704},  {50, 589824, 22080}, {51, 983040, 36864}, {52, 2073600, 36864}};
-    long fs = (long)e->mb_w * e->mb_h, mbps = fs * e->fps_n / (e->fps_d ? e->fps_d : 1);
-    for (int i = 0; i < 8; i++) if (fs <= tab[i][2] && mbps <= tab[i][1]) return tab[i][0];
+    /* Table A-1 {level, MaxMBPS, MaxFS, MaxBR (x1250 bit/s, High profile)}; the level covers 30 Mbit/s, the largest bitrate
+     * ceracoder may ask for at run time (/root/reference/src/core/bitrate_control.h:31) */
+    static const int tab[][4] = {{30, 40500, 1620, 10000},    {31, 108000, 3600, 14000},   {32, 216000, 5120, 20000},
+                                 {40, 245760, 8192, 20000},   {41, 245760, 8192, 50000},   {42, 522240, 8704, 50000},
+                                 {50, 589824, 22080, 135000}, {51, 983040, 36864, 240000}, {52, 2073600, 36864, 240000}};
+    int fd = e->fps_d ? e->fps_d : 1;
+    long fs = (long)e->mb_w * e->mb_h, mbps = (fs * e->fps_n + fd - 1) / fd;
+    for (int i = 0; i < 9; i++) if (fs <= tab[i][2] && mbps <= tab[i][1] && 30000000L <= 1250L * tab[i][3]) return tab[i][0];
     return 52;
 }
 static int write_sps(const ref_enc *e, uint8_t *o) {
