@@ -4,7 +4,7 @@ NVCC ?= /usr/local/cuda/bin/nvcc
 CC = /usr/bin/gcc
 CXX = /usr/bin/g++
 SRC = ceracoder_b200/csrc
-CU = $(SRC)/cc_k_frame.cu $(SRC)/cc_k_motion.cu $(SRC)/cc_k_mb.cu $(SRC)/cc_k_prims.cu
+CU = $(SRC)/cc_k_frame.cu $(SRC)/cc_k_motion.cu $(SRC)/cc_k_mb.cu $(SRC)/cc_k_cavlc.cu $(SRC)/cc_k_prims.cu
 CS = $(SRC)/cc_api.c $(SRC)/cc_bitstream.c $(SRC)/cc_cavlc.c $(SRC)/cc_rc.c
 HDR = $(wildcard $(SRC)/*.h $(SRC)/*.cuh include/*.h)
 NVFLAGS = -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-O2 -Xptxas -v
@@ -17,7 +17,7 @@ $(LIB): $(CU) $(CS) $(HDR)
 	mkdir -p build
 	for f in $(CS); do $(CC) -O2 -fPIC -std=gnu11 -Wall -I/usr/local/cuda/include -c $$f -o build/$$(basename $$f .c).o || exit 1; done
 	for f in $(CU); do $(NVCC) $(NVFLAGS) -c $$f -o build/$$(basename $$f .cu).o 2> build/$$(basename $$f .cu).ptxas.log || { cat build/$$(basename $$f .cu).ptxas.log; exit 1; }; done
-	$(NVCC) -shared -o $@ build/cc_api.o build/cc_bitstream.o build/cc_cavlc.o build/cc_rc.o build/cc_k_frame.o build/cc_k_motion.o build/cc_k_mb.o build/cc_k_prims.o -lm -lpthread
+	$(NVCC) -shared -o $@ build/cc_api.o build/cc_bitstream.o build/cc_cavlc.o build/cc_rc.o build/cc_k_frame.o build/cc_k_motion.o build/cc_k_mb.o build/cc_k_cavlc.o build/cc_k_prims.o -lm -lpthread
 oracle:
 	$(MAKE) -C oracle
 emu: $(EMU)

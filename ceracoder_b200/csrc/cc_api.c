@@ -23,7 +23,7 @@ struct cc_enc {
     cc_seq seq;
     cudaStream_t st;
     cudaEvent_t ev0, ev1;
-    void *dev_alloc[32];
+    void *dev_alloc[48];
     int n_dev_alloc;
     size_t dev_bytes;
     uint8_t *out_host;   /* mapped pinned: packed symbols */
@@ -55,6 +55,7 @@ struct cc_enc {
     unsigned job_gen;
     int job_stop, job_next, job_left, job_ns, job_is_idr, job_err;
     const cc_mbhost *job_mbh; const cc_rowhdr *job_rh; const uint8_t *const *job_rowp;
+    const uint32_t *job_slen; const uint8_t *job_sdata; /* device entropy: per-slice RBSP bytes and the slices' data in the mapped buffer */
     uint8_t **slice_out; size_t *slice_len; size_t slice_cap; /* per slice: its NAL unit */
     uint8_t *worker_rbsp[17];    /* scratch RBSP per thread (index n_workers = the collecting thread) */
     float submit_ms;
@@ -62,6 +63,8 @@ struct cc_enc {
     float dev_ms_hist[4];        /* device latency (submit -> access unit ready) of the last frames: how long collect may sleep */
     unsigned dev_ms_n;
     int sleep_wait;              /* CERACUDA_WAIT=spin turns the sleep off */
+    int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
+    size_t bs_bytes;
     int tail_pending;            /* profile: the stages after ev1 (reference finishing) of the previous frame are not read yet */
 };
 
@@ -89,7 +92,7 @@ void cc_enc_params_default(cc_enc_params *p) {
 }
 
 static int dev_alloc(cc_enc *e, void **p, size_t n) {
-    if (e->n_dev_alloc >= 32) return CC_ERR_NOMEM;
+    if (e->n_dev_alloc >= 48) return CC_ERR_NOMEM;
     if (cudaMalloc(p, n) != cudaSuccess) { fprintf(stderr, "ceracuda: cudaMalloc(%zu) failed\n", n); return CC_ERR_NOMEM; }
     e->dev_alloc[e->n_dev_alloc++] = *p;
     e->dev_bytes += n;
@@ -100,17 +103,23 @@ static size_t roundup(size_t v, size_t a) { return (v + a - 1) / a * a; }
 /* ---- slice-writer pool ------------------------------------------------------------------------------ */
 /* Slices are independent (no prediction, no CAVLC context across slice borders; the per-MB total_coeff array is written
  * by the slice that owns the macroblock), so their NAL units can be written concurrently and concatenated in order. */
-static int write_slice_nal(cc_enc *e, int s, uint8_t *rbsp, uint8_t *out, size_t cap, size_t *len) {
+static int write_slice_nal(cc_enc *e, int s, uint8_t *rbsp, uint8_t *out, size_t cap, size_t *len_out) {
     const cc_kparams *k = &e->k;
     const int r0 = s * k->rps, r1 = r0 + k->rps < k->mb_h ? r0 + k->rps : k->mb_h, is_idr = e->job_is_idr;
+    if (k->dev_entropy) { /* the slice's RBSP is already in host memory (k_cavlc_write): start code, NAL header, emulation prevention */
+        const uint32_t len = e->job_slen[s];
+        if (len == 0 || len > (size_t)k->bs_slice_words * 4) return CC_ERR_STATE;
+        *len_out = cc_write_nal(out, cap, is_idr ? 0x65 : 0x41, e->job_sdata + (size_t)s * k->bs_slice_words * 4, len);
+        return *len_out ? CC_OK : CC_ERR_OVERFLOW;
+    }
     cc_bw b;
     cc_bw_init(&b, rbsp, e->rbsp_cap);
     cc_write_slice_header(&b, r0 * k->mb_w, is_idr, e->frame_num, e->idr_pic_id, e->cur_qp);
     if (cc_cavlc_write_slice(&e->cav, &b, is_idr, r0, r1, e->job_mbh, e->job_rh, e->job_rowp) != 0) return CC_ERR_STATE;
     const size_t m = cc_bw_finish(&b);
     if (b.overflow) return CC_ERR_OVERFLOW;
-    *len = cc_write_nal(out, cap, is_idr ? 0x65 : 0x41, rbsp, m);
-    return *len ? CC_OK : CC_ERR_OVERFLOW;
+    *len_out = cc_write_nal(out, cap, is_idr ? 0x65 : 0x41, rbsp, m);
+    return *len_out ? CC_OK : CC_ERR_OVERFLOW;
 }
 static void pool_take_slices(cc_enc *e, int tid) {
     for (;;) {
@@ -242,15 +251,27 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[2], (size_t)k->mb_h * k->sc);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->uright, (size_t)nmb * 32);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowhdr, sizeof(cc_rowhdr) * k->mb_h);
+    k->dev_entropy = !e->p.host_entropy;
+    const int n_slices_open = (k->mb_h + k->rps - 1) / k->rps;
+    if (k->dev_entropy) {
+        k->bs_slice_words = (uint32_t)roundup((size_t)k->rps * k->mb_w * (CC_BS_BYTES_PER_MB / 4) + 16, 4);
+        e->bs_bytes = (size_t)n_slices_open * k->bs_slice_words * 4;
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbbits, sizeof(uint32_t) * nmb);
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->bs, e->bs_bytes);
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->bs_ctl, sizeof(uint32_t) * 2 * n_slices_open);
+        if (rc == CC_OK) { cudaMemset(k->bs, 0, e->bs_bytes); cudaMemset(k->bs_ctl, 0, sizeof(uint32_t) * 2 * n_slices_open); }
+    }
     if (rc == CC_OK && getenv("CC_DEBUG_CYCLES")) { rc = dev_alloc(e, (void **)&k->cyc, (size_t)k->mb_h * 16 * 8); if (rc == CC_OK) cudaMemset(k->cyc, 0, (size_t)k->mb_h * 16 * 8); }
     if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->me8, 0, sizeof(cc_me8) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
     /* packed symbol buffer: headers + per-MB records + payload (worst case) */
     e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(cc_mbhost) * nmb, 16) + (size_t)nmb * CC_ROW_PAYLOAD_PER_MB + 16 * k->mb_h);
+    /* device entropy: [row headers][slice byte counts][slice RBSPs at fixed distances] */
+    if (k->dev_entropy) e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(uint32_t) * n_slices_open, 16) + e->bs_bytes);
     if (rc == CC_OK && cudaHostAlloc((void **)&e->out_host, e->out_cap, cudaHostAllocMapped) != cudaSuccess) rc = CC_ERR_NOMEM;
     if (rc == CC_OK && cudaHostGetDevicePointer((void **)&k->out_host_dev, e->out_host, 0) != cudaSuccess) rc = CC_ERR_CUDA;
     k->out_cap = e->out_cap;
-    e->au_cap = (size_t)nmb * 1024 + 4096;
-    e->rbsp_cap = (size_t)k->rps * k->mb_w * 1024 + 4096;
+    e->au_cap = (size_t)nmb * CC_BS_BYTES_PER_MB * 3 / 2 + 4096; /* every slice's worst case, with emulation prevention */
+    e->rbsp_cap = (size_t)k->rps * k->mb_w * CC_BS_BYTES_PER_MB + 4096;
     e->au = (uint8_t *)malloc(e->au_cap);
     e->rbsp = (uint8_t *)malloc(e->rbsp_cap);
     e->cav.mb_w = k->mb_w; e->cav.mb_h = k->mb_h; e->cav.rps = k->rps;
@@ -368,6 +389,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (qp < 10) qp = 10;
     if (qp > 51) qp = 51;
     k->qp = qp; k->is_idr = is_idr;
+    k->frame_num = e->frame_num; k->idr_pic_id = e->idr_pic_id;
     set_quant(k);
     e->cur_is_idr = is_idr; e->cur_qp = qp; e->cur_pts = in->pts;
 
@@ -378,6 +400,12 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
             if (e->pev_used[i] && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
         }
         e->tail_pending = 0;
+    }
+    if (e->bs_dirty && k->dev_entropy) {
+        const int nsl = (k->mb_h + k->rps - 1) / k->rps;
+        CUCHECK(cudaMemsetAsync(k->bs, 0, e->bs_bytes, e->st));
+        CUCHECK(cudaMemsetAsync(k->bs_ctl, 0, sizeof(uint32_t) * 2 * nsl, e->st));
+        e->bs_dirty = 0;
     }
     CUCHECK(cudaEventRecord(e->ev0, e->st));
     if (e->profile) { cudaEventRecord(e->pev[CC_STAGE_UPLOAD], e->st); }
@@ -405,7 +433,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
     STAGE(CC_STAGE_PACK);
-    e->launches += cck_pack(k, e->st);
+    e->launches += k->dev_entropy ? cck_cavlc(k, e->st) : cck_pack(k, e->st);
     STAGE(CC_STAGE_DEBLOCK);
     /* the access unit's symbols are in host memory here: cc_enc_collect waits for ev1 only, and the kernels that turn the
      * reconstruction into the next frame's reference run while the host writes the bitstream */
@@ -444,6 +472,7 @@ int cc_enc_collect(cc_enc *e, cc_packet *out) {
          * a following P frame would predict from a picture the decoder never received.  Restart the stream with an IDR. */
         e->inflight = 0;
         e->have_ref = 0;
+        e->bs_dirty = 1;
     }
     return rc;
 }
@@ -482,13 +511,22 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
     const uint8_t *pay = (const uint8_t *)mbh + roundup(sizeof(cc_mbhost) * nmb, 16);
     const uint8_t *rowp[512];
     if (k->mb_h > 512) return CC_ERR_PARAM;
+    const int n_slices = (k->mb_h + k->rps - 1) / k->rps;
     int ns = 0, ni = 0, np = 0, ng = 0, npr = 0;
+    size_t dev_bytes_out = 0;
     for (int r = 0; r < k->mb_h; r++) {
+        ns += (int)rh[r].n_skip; np += (int)rh[r].n_inter; ni += (int)rh[r].n_intra; ng += (int)rh[r].n_gate; npr += (int)rh[r].n_probe;
+        if (k->dev_entropy) continue;
         rowp[r] = pay;
         pay += roundup(rh[r].bytes, 16);
-        ns += (int)rh[r].n_skip; np += (int)rh[r].n_inter; ni += (int)rh[r].n_intra; ng += (int)rh[r].n_gate; npr += (int)rh[r].n_probe;
         if ((size_t)(pay - e->out_host) > e->out_cap) return CC_ERR_OVERFLOW;
     }
+    if (k->dev_entropy) {
+        e->job_slen = (const uint32_t *)(e->out_host + roundup(sizeof(cc_rowhdr) * k->mb_h, 16));
+        e->job_sdata = (const uint8_t *)e->job_slen + roundup(sizeof(uint32_t) * n_slices, 16);
+        dev_bytes_out = roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(uint32_t) * n_slices, 16);
+        for (int s = 0; s < n_slices; s++) dev_bytes_out += roundup(e->job_slen[s], 16);
+    } else dev_bytes_out = (size_t)(pay - e->out_host);
     size_t n = 0;
     uint8_t hdr[64];
     if (is_idr) {
@@ -502,7 +540,6 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
         n += w;
     }
     e->job_is_idr = is_idr; e->job_mbh = mbh; e->job_rh = rh; e->job_rowp = rowp;
-    const int n_slices = (k->mb_h + k->rps - 1) / k->rps;
     if (e->n_workers) { /* cc_enc_params.threads > 1: the slices are written concurrently, then joined in order */
         pthread_mutex_lock(&e->job_mu);
         e->job_ns = n_slices; e->job_left = n_slices; e->job_err = CC_OK; e->job_gen++;
@@ -534,7 +571,7 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
     e->frame_idx++;
     out->data = e->au; out->size = (int)n; out->is_idr = is_idr; out->qp = e->cur_qp; out->pts = e->cur_pts;
     out->n_skip = ns; out->n_inter = np; out->n_intra = ni; out->n_intra_analysed = ng; out->n_skip_probed = npr;
-    out->sym_bytes = (int)(pay - e->out_host);
+    out->sym_bytes = (int)dev_bytes_out;
     out->gpu_ms = gpu_ms; out->host_ms = (float)(now_ms() - t0);
     return CC_OK;
 }

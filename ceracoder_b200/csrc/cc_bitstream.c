@@ -9,6 +9,7 @@
  * so SPS/PPS are repeated in-band at every IDR.
  */
 #include "cc_host.h"
+#include <string.h>
 
 /* Table A-1: {level_idc, MaxMBPS, MaxFS, MaxBR}; MaxBR in units of 1250 bit/s for High profile (cpbBrVclFactor, Table A-2).
  * The bitrate the level must cover is the largest one the `bitrate` property can be set to at run time: 30 Mbit/s
@@ -110,11 +111,18 @@ void cc_write_slice_header(cc_bw *b, int first_mb, int is_idr, int frame_num, in
 
 size_t cc_write_nal(uint8_t *out, size_t cap, int nal_hdr, const uint8_t *rbsp, size_t n) {
     if (cap < n + n / 2 + 8) return 0;
-    size_t k = 0;
+    size_t k = 0, i = 0;
     int zeros = 0;
     out[k++] = 0; out[k++] = 0; out[k++] = 0; out[k++] = 1; out[k++] = (uint8_t)nal_hdr;
-    for (size_t i = 0; i < n; i++) {
-        uint8_t v = rbsp[i];
+    while (i < n) { /* emulation prevention (7.4.1): 00 00 0x -> 00 00 03 0x for x <= 3 */
+        if (!zeros) { /* no zero pending: everything up to the next zero byte is copied as it is (memchr / memcpy run at SIMD speed) */
+            const uint8_t *z = (const uint8_t *)memchr(rbsp + i, 0, n - i);
+            const size_t j = z ? (size_t)(z - rbsp) : n;
+            memcpy(out + k, rbsp + i, j - i);
+            k += j - i; i = j;
+            if (i >= n) break;
+        }
+        const uint8_t v = rbsp[i++];
         if (zeros >= 2 && v <= 3) { out[k++] = 3; zeros = 0; }
         out[k++] = v;
         zeros = v ? 0 : zeros + 1;

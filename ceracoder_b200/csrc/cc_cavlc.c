@@ -1,7 +1,7 @@
 /*
  * cc_cavlc.c — host CAVLC writer: macroblock_layer() and residual_block_cavlc()
  * of ITU-T H.264 7.3.5 / 9.2, fed by the compact per-row symbol stream the encode kernel emits
- * (per coded 4x4 block: a 16-bit significance mask in scan order + the non-zero levels).
+ * (per macroblock: the 16-bit significance masks of its coded 4x4 blocks in scan order, then their non-zero levels).
  * north_star keeps the bitstream writer on the host in C; what crosses PCIe is ~1-3x the final
  * bitstream, not dense coefficients.
  */
@@ -121,12 +121,17 @@ int cc_cavlc_write_slice(cc_cavlc_ctx *c, cc_bw *b, int is_idr, int row0, int ro
             if (m->type == CC_MB_P16 && cl) cc_bw_put(b, 1, m->t8 & 1); /* transform_size_8x8_flag */
             if (!i16 && !m->cbp) continue;
             cc_bw_se(b, 0); /* mb_qp_delta */
+            /* the slot's residual part: one significance mask per coded block in syntax order, then all levels (cc_k_mb.cu emit_mb) */
+            const int nblk = (i16 ? 1 + (cl ? 16 : 0) : 4 * __builtin_popcount((unsigned)cl)) + (cc ? 2 : 0) + (cc == 2 ? 8 : 0);
+            if (pay + 2 * nblk > pay_end) return -1;
+            const uint8_t *mk = pay;
+            pay += 2 * nblk;
 #define NEXT_BLOCK(mask_, lv_)                                              \
     do {                                                                    \
-        if (pay + 2 > pay_end) return -1;                                   \
-        mask_ = (unsigned)pay[0] | ((unsigned)pay[1] << 8);                 \
-        lv_ = (const int16_t *)(pay + 2);                                   \
-        pay += 2 + 2 * __builtin_popcount(mask_);                           \
+        mask_ = (unsigned)mk[0] | ((unsigned)mk[1] << 8);                   \
+        mk += 2;                                                            \
+        lv_ = (const int16_t *)pay;                                         \
+        pay += 2 * __builtin_popcount(mask_);                               \
         if (pay > pay_end) return -1;                                       \
     } while (0)
             unsigned mask;

@@ -81,6 +81,9 @@ typedef struct {
 } cc_rowhdr;
 
 #define CC_ROW_PAYLOAD_PER_MB 1024 /* worst case: 8 (i4 modes) + 27 blocks * (2 + 32) = 926 bytes */
+/* worst-case CAVLC bits of one macroblock: 16 (coeff_token) + 28 per level (escape code) + 9 (total_zeros) per block, 27 blocks
+ * with 400 levels, plus ~300 header bits = ~11.7 kbit; 1536 bytes per macroblock of slice bit buffer can never overflow */
+#define CC_BS_BYTES_PER_MB 1536
 
 typedef struct {
     int w, h;          /* display size */
@@ -116,6 +119,13 @@ typedef struct {
     /* packed output in mapped pinned host memory: [cc_rowhdr * mb_h][cc_mbhost * nmb][payload rows, 16-byte aligned] */
     uint8_t *out_host_dev; /* device pointer of that mapping */
     uint32_t out_cap;
+    /* device-side CAVLC (cc_k_cavlc.cu): */
+    int dev_entropy;       /* 1: the slices' RBSPs are written on the device, 0: packed symbols go to the host writer */
+    int frame_num, idr_pic_id; /* slice header fields of the frame being coded */
+    uint32_t *mbbits;      /* per MB: bit length of its macroblock_layer() (incl. the mb_skip_run before it) */
+    uint32_t *bs;          /* per slice a zero-initialised bit buffer of bs_slice_words words (MSB-first words) */
+    uint32_t bs_slice_words;
+    uint32_t *bs_ctl;      /* [0, ns): row CTAs of the slice that finished; [ns, 2 ns): the slice's RBSP bytes */
     unsigned long long *cyc; /* debug (CC_DEBUG_CYCLES=1): per MB row 8 cycle counters of the wavefront kernel, or NULL */
 } cc_kparams;
 
@@ -133,6 +143,7 @@ int cck_p_code(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);
 int cck_deblock(const cc_kparams *k, cudaStream_t st);
 int cck_pack(const cc_kparams *k, cudaStream_t st);
+int cck_cavlc(const cc_kparams *k, cudaStream_t st); /* k_cavlc_size + k_cavlc_write: slice RBSPs into the mapped host buffer */
 
 #ifdef __cplusplus
 }

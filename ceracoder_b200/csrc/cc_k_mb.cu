@@ -621,26 +621,37 @@ __device__ __forceinline__ int intra_chroma_pred(const MbCtx &c) {
 }
 
 /* ---- symbol stream -------------------------------------------------------------------------------------------------- */
-/* appends block `blk` of m->coef (n scan positions) to the row payload as {u16 mask, levels...}; returns new offset (in int16 units) */
-__device__ __forceinline__ unsigned emit_block(const MbCtx &c, int16_t *out, unsigned off, int blk, int n) {
+/* A macroblock's residual in its symbol slot (int16 units, after the slot's prefix: four mode words of an Intra4x4 macroblock
+ * or the eight mvd of a P_8x8 one): first one 16-bit significance mask (scan order) per coded block, in the order
+ * residual() transmits the blocks (7.3.5.3: [Intra16x16 DC], luma 4x4 blocks of the coded 8x8s, Cb DC, Cr DC, chroma AC), then the
+ * non-zero levels of those blocks back to back.  Masks at fixed positions let the entropy coder (k_cavlc_*, or the host
+ * writer) find every block's levels with one prefix sum over popcounts instead of a chain of dependent reads. */
+__device__ __forceinline__ int mb_nblocks(int type, int cbp) {
+    const int cl = cbp & 15, cc = cbp >> 4;
+    return (type == CC_MB_I16 ? 1 + (cl ? 16 : 0) : 4 * __popc((unsigned)cl)) + (cc ? 2 : 0) + (cc == 2 ? 8 : 0);
+}
+/* block `blk` of m->coef (n scan positions): mask -> out[moff], levels -> out[loff...]; returns the new level offset */
+__device__ __forceinline__ unsigned emit_block(const MbCtx &c, int16_t *out, unsigned moff, unsigned loff, int blk, int n) {
     const int v = c.lane < n ? c.m->coef[blk][c.lane] : 0;
     const unsigned mask = __ballot_sync(FULL, v != 0);
-    if (c.lane == 0) out[off] = (int16_t)mask;
-    if (v != 0) out[off + 1 + __popc(mask & ((1u << c.lane) - 1u))] = (int16_t)v;
-    return off + 1 + (unsigned)__popc(mask);
+    if (c.lane == 0) out[moff] = (int16_t)mask;
+    if (v != 0) out[loff + __popc(mask & ((1u << c.lane) - 1u))] = (int16_t)v;
+    return loff + (unsigned)__popc(mask);
 }
 
 /* all residual blocks of one macroblock in syntax order; the slot length is padded to a 4-byte multiple */
 __device__ __forceinline__ unsigned emit_mb(const MbCtx &c, int16_t *out, unsigned off, int type, int cbp) {
     const int cl = cbp & 15, cc = cbp >> 4;
     if (type == CC_MB_I16 || cbp) {
-        if (type == CC_MB_I16) off = emit_block(c, out, off, 24, 16);
+        unsigned mo = off;
+        off += (unsigned)mb_nblocks(type, cbp);
+        if (type == CC_MB_I16) off = emit_block(c, out, mo++, off, 24, 16);
         for (int blk = 0; blk < 16; blk++)
-            if (cl & (1 << (blk >> 2))) off = emit_block(c, out, off, blk, type == CC_MB_I16 ? 15 : 16);
+            if (cl & (1 << (blk >> 2))) off = emit_block(c, out, mo++, off, blk, type == CC_MB_I16 ? 15 : 16);
         if (cc) {
-            off = emit_block(c, out, off, 25, 4);
-            off = emit_block(c, out, off, 26, 4);
-            if (cc & 2) for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, off, blk, 15);
+            off = emit_block(c, out, mo++, off, 25, 4);
+            off = emit_block(c, out, mo++, off, 26, 4);
+            if (cc & 2) for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, mo++, off, blk, 15);
         }
     }
     if (off & 1u) { if (c.lane == 0) out[off] = 0; off++; }

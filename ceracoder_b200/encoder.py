@@ -20,7 +20,7 @@ class CeraCudaError(RuntimeError):
 
 class Params(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("device", "width", "height", "fps_n", "fps_d", "format", "bitrate_bps", "key_int_max",
-                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max", "partitions", "threads")]
+                                       "rows_per_slice", "qp_fixed", "qp_min", "qp_max", "partitions", "threads", "host_entropy")]
 
 
 class Frame(C.Structure):
@@ -108,7 +108,7 @@ class CudaH264Enc:
     """The `cudah264enc` element as a Python object: same properties as the pipeline line that names x264enc."""
 
     def __init__(self, width, height, fps=(30, 1), bitrate=6000, key_int_max=60, speed_preset=3, tune=0, name="venc_kbps",
-                 fmt="I420", device=0, rows_per_slice=4, qp_fixed=0, lib=None, byte_stream=True, threads=0, partitions=True):
+                 fmt="I420", device=0, rows_per_slice=4, qp_fixed=0, lib=None, byte_stream=True, threads=0, partitions=True, host_entropy=False):
         if isinstance(speed_preset, str):
             if speed_preset not in _SPEED_PRESETS:
                 raise ValueError(f"unknown speed-preset {speed_preset!r}")
@@ -130,6 +130,7 @@ class CudaH264Enc:
         p.key_int_max, p.rows_per_slice, p.qp_fixed = key_int_max, rows_per_slice, qp_fixed
         p.partitions = int(bool(partitions))
         p.threads = int(threads)  # x264enc's `threads`: host threads writing the slices of one access unit
+        p.host_entropy = int(bool(host_entropy))  # True: the host C CAVLC writer instead of the device kernels (same bytes)
         self.fmt = fmt
         self._h = C.c_void_p()
         _check(self.L, self.L.cc_enc_open(C.byref(self._h), C.byref(p)), "cc_enc_open")

@@ -60,6 +60,9 @@ typedef struct {
                           * under tune=zerolatency).  0 / 1: the calling thread alone — right when one thread per stream already keeps
                           * the host busy; 2..16: a single large stream (2160p) whose bitstream writing would otherwise take longer
                           * than its device work.  The access unit is the same bytes either way */
+    int host_entropy;    /* 0 (default): CAVLC runs on the device: finished slice RBSPs cross PCIe and the host only adds
+                          * start codes, NAL headers and emulation prevention.  1: the device hands over packed symbols and the host C
+                          * writer (cc_cavlc.c) codes them — the round-1 path, kept as a cross-check.  Same bytes either way */
 } cc_enc_params;
 
 typedef struct {
@@ -75,7 +78,7 @@ typedef struct {
     int qp;
     int64_t pts;
     int n_skip, n_inter, n_intra; /* macroblock statistics of the frame */
-    int sym_bytes;       /* bytes of packed symbols the device wrote to host memory for this frame */
+    int sym_bytes;       /* bytes the device wrote to host memory for this frame (slice RBSPs, or packed symbols with host_entropy) */
     float gpu_ms;        /* device time of the frame's kernels (CUDA events) */
     float host_ms;       /* host entropy coding + packaging time */
     int n_intra_analysed, n_skip_probed; /* P frames: MBs that took the slow paths of the wavefront kernel */

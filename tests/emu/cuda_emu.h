@@ -154,8 +154,8 @@ static inline int __dp4a(unsigned a, unsigned b, int c) { for (int i = 0; i < 4;
 static inline unsigned __sad(int a, int b, unsigned c) { return c + (unsigned)(a > b ? a - b : b - a); }
 static inline unsigned __usad(unsigned a, unsigned b, unsigned c) { return c + (a > b ? a - b : b - a); }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
-template <typename T> static inline T __ldcg(const T *p) { return *(const volatile T *)p; }
-template <typename T> static inline T __ldcv(const T *p) { return *(const volatile T *)p; }
+template <typename T> static inline T __ldcg(const T *p) { T v; memcpy(&v, (const void *)p, sizeof(T)); return v; } /* the emulator runs one fiber at a time: plain loads */
+template <typename T> static inline T __ldcv(const T *p) { T v; memcpy(&v, (const void *)p, sizeof(T)); return v; }
 template <typename T> static inline void __stcg(T *p, T v) { *p = v; }
 static inline int atomicAdd(int *p, int v) { int o = *p; *p += v; return o; }
 static inline unsigned atomicAdd(unsigned *p, unsigned v) { unsigned o = *p; *p += v; return o; }

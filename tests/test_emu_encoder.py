@@ -132,3 +132,24 @@ def test_slice_writer_threads_give_the_same_access_units(lib):
         assert a.encode(y, u, v, qp=26 + i) == b.encode(y, u, v, qp=26 + i)
         assert c.encode(y, u, v, qp=26 + i) == d.encode(y, u, v, qp=26 + i)
     [e.close() for e in (a, b, c, d)]
+
+
+def test_device_and_host_entropy_coders_write_the_same_bytes(lib):
+    """the device CAVLC kernels (default) and the host C writer (cc_enc_params.host_entropy) produce identical access
+    units — on texture, on noise at the QP extremes (escape-coded levels, every nC class) and on all-skip pictures"""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    rng = np.random.default_rng(11)
+    w, h = 80, 64
+    noise = [(rng.integers(0, 256, (h, w), dtype=np.uint8), rng.integers(0, 256, (h // 2, w // 2), dtype=np.uint8),
+              rng.integers(0, 256, (h // 2, w // 2), dtype=np.uint8)) for _ in range(3)]
+    still = [noise[0]] * 3                                                      # P frames of nothing but P_Skip: one mb_skip_run per slice
+    pan = [make_source("pan", w, h).frame(i) for i in range(4)]
+    for frames, qps, rps in ((noise, [10, 10, 51], 2), (still, [30, 30, 30], 4), (pan, [24, 26, 28, 40], 3), (pan, [33, 30, 27, 24], 1)):
+        a = CudaH264Enc(w, h, lib=lib, rows_per_slice=rps)
+        b = CudaH264Enc(w, h, lib=lib, rows_per_slice=rps, host_entropy=True)
+        for f, qp in zip(frames, qps):
+            x, y = a.encode(*f, qp=qp), b.encode(*f, qp=qp)
+            assert x == y, f"device and host entropy coders differ at qp {qp} ({len(x)} vs {len(y)} bytes)"
+            assert a.last.sym_bytes < b.last.sym_bytes or qp == 10       # finished bits cross PCIe, not symbols
+        a.close(); b.close()

@@ -136,3 +136,19 @@ def test_minimum_and_odd_sizes(lib, w, h, rps):
     """smallest legal pictures, sizes that are not macroblock multiples, one very wide macroblock row: the TMA window tiles of the
     coarse search hang over every edge of the padded plane here"""
     run_parity(lib, "pan", w, h, [30, 31, 22], rps=rps)
+
+
+def test_device_entropy_equals_host_entropy_at_full_size(lib):
+    """SURVEY 8f N3 on the B200: 1080p60 with rate control on (QP moves, IDR + P frames, every macroblock type) — the device CAVLC
+    kernels and the host C writer produce the same access units; 2160p likewise on a few frames"""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    for w, h, n, kbps in ((1920, 1080, 16, 12000), (3840, 2160, 4, 20000), (1280, 720, 8, 1000)):
+        src = make_source("pan", w, h)
+        a = CudaH264Enc(w, h, fps=(60, 1), lib=lib, bitrate=kbps, key_int_max=10)
+        b = CudaH264Enc(w, h, fps=(60, 1), lib=lib, bitrate=kbps, key_int_max=10, host_entropy=True, threads=4)
+        for i in range(n):
+            y, u, v = src.frame(i)
+            assert a.encode(y, u, v) == b.encode(y, u, v), f"{w}x{h} frame {i}"
+            assert a.last.qp == b.last.qp
+        a.close(); b.close()
