@@ -232,6 +232,7 @@ def main():
     ap.add_argument("--input-format", default="I420", choices=["I420", "YUY2", "BGRx"],
                     help="frame format handed to the encoder; packed formats are converted inside the ingest kernel (SURVEY 8f N2). "
                          "The YUY2 pool carries exactly the I420 pool's pictures (chroma rows doubled), so the encoded workload is the same")
+    ap.add_argument("--host-entropy", action="store_true", help="CAVLC by the host C writer instead of the device kernels (round-1 path; comparison runs)")
     ap.add_argument("--frames-per-step", type=int, default=FRAMES_PER_STEP, help="frames each stream encodes per step (shorten for ncu runs)")
     args = ap.parse_args()
     FRAMES_PER_STEP = args.frames_per_step
@@ -277,7 +278,7 @@ def main():
 
     def make_encs():
         return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L, fmt=FMT,
-                            rows_per_slice=args.rows_per_slice, partitions=bool(args.partitions)) for _ in range(S)]
+                            rows_per_slice=args.rows_per_slice, partitions=bool(args.partitions), host_entropy=args.host_entropy) for _ in range(S)]
 
     def timed(device_frames, steps, warmup, profile=False):
         encs = make_encs()
@@ -392,7 +393,7 @@ def main():
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
             "data": "synthetic S2 pan-sprites 1080p (SURVEY.md §8d), 40-frame pool played ping-pong",
             "config": {"workload": f"{S} concurrent 1080p60 cudah264enc streams per GPU, balancer-shaped 12->2->12 Mbps schedule (configs[1] x8, north_star target shape)",
-                       "width": W, "height": H, "fps": FPS, "input_format": FMT, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60,
+                       "width": W, "height": H, "fps": FPS, "input_format": FMT, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60, "entropy_coder": "host C (cc_cavlc.c)" if args.host_entropy else "device (k_cavlc_size + k_cavlc_write)",
                        "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},

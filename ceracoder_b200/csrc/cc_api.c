@@ -42,8 +42,11 @@ struct cc_enc {
     long launches;
     int last_was_p;
     int profile;                 /* per-kernel CUDA events on */
-    cudaEvent_t pev[CC_N_STAGES + 1];
-    int pev_used[CC_N_STAGES + 1];
+    cudaEvent_t pevs[2][CC_N_STAGES + 1]; /* two sets, alternating per frame: the stages behind ev1 (reference finishing) are read when the set
+                                           * comes round again, two frames later, when they are certainly complete */
+    int pevs_used[2][CC_N_STAGES + 1];
+    int pevs_tail[2];            /* set holds unread tail stages */
+    int pb;                      /* set of the frame in flight */
     double stage_ms[CC_N_STAGES];
     long stage_n[CC_N_STAGES];
     uint32_t sym_bytes;
@@ -63,9 +66,12 @@ struct cc_enc {
     float dev_ms_hist[4];        /* device latency (submit -> access unit ready) of the last frames: how long collect may sleep */
     unsigned dev_ms_n;
     int sleep_wait;              /* CERACUDA_WAIT=spin turns the sleep off */
+    uint8_t *stage_host;         /* pinned staging frame: pageable input (a mapped GstBuffer) is copied here by the calling thread, then uploaded
+                                  * asynchronously.  One frame suffices: a handle has one frame in flight and its upload is over by collect */
+    size_t stage_bytes;
+    long staged_frames;
     int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
     size_t bs_bytes;
-    int tail_pending;            /* profile: the stages after ev1 (reference finishing) of the previous frame are not read yet */
 };
 
 static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
@@ -257,6 +263,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
         k->bs_slice_words = (uint32_t)roundup((size_t)k->rps * k->mb_w * (CC_BS_BYTES_PER_MB / 4) + 16, 4);
         e->bs_bytes = (size_t)n_slices_open * k->bs_slice_words * 4;
         if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbbits, sizeof(uint32_t) * nmb);
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->cvrec, (size_t)32 * nmb);
         if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->bs, e->bs_bytes);
         if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->bs_ctl, sizeof(uint32_t) * 2 * n_slices_open);
         if (rc == CC_OK) { cudaMemset(k->bs, 0, e->bs_bytes); cudaMemset(k->bs_ctl, 0, sizeof(uint32_t) * 2 * n_slices_open); }
@@ -272,6 +279,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     k->out_cap = e->out_cap;
     e->au_cap = (size_t)nmb * CC_BS_BYTES_PER_MB * 3 / 2 + 4096; /* every slice's worst case, with emulation prevention */
     e->rbsp_cap = (size_t)k->rps * k->mb_w * CC_BS_BYTES_PER_MB + 4096;
+    e->stage_bytes = (size_t)k->w * k->h * (p->format == CC_FMT_BGRX ? 4 : (p->format == CC_FMT_YUY2 ? 2 : 1)) * (p->format <= CC_FMT_NV12 ? 3 : 2) / 2;
+    if (rc == CC_OK && cudaHostAlloc((void **)&e->stage_host, e->stage_bytes, cudaHostAllocDefault) != cudaSuccess) rc = CC_ERR_NOMEM;
     e->au = (uint8_t *)malloc(e->au_cap);
     e->rbsp = (uint8_t *)malloc(e->rbsp_cap);
     e->cav.mb_w = k->mb_w; e->cav.mb_h = k->mb_h; e->cav.rps = k->rps;
@@ -280,7 +289,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = pool_start(e, p->threads);
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
-    for (int i = 0; i <= CC_N_STAGES && rc == CC_OK; i++) if (cudaEventCreate(&e->pev[i]) != cudaSuccess) rc = CC_ERR_CUDA;
+    for (int i = 0; i < 2 * (CC_N_STAGES + 1) && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
@@ -315,9 +324,10 @@ void cc_enc_close(cc_enc *e) {
     for (int i = 0; i < e->n_dev_alloc; i++) cudaFree(e->dev_alloc[i]);
     pool_stop(e);
     if (e->out_host) cudaFreeHost(e->out_host);
+    if (e->stage_host) cudaFreeHost(e->stage_host);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
-    for (int i = 0; i <= CC_N_STAGES; i++) if (e->pev[i]) cudaEventDestroy(e->pev[i]);
+    for (int i = 0; i < 2 * (CC_N_STAGES + 1); i++) if (e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]) cudaEventDestroy(e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]);
     if (e->st) cudaStreamDestroy(e->st);
     free(e->au); free(e->rbsp); free(e->cav.nnz);
     free(e);
@@ -340,6 +350,7 @@ int cc_enc_set_profile(cc_enc *e, int on) {
     if (!e || e->inflight) return CC_ERR_PARAM;
     e->profile = on != 0;
     memset(e->stage_ms, 0, sizeof e->stage_ms); memset(e->stage_n, 0, sizeof e->stage_n);
+    e->pevs_tail[0] = e->pevs_tail[1] = 0;
     return CC_OK;
 }
 int cc_enc_get_stage_ms(const cc_enc *e, double *ms_sum, long *count) {
@@ -347,6 +358,14 @@ int cc_enc_get_stage_ms(const cc_enc *e, double *ms_sum, long *count) {
     for (int i = 0; i < CC_N_STAGES; i++) { ms_sum[i] = e->stage_ms[i]; count[i] = e->stage_n[i]; }
     return CC_OK;
 }
+
+/* page-locked (cudaHostAlloc / cudaHostRegister) host memory? */
+static int host_is_pinned(const void *p) {
+    struct cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return a.type == cudaMemoryTypeHost;
+}
+long cc_enc_staged_frames(const cc_enc *e) { return e ? e->staged_frames : 0; }
 
 static void set_quant(cc_kparams *k) {
     static const uint8_t chroma_qp[52] = {0,  1,  2,  3,  4,  5,  6,  7,  8,  9,  10, 11, 12, 13, 14, 15, 16, 17,
@@ -394,12 +413,15 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->cur_is_idr = is_idr; e->cur_qp = qp; e->cur_pts = in->pts;
 
     enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    if (e->tail_pending) { /* stages that ran behind the previous collect; skipped if they are still running */
+    e->pb ^= 1;
+    cudaEvent_t *pev = e->pevs[e->pb];
+    int *pev_used = e->pevs_used[e->pb];
+    if (e->pevs_tail[e->pb]) { /* the stages that ran behind the collect of the frame before the previous one */
         for (int i = CC_STAGE_DEBLOCK; i < CC_N_STAGES; i++) {
             float ms = 0;
-            if (e->pev_used[i] && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
+            if (pev_used[i] && cudaEventElapsedTime(&ms, pev[i], pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
         }
-        e->tail_pending = 0;
+        e->pevs_tail[e->pb] = 0;
     }
     if (e->bs_dirty && k->dev_entropy) {
         const int nsl = (k->mb_h + k->rps - 1) / k->rps;
@@ -408,20 +430,38 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
         e->bs_dirty = 0;
     }
     CUCHECK(cudaEventRecord(e->ev0, e->st));
-    if (e->profile) { cudaEventRecord(e->pev[CC_STAGE_UPLOAD], e->st); }
+    if (e->profile) { cudaEventRecord(pev[CC_STAGE_UPLOAD], e->st); }
+    /* Host frames that are not page-locked (what gst_video_frame_map hands the element) cannot be copied asynchronously: the
+     * runtime would stage them through its own bounce buffer inside the call.  Copy them into the handle's pinned frame here
+     * (tight rows), then upload from there like a pinned frame. */
+    const uint8_t *pl[3] = {in->plane[0], in->plane[1], in->plane[2]};
+    int st[3] = {in->stride[0], in->stride[1], in->stride[2]};
+    if (!(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) {
+        uint8_t *d = e->stage_host;
+        const int nplanes = packed ? 1 : (nv12 ? 2 : 3);
+        for (int i = 0; i < nplanes; i++) {
+            const size_t rowb = packed ? (size_t)k->w * (fmt == CC_FMT_YUY2 ? 2 : 4) : (i == 0 ? (size_t)k->w : (nv12 ? (size_t)k->w : (size_t)k->w / 2));
+            const size_t rows = i == 0 ? (size_t)k->h : (size_t)k->h / 2;
+            if ((size_t)in->stride[i] == rowb) memcpy(d, in->plane[i], rowb * rows);
+            else for (size_t r = 0; r < rows; r++) memcpy(d + r * rowb, in->plane[i] + r * (size_t)in->stride[i], rowb);
+            pl[i] = d; st[i] = (int)rowb;
+            d += rowb * rows;
+        }
+        e->staged_frames++;
+    }
     if (packed) {
-        CUCHECK(cudaMemcpy2DAsync(k->pkstage, (size_t)k->pks, in->plane[0], (size_t)in->stride[0], (size_t)k->w * (fmt == CC_FMT_YUY2 ? 2 : 4), (size_t)k->h, kind, e->st));
+        CUCHECK(cudaMemcpy2DAsync(k->pkstage, (size_t)k->pks, pl[0], (size_t)st[0], (size_t)k->w * (fmt == CC_FMT_YUY2 ? 2 : 4), (size_t)k->h, kind, e->st));
     } else {
-        CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st));
+        CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, pl[0], (size_t)st[0], (size_t)k->w, (size_t)k->h, kind, e->st));
         if (nv12) {
-            CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, in->plane[1], (size_t)in->stride[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
+            CUCHECK(cudaMemcpy2DAsync(k->uvstage, (size_t)k->sy, pl[1], (size_t)st[1], (size_t)k->w, (size_t)k->h / 2, kind, e->st));
         } else {
-            CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
-            CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+            CUCHECK(cudaMemcpy2DAsync(k->cur[1], (size_t)k->sc, pl[1], (size_t)st[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
+            CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, pl[2], (size_t)st[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
         }
     }
-#define STAGE(i) do { if (e->profile) { cudaEventRecord(e->pev[i], e->st); e->pev_used[i] = 1; } } while (0)
-    for (int i = 0; i <= CC_N_STAGES; i++) e->pev_used[i] = 0;
+#define STAGE(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
+    for (int i = 0; i <= CC_N_STAGES; i++) pev_used[i] = 0;
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);
     STAGE(CC_STAGE_ME_COARSE);
@@ -447,7 +487,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->launches += cck_l1ref(k, e->st);
     STAGE(CC_N_STAGES);
 #undef STAGE
-    e->tail_pending = e->profile;
+    e->pevs_tail[e->pb] = e->profile;
     CUCHECK(cudaGetLastError());
     /* the new reconstruction becomes the reference of the next frame */
     for (int i = 0; i < 3; i++) { uint8_t *t = k->rec[i]; k->rec[i] = k->ref[i]; k->ref[i] = t; }
@@ -500,7 +540,7 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
     if (e->profile)
         for (int i = 0; i < CC_STAGE_DEBLOCK; i++) {
             float ms = 0;
-            if ((i == CC_STAGE_UPLOAD || e->pev_used[i]) && cudaEventElapsedTime(&ms, e->pev[i], e->pev[i + 1]) == cudaSuccess) {
+            if ((i == CC_STAGE_UPLOAD || e->pevs_used[e->pb][i]) && cudaEventElapsedTime(&ms, e->pevs[e->pb][i], e->pevs[e->pb][i + 1]) == cudaSuccess) {
                 if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
             }
         }

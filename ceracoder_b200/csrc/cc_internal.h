@@ -123,6 +123,7 @@ typedef struct {
     int dev_entropy;       /* 1: the slices' RBSPs are written on the device, 0: packed symbols go to the host writer */
     int frame_num, idr_pic_id; /* slice header fields of the frame being coded */
     uint32_t *mbbits;      /* per MB: bit length of its macroblock_layer() (incl. the mb_skip_run before it) */
+    struct CvRec *cvrec;   /* per MB 32 bytes: what k_cavlc_size found outside the macroblock (nC per block, mb_skip_run) for k_cavlc_write */
     uint32_t *bs;          /* per slice a zero-initialised bit buffer of bs_slice_words words (MSB-first words) */
     uint32_t bs_slice_words;
     uint32_t *bs_ctl;      /* [0, ns): row CTAs of the slice that finished; [ns, 2 ns): the slice's RBSP bytes */

@@ -135,8 +135,7 @@ __device__ __forceinline__ int block_rank(int type, int cbp, int b) {
     return cc == 2 ? j0 + 4 * __popc((unsigned)cl) + 2 + (b - 16) : -1;
 }
 /* total_coeff of block b of macroblock n as its neighbours see it (9.2.1: 0 for P_Skip and for blocks that are not coded) */
-__device__ __forceinline__ int nb_total(const cc_kparams &k, int n, int b) {
-    const uint32_t h = *(const uint32_t *)(k.mbh + n);
+__device__ __forceinline__ int nb_total(const cc_kparams &k, int n, uint32_t h, int b) {
     const int type = (int)(h & 255u), cbp = (int)((h >> 16) & 255u), t8 = (int)(h >> 24);
     if (type == CC_MB_PSKIP) return 0;
     const int r = block_rank(type, cbp, b);
@@ -146,37 +145,42 @@ __device__ __forceinline__ int nb_total(const cc_kparams &k, int n, int b) {
 }
 __device__ __forceinline__ int blk_of_xy(int bx, int by) { return ((by >> 1) << 3) | ((bx >> 1) << 2) | ((by & 1) << 1) | (bx & 1); }
 
-/* One macroblock by one warp.  WRITE = false: returns its bit length (all lanes).  WRITE = true: also ORs the bits into bs at
- * bitpos.  Every lane must call it (warp collectives inside). */
+/* which residual block lane j of a macroblock's warp holds (syntax order): kind 0 luma (incl. the Intra16x16 DC block, which sits
+ * at position 0,0), 1 chroma DC, 2 chroma AC; (bx, by) in 4x4 units inside the macroblock / the plane pl */
+struct LaneBlock { int kind, bx, by, pl, maxc; };
+__device__ __forceinline__ LaneBlock lane_block(int i16, int cl, int nl, int lane) {
+    LaneBlock b = {0, 0, 0, 0, 16};
+    const int j = lane - i16;
+    if (i16 && lane == 0) return b;
+    if (j < nl) {
+        int q = 0, nth = j >> 2; /* the (j >> 2)-th coded 8x8 */
+        for (int i = 0; i < 4; i++) { if ((cl >> i) & 1) { if (nth == 0) { q = i; break; } nth--; } }
+        const int blk = q * 4 + (j & 3);
+        b.maxc = i16 ? 15 : 16;
+        b.bx = ((blk >> 2) & 1) * 2 + (blk & 1); b.by = ((blk >> 3) & 1) * 2 + ((blk >> 1) & 1);
+    } else if (j < nl + 2) { b.kind = 1; b.maxc = 4; b.pl = j - nl; }
+    else { const int i = j - nl - 2; b.kind = 2; b.maxc = 15; b.pl = i >> 2; b.bx = i & 1; b.by = (i >> 1) & 1; }
+    return b;
+}
+
+/* What k_cavlc_size leaves per macroblock for k_cavlc_write (32 bytes): everything that needs other macroblocks, so that the
+ * writer's loads are all independent of each other.  nC[j] = the nC of 9.2.1 for the j-th coded block (-1 = chroma DC) */
+struct __align__(16) CvRec { int8_t nC[28]; uint16_t run, slot_words; };
+
+/* macroblock_layer() of one macroblock by one warp, from its record h, its symbol slot (staged in shared memory), the
+ * mb_skip_run before it and its lanes' nC.  Returns the bit length in all lanes; WRITE: also ORs the bits into bs at bitpos.
+ * Every lane must call it (warp collectives inside). */
 template <bool WRITE>
-__device__ unsigned cavlc_mb(const cc_kparams &k, const VlcTab *t, int mb, int lane, uint32_t *bs, unsigned bitpos) {
-    const int mw = k.mb_w, mbx = mb % mw, row = mb / mw, row0 = (row / k.rps) * k.rps, P = !k.is_idr;
-    const int slice_first = row0 * mw, slice_last = min(row0 + k.rps, k.mb_h) * mw - 1;
-    const uint2 h = *(const uint2 *)(k.mbh + mb);
+__device__ __forceinline__ unsigned mb_code(const VlcTab *t, const uint16_t *slot, uint2 h, int P, int run, int nC, int lane, uint32_t *bs, unsigned bitpos) {
     const int type = (int)(h.x & 255u), modes = (int)((h.x >> 8) & 255u), cbp = (int)((h.x >> 16) & 255u), t8 = (int)(h.x >> 24);
     const int cl = cbp & 15, cc = cbp >> 4, i16 = type == CC_MB_I16;
-    if (type == CC_MB_PSKIP && mb != slice_last) return 0;
-    /* mb_skip_run: the skipped macroblocks straight before this one inside the slice */
-    int run = 0;
-    if (P) {
-        int p = mb - 1;
-        bool more = true;
-        while (more && p >= slice_first) {
-            const int idx = p - lane;
-            const int stop = idx < slice_first ? 1 : (*(const uint8_t *)(k.mbh + idx) != CC_MB_PSKIP);
-            const unsigned bal = __ballot_sync(FULL, stop);
-            if (bal) { run += __ffs((int)bal) - 1; more = false; }
-            else { run += 32; p -= 32; }
-        }
-    }
     if (type == CC_MB_PSKIP) { /* the slice ends in skipped macroblocks: the last one carries the final mb_skip_run */
         BitCount c = {0};
         put_ue(c, (unsigned)run + 1u);
         if (WRITE && lane == 0) { BitRed w = {bs, bitpos}; put_ue(w, (unsigned)run + 1u); }
         return c.n;
     }
-    const uint16_t *slot = (const uint16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
-    auto header = [&](auto &w) { /* macroblock_layer() up to residual(), 7.3.5 */
+    auto header = [&](auto &w) { /* up to residual(), 7.3.5 */
         if (P) put_ue(w, (unsigned)run);
         if (type == CC_MB_P16 && (t8 & 2)) { /* P_8x8: four sub_mb_type P_L0_8x8 (ue 0 each), no ref_idx (one reference), four mvd */
             put_ue(w, 3);
@@ -202,7 +206,6 @@ __device__ unsigned cavlc_mb(const cc_kparams &k, const VlcTab *t, int mb, int l
     header(hc);
     if (WRITE && lane == 0) { BitRed w = {bs, bitpos}; header(w); }
     if (!i16 && !cbp) return hc.n;
-
     /* residual(): lane j = the j-th coded block in syntax order */
     const int nl = i16 ? (cl ? 16 : 0) : 4 * __popc((unsigned)cl), nb = i16 + nl + (cc ? 2 : 0) + (cc == 2 ? 8 : 0);
     const uint16_t *masks = slot + slot_prefix(type, t8);
@@ -213,51 +216,7 @@ __device__ unsigned cavlc_mb(const cc_kparams &k, const VlcTab *t, int mb, int l
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, lo, d); if (lane >= d) lo += v; }
     lo -= total;
-    /* which block this lane holds */
-    int kind, bx = 0, by = 0, pl = 0, maxc; /* kind 0 luma (incl. the Intra16x16 DC block at position 0,0), 1 chroma DC, 2 chroma AC */
-    {
-        const int j = lane - i16;
-        if (i16 && lane == 0) { kind = 0; maxc = 16; }
-        else if (j < nl) {
-            int q = 0, nth = j >> 2; /* the (j >> 2)-th coded 8x8 */
-            for (int i = 0; i < 4; i++) { if ((cl >> i) & 1) { if (nth == 0) { q = i; break; } nth--; } }
-            const int b = q * 4 + (j & 3);
-            kind = 0; maxc = i16 ? 15 : 16;
-            bx = ((b >> 2) & 1) * 2 + (b & 1); by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
-        } else if (j < nl + 2) { kind = 1; maxc = 4; pl = j - nl; }
-        else { const int i = j - nl - 2; kind = 2; maxc = 15; pl = i >> 2; bx = i & 1; by = (i >> 1) & 1; }
-    }
-    /* total_coeff of the blocks across the macroblock's left and top edges: lanes 0-7 the left neighbour's right column
-     * {luma 5, 7, 13, 15, Cb 1, 3, Cr 1, 3}, lanes 8-15 the top neighbour's bottom row {luma 10, 11, 14, 15, Cb 2, 3, Cr 2, 3} */
-    int ext = 0;
-    const int has_left = mbx > 0, has_top = row > row0;
-    if (lane < 16) {
-        const int top = lane >> 3, i = lane & 7;
-        if (top ? has_top : has_left) {
-            const int b = i < 4 ? (top ? (i < 2 ? 10 + i : 12 + i) : (i < 2 ? 5 + 2 * i : 9 + 2 * i)) : 16 + 4 * ((i - 4) >> 1) + (top ? 2 + (i & 1) : 1 + 2 * (i & 1));
-            ext = nb_total(k, mb - (top ? mw : 1), b);
-        }
-    }
-    /* nC, 9.2.1 */
-    int srcA, srcB, extA, extB; /* lane holding the in-macroblock neighbour (or -1), lane holding the outside one */
-    if (kind == 2) {
-        srcA = bx > 0 ? block_rank(type, cbp, 16 + 4 * pl + by * 2) : -1;
-        srcB = by > 0 ? block_rank(type, cbp, 16 + 4 * pl + bx) : -1;
-        extA = 4 + 2 * pl + by; extB = 12 + 2 * pl + bx;
-    } else {
-        srcA = bx > 0 ? block_rank(type, cbp, blk_of_xy(bx - 1, by)) : -1;
-        srcB = by > 0 ? block_rank(type, cbp, blk_of_xy(bx, by - 1)) : -1;
-        extA = by; extB = 8 + bx;
-    }
-    const int inA = __shfl_sync(FULL, total, srcA & 31), inB = __shfl_sync(FULL, total, srcB & 31);
-    const int outA = __shfl_sync(FULL, ext, extA), outB = __shfl_sync(FULL, ext, extB);
-    int nC;
-    {
-        const int availA = bx > 0 || has_left, availB = by > 0 || has_top;
-        const int nA = bx > 0 ? (srcA >= 0 ? inA : 0) : outA, nB = by > 0 ? (srcB >= 0 ? inB : 0) : outB;
-        nC = (availA && availB) ? (nA + nB + 1) >> 1 : (availA ? nA : (availB ? nB : 0));
-        if (kind == 1) nC = -1;
-    }
+    const int maxc = lane_block(i16, cl, nl, lane).maxc;
     const int16_t *lv = (const int16_t *)(masks + nb) + lo;
     BitCount bc = {0};
     if (act) cavlc_block(bc, t, mask, lv, maxc, nC);
@@ -271,41 +230,117 @@ __device__ unsigned cavlc_mb(const cc_kparams &k, const VlcTab *t, int mb, int l
     return hc.n + __shfl_sync(FULL, incl, 31);
 }
 
+/* a macroblock's symbol slot into the warp's shared memory, coalesced (the coder reads the levels one by one, twice when writing) */
+__device__ __forceinline__ void stage_slot(const cc_kparams &k, uint32_t *stage, int mb, unsigned slot_words, int lane) {
+    const uint32_t *src = (const uint32_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
+    __syncwarp();
+    for (unsigned i = lane; i < slot_words; i += 32) stage[i] = src[i];
+    __syncwarp();
+}
+
 /* ---- kernels ---------------------------------------------------------------------------------------------------------- */
 #define CV_WARPS 8
-#define CV_MB_PER_CTA 32
+#define CV_MB_PER_CTA 16
+/* one warp per macroblock: what its bits depend on outside itself (mb_skip_run, nC), then its bit length */
 __global__ void __launch_bounds__(CV_WARPS * 32) k_cavlc_size(cc_kparams k) {
     __shared__ VlcTab tab;
+    __shared__ __align__(16) uint32_t stage_all[CV_WARPS][CC_ROW_PAYLOAD_PER_MB / 4];
     vlc_load(&tab);
     __syncthreads();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nmb = k.mb_w * k.mb_h;
-    for (int i = wid; i < CV_MB_PER_CTA; i += CV_WARPS) {
-        const int mb = blockIdx.x * CV_MB_PER_CTA + i;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nmb = k.mb_w * k.mb_h, mw = k.mb_w, P = !k.is_idr;
+    uint32_t *stage = stage_all[wid];
+    for (int it = wid; it < CV_MB_PER_CTA; it += CV_WARPS) {
+        const int mb = blockIdx.x * CV_MB_PER_CTA + it;
         if (mb >= nmb) break;
-        const unsigned n = cavlc_mb<false>(k, &tab, mb, lane, nullptr, 0);
-        if (lane == 0) k.mbbits[mb] = n;
+        const int mbx = mb % mw, row = mb / mw, row0 = (row / k.rps) * k.rps;
+        const int slice_first = row0 * mw, slice_last = min(row0 + k.rps, k.mb_h) * mw - 1;
+        const int has_left = mbx > 0, has_top = row > row0;
+        /* everything that does not depend on another load goes out first: the record, the neighbours' records, the slot length */
+        const uint2 h = *(const uint2 *)(k.mbh + mb);
+        const uint32_t h_left = has_left ? *(const uint32_t *)(k.mbh + mb - 1) : 0u, h_top = has_top ? *(const uint32_t *)(k.mbh + mb - mw) : 0u;
+        const unsigned slot_words = (unsigned)k.symlen[mb] >> 1;
+        const int type = (int)(h.x & 255u), cbp = (int)((h.x >> 16) & 255u);
+        if (type == CC_MB_PSKIP && mb != slice_last) { if (lane == 0) k.mbbits[mb] = 0; continue; }
+        /* mb_skip_run: the skipped macroblocks straight before this one inside the slice */
+        int run = 0;
+        if (P) {
+            int p = mb - 1;
+            bool more = true;
+            while (more && p >= slice_first) {
+                const int idx = p - lane;
+                const int stop = idx < slice_first ? 1 : (*(const uint8_t *)(k.mbh + idx) != CC_MB_PSKIP);
+                const unsigned bal = __ballot_sync(FULL, stop);
+                if (bal) { run += __ffs((int)bal) - 1; more = false; }
+                else { run += 32; p -= 32; }
+            }
+        }
+        int nC = 0;
+        if (type != CC_MB_PSKIP) {
+            stage_slot(k, stage, mb, slot_words, lane);
+            /* total_coeff of the blocks across the macroblock's left and top edges: lanes 0-7 the left neighbour's right column
+             * {luma 5, 7, 13, 15, Cb 1, 3, Cr 1, 3}, lanes 8-15 the top neighbour's bottom row {luma 10, 11, 14, 15, Cb 2, 3, Cr 2, 3} */
+            int ext = 0;
+            if (lane < 16) {
+                const int top = lane >> 3, i = lane & 7;
+                if (top ? has_top : has_left) {
+                    const int b = i < 4 ? (top ? (i < 2 ? 10 + i : 12 + i) : (i < 2 ? 5 + 2 * i : 9 + 2 * i)) : 16 + 4 * ((i - 4) >> 1) + (top ? 2 + (i & 1) : 1 + 2 * (i & 1));
+                    ext = nb_total(k, mb - (top ? mw : 1), top ? h_top : h_left, b);
+                }
+            }
+            const int t8 = (int)(h.x >> 24), cl = cbp & 15, cc = cbp >> 4, i16 = type == CC_MB_I16;
+            const int nl = i16 ? (cl ? 16 : 0) : 4 * __popc((unsigned)cl), nb = i16 + nl + (cc ? 2 : 0) + (cc == 2 ? 8 : 0);
+            const uint16_t *masks = (const uint16_t *)stage + slot_prefix(type, t8);
+            const int total = lane < nb ? __popc((unsigned)masks[lane]) : 0;
+            const LaneBlock lb = lane_block(i16, cl, nl, lane);
+            int srcA, srcB, extA, extB; /* lane holding the in-macroblock neighbour (or -1), lane holding the outside one */
+            if (lb.kind == 2) {
+                srcA = lb.bx > 0 ? block_rank(type, cbp, 16 + 4 * lb.pl + lb.by * 2) : -1;
+                srcB = lb.by > 0 ? block_rank(type, cbp, 16 + 4 * lb.pl + lb.bx) : -1;
+                extA = 4 + 2 * lb.pl + lb.by; extB = 12 + 2 * lb.pl + lb.bx;
+            } else {
+                srcA = lb.bx > 0 ? block_rank(type, cbp, blk_of_xy(lb.bx - 1, lb.by)) : -1;
+                srcB = lb.by > 0 ? block_rank(type, cbp, blk_of_xy(lb.bx, lb.by - 1)) : -1;
+                extA = lb.by; extB = 8 + lb.bx;
+            }
+            const int inA = __shfl_sync(FULL, total, srcA & 31), inB = __shfl_sync(FULL, total, srcB & 31);
+            const int outA = __shfl_sync(FULL, ext, extA), outB = __shfl_sync(FULL, ext, extB);
+            const int availA = lb.bx > 0 || has_left, availB = lb.by > 0 || has_top;
+            const int nA = lb.bx > 0 ? (srcA >= 0 ? inA : 0) : outA, nB = lb.by > 0 ? (srcB >= 0 ? inB : 0) : outB;
+            nC = (availA && availB) ? (nA + nB + 1) >> 1 : (availA ? nA : (availB ? nB : 0)); /* 9.2.1 */
+            if (lb.kind == 1) nC = -1;
+        }
+        const unsigned n = mb_code<false>(&tab, (const uint16_t *)stage, h, P, run, nC, lane, nullptr, 0);
+        CvRec *rec = k.cvrec + mb;
+        if (lane < 28) rec->nC[lane] = (int8_t)nC;
+        else if (lane == 28) rec->run = (uint16_t)run;
+        else if (lane == 29) rec->slot_words = (uint16_t)slot_words;
+        else if (lane == 30) k.mbbits[mb] = n;
     }
 }
 
 /* layout of the mapped host buffer in device-entropy mode: [cc_rowhdr x mb_h][u32 slice bytes x ns][slice RBSPs, bs_slice_words
  * words apart] (cc_api.c collect reads the same) */
-__global__ void __launch_bounds__(CV_WARPS * 32) k_cavlc_write(cc_kparams k) {
+#define CW_WARPS 16
+__global__ void __launch_bounds__(CW_WARPS * 32) k_cavlc_write(cc_kparams k) {
     __shared__ VlcTab tab;
-    __shared__ unsigned red[CV_WARPS], mboff[513], s_last;
+    __shared__ __align__(16) uint32_t stage_all[CW_WARPS][CC_ROW_PAYLOAD_PER_MB / 4];
+    __shared__ unsigned red[CW_WARPS], mboff[513], s_last, n_work;
+    __shared__ uint16_t work[512]; /* the row's macroblocks that have bits, in order */
     vlc_load(&tab);
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, mw = k.mb_w;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, mw = k.mb_w, P = !k.is_idr;
     const int row = blockIdx.x, s = row / k.rps, row0 = s * k.rps, rows = min(k.rps, k.mb_h - row0), ns = (k.mb_h + k.rps - 1) / k.rps;
     uint32_t *bs = k.bs + (size_t)s * k.bs_slice_words;
+    uint32_t *stage = stage_all[wid];
     { /* bits of the slice's rows above this one */
         unsigned v = 0;
         const uint32_t *src = k.mbbits + (size_t)row0 * mw;
-        for (int i = tid; i < (row - row0) * mw; i += CV_WARPS * 32) v += src[i];
+        for (int i = tid; i < (row - row0) * mw; i += CW_WARPS * 32) v += src[i];
 #pragma unroll
         for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
         if (lane == 0) red[wid] = v;
     }
-    if (wid == 0) { /* exclusive prefix of this row's macroblock lengths; mboff[mw] = the row's total */
-        unsigned run = 0;
+    if (wid == 0) { /* exclusive prefix of this row's macroblock lengths (mboff[mw] = the row's total) and the list of coded macroblocks */
+        unsigned run = 0, nw = 0;
         for (int base = 0; base < mw; base += 32) {
             const int i = base + lane;
             const unsigned len = i < mw ? k.mbbits[(size_t)row * mw + i] : 0u;
@@ -314,18 +349,32 @@ __global__ void __launch_bounds__(CV_WARPS * 32) k_cavlc_write(cc_kparams k) {
             for (int d = 1; d < 32; d <<= 1) { const unsigned v = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += v; }
             if (i < mw) mboff[i] = run + inc - len;
             run += __shfl_sync(FULL, inc, 31);
+            const unsigned bal = __ballot_sync(FULL, len != 0u);
+            if (len) work[nw + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+            nw += (unsigned)__popc(bal);
         }
-        if (lane == 0) mboff[mw] = run;
+        if (lane == 0) { mboff[mw] = run; n_work = nw; }
     }
     __syncthreads();
     BitCount hc = {0};
     slice_header(hc, row0 * mw, k.is_idr, k.frame_num, k.idr_pic_id, k.qp);
     unsigned base = hc.n;
 #pragma unroll
-    for (int i = 0; i < CV_WARPS; i++) base += red[i];
-    for (int x = wid; x < mw; x += CV_WARPS) {
-        const int mb = row * mw + x;
-        if (k.mbbits[mb]) cavlc_mb<true>(k, &tab, mb, lane, bs, base + mboff[x]);
+    for (int i = 0; i < CW_WARPS; i++) base += red[i];
+    for (unsigned j = wid; j < n_work; j += CW_WARPS) {
+        const int x = work[j], mb = row * mw + x;
+        /* three independent loads: the record, what k_cavlc_size left, the head of the slot (the rest only if the slot is longer) */
+        const uint2 h = *(const uint2 *)(k.mbh + mb);
+        const uint32_t rw = ((const uint32_t *)(k.cvrec + mb))[lane & 7];
+        const uint32_t *src = (const uint32_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
+        __syncwarp();
+        stage[lane] = src[lane];
+        const uint32_t tail = __shfl_sync(FULL, rw, 7);
+        const unsigned slot_words = tail >> 16;
+        for (unsigned i = 32 + lane; i < slot_words; i += 32) stage[i] = src[i];
+        __syncwarp();
+        const int nC = (int)(int8_t)(__shfl_sync(FULL, rw, lane >> 2) >> (8 * (lane & 3)));
+        mb_code<true>(&tab, (const uint16_t *)stage, h, P, (int)(tail & 0xffffu), nC, lane, bs, base + mboff[x]);
     }
     if (tid == 0) {
         if (row == row0) { BitRed w = {bs, 0}; slice_header(w, row0 * mw, k.is_idr, k.frame_num, k.idr_pic_id, k.qp); }
@@ -347,7 +396,7 @@ __global__ void __launch_bounds__(CV_WARPS * 32) k_cavlc_write(cc_kparams k) {
     const unsigned hdr_bytes = (unsigned)((sizeof(cc_rowhdr) * k.mb_h + 15) / 16 * 16), len_bytes = (unsigned)((4 * ns + 15) / 16 * 16);
     uint4 *dst = (uint4 *)(k.out_host_dev + hdr_bytes + len_bytes + (size_t)s * k.bs_slice_words * 4);
     uint4 *src = (uint4 *)bs;
-    for (unsigned i = tid; i < nq; i += CV_WARPS * 32) {
+    for (unsigned i = tid; i < nq; i += CW_WARPS * 32) {
         uint4 v = __ldcg(src + i);
         src[i] = make_uint4(0, 0, 0, 0);
         v.x = __byte_perm(v.x, 0, 0x0123); v.y = __byte_perm(v.y, 0, 0x0123); v.z = __byte_perm(v.z, 0, 0x0123); v.w = __byte_perm(v.w, 0, 0x0123);
@@ -362,6 +411,6 @@ __global__ void __launch_bounds__(CV_WARPS * 32) k_cavlc_write(cc_kparams k) {
 extern "C" int cck_cavlc(const cc_kparams *k, cudaStream_t st) {
     const int nmb = k->mb_w * k->mb_h;
     CC_LAUNCH(k_cavlc_size, dim3((unsigned)((nmb + CV_MB_PER_CTA - 1) / CV_MB_PER_CTA)), dim3(CV_WARPS * 32), st, *k);
-    CC_LAUNCH(k_cavlc_write, dim3((unsigned)k->mb_h), dim3(CV_WARPS * 32), st, *k);
+    CC_LAUNCH(k_cavlc_write, dim3((unsigned)k->mb_h), dim3(CW_WARPS * 32), st, *k);
     return 2;
 }

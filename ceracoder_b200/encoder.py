@@ -73,6 +73,8 @@ def load_library(path=None):
     L.cc_enc_device_bytes.restype = C.c_size_t
     L.cc_enc_kernel_launches.argtypes = [vp]
     L.cc_enc_kernel_launches.restype = C.c_long
+    L.cc_enc_staged_frames.argtypes = [vp]
+    L.cc_enc_staged_frames.restype = C.c_long
     L.cc_enc_set_profile.argtypes = [vp, ci]
     L.cc_enc_get_stage_ms.argtypes = [vp, vp, vp]
     L.cc_host_alloc.restype = vp
@@ -249,6 +251,10 @@ class CudaH264Enc:
         ms = (C.c_double * len(self.STAGES))(); n = (C.c_long * len(self.STAGES))()
         _check(self.L, self.L.cc_enc_get_stage_ms(self._h, ms, n), "cc_enc_get_stage_ms")
         return {s: (ms[i], n[i]) for i, s in enumerate(self.STAGES)}
+
+    def staged_frames(self):
+        """frames that arrived in pageable host memory and went through the handle's pinned staging frame"""
+        return self.L.cc_enc_staged_frames(self._h)
 
     def kernel_launches(self):
         return self.L.cc_enc_kernel_launches(self._h)

@@ -137,6 +137,10 @@ enum { CC_STAGE_UPLOAD = 0, CC_STAGE_INGEST, CC_STAGE_ME_COARSE, CC_STAGE_ME_FIN
        complete after CC_STAGE_PACK, the later stages run while the host writes the bitstream */
 int cc_enc_set_profile(cc_enc *h, int on);
 int cc_enc_get_stage_ms(const cc_enc *h, double *ms_sum /*[CC_STAGE_COUNT]*/, long *count /*[CC_STAGE_COUNT]*/);
+/* Frames handed to cc_enc_submit / cc_enc_encode in pageable host memory (a mapped GstBuffer) are first copied, by the calling
+ * thread, into a pinned frame the handle owns, so that the upload itself is asynchronous; page-locked frames (cc_host_alloc) and
+ * device frames are used where they lie.  Count of frames that took the staging copy since open: */
+long cc_enc_staged_frames(const cc_enc *h);
 /* number of kernel launches issued by this handle since open */
 long cc_enc_kernel_launches(const cc_enc *h);
 

@@ -37,6 +37,10 @@ static inline cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, s
     return 0;
 }
 static inline cudaError_t cudaMemcpy2D(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, enum cudaMemcpyKind k) { return cudaMemcpy2DAsync(d, dp, s, sp, w, h, k, 0); }
+enum cudaMemoryType { cudaMemoryTypeUnregistered = 0, cudaMemoryTypeHost = 1, cudaMemoryTypeDevice = 2, cudaMemoryTypeManaged = 3 };
+struct cudaPointerAttributes { enum cudaMemoryType type; int device; void *devicePointer, *hostPointer; };
+/* the emulator cannot tell pinned from pageable memory: report pageable, so the staging copy of cc_enc_submit is exercised */
+static inline cudaError_t cudaPointerGetAttributes(struct cudaPointerAttributes *a, const void *p) { (void)p; a->type = cudaMemoryTypeUnregistered; a->device = 0; a->devicePointer = a->hostPointer = 0; return 0; }
 static inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t st) { (void)st; memset(d, v, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned f) { (void)f; *s = 0; return 0; }
