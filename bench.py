@@ -1,23 +1,35 @@
 #!/usr/bin/env python
 """bench.py — 1080p H.264 encode throughput of libceracuda on B200 (BASELINE.json metric), one JSON line.
 
-Workload (config.workload): BASELINE configs[1] as the target defines it — 1080p60 `cudah264enc` streams under a
-2<->12 Mbps balancer-style bitrate schedule, 8 concurrent streams per GPU (north_star: "8 concurrent 1080p60 streams
-per GPU"), synthetic S2 pan-sprites content.  A *step* = every stream of this rank encodes
-FRAMES_PER_STEP frames.  `value` = frames/s with the frames already resident in HBM (CC_FRAME_DEVICE), `e2e` = the
-same through the public C-ABI call with pinned HOST frames (H2D inside) and the access unit in host memory.
+Workload (config.workload): BASELINE configs[1] in the shape the target is defined on — 1080p60 `cudah264enc` streams under a
+balancer-shaped 12 -> 2 -> 12 Mbit/s bitrate schedule, 8 concurrent streams per GPU (north_star: "8 concurrent 1080p60 streams
+per GPU"), synthetic S2 pan-sprites content as SURVEY.md §8d specifies it: 900 distinct frames = three scenes of 300, played in
+a loop, so every stream meets a scene cut every 300 frames.  A *step* = every stream of this rank encodes FRAMES_PER_STEP
+frames.
+  value         frames/s with the frames already resident in HBM (CC_FRAME_DEVICE)
+  e2e           the same through the public C-ABI call with page-locked HOST frames (H2D inside) and the access unit in host memory
+  e2e_pageable  the same with pageable host frames (what a mapped GstBuffer is): the library's pinned staging copy is inside
 Multi-GPU = independent replicas (one process per GPU, no collective on the data path): scaling "weak".
+
+`--impl reference`: the CPU arm.  x264enc / libx264 do not exist on this image, so it is the oracle port (oracle/, kind "port"),
+all host threads, on a bounded sample of the SAME workload at EQUAL BITRATE: it encodes stream 0's frames with the frame types and
+QPs the CUDA arm's rate control chose for them (tests/golden/qp_trace_1080p60.csv, recorded by tools/record_qp_trace.py), which
+makes its access units byte-identical to the CUDA arm's (checked frame by frame against the sizes and CRCs in the trace).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl cuda|reference]
 """
 import argparse
+import csv
 import ctypes as C
 import json
+import mmap
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -28,22 +40,26 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 W, H, FPS = 1920, 1080, 60
+FSZ = W * H * 3 // 2
 STREAMS = 8
-FRAMES_PER_STEP = 30
-POOL = 40                       # distinct synthetic frames, played ping-pong; 40 * 3.1 MB = 124 MB host, same in HBM
+FRAMES_PER_STEP = 120           # per stream; the driver's --steps 20 gives 2400 timed frames per stream (> 5 s)
+POOL = 900                      # S2 frames 0..899: scenes of 300, looped -> a cut every 300 frames
+STREAM_SHIFT = 113              # stream k plays the loop 113 frames ahead of stream k - 1
+GOP_PHASE = 7                   # and sits 7 frames further into its GOP (live streams do not emit their IDR frames in the same instant)
 ALG_BYTES_PER_FRAME = 4.5 * W * H   # read cur + read ref + write recon (+ bitstream)
 METRIC = "1080p H.264 encode fps per B200 at equal bitrate"
+TRACE = os.path.join(ROOT, "tests", "golden", "qp_trace_1080p60.csv")
+REF_FRAMES_PER_STEP = 12        # reference arm: frames of stream 0 per step (bounded sample; the oracle runs at tens of frames/s)
 
 
 def schedule_kbps(frame_idx):
-    """Balancer-shaped target for config 2: 12 Mbps, emergency drop to 2 Mbps, then +100..300 kbps every 520 ms
-    (the reference's adaptive ladder, /root/reference/src/core/bitrate_control.c:176-206), period 30 s."""
-    t = (frame_idx / FPS) % 30.0
+    """Balancer-shaped target for config 2 (the reference's adaptive ladder, /root/reference/src/core/bitrate_control.c:176-206):
+    12 Mbit/s, emergency drop to 2 Mbit/s after 1 s, then +100..300 kbit/s every 520 ms back to 12; period 30 s."""
+    t = (frame_idx / FPS + 4.0) % 30.0
     if t < 5.0:
         return 12000
-    steps = int((t - 5.0) / 0.52)
     kb = 2000
-    for _ in range(steps):
+    for _ in range(int((t - 5.0) / 0.52)):
         kb = min(12000, kb + 30 + kb // 30)
         kb = kb // 100 * 100 if kb % 100 == 0 else (kb // 100 + 1) * 100
     return kb
@@ -54,10 +70,86 @@ def pingpong(i, n):
     return p if p < n else 2 * n - 2 - p
 
 
-def make_pool():
+# ---- the frame store: S2 frames as tight I420, in a shared-memory file all ranks (and both arms) map ---------------------------
+def _gen_chunk(job):
+    path, a, b, n = job
     from ceracoder_b200.synth import make_source
+    arr = np.memmap(path, dtype=np.uint8, mode="r+", shape=(n, FSZ))
     src = make_source("pan", W, H)
-    return [src.frame(i) for i in range(POOL)]
+    for i in range(a, b):
+        y, u, v = src.frame(i)
+        arr[i, :W * H] = y.ravel(); arr[i, W * H:W * H * 5 // 4] = u.ravel(); arr[i, W * H * 5 // 4:] = v.ravel()
+    arr.flush()
+    return b - a
+
+
+def _store_dir(nbytes):
+    for d in ("/dev/shm", tempfile.gettempdir()):
+        try:
+            st = os.statvfs(d)
+            if os.access(d, os.W_OK) and st.f_bavail * st.f_frsize > nbytes * 1.1:
+                return d
+        except OSError:
+            pass
+    return tempfile.gettempdir()
+
+
+class FrameStore:
+    """n S2 frames.  n = POOL: the specified sequence, looped (index = sequence position mod n); smaller n (--pool, for ncu
+    runs): the first n frames played ping-pong.  One generator per box (local rank 0, one process per host core); everybody maps
+    the same file twice: one mapping gets page-locked (cc_host_register), the other stays pageable."""
+
+    def __init__(self, n, local_rank=0):
+        self.n = n
+        nbytes = n * FSZ
+        done = None
+        for d in ("/dev/shm", tempfile.gettempdir()):  # a store an earlier run on this box left behind
+            p = os.path.join(d, f"ceracuda_s2_{W}x{H}_{n}_v2.i420")
+            if os.path.exists(p + ".done") and os.path.getsize(p) == nbytes:
+                self.path, done = p, p + ".done"
+                break
+        t0 = time.perf_counter()
+        if done is None:
+            self.path = os.path.join(_store_dir(nbytes), f"ceracuda_s2_{W}x{H}_{n}_v2.i420")
+            done = self.path + ".done"
+            if local_rank == 0:
+                with open(self.path, "wb") as f:
+                    f.truncate(nbytes)
+                import multiprocessing as mp
+                procs = max(1, min(os.cpu_count() or 1, 32, n // 8 or 1))
+                step = (n + procs - 1) // procs
+                jobs = [(self.path, a, min(a + step, n), n) for a in range(0, n, step)]
+                with mp.get_context("fork").Pool(procs) as pool:  # nothing CUDA is initialised yet in this process
+                    pool.map(_gen_chunk, jobs)
+                with open(done + ".tmp", "w") as f:
+                    f.write("ok\n")
+                os.replace(done + ".tmp", done)
+            else:
+                while not os.path.exists(done):
+                    time.sleep(0.2)
+                    if time.perf_counter() - t0 > 900:
+                        raise RuntimeError("frame store was not generated by local rank 0")
+        self.gen_s = time.perf_counter() - t0
+        self._f = open(self.path, "r+b")
+        self._m1 = mmap.mmap(self._f.fileno(), nbytes)            # to be page-locked
+        self._m2 = mmap.mmap(self._f.fileno(), nbytes)            # stays pageable
+        self.arr = np.frombuffer(self._m1, dtype=np.uint8).reshape(n, FSZ)
+        self.arr_pageable = np.frombuffer(self._m2, dtype=np.uint8).reshape(n, FSZ)
+
+    def index(self, k, i):
+        """pool frame of stream k at sequence position i"""
+        return (i + STREAM_SHIFT * k) % self.n if self.n >= POOL else pingpong(i + 5 * k, self.n)
+
+    def planes(self, k, i, pageable=False):
+        f = (self.arr_pageable if pageable else self.arr)[self.index(k, i)]
+        return f[:W * H].reshape(H, W), f[W * H:W * H * 5 // 4].reshape(H // 2, W // 2), f[W * H * 5 // 4:].reshape(H // 2, W // 2)
+
+
+def load_trace():
+    """[(is_idr, qp, au_bytes, crc32)] of stream 0 of this workload, as the CUDA arm codes it (tools/record_qp_trace.py)"""
+    with open(TRACE) as f:
+        rows = [r for r in csv.reader(f) if r and not r[0].startswith("#")]
+    return [(int(r[1]), int(r[2]), int(r[3]), int(r[4], 16)) for r in rows[1:]]
 
 
 def dist_info():
@@ -111,33 +203,34 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def prepare_streams(encs, frames_of, n_frames, start_idx, phase=0, warm=False):
+def prepare_streams(encs, frames_of, n_frames, start_idx, warm=False):
     """Per stream the C arrays of frame descriptors (pointers into the resident pool, strides, pts) and bitrates.  Interpreter
     work under the GIL (8 threads would serialise on it), so it is done before the timed region; the frames themselves are
-    copied / encoded inside it."""
+    copied / encoded inside it.  Stream k runs GOP_PHASE * k frames ahead of stream 0 (its warm-up is that much longer)."""
     out = []
     for k, e in enumerate(encs):
-        n = n_frames + (phase * k if warm else 0)
-        first = start_idx + (0 if warm else phase * k)
+        n = n_frames + (GOP_PHASE * k if warm else 0)
+        first = start_idx + (0 if warm else GOP_PHASE * k)
         out.append(e.prepare_sequence([frames_of(k, first + i) for i in range(n)], [schedule_kbps(first + i + 37 * k) for i in range(n)]))
     return out
 
 
+STAT_KEYS = ("frames", "au_bytes", "sym_bytes", "n_skip", "n_inter", "n_intra", "n_intra_analysed", "n_skip_probed", "submit_ms", "wait_ms", "host_ms", "gpu_ms", "n_idr")
+
+
 def run_streams(encs, prepared, device_frames):
-    """Each encoder on its own host thread / CUDA stream; returns (frames, au_bytes, sym_bytes, ...).
-    phase: stream k runs phase*k frames ahead of stream 0 (its warm-up is that much longer), so that independent streams do
-    not sit on the same GOP phase (eight live streams do not emit their IDR frames in the same instant)."""
-    tot = [0, 0, 0, 0, 0, 0, 0, 0, 0.0, 0.0, 0.0, 0.0]
+    """Each encoder on its own host thread / CUDA stream; one C call per stream (cc_enc_encode_sequence: the frame loop the element's
+    streaming thread runs, off the interpreter lock).  Returns the summed statistics."""
+    tot = dict.fromkeys(STAT_KEYS, 0)
     lock = threading.Lock()
     errs = []
 
     def work(k, e):
-        try:  # one C call per stream per run_streams(): the frame loop itself runs in C (cc_enc_encode_sequence), off the interpreter lock
+        try:
             s = e.encode_sequence(prepared[k], device_frame=device_frames)
             with lock:
-                tot[0] += s.frames; tot[1] += s.au_bytes; tot[2] += s.sym_bytes
-                for j, v in enumerate((s.n_skip, s.n_inter, s.n_intra, s.n_intra_analysed, s.n_skip_probed, s.submit_ms, s.wait_ms, s.host_ms, s.gpu_ms)):
-                    tot[3 + j] += v
+                for key in STAT_KEYS:
+                    tot[key] += getattr(s, key)
         except Exception as ex:  # noqa: BLE001
             errs.append(ex)
     th = [threading.Thread(target=work, args=(k, e)) for k, e in enumerate(encs)]
@@ -175,71 +268,88 @@ def int_peaks(L):
     return out
 
 
-def cpu_baseline(pool, n_frames, rps=4):
-    """The oracle (CPU port of the same algorithm, OpenMP over slices/MBs) timed on this box's host cores."""
+def workload_config(args, world):
+    """the `config` object of the JSON line — the same for both arms (the reference arm runs a bounded sample of this workload)"""
+    S = args.streams
+    return {"workload": f"{S} concurrent 1080p60 cudah264enc streams per GPU, balancer-shaped 12->2->12 Mbps schedule (configs[1] x{S}, north_star target shape)",
+            "width": W, "height": H, "fps": FPS, "input_format": args.input_format, "streams_per_gpu": S, "frames_per_step": args.frames_per_step * S,
+            "frames_per_stream_per_step": args.frames_per_step, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16",
+            "key_int_max": 60, "entropy_coder": "host C (cc_cavlc.c)" if args.host_entropy else "device (k_cavlc_size + k_cavlc_write)",
+            "content": (f"S2 pan-sprites (SURVEY.md 8d): {POOL} distinct frames = 3 scenes of 300, looped: a scene cut every 300 frames; stream k offset by {STREAM_SHIFT} k frames"
+                        if args.pool >= POOL else f"S2 pan-sprites, first {args.pool} frames played ping-pong (--pool: short runs under ncu only)"),
+            "bitrate_schedule": "12 Mbit/s for 1 s, drop to 2 Mbit/s, +100..300 kbit/s every 520 ms back to 12 (period 30 s); per-frame QP by the encoder's rate control",
+            "l2": "inputs (2.8 GB frame store) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"}
+
+
+def replay_oracle(store, trace, n_frames, chunk, warm_chunks, threads):
+    """The CPU arm: stream 0's frames through the oracle with the (frame type, QP) trace of the CUDA arm.  Returns
+    (frames/s over the timed chunks, per-chunk seconds, every access unit matched the trace's size and CRC)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from oracle_lib import OracleEncoder, lib as oracle_lib_handle
-    oracle_lib_handle().ref_set_threads(os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1; the baseline uses every host thread
-    enc = OracleEncoder(W, H, FPS, rps)
-    y, u, v = pool[0]
-    enc.encode(y, u, v, True, 30)  # IDR outside the timed sample, like a warm stream
-    t0 = time.perf_counter()
-    for i in range(1, n_frames + 1):
-        y, u, v = pool[pingpong(i, len(pool))]
-        enc.encode(y, u, v, False, 30)
-    dt = time.perf_counter() - t0
+    oracle_lib_handle().ref_set_threads(threads)  # torchrun exports OMP_NUM_THREADS=1; the baseline uses every host thread
+    enc = OracleEncoder(W, H, FPS, 4)
+    secs, same = [], True
+    for c in range(0, n_frames, chunk):
+        t0 = time.perf_counter()
+        for i in range(c, min(c + chunk, n_frames)):
+            idr, qp, size, crc = trace[i]
+            y, u, v = store.planes(0, i)
+            au = enc.encode(y, u, v, bool(idr), qp)
+            same = same and len(au) == size and (zlib.crc32(au) & 0xffffffff) == crc
+        secs.append(time.perf_counter() - t0)
     enc.close()
-    return n_frames / dt
+    timed = secs[warm_chunks:]
+    frames = n_frames - warm_chunks * chunk
+    return frames / max(sum(timed), 1e-9), timed, same
 
 
-def main_reference(args, rank, world):
+def main_reference(args, rank, world, local):
     if rank != 0:
         return 0
-    from ceracoder_b200.synth import make_source
-    src = make_source("pan", W, H)
-    pool = [src.frame(i) for i in range(8)]
-    sample = FRAMES_PER_STEP  # P frames per step: one stream's share of a step of the CUDA arm
-    for _ in range(args.warmup):
-        cpu_baseline(pool, 1)
-    t0 = time.perf_counter()
-    fps_list = [cpu_baseline(pool, sample) for _ in range(args.steps)]
-    dt = time.perf_counter() - t0
-    fps = float(np.mean(fps_list))
+    store = FrameStore(args.pool, 0)
+    trace = load_trace()
+    chunk = REF_FRAMES_PER_STEP
+    n = min((args.steps + args.warmup) * chunk, len(trace))
     cores = os.cpu_count()
+    t0 = time.perf_counter()
+    fps, timed, same = replay_oracle(store, trace, n, chunk, args.warmup, cores)
+    kbps = sum(t[2] for t in trace[args.warmup * chunk:n]) * 8 / max((n - args.warmup * chunk) / FPS, 1e-9) / 1e3
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
-            "data": "synthetic S2 pan-sprites 1080p (tests inputs: ceracoder_b200/synth.py)",
-            "config": {"workload": "1080p60 H.264 encode, CPU reference encoder (oracle port; x264enc/libx264 is not installed on this image)",
-                       "width": W, "height": H, "fps": FPS, "qp": 30},
+            "ms_per_step": 1e3 * float(np.mean(timed)) if timed else None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
+            "data": "synthetic S2 pan-sprites 1080p (ceracoder_b200/synth.py), the CUDA arm's frame store",
+            "config": workload_config(args, args.gpus),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                             "sample": f"{sample} P frames of one 1080p stream per step at QP 30 (IDR untimed), OpenMP on all {cores} host threads"},
+                             "sample": f"frames 0..{n - 1} of stream 0 of the workload ({chunk} per step, the first {args.warmup} steps untimed, IDR frames included), coded by the "
+                                       f"oracle (OpenMP, {cores} host threads) with the frame types and QPs of the CUDA arm's rate control (tests/golden/qp_trace_1080p60.csv): "
+                                       f"equal bitrate, {kbps:.0f} kbit/s over the timed frames",
+                             "note": "x264enc / libx264 are not installed on this box: this is the repo's CPU port of the same encoder, not x264"},
+            "same_output_as_cuda_arm": bool(same), "achieved_kbps": kbps, "wall_s": time.perf_counter() - t0,
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
 
 
 def main():
-    global FRAMES_PER_STEP
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--streams", type=int, default=STREAMS)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU-baseline and quality legs (kernel experiments, ncu runs)")
     ap.add_argument("--rows-per-slice", type=int, default=4, help="macroblock rows per slice (experiments; the reported workload uses 4)")
     ap.add_argument("--partitions", type=int, default=1, help="0: 16x16 partitions only (experiments)")
     ap.add_argument("--input-format", default="I420", choices=["I420", "YUY2", "BGRx"],
-                    help="frame format handed to the encoder; packed formats are converted inside the ingest kernel (SURVEY 8f N2). "
-                         "The YUY2 pool carries exactly the I420 pool's pictures (chroma rows doubled), so the encoded workload is the same")
+                    help="frame format handed to the encoder; packed formats are converted inside the ingest kernel (SURVEY 8f N2); needs --pool <= 100")
     ap.add_argument("--host-entropy", action="store_true", help="CAVLC by the host C writer instead of the device kernels (round-1 path; comparison runs)")
     ap.add_argument("--frames-per-step", type=int, default=FRAMES_PER_STEP, help="frames each stream encodes per step (shorten for ncu runs)")
+    ap.add_argument("--pool", type=int, default=POOL, help=f"distinct frames; {POOL} = the specified S2 sequence looped; smaller = ping-pong over the first frames (ncu runs only)")
     args = ap.parse_args()
-    FRAMES_PER_STEP = args.frames_per_step
     rank, world, local = dist_info()
     if args.impl == "reference":
-        return main_reference(args, rank, world)
+        return main_reference(args, rank, world, local)
 
+    store = FrameStore(args.pool, local)  # before anything CUDA: the generator forks
     import torch
     import torch.distributed as dist
     assert torch.cuda.is_available(), "bench.py --impl cuda needs a CUDA device (there is no CPU fallback)"
@@ -248,30 +358,33 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from ceracoder_b200 import CudaH264Enc, load_library
     L = load_library()
-    S = args.streams
-    pool = make_pool()
-    FMT = args.input_format
+    S, FMT, n_pool, fps_step = args.streams, args.input_format, store.n, args.frames_per_step
     fsz = W * H * {"I420": 3, "YUY2": 4, "BGRx": 8}[FMT] // 2
-    # pinned host pool (e2e leg) and HBM-resident pool (value leg); both > 126 MB L2 together with the encoders' planes
-    hbase = L.cc_host_alloc(fsz * POOL); dbase = L.cc_dev_alloc(fsz * POOL)
-    assert hbase and dbase
-    harr = np.ctypeslib.as_array(C.cast(hbase, C.POINTER(C.c_uint8)), shape=(POOL, fsz))
-    for i, (y, u, v) in enumerate(pool):
-        if FMT == "I420":
-            harr[i, :W * H] = y.ravel(); harr[i, W * H:W * H * 5 // 4] = u.ravel(); harr[i, W * H * 5 // 4:] = v.ravel()
-        elif FMT == "YUY2":
-            f = harr[i].reshape(H, 2 * W)
-            f[:, 0::2] = y; f[:, 1::4] = np.repeat(u, 2, axis=0); f[:, 3::4] = np.repeat(v, 2, axis=0)
-        else:  # BGRx from the same pictures (BT.709 limited range, float; the encoder converts back with its integer matrix)
-            yy = (y.astype(np.float32) - 16) * (255 / 219)
-            uu = np.repeat(np.repeat(u, 2, 0), 2, 1).astype(np.float32) - 128; vv = np.repeat(np.repeat(v, 2, 0), 2, 1).astype(np.float32) - 128
-            f = harr[i].reshape(H, W, 4)
-            f[..., 2] = np.clip(yy + 1.7927 * vv, 0, 255); f[..., 1] = np.clip(yy - 0.2132 * uu - 0.5329 * vv, 0, 255)
-            f[..., 0] = np.clip(yy + 2.1124 * uu, 0, 255); f[..., 3] = 255
-    assert L.cc_dev_upload(dbase, hbase, fsz * POOL) == 0
+    if FMT == "I420":
+        harr, parr = store.arr, store.arr_pageable
+    else:  # packed copies of the same pictures (the encoder converts back with its integer matrix)
+        assert n_pool <= 100, "--input-format YUY2/BGRx: use --pool <= 100"
+        harr = np.empty((n_pool, fsz), np.uint8)
+        for i in range(n_pool):
+            fr = store.arr[i]
+            y, u, v = fr[:W * H].reshape(H, W), fr[W * H:W * H * 5 // 4].reshape(H // 2, W // 2), fr[W * H * 5 // 4:].reshape(H // 2, W // 2)
+            if FMT == "YUY2":
+                f = harr[i].reshape(H, 2 * W)
+                f[:, 0::2] = y; f[:, 1::4] = np.repeat(u, 2, axis=0); f[:, 3::4] = np.repeat(v, 2, axis=0)
+            else:
+                yy = (y.astype(np.float32) - 16) * (255 / 219)
+                uu = np.repeat(np.repeat(u, 2, 0), 2, 1).astype(np.float32) - 128; vv = np.repeat(np.repeat(v, 2, 0), 2, 1).astype(np.float32) - 128
+                f = harr[i].reshape(H, W, 4)
+                f[..., 2] = np.clip(yy + 1.7927 * vv, 0, 255); f[..., 1] = np.clip(yy - 0.2132 * uu - 0.5329 * vv, 0, 255)
+                f[..., 0] = np.clip(yy + 2.1124 * uu, 0, 255); f[..., 3] = 255
+        parr = harr.copy()
+    hbase, pbase = harr.ctypes.data, parr.ctypes.data
+    assert L.cc_host_register(hbase, harr.nbytes) == 0, "cudaHostRegister of the frame store failed"
+    dbase = L.cc_dev_alloc(harr.nbytes)
+    assert dbase and L.cc_dev_upload(dbase, hbase, harr.nbytes) == 0
 
     def planes(base, k, fi):
-        p = base + pingpong(fi + 5 * k, POOL) * fsz
+        p = base + store.index(k, fi) * fsz
         if FMT != "I420":
             return (p, W * (2 if FMT == "YUY2" else 4)), None, None
         return (p, W), (p + W * H, W // 2), (p + W * H * 5 // 4, W // 2)
@@ -280,65 +393,75 @@ def main():
         return [CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, speed_preset="veryfast", device=local, lib=L, fmt=FMT,
                             rows_per_slice=args.rows_per_slice, partitions=bool(args.partitions), host_entropy=args.host_entropy) for _ in range(S)]
 
-    def timed(device_frames, steps, warmup, profile=False):
+    def timed(base, device_frames, steps, warmup, profile=False):
         encs = make_encs()
-        base = dbase if device_frames else hbase
         fo = lambda k, fi: planes(base, k, fi)  # noqa: E731
-        run_streams(encs, prepare_streams(encs, fo, FRAMES_PER_STEP * max(warmup, 1), 0, phase=7, warm=True), device_frames)  # warm-up steps (IDR + RC settle), GOP phases spread
-        prepared = prepare_streams(encs, fo, FRAMES_PER_STEP * steps, FRAMES_PER_STEP * max(warmup, 1), phase=7)
+        run_streams(encs, prepare_streams(encs, fo, fps_step * max(warmup, 1), 0, warm=True), device_frames)  # warm-up steps (IDR + RC settle), GOP phases spread
+        prepared = prepare_streams(encs, fo, fps_step * steps, fps_step * max(warmup, 1))
         if profile:
             [e.set_profile(True) for e in encs]
         launches0 = sum(e.kernel_launches() for e in encs)
+        staged0 = sum(e.staged_frames() for e in encs)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter(); ev0.record()
-        frames, au_bytes, sym_bytes, *mbstats = run_streams(encs, prepared, device_frames)
+        tot = run_streams(encs, prepared, device_frames)
         torch.cuda.synchronize(); ev1.record(); torch.cuda.synchronize()
         wall_ms = 1e3 * (time.perf_counter() - t0)
         ms = max(ev0.elapsed_time(ev1), 1e-3)
         if world > 1:
             dist.barrier()
-        launches = sum(e.kernel_launches() for e in encs) - launches0
-        stages = {}
+        tot.update(ms=ms, wall_ms=wall_ms, launches=sum(e.kernel_launches() for e in encs) - launches0,
+                   staged=sum(e.staged_frames() for e in encs) - staged0, qps=[e.last.qp for e in encs], stages={})
         if profile:
             for e in encs:
                 for s, (tms, n) in e.stage_ms().items():
-                    a = stages.setdefault(s, [0.0, 0]); a[0] += tms; a[1] += n
-        qps = [e.last.qp for e in encs]
+                    a = tot["stages"].setdefault(s, [0.0, 0]); a[0] += tms; a[1] += n
         [e.close() for e in encs]
-        return dict(frames=frames, ms=ms, wall_ms=wall_ms, au_bytes=au_bytes, sym_bytes=sym_bytes, launches=launches, stages=stages, qps=qps, mbstats=mbstats)
+        return tot
 
     sampler = ClockSampler(local)
     sampler.start()
-    r_dev = timed(True, args.steps, args.warmup, profile=True)
+    r_dev = timed(dbase, True, args.steps, args.warmup, profile=True)
     clocks = sampler.stop()
-    r_e2e = timed(False, args.steps, args.warmup)
+    r_e2e = timed(hbase, False, args.steps, args.warmup)
+    r_page = timed(pbase, False, max(args.steps // 4, 1), 1)
 
-    def quality_leg(n_frames=360):
-        """One 1080p60 stream, frame by frame through the public call, under a 12 -> 2 -> 12 Mbps square wave (2 s per level):
-        Y-PSNR of the reconstruction against the source (the decoder reproduces the reconstruction bit-exactly — parity
-        tests) and the bitrate error over 1 s windows.  Untimed."""
-        enc = CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, device=local, lib=L, partitions=bool(args.partitions))
-        bits, targ, psnr = [], [], []
+    def quality_leg(n_frames=600):
+        """Stream 0 of the workload alone, frame by frame through the public call (pageable frames, as the element hands them over):
+        its (frame type, QP, size, CRC) per frame against the committed trace the CPU arm replays, the bitrate error over 1 s
+        windows and the Y-PSNR of the reconstruction against the source (the decoder reproduces the reconstruction
+        bit for bit — parity tests).  Untimed."""
+        enc = CudaH264Enc(W, H, fps=(FPS, 1), bitrate=12000, key_int_max=60, device=local, lib=L, partitions=bool(args.partitions),
+                          rows_per_slice=args.rows_per_slice, host_entropy=args.host_entropy)
+        try:
+            trace = load_trace()
+        except Exception:  # noqa: BLE001
+            trace = []
+        bits, targ, psnr, match = [], [], [], bool(trace)
         for i in range(n_frames):
-            kb = 12000 if (i // (2 * FPS)) % 2 == 0 else 2000
+            kb = schedule_kbps(i)
             enc.set_property("bitrate", kb)
-            y, u, v = pool[pingpong(i, POOL)]
+            y, u, v = store.planes(0, i, pageable=True)
             au = enc.encode(y, u, v)
             bits.append(8 * len(au)); targ.append(kb * 1000.0 / FPS)
+            if i < len(trace):
+                match = match and trace[i] == (int(enc.last.is_idr), int(enc.last.qp), len(au), zlib.crc32(au) & 0xffffffff)
             if i % 12 == 11:
                 ry = enc.recon()[0][:H, :W]
                 mse = float(((ry.astype(np.float32) - y.astype(np.float32)) ** 2).mean())
                 psnr.append((kb, 10 * np.log10(255.0 ** 2 / max(mse, 1e-9))))
         enc.close()
         b, t = np.array(bits, float), np.array(targ, float)
-        err = [abs(b[i:i + FPS].sum() - t[i:i + FPS].sum()) / t[i:i + FPS].sum() for i in range(0, n_frames - FPS + 1, FPS // 4)]
-        return {"frames": n_frames, "schedule": "square wave 12 <-> 2 Mbps, 2 s per level, 1080p60, one stream",
+        err = [abs(b[i:i + FPS].sum() - t[i:i + FPS].sum()) / t[i:i + FPS].sum() for i in range(FPS, n_frames - FPS + 1, FPS // 4)]
+        hi = [p for k, p in psnr if k >= 10000]; lo = [p for k, p in psnr if k <= 3000]
+        return {"frames": n_frames, "schedule": "stream 0 of the workload: 12 Mbit/s for 1 s, drop to 2, ladder back up; scene cut at frame 300",
                 "achieved_kbps": float(b.sum() / (n_frames / FPS) / 1e3), "target_kbps": float(t.sum() / (n_frames / FPS) / 1e3),
-                "bitrate_error_1s_windows": {"mean": float(np.mean(err)), "p95": float(np.percentile(err, 95))},
-                "y_psnr_db": {"at_12mbps": float(np.mean([p for k, p in psnr if k == 12000])), "at_2mbps": float(np.mean([p for k, p in psnr if k == 2000]))},
+                "bitrate_error_1s_windows": {"mean": float(np.mean(err)), "p95": float(np.percentile(err, 95)), "note": "first second left out"},
+                "y_psnr_db": {"at_10_to_12_mbps": float(np.mean(hi)) if hi else None, "at_2_to_3_mbps": float(np.mean(lo)) if lo else None},
+                "qp_trace_match": match, "qp_trace_frames_checked": min(n_frames, len(trace)),
                 "vs_x264enc": None, "note": "x264enc / libx264 are not installed on this box: the PSNR delta against x264 veryfast was not measured"}
 
     quality = quality_leg() if rank == 0 and not args.no_cpu_baseline else None
@@ -346,6 +469,7 @@ def main():
     dev = torch.device("cuda", local)
     f_dev, ms_dev = aggregate(r_dev["frames"], r_dev["ms"], world, device=dev)
     f_e2e, ms_e2e = aggregate(r_e2e["frames"], r_e2e["ms"], world, device=dev)
+    f_pg, ms_pg = aggregate(r_page["frames"], r_page["ms"], world, device=dev)
     launches, _ = aggregate(r_dev["launches"], 0.0, world, device=dev)
     if rank != 0:
         if world > 1:
@@ -354,20 +478,22 @@ def main():
 
     value = f_dev / (ms_dev / 1e3)
     e2e = f_e2e / (ms_e2e / 1e3)
+    e2e_pg = f_pg / (ms_pg / 1e3)
     peak, peak_src = peaks()
     st = r_dev["stages"]
+    names = {"mb_encode": "k_mb_encode", "me_coarse": "k_me_l1", "me_fine": "k_me_l0", "p_code": "k_p_code", "hpel": "k_hpel", "deblock": "k_deblock",
+             "pack": "k_pack" if args.host_entropy else "k_cavlc_size + k_cavlc_write"}
     dom = max((s for s in st if s != "upload"), key=lambda s: st[s][0]) if st else None
     roof = None
     if dom:
         avg_ms = st[dom][0] / max(st[dom][1], 1)
         ach = ALG_BYTES_PER_FRAME / (avg_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": {"mb_encode": "k_mb_encode", "me_coarse": "k_me_l1", "me_fine": "k_me_l0", "hpel": "k_hpel"}.get(dom, dom),
-                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": ncu_traffic({"mb_encode": "k_mb_encode", "me_coarse": "k_me_l1", "me_fine": "k_me_l0", "p_code": "k_p_code"}.get(dom, dom)),
+        roof = {"bound": "hbm", "kernel": names.get(dom, dom), "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": ncu_traffic(names.get(dom, dom)),
                 "avg_launch_ms": avg_ms, "launches_timed": st[dom][1], "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ALG_BYTES_PER_FRAME,
                 "note": "one launch = one 1080p frame of one stream; 8 streams' launches overlap on the GPU, so the per-launch duration includes sharing; "
-                        "aggregate_achieved = value * 4.5*W*H",
+                        "aggregate_achieved = value * 4.5*W*H.  The kernel is bound by the macroblock dependency chain, not by HBM (DESIGN.md 5)",
                 "aggregate_achieved": value * ALG_BYTES_PER_FRAME / 1e9,
                 "stage_ms_per_frame": {s: st[s][0] / max(st[s][1], 1) for s in st}}
     # integer roofline: algorithmic 4-pixel abs-diff-accumulate ops of the exhaustive coarse search
@@ -382,27 +508,40 @@ def main():
                    "achieved": a, "peak": pk.get("vabsdiff4_acc"), "unit": "Gop/s (thread-level)", "frac": a / pk["vabsdiff4_acc"] if pk.get("vabsdiff4_acc") else None,
                    "measured_peaks_gops": pk, "note": "launches of 8 streams overlap on the GPU; the kernel alone (ncu, profiles/) runs faster"}
     cpu = None
-    if not args.no_cpu_baseline:
-        t0 = time.perf_counter()
-        n = 160  # ~10 s of host work
-        fps_cpu = cpu_baseline(pool, n)
-        cpu = {"value": fps_cpu, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
-               "sample": f"{n} P frames of one 1080p stream at QP 30 with the oracle (OpenMP, all host threads), {time.perf_counter() - t0:.1f} s"}
-    steps_frames = FRAMES_PER_STEP * S
+    if not args.no_cpu_baseline and world == 1:
+        try:
+            trace = load_trace()
+            n = min(240, len(trace))  # ~10 s of host work
+            t0 = time.perf_counter()
+            fps_cpu, _, same = replay_oracle(store, trace, n, 12, 1, os.cpu_count())
+            cpu = {"value": fps_cpu, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+                   "sample": f"frames 0..{n - 1} of stream 0 of the workload (the first 12 untimed) coded by the oracle (OpenMP, all host threads) with the frame types and "
+                             f"QPs of this arm's rate control (tests/golden/qp_trace_1080p60.csv): equal bitrate, {time.perf_counter() - t0:.1f} s",
+                   "same_output_as_cuda_arm": bool(same)}
+        except Exception as ex:  # noqa: BLE001
+            cpu = {"value": None, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port", "sample": f"not run: {ex}"}
+    nf = max(r_e2e["frames"], 1)
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32",
-            "data": "synthetic S2 pan-sprites 1080p (SURVEY.md §8d), 40-frame pool played ping-pong",
-            "config": {"workload": f"{S} concurrent 1080p60 cudah264enc streams per GPU, balancer-shaped 12->2->12 Mbps schedule (configs[1] x8, north_star target shape)",
-                       "width": W, "height": H, "fps": FPS, "input_format": FMT, "streams_per_gpu": S, "frames_per_step": steps_frames, "rows_per_slice": args.rows_per_slice, "partitions": "16x16+8x8" if args.partitions else "16x16", "key_int_max": 60, "entropy_coder": "host C (cc_cavlc.c)" if args.host_entropy else "device (k_cavlc_size + k_cavlc_write)",
-                       "l2": "inputs (124 MB pool) + 8 streams' planes exceed the 126 MB L2; no explicit flush", "parallelism": f"replicas x{world}"},
-            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": steps_frames * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
-                    "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps},
+            "data": f"synthetic S2 pan-sprites 1080p (SURVEY.md 8d), {n_pool}-frame store" + (", looped" if n_pool >= POOL else ", ping-pong"),
+            "config": workload_config(args, world),
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": fps_step * S * fsz, "d2h_bytes_per_step": int(r_e2e["sym_bytes"] / args.steps),
+                    "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps, "host_frames": "page-locked (cc_host_register)"},
+            "e2e_pageable": {"value": e2e_pg, "unit": "frames/s", "frames": int(f_pg), "staged_frames": int(r_page["staged"]),
+                             "note": "pageable host frames, as gst_video_frame_map hands them to the element: each frame is copied by the calling thread into the handle's "
+                                     "pinned staging frame (cc_enc_submit), then uploaded asynchronously"},
+            "timed_region": {"frames_per_stream": fps_step * args.steps, "frames": int(f_dev), "idr_frames": int(r_dev["n_idr"]), "seconds": ms_dev / 1e3,
+                             "scene_cuts_per_stream": (fps_step * args.steps) // 300 if n_pool >= POOL else 0},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu, "quality": quality,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
-            "mb_per_frame": dict(zip(("skip", "inter", "intra", "intra_analysed", "skip_probed"), [round(v / max(r_dev["frames"], 1), 1) for v in r_dev["mbstats"][:5]])),
-            "host_ms_per_frame": dict(zip(("submit_api", "wait_device", "cavlc_nal", "device_frame_latency"), [round(v / max(r_e2e["frames"], 1), 4) for v in r_e2e["mbstats"][5:9]])),
-            "wall_ms": {"value_leg": r_dev["wall_ms"], "e2e_leg": r_e2e["wall_ms"]}}
+            "mb_per_frame": {k: round(r_dev["n_" + k] / max(r_dev["frames"], 1), 1) for k in ("skip", "inter", "intra", "intra_analysed", "skip_probed")},
+            "host_ms_per_frame": {"submit_api": round(r_e2e["submit_ms"] / nf, 4), "wait_device": round(r_e2e["wait_ms"] / nf, 4),
+                                  "cavlc_nal": round(r_e2e["host_ms"] / nf, 4), "device_frame_latency": round(r_e2e["gpu_ms"] / nf, 4),
+                                  "submit_api_pageable": round(r_page["submit_ms"] / max(r_page["frames"], 1), 4)},
+            "frame_store": {"path": store.path, "generate_s": round(store.gen_s, 1)},
+            "wall_ms": {"value_leg": r_dev["wall_ms"], "e2e_leg": r_e2e["wall_ms"], "e2e_pageable_leg": r_page["wall_ms"]}}
     print(json.dumps(line))
+    L.cc_host_unregister(hbase)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -293,7 +293,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
-    cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max);
+    cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max, e->p.key_int_max);
     cudaStreamSynchronize(e->st);
     cudaDeviceSynchronize();
     *h = e;
@@ -634,7 +634,7 @@ int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate
         acc->n_skip += pkt.n_skip; acc->n_inter += pkt.n_inter; acc->n_intra += pkt.n_intra;
         acc->n_intra_analysed += pkt.n_intra_analysed; acc->n_skip_probed += pkt.n_skip_probed;
         acc->submit_ms += pkt.submit_ms; acc->wait_ms += pkt.wait_ms; acc->host_ms += pkt.host_ms; acc->gpu_ms += pkt.gpu_ms;
-        acc->last_qp = pkt.qp;
+        acc->last_qp = pkt.qp; acc->n_idr += pkt.is_idr;
     }
     if (last) *last = pkt;
     return CC_OK;
@@ -689,6 +689,8 @@ int cc_enc_get_mbinfo(cc_enc *e, uint8_t *dst8) {
 
 void *cc_host_alloc(size_t bytes) { void *p = NULL; return cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess ? p : NULL; }
 void cc_host_free(void *p) { if (p) cudaFreeHost(p); }
+int cc_host_register(void *p, size_t bytes) { return (p && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) ? CC_OK : CC_ERR_CUDA; }
+int cc_host_unregister(void *p) { return (p && cudaHostUnregister(p) == cudaSuccess) ? CC_OK : CC_ERR_CUDA; }
 void *cc_dev_alloc(size_t bytes) { void *p = NULL; return cudaMalloc(&p, bytes) == cudaSuccess ? p : NULL; }
 void cc_dev_free(void *p) { if (p) cudaFree(p); }
 int cc_dev_upload(void *dst, const void *src, size_t bytes) { return cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? CC_OK : CC_ERR_CUDA; }

@@ -77,8 +77,15 @@ typedef struct {
     double fullness;      /* accumulated (actual - target) bits */
     double last_qp_p;
     int frames;
+    int key_int;          /* IDR period in frames */
+    int step;             /* the target moved by more than a ladder step since the last P frame: follow the model at once */
+    double vbv_fill;      /* leaky bucket: bits sent above the target rate that have not drained yet */
+    double vbv_seconds;   /* bucket size in seconds of the current bitrate (x264enc vbv-buf-capacity: 600 ms) */
+    double ema, max_step; /* weight of a new P frame in the complexity model; largest QP change between P frames */
+    int fast;             /* P frames left that update the model at full speed (after a balancer step) */
+    double vbv_peak;      /* highest fill seen, in seconds of bitrate (reported by tests / tools) */
 } cc_rc;
-void cc_rc_init(cc_rc *rc, double fps, int bitrate, int qp_min, int qp_max);
+void cc_rc_init(cc_rc *rc, double fps, int bitrate, int qp_min, int qp_max, int key_int);
 int cc_rc_frame_qp(cc_rc *rc, int bitrate_now, int is_idr, int nmb);
 void cc_rc_update(cc_rc *rc, int is_idr, int qp, long bits);
 

@@ -35,7 +35,7 @@ class Packet(C.Structure):
 
 class SeqStats(C.Structure):
     _fields_ = [(n, C.c_long) for n in ("frames", "au_bytes", "sym_bytes", "n_skip", "n_inter", "n_intra", "n_intra_analysed", "n_skip_probed")] + \
-               [(n, C.c_double) for n in ("submit_ms", "wait_ms", "host_ms", "gpu_ms")] + [("last_qp", C.c_int)]
+               [(n, C.c_double) for n in ("submit_ms", "wait_ms", "host_ms", "gpu_ms")] + [("last_qp", C.c_int), ("n_idr", C.c_int)]
 
 
 _libs = {}
@@ -80,6 +80,8 @@ def load_library(path=None):
     L.cc_host_alloc.restype = vp
     L.cc_host_alloc.argtypes = [C.c_size_t]
     L.cc_host_free.argtypes = [vp]
+    L.cc_host_register.argtypes = [vp, C.c_size_t]
+    L.cc_host_unregister.argtypes = [vp]
     L.cc_dev_alloc.restype = vp
     L.cc_dev_alloc.argtypes = [C.c_size_t]
     L.cc_dev_free.argtypes = [vp]

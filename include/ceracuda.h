@@ -113,6 +113,7 @@ typedef struct {
     long n_skip, n_inter, n_intra, n_intra_analysed, n_skip_probed;
     double submit_ms, wait_ms, host_ms, gpu_ms;
     int last_qp;
+    int n_idr;           /* IDR frames among the n */
 } cc_seq_stats;
 int cc_enc_encode_sequence(cc_enc *h, const cc_frame *frames, const int *bitrate_bps, int n, unsigned flags, cc_seq_stats *acc, cc_packet *last);
 
@@ -147,6 +148,10 @@ long cc_enc_kernel_launches(const cc_enc *h);
 /* pinned host memory for frames (lets cc_enc_submit's upload run asynchronously) */
 void *cc_host_alloc(size_t bytes);
 void cc_host_free(void *p);
+/* page-lock memory the caller already owns (a buffer pool, a shared-memory frame store) so that frames in it upload without the
+ * staging copy; undo before freeing it */
+int cc_host_register(void *p, size_t bytes);
+int cc_host_unregister(void *p);
 /* device memory helpers for callers that keep frames resident in HBM (CC_FRAME_DEVICE) */
 void *cc_dev_alloc(size_t bytes);
 void cc_dev_free(void *p);

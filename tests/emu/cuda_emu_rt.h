@@ -28,6 +28,9 @@ static inline cudaError_t cudaFree(void *p) { free(p); return 0; }
 static inline cudaError_t cudaHostAlloc(void **p, size_t n, unsigned f) { (void)f; *p = malloc(n ? n : 1); return *p ? 0 : 2; }
 static inline cudaError_t cudaMallocHost(void **p, size_t n) { return cudaHostAlloc(p, n, 0); }
 static inline cudaError_t cudaFreeHost(void *p) { free(p); return 0; }
+enum { cudaHostRegisterDefault = 0 };
+static inline cudaError_t cudaHostRegister(void *p, size_t n, unsigned f) { (void)p; (void)n; (void)f; return 0; }
+static inline cudaError_t cudaHostUnregister(void *p) { (void)p; return 0; }
 static inline cudaError_t cudaHostGetDevicePointer(void **d, void *h, unsigned f) { (void)f; *d = h; return 0; }
 static inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, enum cudaMemcpyKind k) { (void)k; memmove(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, enum cudaMemcpyKind k, cudaStream_t st) { (void)k; (void)st; memmove(d, s, n); return 0; }

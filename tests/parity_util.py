@@ -78,3 +78,27 @@ def run_parity(lib, source, w, h, qps, rps=4, gop=60, fmt="I420", check_decode=T
 def psnr(a, b):
     mse = ((a.astype(np.float64) - b.astype(np.float64)) ** 2).mean()
     return 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)
+
+
+def run_rc_parity(lib, src, w, h, fps, n, kbps_of, gop=60, rps=4, recon_every=10, host_entropy=False):
+    """Rate control ON: the CUDA encoder runs its own per-frame QP decisions under the bitrate schedule kbps_of(i); the oracle is
+    then driven with exactly the frame types and QPs the encoder chose (the QP trace), and every access unit must be
+    byte-identical — the whole stream, across IDR restarts and bitrate steps.  Returns (access units, qp trace)."""
+    enc = CudaH264Enc(w, h, fps=(fps, 1), bitrate=kbps_of(0), rows_per_slice=rps, key_int_max=gop, lib=lib, host_entropy=host_entropy)
+    orc = OracleEncoder(w, h, fps, rps)
+    aus, trace = [], []
+    try:
+        for i in range(n):
+            y, u, v = src.frame(i)
+            enc.set_property("bitrate", kbps_of(i))
+            a = enc.encode(y, u, v)
+            qp, idr = enc.last.qp, bool(enc.last.is_idr)
+            b = orc.encode(y, u, v, idr, qp)
+            assert a == b, f"frame {i} (qp {qp}, idr {idr}): access units differ ({len(a)} vs {len(b)} bytes)"
+            if i % recon_every == recon_every - 1 or i == n - 1:
+                for p, q in zip(enc.recon(), orc.recon()):
+                    assert (p == q).all(), f"frame {i}: reconstruction differs"
+            aus.append(a); trace.append((int(idr), qp, len(a)))
+    finally:
+        enc.close(); orc.close()
+    return aus, trace

@@ -153,3 +153,14 @@ def test_device_and_host_entropy_coders_write_the_same_bytes(lib):
             assert x == y, f"device and host entropy coders differ at qp {qp} ({len(x)} vs {len(y)} bytes)"
             assert a.last.sym_bytes < b.last.sym_bytes or qp == 10       # finished bits cross PCIe, not symbols
         a.close(); b.close()
+
+
+def test_rate_controlled_stream_replayed_by_the_oracle(lib):
+    """the method of tests/test_gpu_parity_long.py at a size the emulator finishes quickly: rate control on, a bitrate step, two
+    IDR restarts, a scene cut; the oracle replays the (frame type, QP) trace and every access unit is byte-identical"""
+    from ceracoder_b200.synth import PanSprites
+    from parity_util import run_rc_parity
+    w, h = 176, 144
+    aus, trace = run_rc_parity(lib, PanSprites(w, h, cut_every=11), w, h, 30, 26, lambda i: 900 if i < 9 else 300, gop=12, rps=3, recon_every=5)
+    assert [i for i, t in enumerate(trace) if t[0]] == [0, 12, 24]
+    assert len({t[1] for t in trace}) > 3

@@ -94,4 +94,54 @@ def test_1080p60_balancer_schedule_bitrate_error():
     total = abs(tb[:, 1].sum() - (tb[:, 0] / 60).sum()) / (tb[:, 0] / 60).sum()
     print(f"mean 1s-window error {err.mean():.3f}, p95 {np.percentile(err, 95):.3f}, whole-run error {total:.3f}")
     assert err.mean() <= 0.05, f"mean bitrate error {err.mean():.3f} > 5 %"
+    assert np.percentile(err, 95) <= 0.06, f"p95 bitrate error {np.percentile(err, 95):.3f} > 6 %"
     assert total <= 0.03
+
+
+def constant_rate_run(lib, source, w, h, fps, kbps, seconds, pool):
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    src = make_source(source, w, h)
+    frames = [src.frame(i) for i in range(pool)] if pool else None
+    enc = CudaH264Enc(w, h, fps=(fps, 1), bitrate=kbps, key_int_max=60, lib=lib)
+    out = []
+    for i in range(int(seconds * fps)):
+        if frames:
+            p = i % (2 * pool - 2)
+            y, u, v = frames[p if p < pool else 2 * pool - 2 - p]
+        else:
+            y, u, v = src.frame(i)
+        out.append((kbps * 1000.0, 8 * len(enc.encode(y, u, v))))
+    enc.close()
+    return np.array(out, dtype=np.float64)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,source,w,h,fps,kbps,pool", [
+    ("config1 1080p30 @ 6 Mbps, S1 testsrc", "testsrc", 1920, 1080, 30, 6000, 0),
+    ("config1 1080p30 @ 6 Mbps, S2 pan-sprites", "pan", 1920, 1080, 30, 6000, 40),
+    ("config3 720p60 @ 4 Mbps, S2 pan-sprites", "pan", 1280, 720, 60, 4000, 40),
+    ("config4 2160p30 @ 20 Mbps, S2 pan-sprites", "pan", 3840, 2160, 30, 20000, 24),
+])
+def test_constant_bitrate_configs_stay_within_five_percent(name, source, w, h, fps, kbps, pool):
+    """BASELINE configs 1, 3, 4 at their constant bitrates, GOP 60: mean 1 s-window error <= 5 %, p95 <= 10 % (the first second is
+    left out: the controller starts without a model).  720p60 runs on S2 content: the S3 ball picture needs 0.4 Mbit/s at the
+    smallest QP the CAVLC level range allows (10) and cannot fill 4 Mbit/s — no encoder pads."""
+    from ceracoder_b200 import load_library
+    tb = constant_rate_run(load_library(), source, w, h, fps, kbps, 7.0, pool)
+    err = window_errors(tb, fps)[fps:]
+    print(f"{name}: mean {err.mean():.3f} p95 {np.percentile(err, 95):.3f} achieved {tb[fps:, 1].sum() / (len(tb) - fps) * fps / 1e3:.0f} kbit/s")
+    assert err.mean() <= 0.05, f"{name}: mean 1 s-window bitrate error {err.mean():.3f} > 5 %"
+    assert np.percentile(err, 95) <= 0.10, f"{name}: p95 {np.percentile(err, 95):.3f} > 10 %"
+
+
+@pytest.mark.gpu
+def test_1080p60_square_wave_step_response():
+    """12 <-> 2 Mbit/s every 2 s (the hardest schedule a balancer can produce: the emergency drop,
+    /root/reference/src/core/bitrate_control.c:176-185): mean 1 s-window error <= 5 %, p95 <= 10 %"""
+    from ceracoder_b200 import load_library
+    sched = [(2000 * i, 12000000 if i % 2 == 0 else 2000000) for i in range(6)]
+    tb = run_schedule(load_library(), 1920, 1080, 60, sched, 12.0, pool=40)
+    err = window_errors(tb, 60)[60:]
+    print(f"square wave: mean {err.mean():.3f} p95 {np.percentile(err, 95):.3f}")
+    assert err.mean() <= 0.05 and np.percentile(err, 95) <= 0.10
