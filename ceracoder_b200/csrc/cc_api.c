@@ -21,8 +21,10 @@ struct cc_enc {
     cc_enc_params p;
     cc_kparams k;
     cc_seq seq;
-    cudaStream_t st;
+    cudaStream_t st;             /* upload, search, coding, entropy coding: what the access unit waits for */
+    cudaStream_t st2;            /* in-loop filter and reference finishing of the same frame, concurrent with the entropy coder */
     cudaEvent_t ev0, ev1;
+    cudaEvent_t ev_enc, ev_tail; /* st -> st2 after k_mb_encode; st2 -> st before the next frame touches what the tail reads */
     void *dev_alloc[48];
     int n_dev_alloc;
     size_t dev_bytes;
@@ -42,9 +44,9 @@ struct cc_enc {
     long launches;
     int last_was_p;
     int profile;                 /* per-kernel CUDA events on */
-    cudaEvent_t pevs[2][CC_N_STAGES + 1]; /* two sets, alternating per frame: the stages behind ev1 (reference finishing) are read when the set
+    cudaEvent_t pevs[2][CC_N_STAGES + 2]; /* two sets, alternating per frame: the stages behind ev1 (reference finishing) are read when the set
                                            * comes round again, two frames later, when they are certainly complete */
-    int pevs_used[2][CC_N_STAGES + 1];
+    int pevs_used[2][CC_N_STAGES + 2];
     int pevs_tail[2];            /* set holds unread tail stages */
     int pb;                      /* set of the frame in flight */
     double stage_ms[CC_N_STAGES];
@@ -288,14 +290,17 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!e->au || !e->rbsp || !e->cav.nnz) rc = CC_ERR_NOMEM;
     if (rc == CC_OK) rc = pool_start(e, p->threads);
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st2, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    if (rc == CC_OK && (cudaEventCreateWithFlags(&e->ev_enc, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ev_tail, cudaEventDisableTiming) != cudaSuccess)) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
-    for (int i = 0; i < 2 * (CC_N_STAGES + 1) && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]) != cudaSuccess) rc = CC_ERR_CUDA;
+    for (int i = 0; i < 2 * (CC_N_STAGES + 2) && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
     cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max, e->p.key_int_max);
     cudaStreamSynchronize(e->st);
     cudaDeviceSynchronize();
+    if (rc == CC_OK) cudaEventRecord(e->ev_tail, e->st2); /* so that the first frame's wait finds a recorded event */
     *h = e;
     return CC_OK;
 }
@@ -308,6 +313,7 @@ void cc_enc_close(cc_enc *e) {
     if (!e) return;
     bind_device(e);
     if (e->st) cudaStreamSynchronize(e->st);
+    if (e->st2) cudaStreamSynchronize(e->st2);
     if (e->k.cyc && e->frame_idx > 0) { /* CC_DEBUG_CYCLES=1: where the wavefront kernel's warps spent their cycles */
         size_t n = (size_t)e->k.mb_h * 16;
         unsigned long long *h = (unsigned long long *)calloc(n, 8), s[16] = {0};
@@ -327,8 +333,11 @@ void cc_enc_close(cc_enc *e) {
     if (e->stage_host) cudaFreeHost(e->stage_host);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
-    for (int i = 0; i < 2 * (CC_N_STAGES + 1); i++) if (e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]) cudaEventDestroy(e->pevs[i / (CC_N_STAGES + 1)][i % (CC_N_STAGES + 1)]);
+    for (int i = 0; i < 2 * (CC_N_STAGES + 2); i++) if (e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) cudaEventDestroy(e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]);
+    if (e->ev_enc) cudaEventDestroy(e->ev_enc);
+    if (e->ev_tail) cudaEventDestroy(e->ev_tail);
     if (e->st) cudaStreamDestroy(e->st);
+    if (e->st2) cudaStreamDestroy(e->st2);
     free(e->au); free(e->rbsp); free(e->cav.nnz);
     free(e);
 }
@@ -461,9 +470,12 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
         }
     }
 #define STAGE(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
-    for (int i = 0; i <= CC_N_STAGES; i++) pev_used[i] = 0;
+    for (int i = 0; i <= CC_N_STAGES + 1; i++) pev_used[i] = 0;
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);
+    /* Upload and ingest only touch the source planes.  Everything from here on reads what the previous frame's tail (in-loop filter,
+     * borders, half-pel planes, half-resolution reference — on st2) produces, or overwrites what it reads (the neighbour records). */
+    CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
     STAGE(CC_STAGE_ME_COARSE);
     if (!is_idr) e->launches += cck_me_l1(k, e->st);
     STAGE(CC_STAGE_ME_FINE);
@@ -473,19 +485,26 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
     STAGE(CC_STAGE_PACK);
+    CUCHECK(cudaEventRecord(e->ev_enc, e->st));
     e->launches += k->dev_entropy ? cck_cavlc(k, e->st) : cck_pack(k, e->st);
-    STAGE(CC_STAGE_DEBLOCK);
-    /* the access unit's symbols are in host memory here: cc_enc_collect waits for ev1 only, and the kernels that turn the
-     * reconstruction into the next frame's reference run while the host writes the bitstream */
+    /* the access unit's bits (or symbols) are in host memory here: cc_enc_collect waits for ev1 only */
     CUCHECK(cudaEventRecord(e->ev1, e->st));
-    e->launches += cck_deblock(k, e->st);
-    STAGE(CC_STAGE_BORDER);
-    e->launches += cck_border(k, e->st);
-    STAGE(CC_STAGE_HPEL);
-    e->launches += cck_hpel(k, e->st);
-    STAGE(CC_STAGE_L1REF);
-    e->launches += cck_l1ref(k, e->st);
-    STAGE(CC_N_STAGES);
+    if (e->profile) { cudaEventRecord(pev[CC_N_STAGES + 1], e->st); pev_used[CC_N_STAGES + 1] = 1; }
+    /* The kernels that turn the reconstruction into the next frame's reference need nothing from the entropy coder and nothing it
+     * writes: they run on the second stream next to it, and then on while the host packages the access unit. */
+    CUCHECK(cudaStreamWaitEvent(e->st2, e->ev_enc, 0));
+#define STAGE2(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st2); pev_used[i] = 1; } } while (0)
+    STAGE2(CC_STAGE_DEBLOCK);
+    e->launches += cck_deblock(k, e->st2);
+    STAGE2(CC_STAGE_BORDER);
+    e->launches += cck_border(k, e->st2);
+    STAGE2(CC_STAGE_HPEL);
+    e->launches += cck_hpel(k, e->st2);
+    STAGE2(CC_STAGE_L1REF);
+    e->launches += cck_l1ref(k, e->st2);
+    STAGE2(CC_N_STAGES);
+#undef STAGE2
+    CUCHECK(cudaEventRecord(e->ev_tail, e->st2));
 #undef STAGE
     e->pevs_tail[e->pb] = e->profile;
     CUCHECK(cudaGetLastError());
@@ -540,7 +559,8 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
     if (e->profile)
         for (int i = 0; i < CC_STAGE_DEBLOCK; i++) {
             float ms = 0;
-            if ((i == CC_STAGE_UPLOAD || e->pevs_used[e->pb][i]) && cudaEventElapsedTime(&ms, e->pevs[e->pb][i], e->pevs[e->pb][i + 1]) == cudaSuccess) {
+            cudaEvent_t end = i == CC_STAGE_PACK ? e->pevs[e->pb][CC_N_STAGES + 1] : e->pevs[e->pb][i + 1];
+            if ((i == CC_STAGE_UPLOAD || e->pevs_used[e->pb][i]) && cudaEventElapsedTime(&ms, e->pevs[e->pb][i], end) == cudaSuccess) {
                 if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
             }
         }
@@ -646,6 +666,7 @@ int cc_enc_get_recon(cc_enc *e, uint8_t *y, uint8_t *u, uint8_t *v) {
     if (bind_device(e) != CC_OK) return CC_ERR_CUDA;
     cc_kparams *k = &e->k; /* after submit the newest reconstruction is k->ref */
     CUCHECK(cudaStreamSynchronize(e->st));
+    CUCHECK(cudaStreamSynchronize(e->st2));
     CUCHECK(cudaMemcpy2D(y, (size_t)k->W, k->ref[0], (size_t)k->sy, (size_t)k->W, (size_t)k->H, cudaMemcpyDeviceToHost));
     CUCHECK(cudaMemcpy2D(u, (size_t)k->W / 2, k->ref[1], (size_t)k->sc, (size_t)k->W / 2, (size_t)k->H / 2, cudaMemcpyDeviceToHost));
     CUCHECK(cudaMemcpy2D(v, (size_t)k->W / 2, k->ref[2], (size_t)k->sc, (size_t)k->W / 2, (size_t)k->H / 2, cudaMemcpyDeviceToHost));

@@ -29,7 +29,7 @@ void cc_rc_init(cc_rc *rc, double fps, int bitrate, int qp_min, int qp_max, int 
     rc->fullness = 0; rc->last_qp_p = -1; rc->frames = 0;
     rc->key_int = key_int > 0 ? key_int : 60;
     rc->vbv_fill = 0; rc->vbv_seconds = 0.6; rc->step = 0; rc->vbv_peak = 0;
-    rc->ema = 0.25; rc->max_step = 3; rc->fast = 0;
+    rc->ema = 0.12; rc->max_step = 3; rc->fast = 0; /* measured on the B200, profiles/rc_grid_r02.txt */
     { /* experiment knobs (tools/rc_report.py sweeps them); the defaults above are what ships */
         const char *v;
         if ((v = getenv("CERACUDA_RC_EMA"))) rc->ema = atof(v);
