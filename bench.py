@@ -287,7 +287,7 @@ def replay_oracle(store, trace, n_frames, chunk, warm_chunks, threads):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from oracle_lib import OracleEncoder, lib as oracle_lib_handle
     oracle_lib_handle().ref_set_threads(threads)  # torchrun exports OMP_NUM_THREADS=1; the baseline uses every host thread
-    enc = OracleEncoder(W, H, FPS, 4)
+    enc = OracleEncoder(W, H, FPS, 8)  # the library default rows_per_slice (what the trace was recorded with)
     secs, same = [], True
     for c in range(0, n_frames, chunk):
         t0 = time.perf_counter()
@@ -337,7 +337,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--streams", type=int, default=STREAMS)
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU-baseline and quality legs (kernel experiments, ncu runs)")
-    ap.add_argument("--rows-per-slice", type=int, default=4, help="macroblock rows per slice (experiments; the reported workload uses 4)")
+    ap.add_argument("--rows-per-slice", type=int, default=8, help="macroblock rows per slice (experiments; the reported workload uses the library default, 8)")
     ap.add_argument("--partitions", type=int, default=1, help="0: 16x16 partitions only (experiments)")
     ap.add_argument("--input-format", default="I420", choices=["I420", "YUY2", "BGRx"],
                     help="frame format handed to the encoder; packed formats are converted inside the ingest kernel (SURVEY 8f N2); needs --pool <= 100")

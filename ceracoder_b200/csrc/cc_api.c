@@ -96,7 +96,7 @@ const char *cc_strerror(int c) {
 void cc_enc_params_default(cc_enc_params *p) {
     memset(p, 0, sizeof *p);
     p->fps_n = 30; p->fps_d = 1; p->format = CC_FMT_I420; p->bitrate_bps = 6000000; /* reference default max, bitrate_control.h:32 */
-    p->key_int_max = 60; p->rows_per_slice = 4; p->qp_min = 10; p->qp_max = 51; p->partitions = 1;
+    p->key_int_max = 60; p->rows_per_slice = 8; p->qp_min = 10; p->qp_max = 51; p->partitions = 1;
 }
 
 static int dev_alloc(cc_enc *e, void **p, size_t n) {
@@ -214,7 +214,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!e) return CC_ERR_NOMEM;
     e->p = *p;
     if (e->p.key_int_max <= 0) e->p.key_int_max = 60;
-    if (e->p.rows_per_slice <= 0) e->p.rows_per_slice = 4;
+    if (e->p.rows_per_slice <= 0) e->p.rows_per_slice = 8;
     if (e->p.qp_min <= 0) e->p.qp_min = 10;
     if (e->p.qp_max <= 0 || e->p.qp_max > 51) e->p.qp_max = 51;
     if (e->p.qp_min < 10) e->p.qp_min = 10;
@@ -254,6 +254,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->pre, sizeof(cc_pre) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->symlen, sizeof(uint16_t) * nmb);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->park, (size_t)384 * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[0], (size_t)k->mb_h * k->sy);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[1], (size_t)k->mb_h * k->sc);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[2], (size_t)k->mb_h * k->sc);
@@ -270,7 +271,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
         if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->bs_ctl, sizeof(uint32_t) * 2 * n_slices_open);
         if (rc == CC_OK) { cudaMemset(k->bs, 0, e->bs_bytes); cudaMemset(k->bs_ctl, 0, sizeof(uint32_t) * 2 * n_slices_open); }
     }
-    if (rc == CC_OK && getenv("CC_DEBUG_CYCLES")) { rc = dev_alloc(e, (void **)&k->cyc, (size_t)k->mb_h * 16 * 8); if (rc == CC_OK) cudaMemset(k->cyc, 0, (size_t)k->mb_h * 16 * 8); }
+    if (rc == CC_OK && getenv("CC_DEBUG_CYCLES")) { rc = dev_alloc(e, (void **)&k->cyc, (size_t)k->mb_h * CC_CYC_N * 8); if (rc == CC_OK) cudaMemset(k->cyc, 0, (size_t)k->mb_h * CC_CYC_N * 8); }
     if (rc == CC_OK) { cudaMemset(k->me, 0, sizeof(cc_me) * nmb); cudaMemset(k->me8, 0, sizeof(cc_me8) * nmb); cudaMemset(k->mbd, 0, sizeof(cc_mbdev) * nmb); }
     /* packed symbol buffer: headers + per-MB records + payload (worst case) */
     e->out_cap = (uint32_t)(roundup(sizeof(cc_rowhdr) * k->mb_h, 16) + roundup(sizeof(cc_mbhost) * nmb, 16) + (size_t)nmb * CC_ROW_PAYLOAD_PER_MB + 16 * k->mb_h);
@@ -315,15 +316,17 @@ void cc_enc_close(cc_enc *e) {
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st2) cudaStreamSynchronize(e->st2);
     if (e->k.cyc && e->frame_idx > 0) { /* CC_DEBUG_CYCLES=1: where the wavefront kernel's warps spent their cycles */
-        size_t n = (size_t)e->k.mb_h * 16;
-        unsigned long long *h = (unsigned long long *)calloc(n, 8), s[16] = {0};
+        size_t n = (size_t)e->k.mb_h * CC_CYC_N;
+        unsigned long long *h = (unsigned long long *)calloc(n, 8), s[CC_CYC_N] = {0};
         if (h && cudaMemcpy(h, e->k.cyc, n * 8, cudaMemcpyDeviceToHost) == cudaSuccess) {
-            for (size_t i = 0; i < n; i++) s[i & 15] += h[i];
+            for (size_t i = 0; i < n; i++) s[i % CC_CYC_N] += h[i];
             double f = 1.0 / ((double)e->frame_idx * e->k.mb_h);
             fprintf(stderr, "ceracuda cycles per MB row per frame: encode wait %.0f fast %.0f (n %.1f) probe %.0f (n %.1f) intra %.0f (n %.1f) | filter wait-enc %.0f wait-up %.0f work %.0f\n",
                     s[0] * f, s[1] * f, s[4] * f, s[2] * f, s[5] * f, s[3] * f, s[6] * f, s[8] * f, s[9] * f, s[10] * f);
             fprintf(stderr, "ceracuda intra path, cycles per MB row per frame: neighbours+i16 analysis %.0f, i4 analysis %.0f (n %.1f), encode+chroma+publish %.0f, emit %.0f\n",
                     s[11] * f, s[12] * f, s[13] * f, s[14] * f, s[15] * f);
+            fprintf(stderr, "ceracuda wavefront detail, per MB row per frame: between macroblocks (record / pixel prefetch) %.0f cycles; P_Skip reconstructed in the wavefront: %.1f MBs, %.0f cycles (%.1f of them predicted here); parked P_L0_16x16 pixels restored %.1f; Intra4x4 analyses started %.1f\n",
+                    s[16] * f, s[18] * f, s[17] * f, s[19] * f, s[21] * f, s[20] * f);
         }
         free(h);
     }

@@ -63,7 +63,8 @@ typedef struct {
  * P_Skip vectors.  The wavefront kernel only decides; it recomputes nothing for macroblocks that stay inter. */
 typedef struct CC_ALIGN16 {
     uint8_t cbp;        /* luma 8x8 bits | chroma << 4, coded at me.mv */
-    uint8_t skip_ok;    /* bit 0: nothing survives at cand[] ; bit 1: nothing survives at (0,0) */
+    uint8_t skip_ok;    /* bit 0: nothing survives at cand[] ; bit 1: nothing survives at (0,0) ; bit 2: k.rec holds the prediction at cand[]
+                         * and the P_L0_16x16 reconstruction is parked in k.park (the pre-pass expects P_Skip at cand) */
     uint16_t nz_luma;
     int16_t cand[2];    /* P_Skip vector predicted from the neighbours' search vectors */
     uint16_t sym_len;   /* int16 units used in the MB's symbol slot */
@@ -80,6 +81,7 @@ typedef struct {
     uint32_t pad;
 } cc_rowhdr;
 
+#define CC_CYC_N 32
 #define CC_ROW_PAYLOAD_PER_MB 1024 /* worst case: 8 (i4 modes) + 27 blocks * (2 + 32) = 926 bytes */
 /* worst-case CAVLC bits of one macroblock: 16 (coeff_token) + 28 per level (escape code) + 9 (total_zeros) per block, 27 blocks
  * with 400 levels, plus ~300 header bits = ~11.7 kbit; 1536 bytes per macroblock of slice bit buffer can never overflow */
@@ -107,6 +109,7 @@ typedef struct {
     uint32_t *nbrec;   /* per MB 5 words {type | t8 << 8 | nz_luma << 16, mv of quadrants 0..3}: what k_deblock needs from k_mb_encode */
     cc_mbhost *mbh;    /* device copy */
     cc_pre *pre;
+    uint8_t *park;     /* per MB 384 bytes (16x16 luma, 8x8 Cb, 8x8 Cr as in WarpMem.recY / recC): see cc_pre.skip_ok bit 2 */
     uint16_t *symlen;  /* per MB: int16 units used in its symbol slot (even; 0 for P_Skip) */
     uint8_t *ubot[3];  /* unfiltered bottom sample line of every MB row: [mb_h][sy] luma, [mb_h][sc] per chroma plane */
     uint8_t *uright;   /* unfiltered right column of every MB: 32 bytes {16 luma, 8 Cb, 8 Cr} */
@@ -127,7 +130,7 @@ typedef struct {
     uint32_t *bs;          /* per slice a zero-initialised bit buffer of bs_slice_words words (MSB-first words) */
     uint32_t bs_slice_words;
     uint32_t *bs_ctl;      /* [0, ns): row CTAs of the slice that finished; [ns, 2 ns): the slice's RBSP bytes */
-    unsigned long long *cyc; /* debug (CC_DEBUG_CYCLES=1): per MB row 8 cycle counters of the wavefront kernel, or NULL */
+    unsigned long long *cyc; /* debug (CC_DEBUG_CYCLES=1): per MB row CC_CYC_N cycle / event counters of the wavefront kernels, or NULL */
 } cc_kparams;
 
 /* kernel launch wrappers (cc_kernels.cu); each returns the number of kernels launched */

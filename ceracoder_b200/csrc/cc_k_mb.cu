@@ -43,6 +43,7 @@ struct __align__(16) WarpMem {
     uint8_t m4code[16];    /* syntax nibble per block: 8 = predicted mode, else rem_intra4x4_pred_mode */
     uint8_t n4[16];
     uint4 pf[4][4];        /* ring of prefetched per-macroblock records (cc_me, cc_pre, cc_me8 = 16 + 16 + 32 bytes), filled by cp.async */
+    uint4 pc[4][24];       /* ring of prefetched source pixels (k_mb_encode): 16 luma rows x 16 bytes, then 8 rows x 8 bytes of Cb and of Cr */
 };
 
 /* intra 4x4 predictors as 3-tap filters over the edge array E (H.264 8.3.1.2):
@@ -720,20 +721,22 @@ __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, 
 }
 
 /* Two P_Skip tests in one pass (the pre-pass probes its two likeliest skip vectors): prediction A in predY / predC, prediction B
- * in recY / recC (free at that point); lanes 0-15 run the luma blocks of A and lanes 16-31 those of B, lanes 0-7 / 8-15 the chroma
+ * in the Intra4x4 level scratch c4 (unused by the pre-pass; recY / recC keep the macroblock's reconstruction); lanes 0-15 run the luma blocks of A and lanes 16-31 those of B, lanes 0-7 / 8-15 the chroma
  * blocks.  Same arithmetic as inter_luma / encode_chroma in probe mode.  Returns bit 0: nothing survives at A, bit 1: at B. */
 __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, int ax, int ay, int bx2, int by2) {
     WarpMem *m = c.m;
     const int lane = c.lane;
     mc_luma16(k, c, ax, ay);
     mc_chroma8(k, c, ax, ay);
-    mc_luma16(k, c, bx2, by2, m->recY);
-    mc_chroma8(k, c, bx2, by2, m->recC);
+    uint32_t *const bY = (uint32_t *)m->c4;
+    uint32_t (*const bC)[16] = (uint32_t (*)[16])(bY + 64);
+    mc_luma16(k, c, bx2, by2, bY);
+    mc_chroma8(k, c, bx2, by2, bC);
     __syncwarp();
     unsigned nzl;
     { /* luma */
         const int b = lane & 15, bx = c_blk_x[b], by = c_blk_y[b];
-        const uint32_t *pred = lane < 16 ? m->predY : m->recY;
+        const uint32_t *pred = lane < 16 ? m->predY : bY;
         uint32_t cw[4], pw[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) { cw[r] = m->curY[(by * 4 + r) * 4 + bx]; pw[r] = pred[(by * 4 + r) * 4 + bx]; }
@@ -753,7 +756,7 @@ __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, 
     unsigned nzc;
     { /* chroma: lanes 0-15 = (probe, plane, block) */
         const int sel = (lane >> 3) & 1, pl = (lane >> 2) & 1, b = lane & 3, bx = b & 1, by = b >> 1;
-        const uint32_t *pred = sel ? m->recC[pl] : m->predC[pl];
+        const uint32_t *pred = sel ? bC[pl] : m->predC[pl];
         const uint16_t *mf = k.qmf[3], *bias = k.qbias[3];
         uint32_t cw[4], pw[4];
 #pragma unroll
@@ -844,32 +847,37 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
     NbRec *nbl = nbline + w * mw;
     const NbRec *nbu = nbl - mw;
     /* Software pipeline: everything a macroblock needs from global memory that does not depend on its neighbours is requested
-     * ahead of its turn, so the latency (HBM when 8 streams share the L2) overlaps earlier macroblocks' work instead of heading
-     * the serial chain: the search / pre-pass records three macroblocks ahead by cp.async into a shared-memory ring (no register
-     * waits on them until they are read), the source pixels one macroblock ahead in registers. */
-    uint32_t ncur[3] = {0, 0, 0};
-    auto fetch = [&](int x) {
-        const uint8_t *cy = k.cur[0] + (size_t)c.py * k.sy + x * 16;
-        ncur[0] = *(const uint32_t *)(cy + (size_t)(lane >> 2) * k.sy + 4 * (lane & 3));
-        ncur[1] = *(const uint32_t *)(cy + (size_t)(8 + (lane >> 2)) * k.sy + 4 * (lane & 3));
-        ncur[2] = *(const uint32_t *)(k.cur[1 + (lane >> 4)] + (size_t)(row * 8 + ((lane >> 1) & 7)) * k.sc + x * 8 + 4 * (lane & 1));
-    };
-    auto fetch_rec = [&](int x) { /* one commit group per call, also when there is nothing left to request */
-        if (x < mw && lane < (k.part8 ? 4 : 2)) {
-            const int mb = row * mw + x;
-            const void *src = lane == 0 ? (const void *)(k.me + mb) : (lane == 1 ? (const void *)(k.pre + mb) : (const void *)((const uint4 *)(k.me8 + mb) + (lane - 2)));
+     * three macroblocks ahead of its turn by cp.async into shared-memory rings (no register waits on it until it is read), so the
+     * latency (HBM when 8 streams share the L2) overlaps earlier macroblocks' work instead of heading the serial chain: the
+     * search / pre-pass records and the source pixels (fresh from the ingest kernel, read once: an HBM miss each). */
+    auto prefetch = [&](int x) { /* one commit group per call, also when there is nothing left to request */
+        if (x < mw) {
+            uint32_t *slot = (uint32_t *)m->pc[x & 3];
+            const void *src; uint32_t *dst;
+            if (lane < 16) { src = k.cur[0] + (size_t)(c.py + lane) * k.sy + x * 16; dst = slot + 4 * lane; }
+            else { const int pl = (lane - 16) >> 3, r = (lane - 16) & 7; src = k.cur[1 + pl] + (size_t)(row * 8 + r) * k.sc + x * 8; dst = slot + 64 + 16 * pl + 2 * r; }
 #ifndef CC_EMU_BUILD
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&m->pf[x & 3][lane])), "l"(src) : "memory");
+            if (lane < 16) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+            else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
 #else
-            m->pf[x & 3][lane] = *(const uint4 *)src;
+            if (lane < 16) *(uint4 *)dst = *(const uint4 *)src; else *(uint2 *)dst = *(const uint2 *)src;
 #endif
+            if (!k.is_idr && lane < (k.part8 ? 4 : 2)) {
+                const int mb = row * mw + x;
+                const void *rs = lane == 0 ? (const void *)(k.me + mb) : (lane == 1 ? (const void *)(k.pre + mb) : (const void *)((const uint4 *)(k.me8 + mb) + (lane - 2)));
+#ifndef CC_EMU_BUILD
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(&m->pf[x & 3][lane])), "l"(rs) : "memory");
+#else
+                m->pf[x & 3][lane] = *(const uint4 *)rs;
+#endif
+            }
         }
 #ifndef CC_EMU_BUILD
         asm volatile("cp.async.commit_group;" ::: "memory");
 #endif
     };
-    fetch(0);
-    if (!k.is_idr) { fetch_rec(0); fetch_rec(1); fetch_rec(2); }
+    prefetch(0); prefetch(1); prefetch(2);
+    long long tprev = k.cyc ? clock64() : 0;
     for (int mbx = 0; mbx < mw; mbx++) {
         c.mbx = mbx; c.px = mbx * 16; c.mb = row * mw + mbx; c.L = mbx > 0; c.TR = c.T && mbx + 1 < mw;
         int16_t *out = (int16_t *)(k.rowbuf + (size_t)c.mb * CC_ROW_PAYLOAD_PER_MB);
@@ -877,20 +885,22 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
         cc_me me = {{0, 0}, {0, 0}, 0, 0};
         cc_pre pre = {0, 0, 0, {0, 0}, 0, 0, 0, 0};
         cc_me8 me8 = {{{0, 0}, {0, 0}, {0, 0}, {0, 0}}, {0, 0, 0, 0}}; /* zeros unless me.part (k_me_l0 clears the record of an unsplit macroblock) */
-        if (!k.is_idr) {
-            fetch_rec(mbx + 3);
+        prefetch(mbx + 3);
 #ifndef CC_EMU_BUILD
-            asm volatile("cp.async.wait_group 3;" ::: "memory"); /* all but the three newest groups: this macroblock's records are in */
+        asm volatile("cp.async.wait_group 3;" ::: "memory"); /* all but the three newest groups: this macroblock's records and pixels are in */
 #endif
-            __syncwarp();
+        __syncwarp();
+        if (!k.is_idr) {
             const uint4 *pf = m->pf[mbx & 3];
             *(uint4 *)&me = pf[0];
             *(uint4 *)&pre = pf[1];
             if (k.part8) { ((uint4 *)&me8)[0] = pf[2]; ((uint4 *)&me8)[1] = pf[3]; }
         }
         const int part = me.part;
-        m->curY[lane] = ncur[0]; m->curY[lane + 32] = ncur[1]; m->curC[lane >> 4][lane & 15] = ncur[2]; /* = stage_cur */
-        if (mbx + 1 < mw) fetch(mbx + 1);
+        { /* = stage_cur, from the ring */
+            const uint32_t *slot = (const uint32_t *)m->pc[mbx & 3];
+            m->curY[lane] = slot[lane]; m->curY[lane + 32] = slot[lane + 32]; m->curC[lane >> 4][lane & 15] = slot[64 + lane];
+        }
         const long long t0 = k.cyc ? clock64() : 0;
         if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
         const long long t1 = k.cyc ? clock64() : 0;
@@ -914,7 +924,13 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             else { n_probe++; path = 1; zero = probe_zero(k, c, skipmv[0], skipmv[1]); pred_ready = true; /* predY / predC hold the prediction at skipmv */ }
             if (zero) {
                 type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
-                if (part || mvx != me.mv[0] || mvy != me.mv[1]) { /* reconstruction = prediction at the skip vector */
+                /* The reconstruction is the prediction at the skip vector.  k.rec already holds it when the pre-pass published the
+                 * prediction at its candidate and that is the vector (pre.skip_ok bit 2), or when the vector is the search vector
+                 * of an unsplit macroblock that coded to nothing there. */
+                const bool spec = (pre.skip_ok & 4) != 0;
+                const bool in_place = spec ? (mvx == pre.cand[0] && mvy == pre.cand[1]) : (!part && mvx == me.mv[0] && mvy == me.mv[1]);
+                if (!in_place) {
+                    const long long ts = k.cyc ? clock64() : 0;
                     if (!pred_ready) {
                         mc_luma16(k, c, mvx, mvy);
                         mc_chroma8(k, c, mvx, mvy);
@@ -924,6 +940,10 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                     m->recC[lane >> 4][lane & 15] = m->predC[lane >> 4][lane & 15];
                     __syncwarp();
                     publish_pixels(k, c);
+                    if (k.cyc && lane == 0) {
+                        unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
+                        cy[17] += (unsigned long long)(clock64() - ts); cy[18] += 1; cy[19] += pred_ready ? 0 : 1;
+                    }
                 }
                 done = true;
             } else if (part) { /* exact cost of the P_8x8 coding: per-quadrant SATD + mvd bits against the real predictors */
@@ -949,9 +969,10 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 cost_i16 = analyse_i16(c, ip, &mode16);
                 const long long tb = k.cyc ? clock64() : 0;
                 /* Intra4x4 wins only if cost_i4 < cost_i16 and (P frames) cost_i4 + 8 lambda < cost_inter */
+                if (k.cyc && lane == 0 && (k.is_idr || cost_i16 * 4 <= cost_inter * 5)) k.cyc[(size_t)row * CC_CYC_N + 20] += 1;
                 if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda));
                 if (k.cyc && lane == 0) {
-                    unsigned long long *cy = k.cyc + (size_t)row * 16;
+                    unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                     cy[11] += (unsigned long long)(tb - ta); cy[12] += (unsigned long long)(clock64() - tb); cy[13] += cost_i4 < (1 << 30);
                 }
                 if (!k.is_idr) { cost_i16 += 8 * c.lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * c.lambda; }
@@ -959,7 +980,14 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             if (!k.is_idr && cost_inter <= cost_i16 && cost_inter <= cost_i4) type = CC_MB_P16;
             else type = cost_i16 <= cost_i4 ? CC_MB_I16 : CC_MB_I4;
 
-            if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec */
+            if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec — or parked beside it */
+                if (pre.skip_ok & 4) {
+                    const uint32_t *park = (const uint32_t *)(k.park + (size_t)c.mb * 384);
+                    m->recY[lane] = park[lane]; m->recY[lane + 32] = park[lane + 32]; m->recC[lane >> 4][lane & 15] = park[64 + lane];
+                    __syncwarp();
+                    publish_pixels(k, c);
+                    if (k.cyc && lane == 0) k.cyc[(size_t)row * CC_CYC_N + 21] += 1;
+                }
                 if (part) { /* the four mvd go to the 8 int16 the pre-pass left free at the head of the slot */
                     mvx = me8.mv[0][0]; mvy = me8.mv[0][1]; mvdx = mvx - mvp8[0][0]; mvdy = mvy - mvp8[0][1];
                     if (lane < 8) {
@@ -1004,7 +1032,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 const long long td = k.cyc ? clock64() : 0;
                 off = emit_mb(c, out, off, type, cbp);
                 if (k.cyc && lane == 0) {
-                    unsigned long long *cy = k.cyc + (size_t)row * 16;
+                    unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                     cy[14] += (unsigned long long)(td - tc); cy[15] += (unsigned long long)(clock64() - td);
                 }
             }
@@ -1040,8 +1068,9 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
         if (lane == 0) progress[w] = mbx + 1;
         if (k.cyc && lane == 0) {
             const long long t2 = clock64();
-            unsigned long long *cy = k.cyc + (size_t)row * 16;
+            unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
             cy[0] += (unsigned long long)(t1 - t0); cy[1 + path] += (unsigned long long)(t2 - t1); cy[4 + path] += 1;
+            cy[16] += (unsigned long long)(t0 - tprev); tprev = t2;
         }
     }
     if (lane == 0) {
@@ -1092,7 +1121,6 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     if (!cbp) t8 = 0; /* the flag is only transmitted with coded luma */
     cbp |= encode_chroma(k, c, false, false) << 4;
     __syncwarp();
-    publish_pixels(k, c);
     int16_t *out = (int16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
     const unsigned off = emit_mb(c, out, part ? 8 : 0, CC_MB_P16, cbp); /* P_8x8: 8 int16 left free for the four mvd */
     /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
@@ -1118,11 +1146,26 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
     int ok = 0;
     /* a P_8x8 search result says nothing about the 16x16 coding at one vector: both probes run for real */
     const bool c_is_me = !part && cand[0] == mvx && cand[1] == mvy, z_is_me = !part && mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
-    if (!c_is_me && !z_is_me && !z_is_c) ok = probe_zero2(k, c, cand[0], cand[1], 0, 0); /* publish_pixels is done: recY / recC are free */
+    if (!c_is_me && !z_is_me && !z_is_c) ok = probe_zero2(k, c, cand[0], cand[1], 0, 0);
     else {
         if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
         if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
     }
+    /* Most macroblocks of a moving picture end up P_Skip at the predicted skip vector, which is rarely the search vector to the
+     * quarter pel: their reconstruction is the prediction at that vector.  When the probe at `cand` leaves nothing (and cand is not
+     * the search vector anyway), the pre-pass therefore publishes THAT prediction — it sits in predY / predC (in every branch
+     * above that sets bit 0 for such a macroblock, the last prediction made is the one at cand) — and parks the P_L0_16x16
+     * reconstruction in a side buffer.  The wavefront then has nothing to move for the common outcome (P_Skip at cand) and
+     * restores the parked pixels in the rare other ones. */
+    if ((ok & 1) && !c_is_me) {
+        ok |= 4;
+        uint32_t *park = (uint32_t *)(k.park + (size_t)mb * 384);
+        park[lane] = m->recY[lane]; park[lane + 32] = m->recY[lane + 32]; park[64 + lane] = m->recC[lane >> 4][lane & 15];
+        m->recY[lane] = m->predY[lane]; m->recY[lane + 32] = m->predY[lane + 32];
+        m->recC[lane >> 4][lane & 15] = m->predC[lane >> 4][lane & 15];
+        __syncwarp();
+    }
+    publish_pixels(k, c);
     if (lane == 0) {
         cc_pre p;
         p.cbp = (uint8_t)cbp; p.skip_ok = (uint8_t)ok; p.nz_luma = (uint16_t)nzmask; p.cand[0] = (int16_t)cand[0]; p.cand[1] = (int16_t)cand[1];
@@ -1186,7 +1229,7 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
         __threadfence_block();
         if (lane == 0) prog[w] = mbx + 1;
         if (k.cyc && lane == 0 && !pl) {
-            unsigned long long *cy = k.cyc + (size_t)row * 16 + 8;
+            unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N + 8;
             cy[1] += (unsigned long long)(t2 - t1); cy[2] += (unsigned long long)(clock64() - t2);
         }
     }

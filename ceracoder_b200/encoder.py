@@ -112,7 +112,7 @@ class CudaH264Enc:
     """The `cudah264enc` element as a Python object: same properties as the pipeline line that names x264enc."""
 
     def __init__(self, width, height, fps=(30, 1), bitrate=6000, key_int_max=60, speed_preset=3, tune=0, name="venc_kbps",
-                 fmt="I420", device=0, rows_per_slice=4, qp_fixed=0, lib=None, byte_stream=True, threads=0, partitions=True, host_entropy=False):
+                 fmt="I420", device=0, rows_per_slice=8, qp_fixed=0, lib=None, byte_stream=True, threads=0, partitions=True, host_entropy=False):
         if isinstance(speed_preset, str):
             if speed_preset not in _SPEED_PRESETS:
                 raise ValueError(f"unknown speed-preset {speed_preset!r}")
