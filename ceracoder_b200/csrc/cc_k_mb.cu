@@ -1298,10 +1298,12 @@ extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
         if (pad_kb > 0 && dyn < (size_t)pad_kb * 1024) dyn = (size_t)pad_kb * 1024;
         if (dyn > 190 * 1024) dyn = 190 * 1024;
     }
-    /* static (31.5 KB) + dynamic shared memory passes the default 48 KB limit from ~3300-pixel-wide pictures on: opt in */
-    if (dyn > 16 * 1024) { /* per device; cheap */
-        if (k->rps <= 4) cudaFuncSetAttribute(k_mb_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
-        else cudaFuncSetAttribute(k_mb_encode<MB_MAX_RPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
+    /* static + dynamic shared memory passes the default 48 KB limit for wide pictures / tall slices: opt in to what this launch needs
+     * (per device; cheap).  The request counts against 227 KB together with the kernel's static shared memory. */
+    if (dyn > 8 * 1024) {
+        cudaError_t er = k->rps <= 4 ? cudaFuncSetAttribute(k_mb_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)
+                                     : cudaFuncSetAttribute(k_mb_encode<MB_MAX_RPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+        (void)er; /* a failure shows as a launch error below */
     }
 #endif
     if (k->rps <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
@@ -1312,7 +1314,7 @@ extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
     const int ns = (k->mb_h + k->rps - 1) / k->rps;
     const size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
 #ifndef CC_EMU_BUILD
-    if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024);
+    if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
 #endif
     CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
     return 1;

@@ -91,6 +91,7 @@ static int analyse_i4(struct ref_enc *e, int mbx, int mby, int16_t coef[16][16],
             if (c < best) { best = c; bm = m; memcpy(bpred, pred, 16); }
         }
         cost += best;
+        MBI(e, mbx, mby)->dbg_i4_blk[blk] = (uint16_t)(best > 65535 ? 65535 : best);
         modes[blk] = (uint8_t)bm;
         nnz[blk] = (uint8_t)fwd4x4(cur, sy, bpred, 4, mf, bias, coef[blk], 0, 0);
         if (nnz[blk]) rec4x4(rec, sy, bpred, 4, coef[blk], qp, 0, 0);
@@ -424,6 +425,7 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         if (!e->is_idr) { cost_i16 += 8 * lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * lambda; } /* intra mb_type/chroma-mode overhead in P slices */
     }
 
+    mi->dbg_cost_inter = cost_inter; mi->dbg_cost_i16 = cost_i16; mi->dbg_cost_i4 = cost_i4;
     int type;
     if (!e->is_idr && cost_inter <= cost_i16 && cost_inter <= cost_i4) type = REF_MB_P16;
     else type = cost_i16 <= cost_i4 ? REF_MB_I16 : REF_MB_I4;
