@@ -335,7 +335,10 @@ __device__ __forceinline__ int encode_i16(const cc_kparams &k, const MbCtx &c, c
 /* thresh: Intra4x4 can only be chosen with a cost below it, and the running cost never decreases, so the analysis stops as
  * soon as it is reached ([EXT] x264_mb_analyse_intra's i_satd_thresh early termination).  The decision is the same as
  * without the early exit; only the work differs.  Returns 1 << 30 when abandoned. */
-__device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, int thresh) {
+/* proj (P frames): also give up when, from the step that completes the fourth block on, the cost so far projected to sixteen
+ * blocks exceeds thresh by a quarter (oracle/ref_mb.c analyse_i4 states the rule and what it costs: it halves the steps taken in
+ * P frames, where one analysis in a hundred ends in an Intra4x4 macroblock).  Unlike the exact test this one is a decision rule. */
+__device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, int thresh, bool proj) {
     WarpMem *m = c.m;
     const int lane = c.lane, half = lane >> 4, l = lane & 15;
     /* neighbour macroblocks' modes (global memory): one round trip for the whole macroblock, before the block loop */
@@ -441,6 +444,10 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
             cost += mine + __shfl_xor_sync(FULL, mine, 16);
         }
         if (cost >= thresh) return 1 << 30; /* uniform across the warp */
+        if (proj && t >= 2 && t < 9) {
+            const int nd = t < 8 ? 2 * t : 15; /* blocks done after step t: 1, 2, 4, 6, 8, 10, 12, 14, 15, 16 */
+            if ((long long)(cost - 24 * c.lambda) * 64 > (long long)(thresh - 24 * c.lambda) * nd * 5) return 1 << 30;
+        }
 #pragma unroll
         for (int r = 0; r < 4; r++) pw[r] = __shfl_sync(FULL, pw[r], bm, 16);
         /* forward transform of this lane's coefficient (horizontal pass as byte dot products, then its column of Cf^T),
@@ -970,7 +977,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 const long long tb = k.cyc ? clock64() : 0;
                 /* Intra4x4 wins only if cost_i4 < cost_i16 and (P frames) cost_i4 + 8 lambda < cost_inter */
                 if (k.cyc && lane == 0 && (k.is_idr || cost_i16 * 4 <= cost_inter * 5)) k.cyc[(size_t)row * CC_CYC_N + 20] += 1;
-                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda));
+                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda), !k.is_idr);
                 if (k.cyc && lane == 0) {
                     unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                     cy[11] += (unsigned long long)(tb - ta); cy[12] += (unsigned long long)(clock64() - tb); cy[13] += cost_i4 < (1 << 30);
