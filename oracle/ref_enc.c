@@ -50,6 +50,7 @@ void ref_enc_close(ref_enc *e) {
     free(e);
 }
 void ref_enc_set_partitions(ref_enc *e, int on) { e->part8 = on != 0; }
+void ref_enc_set_effort(ref_enc *e, int on) { e->effort = on != 0; }
 #ifdef _OPENMP
 #include <omp.h>
 void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); } /* launchers such as torchrun export OMP_NUM_THREADS=1 */
@@ -131,6 +132,16 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
     }
     unsigned best = ~0u;
     int bmx = 0, bmy = 0;
+    if (e->effort) { /* upper-bound mode: every full-pel vector within +-24 of the coarse result (and the predictor / zero as below) */
+        for (int dy = -24; dy <= 24; dy++)
+            for (int dx = -24; dx <= 24; dx++) {
+                int mx = 2 * mi->l1_mv[0] + dx, my = 2 * mi->l1_mv[1] + dy;
+                if (mx < -40 || mx > 40 || my < -40 || my > 40) continue; /* stay inside the padded reference */
+                unsigned c = (unsigned)ref_sad(cur, sy, ref + my * sy + mx, sy, 16, 16) +
+                             (unsigned)(lambda * (ref_mv_bits(4 * (mx - pm[0])) + ref_mv_bits(4 * (my - pm[1]))));
+                if (c < (best >> 5)) { best = c << 5; bmx = mx; bmy = my; }
+            }
+    }
     for (int i = 0; i < 27; i++) {
         int mx, my;
         if (i == 0) { mx = pm[0]; my = pm[1]; }
@@ -183,7 +194,7 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
      * partition overhead already beat the full-pel 16x16 cost, the sub-pel refinement of the quadrants is not run and the
      * macroblock stays one partition */
     memset(mi->me_mv8, 0, sizeof mi->me_mv8); memset(mi->me_satd8, 0, sizeof mi->me_satd8);
-    if (full8 >= (best >> 5)) return;
+    if (full8 >= (best >> 5) && !e->effort) return;
     for (int p = 0; p < 4; p++) {
         const uint8_t *c8 = cur + (p >> 1) * 8 * sy + (p & 1) * 8, *r8 = ref + (p >> 1) * 8 * sy + (p & 1) * 8;
         const int fx = f8[p][0], fy = f8[p][1];
@@ -304,7 +315,7 @@ int ref_enc_encode(ref_enc *e, const uint8_t *y, int sy_, const uint8_t *u, int 
     for (int s = 0; s < ns; s++) {
         int r0 = s * e->rps, r1 = r0 + e->rps < mh ? r0 + e->rps : mh;
         for (int my = r0; my < r1; my++)
-            for (int mx = 0; mx < mw; mx++) ref_mb_encode(e, mx, my);
+            for (int mx = 0; mx < mw; mx++) { if (e->effort) ref_mb_encode_rd(e, mx, my); else ref_mb_encode(e, mx, my); }
         /* bitstream before deblocking (needs nothing from rec) */
         uint8_t *sb = e->slice_buf + (size_t)s * e->slice_cap;
         int bp = 0, skip_run = 0;

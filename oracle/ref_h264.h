@@ -98,6 +98,10 @@ ref_enc *ref_enc_open(int width, int height, int fps_n, int fps_d, int rows_per_
 void ref_enc_close(ref_enc *e);
 /* enable (1) / disable (0) P_8x8 partitions; ref_enc_open leaves them on.  Mirrors cc_enc_params.partitions of the product. */
 void ref_enc_set_partitions(ref_enc *e, int on);
+/* 1: upper-bound mode — NOT the parity oracle: exhaustive +-24 full-pel search, 8x8 partitions always refined, and per macroblock the
+ * candidate (P_Skip, P_L0_16x16 with either transform size, P_8x8, Intra16x16, Intra4x4) with the smallest SSD + lambda * real CAVLC
+ * bits.  tools/rd_oracle.py measures the product's RD curve against it. */
+void ref_enc_set_effort(ref_enc *e, int on);
 /* OpenMP threads the slice / macroblock loops use (0 = leave as is) */
 void ref_set_threads(int n);
 /* encode one frame (I420, arbitrary strides). is_idr: 1 = IDR, 0 = P. qp 10..51.

@@ -21,10 +21,12 @@ struct ref_enc {
     int slice_cap;
     int *slice_bits;
     int part8;                  /* 1: the motion search may choose P_8x8 (four 8x8 partitions) */
+    int effort;                 /* 0: the parity oracle.  1: upper-bound mode (ref_enc_set_effort): exhaustive full-pel search, RD mode decision */
 };
 
 /* ref_mb.c */
 void ref_mb_encode(struct ref_enc *e, int mbx, int mby);
+void ref_mb_encode_rd(struct ref_enc *e, int mbx, int mby);
 void ref_mb_deblock(struct ref_enc *e, int mbx, int mby);
 void ref_mb_write(struct ref_enc *e, int mbx, int mby, uint8_t *out, int *bitpos, int *skip_run);
 

@@ -11,6 +11,7 @@
 #include "ref_int.h"
 #include "ref_tables.h"
 #include <string.h>
+#include <math.h>
 
 static const uint8_t blk_of[4][4] = {{0, 1, 4, 5}, {2, 3, 6, 7}, {8, 9, 12, 13}, {10, 11, 14, 15}};
 static const uint8_t mode_bits4[4] = {1, 3, 3, 5}; /* ue() length of 0..3 */
@@ -340,7 +341,7 @@ static void set_mv_all(ref_mb_info *mi, int mx, int my) {
 /* ---- macroblock analysis + encode ---------------------------------------------- */
 /* the MB as P_L0_16x16 at its search vector: luma with the transform size chosen by
  * [EXT] x264_mb_analyse_transform (sa8d of the residual < satd of the residual -> 8x8), then chroma */
-static void code_inter_at_me(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, int16_t *coef) {
+static void code_inter_at_me(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, int16_t *coef, int force_t8) {
     const int sy = e->sy, sc = e->sc;
     uint8_t predY[256], predC[2][64];
     const uint8_t *cur = e->cur[0] + mby * 16 * sy + mbx * 16;
@@ -370,17 +371,35 @@ static void code_inter_at_me(struct ref_enc *e, int mbx, int mby, ref_mb_info *m
     int s8 = 0;
     for (int i8 = 0; i8 < 4; i8++) s8 += ref_sa8d_8x8_raw(cur + (i8 >> 1) * 8 * sy + (i8 & 1) * 8, sy, predY + (i8 >> 1) * 128 + (i8 & 1) * 8, 16);
     mi->t8 = (uint8_t)(((s8 + 2) >> 2) < satd4);
+    if (force_t8 >= 0) mi->t8 = (uint8_t)force_t8; /* upper-bound mode only (ref_mb_encode_rd) */
     if (mi->t8) encode_inter_luma8(e, mbx, mby, predY, mi, coef);
     else encode_inter_luma(e, mbx, mby, predY, mi, coef);
     if (!(mi->cbp & 15)) mi->t8 = 0; /* the flag is only transmitted with coded luma */
     encode_chroma(e, mbx, mby, predC, 0, mi, coef);
 }
 
+/* chroma of an intra macroblock: mode by SATD over both planes, then the residual */
+static void intra_chroma(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, int16_t *coef) {
+    const int sc = e->sc, lambda = ref_lambda[e->qp], L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
+    uint8_t predC[2][64], p[2][64];
+    int best = 1 << 30, bm = 0;
+    for (int m = 0; m < 4; m++) {
+        int ok = m == 0 || (m == 1 && L) || (m == 2 && T) || (m == 3 && T && L), c = lambda * mode_bits4[m];
+        if (!ok) continue;
+        for (int pl = 0; pl < 2; pl++) {
+            ref_pred8x8c(p[pl], 8, m, e->rec[1 + pl] + mby * 8 * sc + mbx * 8, sc, T, L);
+            c += ref_satd(e->cur[1 + pl] + mby * 8 * sc + mbx * 8, sc, p[pl], 8, 8, 8);
+        }
+        if (c < best) { best = c; bm = m; memcpy(predC, p, sizeof p); }
+    }
+    mi->chroma_mode = (uint8_t)bm;
+    encode_chroma(e, mbx, mby, predC, 1, mi, coef);
+}
+
 void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     const int sy = e->sy, sc = e->sc, lambda = ref_lambda[e->qp];
     ref_mb_info *mi = MBI(e, mbx, mby);
     int16_t *coef = COEF(e, mbx, mby);
-    const int L = av_left(e, mbx, mby), T = av_top(e, mbx, mby);
     uint8_t predY[256], predC[2][64];
     int mvp[2] = {0, 0}, skipmv[2] = {0, 0};
     int cost_inter = 1 << 30, cost_i16, cost_i4 = 1 << 30, mode16 = 2;
@@ -402,7 +421,7 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
          * vector IS the search vector the answer is the real coding at that vector (with its transform-size choice),
          * otherwise a 4x4-transform probe. */
         if (!mi->me_part && skipmv[0] == mi->me_mv[0] && skipmv[1] == mi->me_mv[1]) {
-            code_inter_at_me(e, mbx, mby, mi, coef);
+            code_inter_at_me(e, mbx, mby, mi, coef, -1);
         } else {
             ref_mc_luma(predY, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, skipmv[0], skipmv[1], 16, 16);
             encode_inter_luma(e, mbx, mby, predY, mi, coef);
@@ -460,7 +479,7 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     } else if (type == REF_MB_I16) {
         encode_i16(e, mbx, mby, mode16, mi, coef);
     } else {
-        code_inter_at_me(e, mbx, mby, mi, coef);
+        code_inter_at_me(e, mbx, mby, mi, coef, -1);
         if (mi->part) {
             for (int p = 0; p < 4; p++) {
                 int mp[2];
@@ -475,21 +494,111 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         return;
     }
 
-    if (type >= REF_MB_I16) { /* chroma intra mode by SATD over both planes */
-        int best = 1 << 30, bm = 0;
-        uint8_t p[2][64];
-        for (int m = 0; m < 4; m++) {
-            int ok = m == 0 || (m == 1 && L) || (m == 2 && T) || (m == 3 && T && L), c = lambda * mode_bits4[m];
-            if (!ok) continue;
-            for (int pl = 0; pl < 2; pl++) {
-                ref_pred8x8c(p[pl], 8, m, e->rec[1 + pl] + mby * 8 * sc + mbx * 8, sc, T, L);
-                c += ref_satd(e->cur[1 + pl] + mby * 8 * sc + mbx * 8, sc, p[pl], 8, 8, 8);
-            }
-            if (c < best) { best = c; bm = m; memcpy(predC, p, sizeof p); }
-        }
-        mi->chroma_mode = (uint8_t)bm;
-        encode_chroma(e, mbx, mby, predC, 1, mi, coef);
+    if (type >= REF_MB_I16) intra_chroma(e, mbx, mby, mi, coef);
+}
+
+/* ---- upper-bound mode decision (ref_enc_set_effort) ------------------------------------------------------------------
+ * NOT the parity oracle: a slow encoder over the same toolset (P_Skip, P_L0_16x16 with either transform size, P_8x8,
+ * Intra16x16, Intra4x4, CAVLC) that picks, per macroblock, the candidate with the smallest SSD + lambda * bits, the bits counted
+ * by writing the macroblock for real.  tools/rd_oracle.py runs it (with an exhaustive full-pel search and one slice per picture)
+ * to bound how far the product's fast decisions and its slice structure are from the best this toolset does. */
+typedef struct { ref_mb_info mi; int16_t coef[COEF_PER_MB]; uint8_t y[256], c[2][64]; } mb_snap;
+static void snap_save(struct ref_enc *e, int mbx, int mby, mb_snap *s) {
+    s->mi = *MBI(e, mbx, mby);
+    memcpy(s->coef, COEF(e, mbx, mby), sizeof s->coef);
+    for (int r = 0; r < 16; r++) memcpy(s->y + 16 * r, e->rec[0] + (mby * 16 + r) * e->sy + mbx * 16, 16);
+    for (int p = 0; p < 2; p++) for (int r = 0; r < 8; r++) memcpy(s->c[p] + 8 * r, e->rec[1 + p] + (mby * 8 + r) * e->sc + mbx * 8, 8);
+}
+static void snap_load(struct ref_enc *e, int mbx, int mby, const mb_snap *s) {
+    *MBI(e, mbx, mby) = s->mi;
+    memcpy(COEF(e, mbx, mby), s->coef, sizeof s->coef);
+    for (int r = 0; r < 16; r++) memcpy(e->rec[0] + (mby * 16 + r) * e->sy + mbx * 16, s->y + 16 * r, 16);
+    for (int p = 0; p < 2; p++) for (int r = 0; r < 8; r++) memcpy(e->rec[1 + p] + (mby * 8 + r) * e->sc + mbx * 8, s->c[p] + 8 * r, 8);
+}
+static double rd_cost(struct ref_enc *e, int mbx, int mby, double lambda2) {
+    uint8_t scratch[4096];
+    int bp = 0, sr = 0;
+    long ssd = 0;
+    ref_mb_write(e, mbx, mby, scratch, &bp, &sr);
+    for (int r = 0; r < 16; r++) {
+        const uint8_t *a = e->cur[0] + (mby * 16 + r) * e->sy + mbx * 16, *b = e->rec[0] + (mby * 16 + r) * e->sy + mbx * 16;
+        for (int x = 0; x < 16; x++) ssd += (a[x] - b[x]) * (a[x] - b[x]);
     }
+    for (int p = 0; p < 2; p++)
+        for (int r = 0; r < 8; r++) {
+            const uint8_t *a = e->cur[1 + p] + (mby * 8 + r) * e->sc + mbx * 8, *b = e->rec[1 + p] + (mby * 8 + r) * e->sc + mbx * 8;
+            for (int x = 0; x < 8; x++) ssd += (a[x] - b[x]) * (a[x] - b[x]);
+        }
+    return (double)ssd + lambda2 * bp;
+}
+void ref_mb_encode_rd(struct ref_enc *e, int mbx, int mby) {
+    const int sy = e->sy, sc = e->sc;
+    ref_mb_info *mi = MBI(e, mbx, mby);
+    int16_t *coef = COEF(e, mbx, mby);
+    const double lambda2 = 0.85 * pow(2.0, (e->qp - 12) / 3.0);
+    const ref_mb_info keep = *mi; /* search results */
+    mb_snap best;
+    double bestj = 1e300;
+#define RESET() do { *mi = keep; memset(coef, 0, COEF_PER_MB * sizeof(int16_t)); memset(mi->nnz, 0, sizeof mi->nnz); memset(mi->i4_mode, 2, 16); \
+                     mi->cbp = 0; mi->mvd[0] = mi->mvd[1] = 0; mi->i16_mode = 0; mi->chroma_mode = 0; mi->part = 0; mi->t8 = 0; set_mv_all(mi, 0, 0); memset(mi->mvd4, 0, sizeof mi->mvd4); } while (0)
+#define TRY() do { double j_ = rd_cost(e, mbx, mby, lambda2); if (j_ < bestj) { bestj = j_; snap_save(e, mbx, mby, &best); } } while (0)
+    if (!e->is_idr) {
+        int mvp[2], skipmv[2];
+        predict_mv(e, mbx, mby, mvp, skipmv);
+        { /* P_Skip: the prediction at the skip vector, no residual */
+            uint8_t py[256], pc[2][64];
+            RESET();
+            ref_mc_luma(py, 16, e->ref[0] + mby * 16 * sy + mbx * 16, sy, skipmv[0], skipmv[1], 16, 16);
+            copy_blk(e->rec[0] + mby * 16 * sy + mbx * 16, sy, py, 16, 16, 16);
+            for (int pl = 0; pl < 2; pl++) {
+                ref_mc_chroma(pc[pl], 8, e->ref[1 + pl] + mby * 8 * sc + mbx * 8, sc, skipmv[0], skipmv[1], 8, 8);
+                copy_blk(e->rec[1 + pl] + mby * 8 * sc + mbx * 8, sc, pc[pl], 8, 8, 8);
+            }
+            mi->type = REF_MB_PSKIP; set_mv_all(mi, skipmv[0], skipmv[1]);
+            TRY();
+        }
+        for (int part = 0; part <= (e->part8 && keep.me_cost8 > 0); part++)
+            for (int t8 = 0; t8 <= 1; t8++) {
+                RESET();
+                mi->me_part = (uint8_t)part;
+                mi->type = REF_MB_P16;
+                code_inter_at_me(e, mbx, mby, mi, coef, t8);
+                if (mi->part) {
+                    for (int p = 0; p < 4; p++) {
+                        int mp[2];
+                        predict_mv8(e, mbx, mby, p, mi->mv4, mp);
+                        mi->mvd4[p][0] = (int16_t)(mi->mv4[p][0] - mp[0]); mi->mvd4[p][1] = (int16_t)(mi->mv4[p][1] - mp[1]);
+                    }
+                    mi->mvd[0] = mi->mvd4[0][0]; mi->mvd[1] = mi->mvd4[0][1];
+                } else { mi->mvd[0] = (int16_t)(mi->mv[0] - mvp[0]); mi->mvd[1] = (int16_t)(mi->mv[1] - mvp[1]); }
+                TRY();
+            }
+    }
+    { /* Intra16x16 */
+        int mode16;
+        RESET();
+        analyse_i16(e, mbx, mby, &mode16, e->rec[0]);
+        mi->type = REF_MB_I16;
+        encode_i16(e, mbx, mby, mode16, mi, coef);
+        intra_chroma(e, mbx, mby, mi, coef);
+        TRY();
+    }
+    { /* Intra4x4 */
+        int16_t c4[16][16];
+        uint8_t m4[16], n4[16];
+        int cbp = 0;
+        RESET();
+        analyse_i4(e, mbx, mby, c4, m4, n4, 0);
+        memcpy(coef, c4, sizeof c4); memcpy(mi->i4_mode, m4, 16); memcpy(mi->nnz, n4, 16);
+        for (int b = 0; b < 16; b++) if (n4[b]) cbp |= 1 << (b >> 2);
+        mi->cbp = (uint8_t)cbp; mi->type = REF_MB_I4;
+        intra_chroma(e, mbx, mby, mi, coef);
+        TRY();
+    }
+#undef RESET
+#undef TRY
+    snap_load(e, mbx, mby, &best);
+    MBI(e, mbx, mby)->me_part = keep.me_part;
 }
 
 /* ---- deblocking, H.264 8.7 (disable_deblocking_filter_idc = 2: slice-local) ---- */
