@@ -476,11 +476,13 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     for (int i = 0; i <= CC_N_STAGES + 1; i++) pev_used[i] = 0;
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);
-    /* Upload and ingest only touch the source planes.  Everything from here on reads what the previous frame's tail (in-loop filter,
-     * borders, half-pel planes, half-resolution reference — on st2) produces, or overwrites what it reads (the neighbour records). */
-    CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
+    /* Upload, ingest and the coarse search touch the source planes and the half-resolution reference, which the coding kernels of the
+     * previous frame wrote (unfiltered reconstruction): they run while that frame's tail is still filtering.  Everything after
+     * them reads what the tail (in-loop filter, borders, half-pel planes — on st2) produces, or overwrites what it reads (the
+     * neighbour records). */
     STAGE(CC_STAGE_ME_COARSE);
-    if (!is_idr) e->launches += cck_me_l1(k, e->st);
+    if (!is_idr) { e->launches += cck_l1border(k, e->st); e->launches += cck_me_l1(k, e->st); }
+    CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
     STAGE(CC_STAGE_ME_FINE);
     if (!is_idr) e->launches += cck_me_l0(k, e->st);
     STAGE(CC_STAGE_P_CODE);
@@ -503,8 +505,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->launches += cck_border(k, e->st2);
     STAGE2(CC_STAGE_HPEL);
     e->launches += cck_hpel(k, e->st2);
-    STAGE2(CC_STAGE_L1REF);
-    e->launches += cck_l1ref(k, e->st2);
+    STAGE2(CC_STAGE_L1REF); /* nothing left here: the half-resolution reference is written with the reconstruction */
     STAGE2(CC_N_STAGES);
 #undef STAGE2
     CUCHECK(cudaEventRecord(e->ev_tail, e->st2));

@@ -7,7 +7,7 @@
  *   k_hpel        half-pel planes b (horizontal), h (vertical), j (centre) of the reconstruction with the
  *                 6-tap filter of H.264 8.4.2.2.1; every quarter-pel predictor is then the average of
  *                 two samples of {G,b,h,j}
- *   k_l1ref       half-resolution reconstruction (2x2 box mean) incl. border for the coarse search
+ *   k_l1border    border of the half-resolution reference (the plane itself is written with the reconstruction, cc_k_mb.cu)
  * All are HBM/L2 streaming kernels: one pass, 4-byte or wider accesses, grid >> 148 SMs.
  * Oracle counterparts: oracle/ref_enc.c load_plane / extend_border / downsample2, ref_prims.c hpel_*.
  */
@@ -172,21 +172,20 @@ __global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
     *(uint32_t *)(k.hj + o) = vj;
 }
 
-/* ---- k_l1ref ----------------------------------------------------------------------------------------- */
-/* half-res reconstruction over the picture and a 24-pixel border; one thread = 4 output pixels */
-__global__ void k_l1ref(cc_kparams k) {
+/* ---- k_l1border -------------------------------------------------------------------------------------- */
+/* The half-resolution reference is written macroblock by macroblock where the reconstruction is published (cc_k_mb.cu
+ * publish_pixels); this replicates its edge samples into the 24-pixel border the coarse search windows reach into.
+ * One thread = one border sample. */
+__global__ void k_l1border(cc_kparams k) {
     const int B = 24, W2 = k.W >> 1, H2 = k.H >> 1;
-    int gx = blockIdx.x * blockDim.x + threadIdx.x, y = (int)blockIdx.y - B;
-    int x = -B + 4 * gx;
-    if (x >= W2 + B || y >= H2 + B) return;
-    const uint8_t *r0 = k.rec[0] + (ptrdiff_t)(2 * y) * k.sy + 2 * x, *r1 = r0 + k.sy;
-    uint32_t a0 = *(const uint32_t *)r0, a1 = *(const uint32_t *)(r0 + 4), b0 = *(const uint32_t *)r1, b1 = *(const uint32_t *)(r1 + 4);
-    uint32_t v = 0;
-    v |= (uint32_t)((cc_byte(a0, 0) + cc_byte(a0, 1) + cc_byte(b0, 0) + cc_byte(b0, 1) + 2) >> 2);
-    v |= (uint32_t)((cc_byte(a0, 2) + cc_byte(a0, 3) + cc_byte(b0, 2) + cc_byte(b0, 3) + 2) >> 2) << 8;
-    v |= (uint32_t)((cc_byte(a1, 0) + cc_byte(a1, 1) + cc_byte(b1, 0) + cc_byte(b1, 1) + 2) >> 2) << 16;
-    v |= (uint32_t)((cc_byte(a1, 2) + cc_byte(a1, 3) + cc_byte(b1, 2) + cc_byte(b1, 3) + 2) >> 2) << 24;
-    *(uint32_t *)(k.l1ref + (ptrdiff_t)y * k.sc + x) = v;
+    const int nside = 2 * B * H2, ntb = 2 * B * (W2 + 2 * B);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int x, y;
+    if (i < nside) { y = i / (2 * B); const int j = i - y * 2 * B; x = j < B ? j - B : W2 + j - B; }        /* left / right strips */
+    else if (i < nside + ntb) { const int j = i - nside, w = W2 + 2 * B; const int r = j / w; x = j - r * w - B; y = r < B ? r - B : H2 + r - B; } /* top / bottom */
+    else return;
+    const int sx = x < 0 ? 0 : (x >= W2 ? W2 - 1 : x), sy = y < 0 ? 0 : (y >= H2 ? H2 - 1 : y);
+    k.l1ref[(ptrdiff_t)y * k.sc + x] = k.l1ref[(ptrdiff_t)sy * k.sc + sx];
 }
 
 /* ---- launch wrappers --------------------------------------------------------------------------------- */
@@ -206,10 +205,9 @@ extern "C" int cck_hpel(const cc_kparams *k, cudaStream_t st) {
     CC_LAUNCH(k_hpel, gh, dim3(256), st, *k);
     return 1;
 }
-extern "C" int cck_l1ref(const cc_kparams *k, cudaStream_t st) {
-    int n4 = (k->W / 2 + 48) / 4;
-    dim3 gl((unsigned)((n4 + 127) / 128), (unsigned)(k->H / 2 + 48));
-    CC_LAUNCH(k_l1ref, gl, dim3(128), st, *k);
+extern "C" int cck_l1border(const cc_kparams *k, cudaStream_t st) {
+    const int n = 48 * (k->H / 2) + 48 * (k->W / 2 + 48);
+    CC_LAUNCH(k_l1border, dim3((unsigned)((n + 255) / 256)), dim3(256), st, *k);
     return 1;
 }
-extern "C" int cck_finish_ref(const cc_kparams *k, cudaStream_t st) { return cck_border(k, st) + cck_hpel(k, st) + cck_l1ref(k, st); }
+extern "C" int cck_finish_ref(const cc_kparams *k, cudaStream_t st) { return cck_border(k, st) + cck_hpel(k, st); }

@@ -806,7 +806,9 @@ __device__ __forceinline__ void publish_unfiltered(const cc_kparams &k, int lane
     else if (lane < 24) ur[lane] = (uint8_t)(recC0[(lane - 16) * 2 + 1] >> 24);
     else ur[lane] = (uint8_t)(recC1[(lane - 24) * 2 + 1] >> 24);
 }
-/* recY/recC of the warp's WarpMem -> k.rec, k.ubot, k.uright */
+/* recY/recC of the warp's WarpMem -> k.rec, k.ubot, k.uright, and the macroblock's 8x8 block of the half-resolution reference
+ * (2x2 box means of the UNFILTERED reconstruction: the coarse search of the next frame then needs nothing from the in-loop filter
+ * and runs next to it; oracle/ref_enc.c writes the same plane) */
 __device__ __forceinline__ void publish_pixels(const cc_kparams &k, const MbCtx &c) {
     WarpMem *m = c.m;
     const int lane = c.lane, r = lane >> 1, h = lane & 1;
@@ -815,6 +817,15 @@ __device__ __forceinline__ void publish_pixels(const cc_kparams &k, const MbCtx 
     *(uint32_t *)(ry + (size_t)r * k.sy + h * 8 + 4) = m->recY[r * 4 + h * 2 + 1];
     const int pl = lane >> 4, cr = (lane >> 1) & 7;
     *(uint32_t *)(k.rec[1 + pl] + (size_t)(c.mby * 8 + cr) * k.sc + c.mbx * 8 + 4 * h) = m->recC[pl][cr * 2 + h];
+    if (lane < 16) { /* half-resolution row r (lanes 0..15: r = 0..7), 4 pixels of its half h */
+        const uint32_t a0 = m->recY[(2 * r) * 4 + 2 * h], a1 = m->recY[(2 * r) * 4 + 2 * h + 1];
+        const uint32_t b0 = m->recY[(2 * r + 1) * 4 + 2 * h], b1 = m->recY[(2 * r + 1) * 4 + 2 * h + 1];
+        uint32_t v = (uint32_t)((cc_byte(a0, 0) + cc_byte(a0, 1) + cc_byte(b0, 0) + cc_byte(b0, 1) + 2) >> 2);
+        v |= (uint32_t)((cc_byte(a0, 2) + cc_byte(a0, 3) + cc_byte(b0, 2) + cc_byte(b0, 3) + 2) >> 2) << 8;
+        v |= (uint32_t)((cc_byte(a1, 0) + cc_byte(a1, 1) + cc_byte(b1, 0) + cc_byte(b1, 1) + 2) >> 2) << 16;
+        v |= (uint32_t)((cc_byte(a1, 2) + cc_byte(a1, 3) + cc_byte(b1, 2) + cc_byte(b1, 3) + 2) >> 2) << 24;
+        *(uint32_t *)(k.l1ref + (size_t)(c.mby * 8 + r) * k.sc + c.mbx * 8 + 4 * h) = v;
+    }
     publish_unfiltered(k, lane, c.mb, c.mbx, c.mby, m->recY, m->recC[0], m->recC[1]);
 }
 __device__ __forceinline__ void stage_cur(const cc_kparams &k, const MbCtx &c) {

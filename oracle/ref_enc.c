@@ -302,8 +302,10 @@ int ref_enc_encode(ref_enc *e, const uint8_t *y, int sy_, const uint8_t *u, int 
     load_plane(e->cur[2], e->sc, v, sv, e->w / 2, e->h / 2, W / 2, H / 2);
 
     if (!is_idr) {
+        /* l1ref: the half-resolution picture of the previous frame's UNFILTERED reconstruction, written in that frame's slice
+         * loop below; its border is edge replication of the half-resolution samples */
         downsample2(e->l1cur, e->s1, e->cur[0], e->sy, W, H, 0);
-        downsample2(e->l1ref, e->s1, e->ref[0], e->sy, W, H, REF_PAD);
+        extend_border(e->l1ref, e->s1, W / 2, H / 2, REF_PAD / 2);
 #pragma omp parallel for schedule(dynamic, 4)
         for (int i = 0; i < mw * mh; i++) me_l1(e, i % mw, i / mw);
 #pragma omp parallel for schedule(dynamic, 4)
@@ -326,6 +328,14 @@ int ref_enc_encode(ref_enc *e, const uint8_t *y, int sy_, const uint8_t *u, int 
         ref_put_bits(sb, &bp, 1, 1);
         while (bp & 7) ref_put_bits(sb, &bp, 1, 0);
         e->slice_bits[s] = bp;
+        /* half-resolution reference of the next frame's coarse search: 2x2 box means of this slice's reconstruction BEFORE the
+         * in-loop filter (the product writes them where it publishes the reconstruction, so that the coarse search does not have
+         * to wait for the filter); the motion search of this frame, which read the plane, is over */
+        for (int y = r0 * 8; y < r1 * 8; y++)
+            for (int x = 0; x < W / 2; x++) {
+                const uint8_t *p = e->rec[0] + (size_t)(2 * y) * e->sy + 2 * x;
+                e->l1ref[(size_t)y * e->s1 + x] = (uint8_t)((p[0] + p[1] + p[e->sy] + p[e->sy + 1] + 2) >> 2);
+            }
         for (int my = r0; my < r1; my++)
             for (int mx = 0; mx < mw; mx++) ref_mb_deblock(e, mx, my);
     }
