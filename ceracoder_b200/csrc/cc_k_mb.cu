@@ -592,34 +592,29 @@ __device__ __forceinline__ void c8_pred_block(const MbCtx &c, const C8Params &p,
         pw[r] = w;
     }
 }
-/* picks the chroma mode by SATD over both planes and leaves the predictor in m->predC; returns the mode */
+/* picks the chroma mode by SATD over both planes and leaves the predictor in m->predC; returns the mode.
+ * All 32 (mode, plane, block) pairs at once: lane = mode * 8 + plane * 4 + block. */
 __device__ __forceinline__ int intra_chroma_pred(const MbCtx &c) {
     WarpMem *m = c.m;
-    const int lane = c.lane, pl = (lane >> 2) & 1, b = lane & 3, bx = b & 1, by = b >> 1;
+    const int lane = c.lane, mode = lane >> 3, pl = (lane >> 2) & 1, b = lane & 3, bx = b & 1, by = b >> 1;
     C8Params p;
     c8_params(c, pl, p);
-    uint32_t cw[4];
+    uint32_t cw[4], pw[4];
 #pragma unroll
     for (int r = 0; r < 4; r++) cw[r] = m->curC[pl][(by * 4 + r) * 2 + bx];
-    unsigned best = 0xffffffffu;
-    for (int mode = 0; mode < 4; mode++) {
-        const bool ok = mode == 0 || (mode == 1 && c.L) || (mode == 2 && c.T) || (mode == 3 && c.T && c.L);
-        int satd = 0;
-        if (ok && lane < 8) {
-            uint32_t pw[4];
-            c8_pred_block(c, p, pl, mode, bx, by, pw);
-            satd = cc_satd4x4_words(cw, pw);
-        }
-        satd += __shfl_xor_sync(FULL, satd, 1); satd += __shfl_xor_sync(FULL, satd, 2); satd += __shfl_xor_sync(FULL, satd, 4);
-        if (ok) {
-            const int bits = mode == 0 ? 1 : (mode == 3 ? 5 : 3);
-            best = min(best, ((unsigned)(satd + c.lambda * bits) << 2) | (unsigned)mode);
-        }
+    const bool ok = mode == 0 || (mode == 1 && c.L) || (mode == 2 && c.T) || (mode == 3 && c.T && c.L);
+    int satd = 0;
+    if (ok) {
+        c8_pred_block(c, p, pl, mode, bx, by, pw);
+        satd = cc_satd4x4_words(cw, pw);
     }
-    best = __shfl_sync(FULL, best, 0);
+    satd += __shfl_xor_sync(FULL, satd, 1); satd += __shfl_xor_sync(FULL, satd, 2); satd += __shfl_xor_sync(FULL, satd, 4);
+    const int bits = mode == 0 ? 1 : (mode == 3 ? 5 : 3);
+    unsigned best = ok ? (((unsigned)(satd + c.lambda * bits) << 2) | (unsigned)mode) : 0xffffffffu;
+    best = min(best, __shfl_xor_sync(FULL, best, 8));
+    best = min(best, __shfl_xor_sync(FULL, best, 16));
     const int bm = (int)(best & 3u);
     if (lane < 8) {
-        uint32_t pw[4];
         c8_pred_block(c, p, pl, bm, bx, by, pw);
 #pragma unroll
         for (int r = 0; r < 4; r++) m->predC[pl][(by * 4 + r) * 2 + bx] = pw[r];
