@@ -72,6 +72,7 @@ struct cc_enc {
                                   * asynchronously.  One frame suffices: a handle has one frame in flight and its upload is over by collect */
     size_t stage_bytes;
     long staged_frames;
+    unsigned long long tmaps[5 * 16] __attribute__((aligned(64))); /* five CUtensorMap (k_me_l0's sub-pel windows) */
     int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
     size_t bs_bytes;
 };
@@ -249,6 +250,10 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     k->part8 = e->p.partitions != 0;
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbd, sizeof(cc_mbdev) * nmb);
     if (rc == CC_OK) rc = cck_me_l1_prepare(k);
+    if (rc == CC_OK) {
+        uint8_t *const planes[5] = {k->rec[0], k->ref[0], k->hb, k->hh, k->hj};
+        rc = cck_me_l0_prepare(k, planes, e->tmaps);
+    }
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->nbrec, (size_t)20 * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->mbh, sizeof(cc_mbhost) * nmb);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowbuf, (size_t)nmb * CC_ROW_PAYLOAD_PER_MB);

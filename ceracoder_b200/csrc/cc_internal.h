@@ -99,6 +99,8 @@ typedef struct {
     uint8_t *l1cur, *l1ref;
     unsigned long long tmap_l1[16]; /* CUtensorMap (128 B, opaque here) over the allocation of l1ref: k_me_l1 loads its search windows with TMA */
     int tmap_l1_ok;
+    const void *tmaps;       /* host memory: five CUtensorMap over the luma-sized planes {rec A, rec B, b, h, j} (k_me_l0's sub-pel windows) */
+    const uint8_t *tmap_plane[2]; /* origins of rec A / rec B: which map belongs to this frame's reference */
     uint8_t *uvstage;  /* NV12 interleaved chroma staging (pitch sy), or NULL */
     uint8_t *pkstage;  /* packed-input staging (YUY2: 2 bytes / pixel, BGRx: 4), pitch pks, or NULL */
     int pks;
@@ -142,6 +144,7 @@ int cck_l1border(const cc_kparams *k, cudaStream_t st); /* edge replication of t
 int cck_me_l1_prepare(cc_kparams *k); /* builds k->tmap_l1 (after the planes are allocated); CC_OK or CC_ERR_CUDA */
 int cck_me_l1(const cc_kparams *k, cudaStream_t st);
 int cck_me_l0(const cc_kparams *k, cudaStream_t st);
+int cck_me_l0_prepare(cc_kparams *k, uint8_t *const planes[5], void *maps); /* tensor maps of the sub-pel windows; 0 or CC_ERR_CUDA */
 int cck_motion(const cc_kparams *k, cudaStream_t st);
 int cck_p_code(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);

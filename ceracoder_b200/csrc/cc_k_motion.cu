@@ -128,6 +128,21 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + (ptrdiff_t)r * k.sy), cc_ld32u(B + (ptrdiff_t)r * k.sy));
 }
 
+/* The same from the warp's staged window: tiles[p] = plane p (G, b, h, j) over SP_W x SP_H bytes whose top-left sample is
+ * (wx, wy) relative to the macroblock origin; (bx, by) = the block's offset inside the macroblock */
+#define SP_W 32
+#define SP_H 28
+#define SP_ORG 4 /* the window starts 4 samples left of / above the best full-pel position */
+__device__ __forceinline__ void cc_qpel4x4_s(const uint8_t *tiles, int wx, int wy, int bx, int by, int mvx, int mvy, uint32_t out[4]) {
+    const int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
+    const int pa = e & 3, pb = (e >> 4) & 3;
+    const int base = (by + (mvy >> 2) - wy) * SP_W + bx + (mvx >> 2) - wx;
+    const uint8_t *A = tiles + pa * (SP_W * SP_H) + base + ((e >> 2) & 1) + ((e >> 3) & 1) * SP_W;
+    const uint8_t *B = tiles + pb * (SP_W * SP_H) + base + ((e >> 6) & 1) + ((e >> 7) & 1) * SP_W;
+#pragma unroll
+    for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + r * SP_W), cc_ld32u(B + r * SP_W));
+}
+
 /* Full-pel SADs of five horizontally adjacent candidates at once.  A lane takes four source rows (4 g .. 4 g + 3) of one
  * candidate row: it loads the 24-byte strip of the reference row once (six aligned words, realigned with five funnel shifts) and
  * slides the 16-pixel window over it in registers — a quarter of the loads of "lane = candidate", and every load is used by five
@@ -163,7 +178,7 @@ __device__ __forceinline__ void sad_strip5(const uint8_t *r, int sy, const uint3
  * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks
  * (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
  * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
-__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
+__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, const uint8_t *tiles, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
     /* lanes 0..19 = (candidate row dy = lane >> 2, source rows 4 g .. 4 g + 3 with g = lane & 3): rows of g < 2 belong to the top
      * quadrants, the others to the bottom ones */
     unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
@@ -223,7 +238,7 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, i
             int satd = 0;
             if (valid) {
                 uint32_t pw[4];
-                cc_qpel4x4(k, px + ox, py + oy, cx + dx, cy + dy, pw);
+                cc_qpel4x4_s(tiles, fbx - SP_ORG, fby - SP_ORG, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
             satd += __shfl_xor_sync(FULL, satd, 1);
@@ -250,7 +265,17 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, i
     return cost8 + 8 * lambda;
 }
 
+/* Sub-pel stages (north_star: "Hadamard SATD on TMA/shared-memory-staged reference tiles"): once the best full-pel vector is
+ * known, the warp stages the 32 x 28 window around it of all four planes (G, b, h, j: 3.5 KB) with four TMA loads
+ * (cp.async.bulk.tensor.2d, one mbarrier per warp), and all 17 + 4 x 17 quarter-pel predictors of the 16x16 and 8x8 refinements are
+ * built from shared memory — instead of two unaligned global word pairs per predictor row from four planes. */
+#ifndef CC_EMU_BUILD
+__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k, const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmB,
+                                                         const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmJ) {
+#else
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
+#endif
+    __shared__ __align__(128) uint8_t swin[ME_WARPS][4 * SP_W * SP_H];
     __shared__ uint32_t scur[ME_WARPS][64]; /* current MB, 16 rows x 4 words */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
@@ -307,6 +332,46 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     const int fbx = bl == 0 ? pm[0] : (bl == 1 ? 0 : l1x + (bl - 2) % 5 - 2), fby = bl == 0 ? pm[1] : (bl == 1 ? 0 : l1y + (bl - 2) / 5 - 2);
     int bx = 4 * fbx, by = 4 * fby;
 
+    /* stage the sub-pel window of the four planes */
+    const uint8_t *tiles = swin[wid];
+    {
+        const int tx = CC_PAD + px + fbx - SP_ORG, ty = CC_PAD + py + fby - SP_ORG; /* allocation coordinates: the plane starts CC_PAD in */
+#ifndef CC_EMU_BUILD
+        __shared__ __align__(8) unsigned long long mbar[ME_WARPS];
+        const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar[wid]), win_a = (uint32_t)__cvta_generic_to_shared(swin[wid]);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_a), "r"(4 * SP_W * SP_H) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(win_a), "l"((unsigned long long)&tmG), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(win_a + SP_W * SP_H), "l"((unsigned long long)&tmB), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(win_a + 2 * SP_W * SP_H), "l"((unsigned long long)&tmH), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(win_a + 3 * SP_W * SP_H), "l"((unsigned long long)&tmJ), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+        }
+        __syncwarp();
+        {
+            uint32_t ok;
+            do {
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a) : "memory");
+            } while (!ok);
+        }
+#else
+        (void)tx; (void)ty;
+        const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
+        for (int p = 0; p < 4; p++)
+            for (int i = lane; i < SP_W * SP_H / 4; i += 32) {
+                const int r = i / (SP_W / 4), cw4 = i - r * (SP_W / 4);
+                *(uint32_t *)(swin[wid] + p * SP_W * SP_H + r * SP_W + 4 * cw4) =
+                    cc_ld32u(pl[p] + (ptrdiff_t)(py + fby - SP_ORG + r) * k.sy + px + fbx - SP_ORG + 4 * cw4);
+            }
+        __syncwarp();
+#endif
+    }
+
     /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */
     const int blk = lane & 15, half = lane >> 4, ox = (blk & 3) * 4, oy = (blk >> 2) * 4;
     uint32_t cw[4];
@@ -326,7 +391,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
             int satd = 0;
             if (valid) { /* uniform within each half-warp; no collectives inside */
                 uint32_t pw[4];
-                cc_qpel4x4(k, px + ox, py + oy, cx + dx, cy + dy, pw);
+                cc_qpel4x4_s(tiles, fbx - SP_ORG, fby - SP_ORG, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
 #pragma unroll
@@ -347,7 +412,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     }
     const int cost16 = (int)(bestkey >> 5);
     int part = 0;
-    if (k.part8) part = me_8x8(k, sc, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
+    if (k.part8) part = me_8x8(k, sc, tiles, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
     if (lane == 0) {
         k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd; k.me[mb].part = part;
     }
@@ -389,7 +454,35 @@ extern "C" int cck_me_l1_prepare(cc_kparams *k) {
 }
 extern "C" int cck_me_l0(const cc_kparams *k, cudaStream_t st) {
     int nmb = k->mb_w * k->mb_h;
+#ifndef CC_EMU_BUILD
+    const CUtensorMap *tm = (const CUtensorMap *)k->tmaps; /* [0], [1]: the two reconstruction planes; [2..4]: b, h, j */
+    const CUtensorMap *g = k->ref[0] == k->tmap_plane[0] ? &tm[0] : &tm[1];
+    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k, *g, tm[2], tm[3], tm[4]);
+#else
     CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k);
+#endif
     return 1;
+}
+/* Tensor maps over the allocations of the five luma-sized planes the sub-pel search reads (pitch sy, CC_PAD border rows / columns):
+ * box = one warp's SP_W x SP_H window.  planes[i] = origin (pixel 0,0) of plane i; maps = room for five CUtensorMap (128 B each). */
+extern "C" int cck_me_l0_prepare(cc_kparams *k, uint8_t *const planes[5], void *maps) {
+    k->tmaps = maps;
+    k->tmap_plane[0] = planes[0]; k->tmap_plane[1] = planes[1];
+#ifndef CC_EMU_BUILD
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void *fn = NULL;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) return -2; /* CC_ERR_CUDA */
+    const cuuint64_t dims[2] = {(cuuint64_t)k->sy, (cuuint64_t)(k->H + 2 * CC_PAD)};
+    const cuuint64_t strides[1] = {(cuuint64_t)k->sy};
+    const cuuint32_t box[2] = {SP_W, SP_H}, es[2] = {1, 1};
+    for (int i = 0; i < 5; i++) {
+        uint8_t *base = planes[i] - ((size_t)CC_PAD * k->sy + CC_PAD);
+        if (((encode_fn)fn)((CUtensorMap *)maps + i, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -2;
+    }
+#endif
+    return 0;
 }
 extern "C" int cck_motion(const cc_kparams *k, cudaStream_t st) { return cck_me_l1(k, st) + cck_me_l0(k, st); }
