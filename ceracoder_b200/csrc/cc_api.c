@@ -73,6 +73,7 @@ struct cc_enc {
     size_t stage_bytes;
     long staged_frames;
     unsigned long long tmaps[5 * 16] __attribute__((aligned(64))); /* five CUtensorMap (k_me_l0's sub-pel windows) */
+    int debug_sync;
     int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
     size_t bs_bytes;
 };
@@ -303,6 +304,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
+    e->debug_sync = getenv("CC_DEBUG_SYNC") != NULL;
+    { const char *v = getenv("CC_DBG_ME"); e->k.dbg = v ? atoi(v) : 0; }
     cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max, e->p.key_int_max);
     cudaStreamSynchronize(e->st);
     cudaDeviceSynchronize();
@@ -477,7 +480,10 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
             CUCHECK(cudaMemcpy2DAsync(k->cur[2], (size_t)k->sc, pl[2], (size_t)st[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st));
         }
     }
-#define STAGE(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
+    /* CC_DEBUG_SYNC=1: wait after every stage and name the one that faulted (compute-sanitizer is not always available) */
+#define STAGE(i) do { if (e->debug_sync) { cudaError_t er_ = cudaStreamSynchronize(e->st); if (er_ == cudaSuccess) er_ = cudaStreamSynchronize(e->st2); \
+                                           if (er_ != cudaSuccess) { fprintf(stderr, "ceracuda: device fault before stage %d of frame %d: %s\n", (int)(i), e->frame_idx, cudaGetErrorString(er_)); return CC_ERR_CUDA; } } \
+                      if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
     for (int i = 0; i <= CC_N_STAGES + 1; i++) pev_used[i] = 0;
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);

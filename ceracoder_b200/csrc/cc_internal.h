@@ -132,6 +132,7 @@ typedef struct {
     uint32_t *bs;          /* per slice a zero-initialised bit buffer of bs_slice_words words (MSB-first words) */
     uint32_t bs_slice_words;
     uint32_t *bs_ctl;      /* [0, ns): row CTAs of the slice that finished; [ns, 2 ns): the slice's RBSP bytes */
+    int dbg;               /* debug switch (CC_DBG_ME): 1 = k_me_l0 stages its sub-pel windows with plain loads instead of TMA */
     unsigned long long *cyc; /* debug (CC_DEBUG_CYCLES=1): per MB row CC_CYC_N cycle / event counters of the wavefront kernels, or NULL */
 } cc_kparams;
 

@@ -130,15 +130,16 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
 
 /* The same from the warp's staged window: tiles[p] = plane p (G, b, h, j) over SP_W x SP_H bytes whose top-left sample is
  * (wx, wy) relative to the macroblock origin; (bx, by) = the block's offset inside the macroblock */
-#define SP_W 32
+#define SP_W 48 /* 32 columns are needed; the window starts on a 16-byte boundary of the plane (TMA), up to 15 columns further left */
 #define SP_H 28
-#define SP_ORG 4 /* the window starts 4 samples left of / above the best full-pel position */
+#define SP_ORG 4 /* the window starts (at least) 4 samples left of / above the best full-pel position */
+#define SP_PLANE 1408 /* bytes from one plane's tile to the next: SP_W * SP_H rounded up to the 128 bytes a TMA destination must be aligned to */
 __device__ __forceinline__ void cc_qpel4x4_s(const uint8_t *tiles, int wx, int wy, int bx, int by, int mvx, int mvy, uint32_t out[4]) {
     const int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
     const int pa = e & 3, pb = (e >> 4) & 3;
     const int base = (by + (mvy >> 2) - wy) * SP_W + bx + (mvx >> 2) - wx;
-    const uint8_t *A = tiles + pa * (SP_W * SP_H) + base + ((e >> 2) & 1) + ((e >> 3) & 1) * SP_W;
-    const uint8_t *B = tiles + pb * (SP_W * SP_H) + base + ((e >> 6) & 1) + ((e >> 7) & 1) * SP_W;
+    const uint8_t *A = tiles + pa * SP_PLANE + base + ((e >> 2) & 1) + ((e >> 3) & 1) * SP_W;
+    const uint8_t *B = tiles + pb * SP_PLANE + base + ((e >> 6) & 1) + ((e >> 7) & 1) * SP_W;
 #pragma unroll
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + r * SP_W), cc_ld32u(B + r * SP_W));
 }
@@ -178,7 +179,7 @@ __device__ __forceinline__ void sad_strip5(const uint8_t *r, int sy, const uint3
  * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks
  * (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
  * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
-__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, const uint8_t *tiles, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
+__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, const uint8_t *tiles, int wx, int wy, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
     /* lanes 0..19 = (candidate row dy = lane >> 2, source rows 4 g .. 4 g + 3 with g = lane & 3): rows of g < 2 belong to the top
      * quadrants, the others to the bottom ones */
     unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
@@ -238,7 +239,7 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, c
             int satd = 0;
             if (valid) {
                 uint32_t pw[4];
-                cc_qpel4x4_s(tiles, fbx - SP_ORG, fby - SP_ORG, ox, oy, cx + dx, cy + dy, pw);
+                cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
             satd += __shfl_xor_sync(FULL, satd, 1);
@@ -275,7 +276,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k, const __g
 #else
 __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
 #endif
-    __shared__ __align__(128) uint8_t swin[ME_WARPS][4 * SP_W * SP_H];
+    __shared__ __align__(128) uint8_t swin[ME_WARPS][4 * SP_PLANE];
     __shared__ uint32_t scur[ME_WARPS][64]; /* current MB, 16 rows x 4 words */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
@@ -334,11 +335,16 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
 
     /* stage the sub-pel window of the four planes */
     const uint8_t *tiles = swin[wid];
+    /* window origin relative to the macroblock: rows from fby - 4; columns from the 16-byte boundary of the plane at or left of
+     * fbx - 4 (the plane's origin is 16-byte aligned and CC_PAD is a multiple of 16, so the boundary is the same in allocation
+     * coordinates) */
+    const int wy = fby - SP_ORG, wx = fbx - SP_ORG - ((px + fbx - SP_ORG) & 15);
     {
-        const int tx = CC_PAD + px + fbx - SP_ORG, ty = CC_PAD + py + fby - SP_ORG; /* allocation coordinates: the plane starts CC_PAD in */
+        const int tx = CC_PAD + px + wx, ty = CC_PAD + py + wy; /* allocation coordinates: the plane starts CC_PAD in */
 #ifndef CC_EMU_BUILD
         __shared__ __align__(8) unsigned long long mbar[ME_WARPS];
         const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar[wid]), win_a = (uint32_t)__cvta_generic_to_shared(swin[wid]);
+        if (k.dbg != 1) {
         if (lane == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -346,11 +352,11 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                          ::"r"(win_a), "l"((unsigned long long)&tmG), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + SP_W * SP_H), "l"((unsigned long long)&tmB), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                         ::"r"(win_a + SP_PLANE), "l"((unsigned long long)&tmB), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + 2 * SP_W * SP_H), "l"((unsigned long long)&tmH), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                         ::"r"(win_a + 2 * SP_PLANE), "l"((unsigned long long)&tmH), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + 3 * SP_W * SP_H), "l"((unsigned long long)&tmJ), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                         ::"r"(win_a + 3 * SP_PLANE), "l"((unsigned long long)&tmJ), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
         }
         __syncwarp();
         {
@@ -359,17 +365,20 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
                 asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a) : "memory");
             } while (!ok);
         }
+        } else
 #else
         (void)tx; (void)ty;
-        const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
-        for (int p = 0; p < 4; p++)
-            for (int i = lane; i < SP_W * SP_H / 4; i += 32) {
-                const int r = i / (SP_W / 4), cw4 = i - r * (SP_W / 4);
-                *(uint32_t *)(swin[wid] + p * SP_W * SP_H + r * SP_W + 4 * cw4) =
-                    cc_ld32u(pl[p] + (ptrdiff_t)(py + fby - SP_ORG + r) * k.sy + px + fbx - SP_ORG + 4 * cw4);
-            }
-        __syncwarp();
 #endif
+        { /* the same window by plain loads (the CPU emulation build; CC_DBG_ME=1 on the device) */
+            const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
+            for (int p = 0; p < 4; p++)
+                for (int i = lane; i < SP_W * SP_H / 4; i += 32) {
+                    const int r = i / (SP_W / 4), cw4 = i - r * (SP_W / 4);
+                    *(uint32_t *)(swin[wid] + p * SP_PLANE + r * SP_W + 4 * cw4) =
+                        *(const uint32_t *)(pl[p] + (ptrdiff_t)(py + wy + r) * k.sy + px + wx + 4 * cw4);
+                }
+            __syncwarp();
+        }
     }
 
     /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */
@@ -391,7 +400,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
             int satd = 0;
             if (valid) { /* uniform within each half-warp; no collectives inside */
                 uint32_t pw[4];
-                cc_qpel4x4_s(tiles, fbx - SP_ORG, fby - SP_ORG, ox, oy, cx + dx, cy + dy, pw);
+                cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
 #pragma unroll
@@ -412,7 +421,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     }
     const int cost16 = (int)(bestkey >> 5);
     int part = 0;
-    if (k.part8) part = me_8x8(k, sc, tiles, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
+    if (k.part8) part = me_8x8(k, sc, tiles, wx, wy, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
     if (lane == 0) {
         k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd; k.me[mb].part = part;
     }
