@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Turn the scratch captures of tools/profile_r1.sh (gpurun_out/<TAG>_*) into the committed summaries under profiles/:
+"""Turn the scratch captures of tools/profile_r2.sh (gpurun_out/<TAG>_*) into the committed summaries under profiles/:
   launches_<TAG>.csv / launches_<TAG>_summary.txt   per-launch times (ncu --metrics gpu__time_duration.sum), shares per kernel
   <kernel>_<TAG>_metrics.txt                        key counters of one `ncu --set full` capture per hot kernel
   mb_encode_<TAG>_source.txt                        stall samples / instructions per source line of the wavefront kernel
@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G = os.path.join(ROOT, "gpurun_out")
 P = os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
-CMD = "python bench.py --steps 1 --warmup 1 --streams 2 --frames-per-step 6 --no-cpu-baseline"
+CMD = "python bench.py --steps 1 --warmup 1 --streams 2 --frames-per-step 6 --no-cpu-baseline --pool 24"
 
 METRICS = [
     "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
@@ -94,7 +94,7 @@ if __name__ == "__main__":
     os.makedirs(P, exist_ok=True)
     launches()
     traffic = {}
-    for kn in ("k_mb_encode", "k_deblock", "k_p_code", "k_me_l1", "k_me_l0", "k_hpel", "k_ingest", "k_border", "k_l1ref", "k_pack"):
+    for kn in ("k_mb_encode", "k_deblock", "k_p_code", "k_me_l1", "k_me_l0", "k_cavlc_size", "k_cavlc_write", "k_hpel", "k_ingest", "k_border", "k_pack"):
         kernel(kn, traffic)
     json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
     for f in (f"{tag}_cycles.err",):
@@ -102,4 +102,17 @@ if __name__ == "__main__":
             lines = [l for l in open(os.path.join(G, f)) if "cycles" in l]
             open(os.path.join(P, f"wavefront_cycles_{tag}.txt"), "w").write(
                 "CC_DEBUG_CYCLES=1 python bench.py --steps 2 --warmup 1 --no-cpu-baseline   (clock64 counters of k_mb_encode, 8 streams; one pair of lines per stream)\n" + "".join(lines))
+    ins = os.path.join(G, f"{tag}_insts.csv")
+    if os.path.exists(ins):  # one stream alone: per-launch duration / instructions / utilisation
+        rows = list(csv.reader(l for l in open(ins) if l.startswith('"')))
+        h = rows[0]
+        ki, mi, vi, ii = h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value"), h.index("ID")
+        d = collections.OrderedDict()
+        for r in rows[1:]:
+            d.setdefault((r[ii], r[ki].split("(")[0]), {})[r[mi]] = r[vi]
+        with open(os.path.join(P, f"insts_{tag}.txt"), "w") as f:
+            f.write("one stream alone on the GPU (bench.py --streams 1 --pool 24): consecutive launches under ncu (serialised, cold cache)\n")
+            for (i, k), m in d.items():
+                f.write(f"{i:>4} {k:24s} dur_us={float(m['gpu__time_duration.sum'].replace(',', '')) / 1000:8.1f} inst={float(m['smsp__inst_executed.sum'].replace(',', '')) / 1e6:7.2f}M "
+                        f"sm%={m['sm__throughput.avg.pct_of_peak_sustained_elapsed'][:5]} issue%={m['smsp__issue_active.avg.pct_of_peak_sustained_active'][:5]}\n")
     print("profiles written for", tag)
