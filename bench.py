@@ -119,7 +119,9 @@ class FrameStore:
                 procs = max(1, min(os.cpu_count() or 1, 32, n // 8 or 1))
                 step = (n + procs - 1) // procs
                 jobs = [(self.path, a, min(a + step, n), n) for a in range(0, n, step)]
-                with mp.get_context("fork").Pool(procs) as pool:  # nothing CUDA is initialised yet in this process
+                # fork: the children only draw frames with numpy (no CUDA, no threads of the parent are touched); spawn would need an
+                # importable __main__, which a harness that feeds this module from stdin does not have
+                with mp.get_context("fork").Pool(procs) as pool:
                     pool.map(_gen_chunk, jobs)
                 with open(done + ".tmp", "w") as f:
                     f.write("ok\n")
@@ -349,7 +351,7 @@ def main():
     if args.impl == "reference":
         return main_reference(args, rank, world, local)
 
-    store = FrameStore(args.pool, local)  # before anything CUDA: the generator forks
+    store = FrameStore(args.pool, local)  # before anything CUDA in this process
     import torch
     import torch.distributed as dist
     assert torch.cuda.is_available(), "bench.py --impl cuda needs a CUDA device (there is no CPU fallback)"

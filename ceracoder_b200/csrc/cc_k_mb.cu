@@ -969,8 +969,9 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             } else cost_inter = me.satd + c.lambda * (cc_se_bits(me.mv[0] - mvp[0]) + cc_se_bits(me.mv[1] - mvp[1]));
         }
         if (!done) {
-            /* P frames: real intra analysis only when the pre-pass' source-based estimate is within 25 % of inter */
-            const bool gate = k.is_idr || pre.est_intra * 4 <= cost_inter * 5;
+            /* P frames: real intra analysis only when the pre-pass' source-based estimate is within 12.5 % of inter (oracle/ref_mb.c
+             * ref_mb_encode states what the gate costs) */
+            const bool gate = k.is_idr || pre.est_intra * 8 <= cost_inter * 9;
             I16Params ip;
             int cost_i16 = 1 << 30;
             if (gate) {

@@ -89,6 +89,7 @@ typedef struct {
     int32_t me_cost16, me_cost8;   /* search costs (SATD + lambda * approximate mvd bits [+ partition overhead]) */
     uint16_t dbg_i4_blk[16];                           /* per 4x4 block (decoding order): best Intra4x4 cost (SATD + lambda * mode bits), clamped */
     int32_t dbg_i4_blk_exact[16];                      /* the same, not clamped (the projection test of analyse_i4 reads these) */
+    int32_t dbg_est_intra;                             /* P frames: the source-based Intra16x16 estimate behind the intra gate */
     int32_t dbg_cost_inter, dbg_cost_i16, dbg_cost_i4; /* mode-decision costs of the last ref_mb_encode (1 << 30 = not evaluated); analysis tools only */
 } ref_mb_info;
 

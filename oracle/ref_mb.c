@@ -448,12 +448,16 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         } else
         cost_inter = mi->me_satd + lambda * (ref_mv_bits(mi->me_mv[0] - mvp[0]) + ref_mv_bits(mi->me_mv[1] - mvp[1]));
     }
-    /* P frames: intra is analysed for real only when a source-based Intra16x16 estimate comes within 25 % of the inter
-     * cost [EXT: x264 makes the same kind of early-out in x264_mb_analyse_intra / fast_intra] */
+    /* P frames: intra is analysed for real only when a source-based Intra16x16 estimate comes within 12.5 % of the inter
+     * cost [EXT: x264 makes the same kind of early-out in x264_mb_analyse_intra / fast_intra, at 25 %].  Measured on S2 1080p
+     * (the oracle over 7 P frames at QP 24 / 30 / 36): against 25 % the tighter gate starts 77 / 50 / 15 % fewer analyses and
+     * loses 6 - 8 intra macroblocks per frame, 0.02 - 0.06 % of the coded macroblocks' cost. */
     int gate = 1;
     if (!e->is_idr) {
         int dummy;
-        gate = analyse_i16(e, mbx, mby, &dummy, e->cur[0]) * 4 <= cost_inter * 5;
+        const int est = analyse_i16(e, mbx, mby, &dummy, e->cur[0]);
+        mi->dbg_est_intra = est; mi->dbg_cost_inter = cost_inter;
+        gate = est * 8 <= cost_inter * 9;
     }
     cost_i16 = 1 << 30;
     if (gate) {

@@ -15,7 +15,7 @@ class MbInfo(C.Structure):
                 ("t8", C.c_uint8), ("part", C.c_uint8), ("me_part", C.c_uint8), ("pad8", C.c_uint8),
                 ("mv4", C.c_int16 * 8), ("mvd4", C.c_int16 * 8), ("me_mv8", C.c_int16 * 8), ("me_satd8", C.c_int32 * 4),
                 ("me_cost16", C.c_int32), ("me_cost8", C.c_int32),
-                ("dbg_i4_blk", C.c_uint16 * 16), ("dbg_i4_blk_exact", C.c_int32 * 16), ("dbg_cost_inter", C.c_int32), ("dbg_cost_i16", C.c_int32), ("dbg_cost_i4", C.c_int32)]
+                ("dbg_i4_blk", C.c_uint16 * 16), ("dbg_i4_blk_exact", C.c_int32 * 16), ("dbg_est_intra", C.c_int32), ("dbg_cost_inter", C.c_int32), ("dbg_cost_i16", C.c_int32), ("dbg_cost_i4", C.c_int32)]
 
 
 def build():
