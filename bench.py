@@ -532,8 +532,8 @@ def main():
             "e2e_pageable": {"value": e2e_pg, "unit": "frames/s", "frames": int(f_pg), "staged_frames": int(r_page["staged"]),
                              "note": "pageable host frames, as gst_video_frame_map hands them to the element: each frame is copied by the calling thread into the handle's "
                                      "pinned staging frame (cc_enc_submit), then uploaded asynchronously"},
-            "timed_region": {"frames_per_stream": fps_step * args.steps, "frames": int(f_dev), "idr_frames": int(r_dev["n_idr"]), "seconds": ms_dev / 1e3,
-                             "scene_cuts_per_stream": (fps_step * args.steps) // 300 if n_pool >= POOL else 0},
+            "timed_region": {"frames_per_stream": fps_step * args.steps, "frames": int(f_dev), "idr_frames_rank0": int(r_dev["n_idr"]), "frames_rank0": int(r_dev["frames"]),
+                             "seconds": ms_dev / 1e3, "scene_cuts_per_stream": (fps_step * args.steps) // 300 if n_pool >= POOL else 0},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu, "quality": quality,
             "achieved_kbps_per_stream": r_dev["au_bytes"] * 8 / (r_dev["frames"] / FPS) / 1e3, "last_qp": r_dev["qps"],
             "mb_per_frame": {k: round(r_dev["n_" + k] / max(r_dev["frames"], 1), 1) for k in ("skip", "inter", "intra", "intra_analysed", "skip_probed")},
