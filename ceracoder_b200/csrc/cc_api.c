@@ -197,7 +197,9 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (p->width < 16 || p->height < 16 || (p->width & 1) || (p->height & 1) || p->width > 8192 || p->height > 8192) return CC_ERR_PARAM;
     if (p->format < CC_FMT_I420 || p->format > CC_FMT_BGRX) return CC_ERR_PARAM;
     if (p->fps_n <= 0 || p->fps_d <= 0) return CC_ERR_PARAM;
-    if (p->rows_per_slice < 0 || p->rows_per_slice > 8) return CC_ERR_PARAM; /* one warp per MB row, at most 8 rows (256 threads) per slice CTA */
+    /* one warp per macroblock row, at most 8 rows (256 threads) per CTA: slices of 1..8 rows are one CTA; taller slices are whole
+     * bands of 8 rows (a multiple of 8) or the whole picture (anything >= its macroblock rows) */
+    if (p->rows_per_slice < 0 || (p->rows_per_slice > 8 && p->rows_per_slice % 8 != 0 && p->rows_per_slice < (p->height + 15) / 16)) return CC_ERR_PARAM;
     { /* the SPS must be able to name a level that covers the stream: nothing beyond level 5.2 (Table A-1: 36 864 macroblocks per
        * picture, 2 073 600 per second — 2160p60 fits, 8192 x 8192 does not) */
         const long fs = (long)((p->width + 15) / 16) * ((p->height + 15) / 16);
@@ -224,7 +226,9 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     cc_kparams *k = &e->k;
     k->w = p->width; k->h = p->height;
     k->mb_w = (p->width + 15) / 16; k->mb_h = (p->height + 15) / 16;
+    if (e->p.rows_per_slice > k->mb_h) e->p.rows_per_slice = k->mb_h > 8 ? (k->mb_h + 7) / 8 * 8 : k->mb_h; /* one slice */
     k->W = k->mb_w * 16; k->H = k->mb_h * 16; k->rps = e->p.rows_per_slice;
+    k->band = k->rps < 8 ? k->rps : 8;
     k->sy = (int)roundup((size_t)k->W + 2 * CC_PAD, 128);
     k->sc = (int)roundup((size_t)k->W / 2 + 2 * CC_PADC, 64);
     e->seq.w = k->w; e->seq.h = k->h; e->seq.mb_w = k->mb_w; e->seq.mb_h = k->mb_h; e->seq.fps_n = p->fps_n; e->seq.fps_d = p->fps_d;
@@ -266,6 +270,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->ubot[2], (size_t)k->mb_h * k->sc);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->uright, (size_t)nmb * 32);
     if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->rowhdr, sizeof(cc_rowhdr) * k->mb_h);
+    if (rc == CC_OK) rc = dev_alloc(e, (void **)&k->gprog, sizeof(uint32_t) * 3 * k->mb_h);
+    if (rc == CC_OK) cudaMemset(k->gprog, 0, sizeof(uint32_t) * 3 * k->mb_h);
     k->dev_entropy = !e->p.host_entropy;
     const int n_slices_open = (k->mb_h + k->rps - 1) / k->rps;
     if (k->dev_entropy) {
@@ -429,6 +435,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (qp > 51) qp = 51;
     k->qp = qp; k->is_idr = is_idr;
     k->frame_num = e->frame_num; k->idr_pic_id = e->idr_pic_id;
+    k->frame_seq = (k->frame_seq + 1) & 0xfffff; if (!k->frame_seq) k->frame_seq = 1;
     set_quant(k);
     e->cur_is_idr = is_idr; e->cur_qp = qp; e->cur_pts = in->pts;
 

@@ -104,7 +104,8 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
  * of the slice's CTA as independent wavefronts — in one warp their different code paths would be serialised).
  * L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
 template <int PL>
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T) {
+/* xband: the row above was filtered by another CTA (a slice taller than a band): its pixels are read past the L1 */
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T, bool xband) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
@@ -128,13 +129,15 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
 #pragma unroll
         for (int it = 0; it < 4; it++) {
             const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
-            ly[it] = idx < 100 ? *(const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw) : 0u;
+            const uint32_t *src = (const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw);
+            ly[it] = idx < 100 ? ((xband && r < 4) ? __ldcg(src) : *src) : 0u;
         }
     } else {
 #pragma unroll
         for (int it = 0; it < 3; it++) {
             const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
-            lc[it] = idx < 72 ? *(const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw) : 0u;
+            const uint32_t *src = (const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw);
+            lc[it] = idx < 72 ? ((xband && r < 4) ? __ldcg(src) : *src) : 0u;
         }
     }
     const uint32_t q0 = nq.x;

@@ -90,7 +90,10 @@ typedef struct {
 typedef struct {
     int w, h;          /* display size */
     int W, H;          /* coded size (multiples of 16) */
-    int mb_w, mb_h, rps;
+    int mb_w, mb_h, rps; /* rps: macroblock rows per slice */
+    int band;            /* macroblock rows per CTA of the wavefront kernels: min(rps, 8); a taller slice spans several bands */
+    int frame_seq;       /* frame counter (from 1): tag of the cross-band progress words */
+    uint32_t *gprog;     /* [3][mb_h] progress words (tag << 12 | macroblocks done) of k_mb_encode, the luma filter, the chroma filter */
     int sy, sc;        /* pitches: luma-sized planes, chroma-sized planes (also half-res luma) */
     uint8_t *cur[3];   /* origins (pixel 0,0) */
     uint8_t *rec[3];   /* reconstruction being written */

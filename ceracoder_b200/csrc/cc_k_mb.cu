@@ -2,9 +2,12 @@
  * cc_k_mb.cu — macroblock analysis, mode decision, transform/quant/reconstruction and in-loop deblocking
  * (SURVEY.md §8a rows K4, K5, K6, K7, K8).
  *
- * Execution model.  A slice is a band of `rps` macroblock rows and shares nothing with other slices
- * (intra/MV prediction stop at slice edges; deblocking uses disable_deblocking_filter_idc=2), so
- * one CTA = one slice, one warp = one macroblock row.  Rows of a slice advance as a wavefront with a
+ * Execution model.  A slice is a run of `rps` macroblock rows and shares nothing with other slices
+ * (intra/MV prediction stop at slice edges; deblocking uses disable_deblocking_filter_idc=2).  One CTA = one BAND of up to 8
+ * rows, one warp = one macroblock row; a slice of up to 8 rows is one band, a taller slice (rps a multiple of 8, or the whole
+ * picture) is several bands whose wavefronts chain through frame-tagged progress words and the per-macroblock records in global
+ * memory (the band below spins on the last row of the band above; CTAs of a launch are dispatched in index order, so the band it
+ * waits for is already running).  Rows of a slice advance as a wavefront with a
  * 2-MB lag (top-right neighbour), synchronised through shared-memory progress counters — all waiting is
  * inside a CTA, whose warps are co-resident by construction.  After a CTA-wide barrier the same warps
  * run the deblocking filter over the slice in the same wavefront order (the filter is normatively
@@ -347,7 +350,7 @@ __device__ __forceinline__ int analyse_i4(const cc_kparams &k, const MbCtx &c, i
         int v = 255;
         if (top ? c.T : c.L) {
             const cc_mbdev *n = k.mbd + c.mb - (top ? k.mb_w : 1);
-            v = n->type == CC_MB_I4 ? n->i4_mode[c_blk_of[top ? 12 + i : i * 4 + 3]] : 2;
+            v = __ldcg(&n->type) == CC_MB_I4 ? __ldcg(&n->i4_mode[c_blk_of[top ? 12 + i : i * 4 + 3]]) : 2;
         }
         m->nbm[lane] = (uint8_t)v;
     }
@@ -668,6 +671,21 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
     __threadfence_block();
 }
 
+/* the same across CTAs: *flag is a frame-tagged progress word in global memory (tag + macroblocks done); returns the count */
+__device__ __forceinline__ int wait_progress_global(const uint32_t *flag, uint32_t tag, int need, int lane) {
+    uint32_t v = 0;
+    if (lane == 0) {
+        for (;;) {
+            v = *(const volatile uint32_t *)flag;
+            if ((int)(v - (tag + (uint32_t)need)) >= 0) break;
+            CC_SPIN_PAUSE();
+        }
+    }
+    v = __shfl_sync(FULL, v, 0);
+    __threadfence();
+    return (int)(v - tag);
+}
+
 /* does the macroblock coded at (mvx,mvy) leave nothing after quantisation + decimation?  (P_Skip test) */
 /* One pass: lanes 0-15 take the luma blocks, lanes 16-23 the chroma blocks (same arithmetic as inter_luma / encode_chroma in
  * probe mode; the two only differ in quantiser tables, the DC handling of chroma and the decimation rule). */
@@ -840,25 +858,29 @@ __device__ __forceinline__ void stage_neighbours(const cc_kparams &k, const MbCt
     if (lane < 21) { /* top-left, top, top-right */
         const int x = lane - 1;
         const bool ok = c.T && (x < 0 ? c.L : (x < 16 ? true : c.TR));
-        m->tile[0][3 + lane] = ok ? k.ubot[0][(size_t)(c.mby - 1) * k.sy + c.px + x] : 0;
+        m->tile[0][3 + lane] = ok ? __ldcg(k.ubot[0] + (size_t)(c.mby - 1) * k.sy + c.px + x) : 0; /* .cg: the row above may be another CTA's */
     }
     if (lane >= 16) m->tile[1 + lane - 16][3] = c.L ? ur[lane - 16] : 0;
     if (lane < 18) {
         const int p2 = lane >= 9, i = lane - 9 * p2; /* i = 0: top-left, 1..8: top */
         const bool ok = i == 0 ? (c.T && c.L) : c.T;
-        m->edgeC[p2][i] = ok ? k.ubot[1 + p2][(size_t)(c.mby - 1) * k.sc + c.mbx * 8 + i - 1] : 0;
+        m->edgeC[p2][i] = ok ? __ldcg(k.ubot[1 + p2] + (size_t)(c.mby - 1) * k.sc + c.mbx * 8 + i - 1) : 0;
     }
     if (lane < 16) m->edgeC[lane >> 3][9 + (lane & 7)] = c.L ? ur[16 + lane] : 0;
 }
 
-__device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volatile int *progress, int w, int row, int row0, int lane) {
+/* srow0: first row of the slice; last: this is the band's last row and the slice goes on below it (another CTA follows this row) */
+__device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volatile int *progress, int w, int row, int srow0, bool last, int lane) {
     const int mw = k.mb_w, qp = k.qp;
     MbCtx c;
     c.lane = lane; c.mby = row; c.py = row * 16; c.qp = qp; c.qpc = c_chroma_qp[qp]; c.lambda = c_lambda[qp]; c.m = m;
-    c.T = row > row0;
+    c.T = row > srow0;
     unsigned total = 0, n_skip = 0, n_inter = 0, n_intra = 0, n_gate = 0, n_probe = 0;
-    NbRec *nbl = nbline + w * mw;
-    const NbRec *nbu = nbl - mw;
+    NbRec *nbl = nbline + (w + 1) * mw; /* line 0 = the row above the band */
+    NbRec *nbu = nbl - mw;
+    const bool xband = c.T && w == 0;   /* the row above belongs to the band above */
+    const uint32_t tag = (uint32_t)k.frame_seq << 12;
+    int up_loaded = 0;                  /* records of the row above copied into line 0 so far */
     /* Software pipeline: everything a macroblock needs from global memory that does not depend on its neighbours is requested
      * three macroblocks ahead of its turn by cp.async into shared-memory rings (no register waits on it until it is read), so the
      * latency (HBM when 8 streams share the L2) overlaps earlier macroblocks' work instead of heading the serial chain: the
@@ -915,7 +937,13 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             m->curY[lane] = slot[lane]; m->curY[lane + 32] = slot[lane + 32]; m->curC[lane >> 4][lane & 15] = slot[64 + lane];
         }
         const long long t0 = k.cyc ? clock64() : 0;
-        if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
+        if (xband) { /* the band above: its progress word, then the records it published since */
+            const int have = min(wait_progress_global(k.gprog + row - 1, tag, min(mbx + 2, mw), lane), mw);
+            const uint32_t *src = k.nbrec + (size_t)(row - 1) * mw * 5;
+            for (int i = up_loaded * 5 + lane; i < have * 5; i += 32) ((uint32_t *)nbu)[i] = __ldcg(src + i);
+            up_loaded = have;
+            __syncwarp();
+        } else if (c.T) wait_progress(progress + w - 1, min(mbx + 2, mw), lane);
         const long long t1 = k.cyc ? clock64() : 0;
         int path = 0; /* 0 fast, 1 skip probe, 2 intra analysis */
 
@@ -1078,7 +1106,10 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
         __syncwarp();
-        __threadfence_block();
+        if (last) { /* the band below reads what this row published (records, unfiltered lines) from global memory */
+            __threadfence();
+            if (lane == 0) *(volatile uint32_t *)(k.gprog + row) = tag + (uint32_t)(mbx + 1);
+        } else __threadfence_block();
         if (lane == 0) progress[w] = mbx + 1;
         if (k.cyc && lane == 0) {
             const long long t2 = clock64();
@@ -1203,44 +1234,56 @@ template <int RPS> /* RPS = most rows per slice this instance serves: 4 (256 thr
 __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
     __shared__ WarpMem wm[RPS];
     __shared__ volatile int progress[RPS];
-    CC_DYN_SMEM(dsm); /* rps lines of mb_w neighbour records (NbRec) */
+    CC_DYN_SMEM(dsm); /* band + 1 lines of mb_w neighbour records (NbRec): the row above the band, then the band's rows */
     NbRec *nbline = (NbRec *)dsm;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int row0 = blockIdx.x * k.rps, row = row0 + w;
+    const int row0 = blockIdx.x * k.band, row = row0 + w;
     if (lane == 0) progress[w] = 0;
     __syncthreads();
     if (row >= k.mb_h) return;
-    encode_row(k, &wm[w], nbline, progress, w, row, row0, lane);
+    const int srow0 = (row / k.rps) * k.rps, send = min(srow0 + k.rps, k.mb_h);
+    encode_row(k, &wm[w], nbline, progress, w, row, srow0, w == k.band - 1 && row + 1 < send, lane);
 }
 
-/* In-loop filter: CTA = one slice; per macroblock row one luma warp and one chroma warp, each 2 macroblocks behind the warp of
- * the same kind in the row above (H.264 8.7 is raster-ordered; luma and chroma are independent wavefronts).  The neighbour
- * records the encode kernel left in global memory are staged into shared memory first. */
+/* In-loop filter: CTA = one band of a slice (the same bands as k_mb_encode); per macroblock row one luma warp and one chroma warp,
+ * each 2 macroblocks behind the warp of the same kind in the row above (H.264 8.7 is raster-ordered; luma and chroma are
+ * independent wavefronts).  The neighbour records the encode kernel left in global memory are staged into shared memory first
+ * (line 0 = the row above the band).  A band whose slice started further up chains to the band above through frame-tagged
+ * progress words, and reads the pixels that band filtered past the L1 (deblock_mb's xband). */
 __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress2[2][MB_MAX_RPS];
     CC_DYN_SMEM(dsm);
     NbRec *nbline = (NbRec *)dsm;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int pl = wid >= k.rps, w = pl ? wid - k.rps : wid; /* warps [0, rps): luma rows, [rps, 2 rps): chroma rows */
-    const int row0 = blockIdx.x * k.rps, row = row0 + w;
-    const int rows = min(k.rps, k.mb_h - row0);
+    const int pl = wid >= k.band, w = pl ? wid - k.band : wid; /* warps [0, band): luma rows, [band, 2 band): chroma rows */
+    const int row0 = blockIdx.x * k.band, row = row0 + w;
+    const int rows = min(k.band, k.mb_h - row0);
+    const int srow0 = (row0 / k.rps) * k.rps, send = min(srow0 + k.rps, k.mb_h);
     {
-        const uint32_t *src = (const uint32_t *)k.nbrec + (size_t)row0 * k.mb_w * 5;
-        uint32_t *dst = (uint32_t *)nbline;
-        for (int i = threadIdx.x; i < rows * k.mb_w * 5; i += blockDim.x) dst[i] = src[i];
+        const int above = row0 > srow0; /* the slice started further up: stage the last row of the band above as well */
+        const uint32_t *src = (const uint32_t *)k.nbrec + (size_t)(row0 - above) * k.mb_w * 5;
+        uint32_t *dst = (uint32_t *)(nbline + (1 - above) * k.mb_w);
+        for (int i = threadIdx.x; i < (rows + above) * k.mb_w * 5; i += blockDim.x) dst[i] = src[i];
     }
     if (lane == 0) progress2[pl][w] = 0;
     __syncthreads();
     if (row >= k.mb_h) return;
     volatile int *prog = progress2[pl];
+    const bool T = row > srow0, xband = T && w == 0, last = w == k.band - 1 && row + 1 < send;
+    const uint32_t tag = (uint32_t)k.frame_seq << 12;
+    uint32_t *gp = k.gprog + (size_t)(1 + pl) * k.mb_h; /* [0]: k_mb_encode's, [1]: luma filter, [2]: chroma filter */
     for (int mbx = 0; mbx < k.mb_w; mbx++) {
         const long long t1 = k.cyc ? clock64() : 0;
-        if (w > 0) wait_progress(prog + w - 1, min(mbx + 2, k.mb_w), lane);
+        if (xband) wait_progress_global(gp + row - 1, tag, min(mbx + 2, k.mb_w), lane);
+        else if (T) wait_progress(prog + w - 1, min(mbx + 2, k.mb_w), lane);
         const long long t2 = k.cyc ? clock64() : 0;
-        if (pl) deblock_mb<1>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
-        else deblock_mb<0>(k, &dbm[w], nbline + w * k.mb_w, lane, mbx, row, mbx > 0, w > 0);
-        __threadfence_block();
+        if (pl) deblock_mb<1>(k, &dbm[w], nbline + (w + 1) * k.mb_w, lane, mbx, row, mbx > 0, T, xband);
+        else deblock_mb<0>(k, &dbm[w], nbline + (w + 1) * k.mb_w, lane, mbx, row, mbx > 0, T, xband);
+        if (last) {
+            __threadfence();
+            if (lane == 0) *(volatile uint32_t *)(gp + row) = tag + (uint32_t)(mbx + 1);
+        } else __threadfence_block();
         if (lane == 0) prog[w] = mbx + 1;
         if (k.cyc && lane == 0 && !pl) {
             unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N + 8;
@@ -1303,8 +1346,8 @@ __global__ void k_pack(cc_kparams k) {
 }
 
 extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
-    const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
+    const int ns = (k->mb_h + k->band - 1) / k->band; /* bands */
+    size_t dyn = (size_t)(k->band + 1) * k->mb_w * sizeof(NbRec);
 #ifndef CC_EMU_BUILD
     { /* experiment knob: pad the request so fewer foreign CTAs share the SM with a wavefront CTA (CC_WAVEFRONT_SMEM_KB) */
         static int pad_kb = -1;
@@ -1315,22 +1358,22 @@ extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     /* static + dynamic shared memory passes the default 48 KB limit for wide pictures / tall slices: opt in to what this launch needs
      * (per device; cheap).  The request counts against 227 KB together with the kernel's static shared memory. */
     if (dyn > 8 * 1024) {
-        cudaError_t er = k->rps <= 4 ? cudaFuncSetAttribute(k_mb_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)
+        cudaError_t er = k->band <= 4 ? cudaFuncSetAttribute(k_mb_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)
                                      : cudaFuncSetAttribute(k_mb_encode<MB_MAX_RPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
         (void)er; /* a failure shows as a launch error below */
     }
 #endif
-    if (k->rps <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
-    else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->rps * 32), dyn, st, *k);
+    if (k->band <= 4) CC_LAUNCH_SMEM(k_mb_encode<4>, dim3((unsigned)ns), dim3((unsigned)k->band * 32), dyn, st, *k);
+    else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->band * 32), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
-    const int ns = (k->mb_h + k->rps - 1) / k->rps;
-    const size_t dyn = (size_t)k->rps * k->mb_w * sizeof(NbRec);
+    const int ns = (k->mb_h + k->band - 1) / k->band;
+    const size_t dyn = (size_t)(k->band + 1) * k->mb_w * sizeof(NbRec);
 #ifndef CC_EMU_BUILD
     if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
 #endif
-    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->rps * 64), dyn, st, *k);
+    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->band * 64), dyn, st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

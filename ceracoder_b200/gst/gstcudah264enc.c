@@ -250,7 +250,7 @@ static void gst_cuda_h264_enc_class_init(GstCudaH264EncClass *klass) {
     g_object_class_install_property(oc, PROP_BYTE_STREAM, g_param_spec_boolean("byte-stream", "Byte stream", "Always Annex-B byte-stream", TRUE, rw));
     g_object_class_install_property(oc, PROP_THREADS, g_param_spec_uint("threads", "Threads", "Host threads packaging the slices of one access unit (0 = the streaming thread alone)", 0, 1024, 0, rw));
     g_object_class_install_property(oc, PROP_DEVICE, g_param_spec_int("device", "CUDA device", "CUDA device ordinal", 0, 63, 0, rw));
-    g_object_class_install_property(oc, PROP_ROWS_PER_SLICE, g_param_spec_uint("rows-per-slice", "MB rows per slice", "Macroblock rows per slice (0 = 8)", 0, 8, 0, rw));
+    g_object_class_install_property(oc, PROP_ROWS_PER_SLICE, g_param_spec_uint("rows-per-slice", "MB rows per slice", "Macroblock rows per slice: 1..8, a multiple of 8, or >= the picture height in macroblocks for one slice per picture (0 = 8)", 0, 1024, 0, rw));
     gst_element_class_set_static_metadata(ec, "CUDA H.264 encoder (ceracuda)", "Codec/Encoder/Video/Hardware",
                                           "H.264 encoder on sm_100a CUDA kernels; drop-in for x264enc in ceracoder pipelines", "ceracuda");
     gst_element_class_add_static_pad_template(ec, &sink_tmpl);

@@ -52,10 +52,12 @@ typedef struct {
     int format;          /* CC_FMT_* of the frames handed to cc_enc_encode */
     int bitrate_bps;     /* initial target bitrate (ceracoder writes max_bitrate before PLAYING, src/ceracoder.c:515-518) */
     int key_int_max;     /* IDR period in frames; 60 in every reference pipeline file; 0 -> 60 */
-    int rows_per_slice;  /* macroblock rows per slice, 1..8; 0 -> 8 (nine slices per 1080p picture).  A slice is one CTA of the wavefront kernel
-                          * and one independent unit of prediction: P_Skip cannot carry motion in a slice's first row (8.4.1.1), so fewer,
-                          * taller slices cost fewer bits — measured on S2 1080p: 8 rows -8.7 %, 2 rows +13 %, 1 row +34 % against 4 rows
-                          * at equal Y-PSNR (profiles/rd_slices_r02.txt) */
+    int rows_per_slice;  /* macroblock rows per slice: 1..8, a multiple of 8, or anything >= the picture's macroblock rows (one slice per
+                          * picture); 0 -> 8 (nine slices per 1080p picture).  A slice is an independent unit of prediction: P_Skip cannot
+                          * carry motion in a slice's first row (8.4.1.1), so fewer, taller slices cost fewer bits — measured on S2 1080p:
+                          * 8 rows -8.7 %, 2 rows +13 %, 1 row +34 % against 4 rows at equal Y-PSNR, one slice per picture another -15 %
+                          * (profiles/rd_slices_r02.txt) — and more time: the macroblock wavefront of a slice is mb_w + 2 (rows - 1) steps long.
+                          * Up to 8 rows a slice is one CTA of the wavefront kernels; taller slices chain 8-row bands across CTAs */
     int qp_fixed;        /* > 0: constant-QP mode (rate control off); used by parity tests */
     int qp_min, qp_max;  /* 0 -> 10 / 51 */
     int partitions;      /* 1: the motion search may split a macroblock into four 8x8 partitions (P_8x8); cc_enc_params_default sets 1 */

@@ -164,3 +164,15 @@ def test_rate_controlled_stream_replayed_by_the_oracle(lib):
     aus, trace = run_rc_parity(lib, PanSprites(w, h, cut_every=11), w, h, 30, 26, lambda i: 900 if i < 9 else 300, gop=12, rps=3, recon_every=5)
     assert [i for i, t in enumerate(trace) if t[0]] == [0, 12, 24]
     assert len({t[1] for t in trace}) > 3
+
+
+@pytest.mark.parametrize("w,h,rps,qps", [
+    (64, 320, 16, [28, 30, 26, 34]),      # 20 rows: a two-band slice of 16 rows + a slice of 4
+    (96, 400, 24, [30, 27, 33]),          # 25 rows: three bands + one row
+    (80, 272, 100, [26, 29, 31, 24]),     # one slice per picture (17 rows: 8 + 8 + 1)
+    (48, 144, 9, [30, 28]),               # rps >= picture rows, 9 rows: 8 + 1
+])
+def test_slices_taller_than_a_band(lib, w, h, rps, qps):
+    """rows_per_slice > 8: the slice's wavefront chains 8-row bands across CTAs (frame-tagged progress words, neighbour records and
+    unfiltered lines through global memory) in the encode and the filter kernel; bytes and reconstruction stay the oracle's"""
+    run_parity(lib, "pan", w, h, qps, rps=rps, gop=60)

@@ -152,3 +152,42 @@ def test_device_entropy_equals_host_entropy_at_full_size(lib):
             assert a.encode(y, u, v) == b.encode(y, u, v), f"{w}x{h} frame {i}"
             assert a.last.qp == b.last.qp
         a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,rps,qps", [
+    (64, 320, 16, [28, 30, 26, 34]),
+    (96, 400, 24, [30, 27, 33]),
+    (80, 272, 100, [26, 29, 31, 24]),
+    (640, 368, 16, [27, 30, 33, 24, 29]),
+    (1920, 1080, 68, [28, 30, 32]),       # one slice per 1080p picture: nine bands chained across CTAs
+    (1920, 1080, 32, [30, 26]),
+])
+def test_slices_taller_than_a_band(lib, w, h, rps, qps):
+    """rows_per_slice > 8 on the B200: bands of a slice run as concurrent CTAs that wait on one another through global memory —
+    the case the sequential CPU emulation cannot show.  Bytes, reconstruction (after the cross-band in-loop filter) and decoder
+    output are the oracle's."""
+    run_parity(lib, "pan", w, h, qps, rps=rps, gop=60)
+
+
+@pytest.mark.gpu
+def test_one_slice_per_picture_under_rate_control_many_frames(lib):
+    """60 rate-controlled 1080p frames with one slice per picture, eight streams at once (so the bands' CTAs share the GPU with other
+    streams' kernels): identical to a solo run"""
+    import threading
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    w, h, n = 1920, 1080, 24
+    src = make_source("pan", w, h)
+    frames = [src.frame(i) for i in range(8)]
+
+    def run(out, k):
+        e = CudaH264Enc(w, h, fps=(60, 1), lib=lib, bitrate=4000 + 2000 * (k % 2), key_int_max=7, rows_per_slice=68)
+        out[k] = [e.encode(*frames[i % 8]) for i in range(n)]
+        e.close()
+    res, solo = {}, {}
+    ths = [threading.Thread(target=run, args=(res, k)) for k in range(8)]
+    [t.start() for t in ths]; [t.join() for t in ths]
+    run(solo, 0); run(solo, 1)
+    for k in range(8):
+        assert res[k] == solo[k % 2], f"stream {k} differs from its solo run"

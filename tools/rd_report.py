@@ -20,6 +20,10 @@ CONFIGS = [("rps4_part (default)", dict(rows_per_slice=4, partitions=True)),
            ("rps1_part", dict(rows_per_slice=1, partitions=True)),
            ("rps2_part", dict(rows_per_slice=2, partitions=True)),
            ("rps8_part", dict(rows_per_slice=8, partitions=True)),
+           ("rps16_part", dict(rows_per_slice=16, partitions=True)),
+           ("rps24_part", dict(rows_per_slice=24, partitions=True)),
+           ("rps32_part", dict(rows_per_slice=32, partitions=True)),
+           ("one_slice_part", dict(rows_per_slice=68, partitions=True)),
            ("rps4_16x16only", dict(rows_per_slice=4, partitions=False))]
 
 
