@@ -341,6 +341,8 @@ void cc_enc_close(cc_enc *e) {
                     s[11] * f, s[12] * f, s[13] * f, s[14] * f, s[15] * f);
             fprintf(stderr, "ceracuda wavefront detail, per MB row per frame: between macroblocks (record / pixel prefetch) %.0f cycles; P_Skip reconstructed in the wavefront: %.1f MBs, %.0f cycles (%.1f of them predicted here); parked P_L0_16x16 pixels restored %.1f; Intra4x4 analyses started %.1f\n",
                     s[16] * f, s[18] * f, s[17] * f, s[19] * f, s[21] * f, s[20] * f);
+            fprintf(stderr, "ceracuda P_Skip predicted in the wavefront without a probe, per MB row per frame: at the search vector (speculation lost) %.1f, at the zero vector %.1f (%.1f of them with the candidate probe also passing), other %.1f\n",
+                    s[22] * f, s[23] * f, s[25] * f, s[24] * f);
         }
         free(h);
     }

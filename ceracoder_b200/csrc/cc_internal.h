@@ -64,7 +64,8 @@ typedef struct {
 typedef struct CC_ALIGN16 {
     uint8_t cbp;        /* luma 8x8 bits | chroma << 4, coded at me.mv */
     uint8_t skip_ok;    /* bit 0: nothing survives at cand[] ; bit 1: nothing survives at (0,0) ; bit 2: k.rec holds the prediction at cand[]
-                         * and the P_L0_16x16 reconstruction is parked in k.park (the pre-pass expects P_Skip at cand) */
+                         * and the P_L0_16x16 reconstruction is parked in k.park (the pre-pass expects P_Skip at cand) ; bit 3: the same
+                         * with the prediction at (0,0) (never together with bit 2) */
     uint16_t nz_luma;
     int16_t cand[2];    /* P_Skip vector predicted from the neighbours' search vectors */
     uint16_t sym_len;   /* int16 units used in the MB's symbol slot */

@@ -966,10 +966,10 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             if (zero) {
                 type = CC_MB_PSKIP; mvx = skipmv[0]; mvy = skipmv[1];
                 /* The reconstruction is the prediction at the skip vector.  k.rec already holds it when the pre-pass published the
-                 * prediction at its candidate and that is the vector (pre.skip_ok bit 2), or when the vector is the search vector
+                 * prediction at its candidate (pre.skip_ok bit 2) or at the zero vector (bit 3) and that is the vector, or when the vector is the search vector
                  * of an unsplit macroblock that coded to nothing there. */
-                const bool spec = (pre.skip_ok & 4) != 0;
-                const bool in_place = spec ? (mvx == pre.cand[0] && mvy == pre.cand[1]) : (!part && mvx == me.mv[0] && mvy == me.mv[1]);
+                const bool spec = (pre.skip_ok & 4) != 0, spec0 = (pre.skip_ok & 8) != 0;
+                const bool in_place = spec0 ? (mvx | mvy) == 0 : (spec ? (mvx == pre.cand[0] && mvy == pre.cand[1]) : (!part && mvx == me.mv[0] && mvy == me.mv[1]));
                 if (!in_place) {
                     const long long ts = k.cyc ? clock64() : 0;
                     if (!pred_ready) {
@@ -984,6 +984,8 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                     if (k.cyc && lane == 0) {
                         unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                         cy[17] += (unsigned long long)(clock64() - ts); cy[18] += 1; cy[19] += pred_ready ? 0 : 1;
+                        if (!pred_ready) cy[(!part && mvx == me.mv[0] && mvy == me.mv[1]) ? 22 : ((mvx | mvy) == 0 ? 23 : 24)] += 1;
+                        if (!pred_ready && (mvx | mvy) == 0 && (pre.skip_ok & 1)) cy[25] += 1;
                     }
                 }
                 done = true;
@@ -1023,7 +1025,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             else type = cost_i16 <= cost_i4 ? CC_MB_I16 : CC_MB_I4;
 
             if (type == CC_MB_P16) { /* already coded by the pre-pass: levels in the slot, pixels in k.rec — or parked beside it */
-                if (pre.skip_ok & 4) {
+                if (pre.skip_ok & 12) {
                     const uint32_t *park = (const uint32_t *)(k.park + (size_t)c.mb * 384);
                     m->recY[lane] = park[lane]; m->recY[lane + 32] = park[lane + 32]; m->recC[lane >> 4][lane & 15] = park[64 + lane];
                     __syncwarp();
@@ -1201,13 +1203,23 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
      * the search vector anyway), the pre-pass therefore publishes THAT prediction — it sits in predY / predC (in every branch
      * above that sets bit 0 for such a macroblock, the last prediction made is the one at cand) — and parks the P_L0_16x16
      * reconstruction in a side buffer.  The wavefront then has nothing to move for the common outcome (P_Skip at cand) and
-     * restores the parked pixels in the rare other ones. */
-    if ((ok & 1) && !c_is_me) {
-        ok |= 4;
+     * restores the parked pixels in the rare other ones.
+     * Which of the two, when both probes pass: the zero vector.  8.4.1.1 forces the skip vector to zero next to a neighbour that
+     * does not move, so one macroblock skipped at zero (every first macroblock of a slice row is, if at all) hands the zero vector on
+     * to its right and lower neighbours for as long as their zero probe passes — at the coarse quantisers of a rate-starved stream
+     * that is most of the picture (measured on the bench workload: 52 of 67 in-wavefront P_Skip reconstructions per macroblock row
+     * were at the zero vector, 48 of them with the candidate's prediction published in vain). */
+    const bool pub0 = (ok & 2) && !z_is_me && !z_is_c, two = !c_is_me && !z_is_me && !z_is_c;
+    if (pub0 || ((ok & 1) && !c_is_me)) {
+        ok |= pub0 ? 8 : 4;
         uint32_t *park = (uint32_t *)(k.park + (size_t)mb * 384);
         park[lane] = m->recY[lane]; park[lane + 32] = m->recY[lane + 32]; park[64 + lane] = m->recC[lane >> 4][lane & 15];
-        m->recY[lane] = m->predY[lane]; m->recY[lane + 32] = m->predY[lane + 32];
-        m->recC[lane >> 4][lane & 15] = m->predC[lane >> 4][lane & 15];
+        /* the prediction at zero: B of probe_zero2 (in the Intra4x4 level scratch) when both probes ran as a pair, else the last
+         * prediction made (pub0 without the pair means the candidate is the search vector, and the zero probe ran last) */
+        const uint32_t *sY = (pub0 && two) ? (const uint32_t *)m->c4 : m->predY;
+        const uint32_t *sC = (pub0 && two) ? (const uint32_t *)m->c4 + 64 : &m->predC[0][0];
+        m->recY[lane] = sY[lane]; m->recY[lane + 32] = sY[lane + 32];
+        m->recC[lane >> 4][lane & 15] = sC[lane];
         __syncwarp();
     }
     publish_pixels(k, c);
@@ -1250,7 +1262,10 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
  * independent wavefronts).  The neighbour records the encode kernel left in global memory are staged into shared memory first
  * (line 0 = the row above the band).  A band whose slice started further up chains to the band above through frame-tagged
  * progress words, and reads the pixels that band filtered past the L1 (deblock_mb's xband). */
-__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32) k_deblock(cc_kparams k) {
+#ifndef CC_DB_MINBLOCKS
+#define CC_DB_MINBLOCKS 1
+#endif
+__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress2[2][MB_MAX_RPS];
     CC_DYN_SMEM(dsm);
