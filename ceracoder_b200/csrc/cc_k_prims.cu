@@ -11,6 +11,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <pthread.h>
 
 extern "C" void cc_quant_tables(int qp, int intra, uint16_t mf[3], uint16_t bias[3]);
 extern "C" void cc_quant8_tables(int qp, uint16_t mf[6], uint16_t bias[6]);
@@ -261,4 +262,56 @@ extern "C" int cc_prim_mc_luma(const uint8_t *plane, int w, int h, const int16_t
     CC_LAUNCH(kp_mc, grid_for(n), dim3(128), 0, k, (const int16_t *)dxy.p, (const int16_t *)dmv.p, n, (uint8_t *)dout.p);
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) return CC_ERR_CUDA;
     return cudaMemcpy(out, dout.p, (size_t)n * 256, cudaMemcpyDeviceToHost) == cudaSuccess ? CC_OK : CC_ERR_CUDA;
+}
+
+/* ---- allocation-free variant (include/ceracuda.h cc_prim_satd16x16_noalloc) -----------------------------------------------
+ * For callers that must not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+ * the same kernel as cc_prim_satd16x16 (kp_satd), with the device staging of the two block arrays and of the results in a
+ * file-scope device array instead of three cudaMalloc'ed buffers.  Every GPU that loads the library holds the array
+ * (CC_NOALLOC_BYTES = 516 KiB) until the process exits.
+ * The array's NAME is only a host-side stand-in in host code, not a device address: its device address is asked for once per
+ * device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel gets.
+ * All calls share the array and it keeps the last call's contents.  Nothing in it has to start at zero: a call overwrites the
+ * 256 n bytes of each input region and the kernel writes all n results before they are read back.  Calls that overlap on one
+ * GPU (two host threads) would race on it: the entry point serialises them with a mutex and is synchronous. */
+#define CC_NOALLOC_BYTES ((size_t)CC_PRIM_NOALLOC_MAX_BLOCKS * (256 + 256 + 4))
+static __device__ __align__(256) uint8_t g_noalloc_scratch[CC_NOALLOC_BYTES];
+#define CC_NOALLOC_MAX_DEV 64
+static uint8_t *g_noalloc_ptr[CC_NOALLOC_MAX_DEV]; /* device address of g_noalloc_scratch on device i, once known */
+static pthread_mutex_t g_noalloc_mu = PTHREAD_MUTEX_INITIALIZER;
+
+extern "C" int cc_prim_satd16x16_noalloc(const uint8_t *a, const uint8_t *b, int n, int32_t *out) {
+    if (!a || !b || !out || n <= 0) return CC_ERR_PARAM;
+    if (n > CC_PRIM_NOALLOC_MAX_BLOCKS) {
+        fprintf(stderr, "ceracuda: cc_prim_satd16x16_noalloc: %d blocks exceed the fixed scratch of %d blocks (CC_PRIM_NOALLOC_MAX_BLOCKS); split the batch or use cc_prim_satd16x16\n",
+                n, CC_PRIM_NOALLOC_MAX_BLOCKS);
+        return CC_ERR_PARAM;
+    }
+    if (!have_device()) return CC_ERR_CUDA;
+    int dev = -1, rc = CC_OK;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= CC_NOALLOC_MAX_DEV) return CC_ERR_CUDA;
+    pthread_mutex_lock(&g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) { /* once per device, with that device current */
+        void *p = nullptr;
+        const cudaError_t er = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (er != cudaSuccess || !p) {
+            fprintf(stderr, "ceracuda: cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s\n", dev, cudaGetErrorString(er));
+            pthread_mutex_unlock(&g_noalloc_mu);
+            return CC_ERR_CUDA;
+        }
+        g_noalloc_ptr[dev] = (uint8_t *)p;
+    }
+    {
+        uint8_t *da = g_noalloc_ptr[dev], *db = da + (size_t)CC_PRIM_NOALLOC_MAX_BLOCKS * 256;
+        int32_t *dout = (int32_t *)(db + (size_t)CC_PRIM_NOALLOC_MAX_BLOCKS * 256);
+        PCHECK(cudaMemcpy(da, a, (size_t)n * 256, cudaMemcpyHostToDevice));
+        PCHECK(cudaMemcpy(db, b, (size_t)n * 256, cudaMemcpyHostToDevice));
+        CC_LAUNCH(kp_satd, grid_for(n), dim3(128), 0, (const uint8_t *)da, (const uint8_t *)db, 16, n, dout);
+        PCHECK(cudaGetLastError());
+        PCHECK(cudaDeviceSynchronize());
+        PCHECK(cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    }
+done:
+    pthread_mutex_unlock(&g_noalloc_mu);
+    return rc;
 }

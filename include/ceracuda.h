@@ -184,6 +184,17 @@ int cc_prim_pred4x4(const uint8_t *edge, int mode, int n, uint8_t *out);
 /* quarter-pel luma interpolation of n 16x16 blocks taken at (x,y)[i] + mv[i] from one w*h plane (borders replicated) */
 int cc_prim_mc_luma(const uint8_t *plane, int w, int h, const int16_t *xy, const int16_t *mv, int n, uint8_t *out);
 
+/* Allocation-free variant of cc_prim_satd16x16.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same inputs, same outputs, same kernel; the device staging lives in a fixed device array inside the library
+ * (516 bytes per block x CC_PRIM_NOALLOC_MAX_BLOCKS = 516 KiB, held by every GPU that loads the library until the process
+ * exits) instead of cudaMalloc'ed buffers, and the call makes no cudaMalloc / cudaFree / allocating library call.
+ * n > CC_PRIM_NOALLOC_MAX_BLOCKS is rejected with CC_ERR_PARAM (and a line on stderr).  All calls share the one array, which
+ * keeps the previous call's contents; calls that would overlap on a GPU race on it, so the entry point is synchronous and
+ * serialises concurrent callers with a mutex. */
+#define CC_PRIM_NOALLOC_MAX_BLOCKS 1024
+int cc_prim_satd16x16_noalloc(const uint8_t *a, const uint8_t *b, int n, int32_t *out);
+
 /* Integer-pipe peak of the device, measured: thread-level G-ops/s of a register-resident loop of independent
  * operations on every SM.  kind 0: VABSDIFF4.U8.ACC (4-pixel abs-diff-accumulate, the SAD searches' op), 1: IADD, 2: LOP3,
  * 3: IDP.4A (the SATD / DCT row dot products).  Used by bench.py for the integer roofline. */

@@ -44,6 +44,8 @@ enum cudaMemoryType { cudaMemoryTypeUnregistered = 0, cudaMemoryTypeHost = 1, cu
 struct cudaPointerAttributes { enum cudaMemoryType type; int device; void *devicePointer, *hostPointer; };
 /* the emulator cannot tell pinned from pageable memory: report pageable, so the staging copy of cc_enc_submit is exercised */
 static inline cudaError_t cudaPointerGetAttributes(struct cudaPointerAttributes *a, const void *p) { (void)p; a->type = cudaMemoryTypeUnregistered; a->device = 0; a->devicePointer = a->hostPointer = 0; return 0; }
+/* a "device" symbol of the emulation build is a host object */
+#define cudaGetSymbolAddress(pp, sym) (*(pp) = (void *)&(sym), 0)
 static inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t st) { (void)st; memset(d, v, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned f) { (void)f; *s = 0; return 0; }
