@@ -74,6 +74,7 @@ struct cc_enc {
     long staged_frames;
     unsigned long long tmaps[5 * 16] __attribute__((aligned(64))); /* five CUtensorMap (k_me_l0's sub-pel windows) */
     int debug_sync;
+    int dbg_dup, dbg_skip; /* CC_DBG_DUP / CC_DBG_SKIP: stage bit masks (1 << CC_STAGE_*) — launch a stage twice / not at all (marginal-cost experiments) */
     int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
     size_t bs_bytes;
 };
@@ -311,6 +312,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
     e->debug_sync = getenv("CC_DEBUG_SYNC") != NULL;
+    e->dbg_dup = getenv("CC_DBG_DUP") ? atoi(getenv("CC_DBG_DUP")) : 0;
+    e->dbg_skip = getenv("CC_DBG_SKIP") ? atoi(getenv("CC_DBG_SKIP")) : 0;
     { const char *v = getenv("CC_DBG_ME"); e->k.dbg = v ? atoi(v) : 0; }
     cc_rc_init(&e->rc, (double)p->fps_n / p->fps_d, e->p.bitrate_bps, e->p.qp_min, e->p.qp_max, e->p.key_int_max);
     cudaStreamSynchronize(e->st);
@@ -494,21 +497,24 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
                                            if (er_ != cudaSuccess) { fprintf(stderr, "ceracuda: device fault before stage %d of frame %d: %s\n", (int)(i), e->frame_idx, cudaGetErrorString(er_)); return CC_ERR_CUDA; } } \
                       if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
     for (int i = 0; i <= CC_N_STAGES + 1; i++) pev_used[i] = 0;
+#define DUP(i) (e->dbg_dup & (1 << (i)))
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);
+    if (DUP(CC_STAGE_INGEST)) cck_ingest(k, fmt, e->st);
     /* Upload, ingest and the coarse search touch the source planes and the half-resolution reference, which the coding kernels of the
      * previous frame wrote (unfiltered reconstruction): they run while that frame's tail is still filtering.  Everything after
      * them reads what the tail (in-loop filter, borders, half-pel planes — on st2) produces, or overwrites what it reads (the
      * neighbour records). */
     STAGE(CC_STAGE_ME_COARSE);
-    if (!is_idr) { e->launches += cck_l1border(k, e->st); e->launches += cck_me_l1(k, e->st); }
+    if (!is_idr) { e->launches += cck_l1border(k, e->st); e->launches += cck_me_l1(k, e->st); if (DUP(CC_STAGE_ME_COARSE)) cck_me_l1(k, e->st); }
     CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
     STAGE(CC_STAGE_ME_FINE);
-    if (!is_idr) e->launches += cck_me_l0(k, e->st);
+    if (!is_idr) { e->launches += cck_me_l0(k, e->st); if (DUP(CC_STAGE_ME_FINE)) cck_me_l0(k, e->st); }
     STAGE(CC_STAGE_P_CODE);
-    if (!is_idr) e->launches += cck_p_code(k, e->st);
+    if (!is_idr) { e->launches += cck_p_code(k, e->st); if (DUP(CC_STAGE_P_CODE)) cck_p_code(k, e->st); }
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
+    if (DUP(CC_STAGE_MB_ENCODE)) cck_encode(k, e->st);
     STAGE(CC_STAGE_PACK);
     CUCHECK(cudaEventRecord(e->ev_enc, e->st));
     e->launches += k->dev_entropy ? cck_cavlc(k, e->st) : cck_pack(k, e->st);
@@ -520,14 +526,16 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     CUCHECK(cudaStreamWaitEvent(e->st2, e->ev_enc, 0));
 #define STAGE2(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st2); pev_used[i] = 1; } } while (0)
     STAGE2(CC_STAGE_DEBLOCK);
-    e->launches += cck_deblock(k, e->st2);
+    if (!(e->dbg_skip & (1 << CC_STAGE_DEBLOCK))) e->launches += cck_deblock(k, e->st2);
     STAGE2(CC_STAGE_BORDER);
     e->launches += cck_border(k, e->st2);
     STAGE2(CC_STAGE_HPEL);
     e->launches += cck_hpel(k, e->st2);
+    if (DUP(CC_STAGE_HPEL)) cck_hpel(k, e->st2);
     STAGE2(CC_STAGE_L1REF); /* nothing left here: the half-resolution reference is written with the reconstruction */
     STAGE2(CC_N_STAGES);
 #undef STAGE2
+#undef DUP
     CUCHECK(cudaEventRecord(e->ev_tail, e->st2));
 #undef STAGE
     e->pevs_tail[e->pb] = e->profile;
