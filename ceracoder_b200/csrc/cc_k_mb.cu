@@ -1134,13 +1134,39 @@ __device__ __forceinline__ void search_mv(const cc_kparams &k, int n, int q, int
 }
 
 /* ---- P-frame pre-pass: every macroblock coded as P_L0_16x16 at its search vector, fully parallel ------------------------ */
-#define PC_WARPS 4
-__global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
+/* Warps (macroblocks) per CTA.  The kernel is 114 KB of straight-line code and a warp runs through ~50 KB of it per macroblock:
+ * with small CTAs the two dozen warps of an SM sit at unrelated places of it and instruction fetch, not data, is what they wait for
+ * (ncu, 4 warps per CTA: stall no_instruction 2.7 per issue, more than long_scoreboard) — and the fetches crowd the wavefront
+ * kernels' out of the SM's instruction caches as well.  Warps of one CTA start together and stay close: one CTA of 32 warps per SM
+ * (64 registers, 214 KB of shared memory) measured +11.6 % / +13.2 % frames/s at 8 / 16 streams over 4-warp CTAs
+ * (profiles/cta_size_r02.txt). */
+#ifndef PC_WARPS
+#define PC_WARPS 32
+#endif
+#ifndef PC_SYNC
+#define PC_SYNC 0
+#endif
+#if PC_SYNC
+#define PC_BAR() __syncthreads()
+#else
+#define PC_BAR() do { } while (0)
+#endif
+#ifndef PC_MINB
+#define PC_MINB 1
+#endif
+__global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k) {
+#if PC_WARPS > 6
+    CC_DYN_SMEM(pc_dsm);
+    WarpMem *wm = (WarpMem *)pc_dsm;
+    X8Mem *x8m = (X8Mem *)(wm + PC_WARPS);
+#else
     __shared__ WarpMem wm[PC_WARPS];
     __shared__ X8Mem x8m[PC_WARPS];
+#endif
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int mb = blockIdx.x * PC_WARPS + wid, mw = k.mb_w;
-    if (mb >= mw * k.mb_h) return;
+    const int mw = k.mb_w;
+    /* a warp past the last macroblock codes the last one again (same values to the same places): the CTA's warps meet at barriers */
+    const int mb = min((int)(blockIdx.x * PC_WARPS) + wid, mw * k.mb_h - 1);
     X8Mem *x8 = &x8m[wid];
     x8->zz[lane] = c_zigzag8[lane]; x8->zz[lane + 32] = c_zigzag8[lane + 32];
     MbCtx c;
@@ -1161,15 +1187,19 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
         mc_chroma8(k, c, mvx, mvy);
     }
     __syncwarp();
+    PC_BAR();
     unsigned nzmask;
     /* transform size [EXT: x264_mb_analyse_transform]: 8x8 when the residual's sa8d is below its 4x4 satd */
     int t8 = sa8d_mb(x8, m->curY, m->predY, lane) < satd4;
     int cbp = t8 ? inter_luma8(k, x8, m->curY, m->predY, m->recY, m->coef, c.qp, lane, &nzmask) : inter_luma(k, c, false, &nzmask);
     if (!cbp) t8 = 0; /* the flag is only transmitted with coded luma */
+    PC_BAR();
     cbp |= encode_chroma(k, c, false, false) << 4;
     __syncwarp();
+    PC_BAR();
     int16_t *out = (int16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
     const unsigned off = emit_mb(c, out, part ? 8 : 0, CC_MB_P16, cbp); /* P_8x8: 8 int16 left free for the four mvd */
+    PC_BAR();
     /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
     int est;
     {
@@ -1182,6 +1212,7 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
         i16_params(c, ip);
         est = analyse_i16(c, ip, &dummy);
     }
+    PC_BAR();
     /* likeliest P_Skip vector: 8.4.1.1 applied to the neighbours' search vectors */
     int cand[2], mvp[2], a[2] = {0, 0}, b[2] = {0, 0}, cc[2] = {0, 0};
     int rA = -2, rB = -2, rC = -2;
@@ -1209,6 +1240,7 @@ __global__ void __launch_bounds__(PC_WARPS * 32) k_p_code(cc_kparams k) {
      * to its right and lower neighbours for as long as their zero probe passes — at the coarse quantisers of a rate-starved stream
      * that is most of the picture (measured on the bench workload: 52 of 67 in-wavefront P_Skip reconstructions per macroblock row
      * were at the zero vector, 48 of them with the candidate's prediction published in vain). */
+    PC_BAR();
     const bool pub0 = (ok & 2) && !z_is_me && !z_is_c, two = !c_is_me && !z_is_me && !z_is_c;
     if (pub0 || ((ok & 1) && !c_is_me)) {
         ok |= pub0 ? 8 : 4;
@@ -1393,7 +1425,16 @@ extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {
     const int nmb = k->mb_w * k->mb_h;
+#if PC_WARPS > 6
+    const size_t dyn = PC_WARPS * (sizeof(WarpMem) + sizeof(X8Mem)) + 16;
+#ifndef CC_EMU_BUILD
+    /* per device; cheap enough to repeat per launch */
+    cudaFuncSetAttribute(k_p_code, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+#endif
+    CC_LAUNCH_SMEM(k_p_code, dim3((unsigned)((nmb + PC_WARPS - 1) / PC_WARPS)), dim3(PC_WARPS * 32), dyn, st, *k);
+#else
     CC_LAUNCH(k_p_code, dim3((unsigned)((nmb + PC_WARPS - 1) / PC_WARPS)), dim3(PC_WARPS * 32), st, *k);
+#endif
     return 1;
 }
 extern "C" int cck_pack(const cc_kparams *k, cudaStream_t st) {

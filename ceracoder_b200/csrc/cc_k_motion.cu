@@ -20,7 +20,10 @@
 #ifndef CC_EMU_BUILD
 #include <cuda.h>          /* CUtensorMap */
 #endif
-#define ME_WARPS 4
+#define ME_WARPS 4 /* k_me_l1: four macroblocks share one window tile */
+#ifndef ME0_WARPS
+#define ME0_WARPS 4 /* k_me_l0: warps (macroblocks) per CTA */
+#endif
 
 /* Work item = (pair of consecutive dy, group of 4 consecutive dx) = 8 candidates.  The 4 dx share the same three aligned words
  * of every window row and the two dy share 7 of their 8 rows, so the item reads 9 rows: 27 LDS + 54 funnel shifts for
@@ -271,15 +274,22 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, c
  * (cp.async.bulk.tensor.2d, one mbarrier per warp), and all 17 + 4 x 17 quarter-pel predictors of the 16x16 and 8x8 refinements are
  * built from shared memory — instead of two unaligned global word pairs per predictor row from four planes. */
 #ifndef CC_EMU_BUILD
-__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k, const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmB,
-                                                         const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmJ) {
+__global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k, const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmB,
+                                                          const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmJ) {
 #else
-__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
+__global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
 #endif
-    __shared__ __align__(128) uint8_t swin[ME_WARPS][4 * SP_PLANE];
-    __shared__ uint32_t scur[ME_WARPS][64]; /* current MB, 16 rows x 4 words */
+#if ME0_WARPS > 8
+    CC_DYN_SMEM(me_dsm0);
+    uint8_t *const me_dsm = (uint8_t *)(((uintptr_t)me_dsm0 + 127) & ~(uintptr_t)127);
+    uint8_t (*swin)[4 * SP_PLANE] = (uint8_t (*)[4 * SP_PLANE])me_dsm;
+    uint32_t (*scur)[64] = (uint32_t (*)[64])(me_dsm + ME0_WARPS * 4 * SP_PLANE);
+#else
+    __shared__ __align__(128) uint8_t swin[ME0_WARPS][4 * SP_PLANE];
+    __shared__ uint32_t scur[ME0_WARPS][64]; /* current MB, 16 rows x 4 words */
+#endif
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int mb = blockIdx.x * ME_WARPS + wid, nmb = k.mb_w * k.mb_h;
+    const int mb = blockIdx.x * ME0_WARPS + wid, nmb = k.mb_w * k.mb_h;
     if (mb >= nmb) return;
     const int mw = k.mb_w, mbx = mb % mw, mby = mb / mw, lambda = c_lambda[k.qp];
     const int px = mbx * 16, py = mby * 16;
@@ -342,7 +352,7 @@ __global__ void __launch_bounds__(ME_WARPS * 32) k_me_l0(cc_kparams k) {
     {
         const int tx = CC_PAD + px + wx, ty = CC_PAD + py + wy; /* allocation coordinates: the plane starts CC_PAD in */
 #ifndef CC_EMU_BUILD
-        __shared__ __align__(8) unsigned long long mbar[ME_WARPS];
+        __shared__ __align__(8) unsigned long long mbar[ME0_WARPS];
         const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar[wid]), win_a = (uint32_t)__cvta_generic_to_shared(swin[wid]);
         if (k.dbg != 1) {
         if (lane == 0) {
@@ -466,9 +476,15 @@ extern "C" int cck_me_l0(const cc_kparams *k, cudaStream_t st) {
 #ifndef CC_EMU_BUILD
     const CUtensorMap *tm = (const CUtensorMap *)k->tmaps; /* [0], [1]: the two reconstruction planes; [2..4]: b, h, j */
     const CUtensorMap *g = k->ref[0] == k->tmap_plane[0] ? &tm[0] : &tm[1];
-    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k, *g, tm[2], tm[3], tm[4]);
+#if ME0_WARPS > 8
+    const size_t dyn = (size_t)ME0_WARPS * (4 * SP_PLANE + 256) + 128;
+    cudaFuncSetAttribute(k_me_l0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    CC_LAUNCH_SMEM(k_me_l0, dim3((unsigned)((nmb + ME0_WARPS - 1) / ME0_WARPS)), dim3(ME0_WARPS * 32), dyn, st, *k, *g, tm[2], tm[3], tm[4]);
 #else
-    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME_WARPS - 1) / ME_WARPS)), dim3(ME_WARPS * 32), st, *k);
+    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME0_WARPS - 1) / ME0_WARPS)), dim3(ME0_WARPS * 32), st, *k, *g, tm[2], tm[3], tm[4]);
+#endif
+#else
+    CC_LAUNCH(k_me_l0, dim3((unsigned)((nmb + ME0_WARPS - 1) / ME0_WARPS)), dim3(ME0_WARPS * 32), st, *k);
 #endif
     return 1;
 }
