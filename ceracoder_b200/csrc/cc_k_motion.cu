@@ -1,9 +1,10 @@
 /*
  * cc_k_motion.cu — motion estimation: fully parallel over macroblocks, one warp
  * per macroblock, integer pipes only.
- *   k_me_l1  coarse level: exhaustive +-16 search at half resolution on the MB's 8x8 footprint.  The
- *            40x40 reference window is staged in shared memory; every lane scores whole candidates with
- *            __vsadu4 on funnel-shifted words.  cost = 4*SAD + |dx| + |dy|, lowest candidate index wins ties.
+ *   k_me_l1  coarse level: exhaustive +-16 search at half resolution on the MB's 8x8 footprint.  Eight macroblocks
+ *            share one TMA-staged window tile, expanded into four byte-phase planes; a thread scores the 33 candidates
+ *            of one column of one macroblock's window with VABSDIFF4.ACC on aligned 64-bit loads.
+ *            cost = 4*SAD + |dx| + |dy|, lowest candidate index wins ties.
  *   k_me_l0  fine level: 27 full-pel candidates (SAD + lambda*mvd bits) around twice the coarse vector, then
  *            9 half-pel and 8 quarter-pel candidates scored by 4x4-Hadamard SATD.  Quarter-pel predictors are
  *            averages (__vavgu4) of two samples from the {G,b,h,j} planes built by k_hpel.
@@ -13,108 +14,138 @@
  */
 #include "cc_dev.cuh"
 
-#define L1_WIN 40          /* 8 + 2*16 */
-#define L1_PITCHW 20       /* words per staged row: the CTA's four macroblocks share one 64-pixel-wide window (16 words) + the 2 words the
-                            * last candidate group reads past it; 20 keeps the rows of a warp's work items on different banks */
-#define L1_ROWS (L1_WIN + 1) /* + 1 row read (and discarded) by the candidate pair that starts at dy = 32 */
+#define L1_MBS 8           /* k_me_l1: macroblocks per CTA (they share one window tile) */
+#define L1_PITCHW 28       /* words per staged row: 8 macroblocks x 8 pixels + 32 of search range = 96 bytes, + the bytes the last phase-plane pair
+                            * reads past them, rounded up to the 16 bytes a TMA box row is a multiple of */
+#define L1_ROWS 40         /* 8 + 2 * 16 */
 #ifndef CC_EMU_BUILD
 #include <cuda.h>          /* CUtensorMap */
 #endif
-#define ME_WARPS 4 /* k_me_l1: four macroblocks share one window tile */
 #ifndef ME0_WARPS
 #define ME0_WARPS 4 /* k_me_l0: warps (macroblocks) per CTA */
 #endif
 
-/* Work item = (pair of consecutive dy, group of 4 consecutive dx) = 8 candidates.  The 4 dx share the same three aligned words
- * of every window row and the two dy share 7 of their 8 rows, so the item reads 9 rows: 27 LDS + 54 funnel shifts for
- * 128 VABSDIFF4.ACC (algorithmic integer ops, SURVEY.md 8d: 16 per candidate). */
-/* CTA = four horizontally adjacent macroblocks (grid = (mb_w / 4, mb_h)): their search windows overlap, so the CTA stages ONE
- * 80-byte x 41-row tile of the half-resolution reference with a single TMA load (cp.async.bulk.tensor.2d into shared memory,
- * completion on an mbarrier) instead of 4 x 400 per-lane word loads. */
+/* CTA = eight horizontally adjacent macroblocks (grid = (mb_w / 8, mb_h)): their search windows overlap, so the CTA stages ONE
+ * 112-byte x 40-row tile of the half-resolution reference with a single TMA load (cp.async.bulk.tensor.2d into shared memory,
+ * completion on an mbarrier).
+ *
+ * The kernel is bound by the VABSDIFF4 pipe (half rate: the measured peak is one per two issue slots), so everything else has to
+ * fit into the other half of the slots.  Two things make it fit:
+ *   - the tile is expanded once per CTA into four byte-phase planes of (word, next word) pairs: a candidate whose window starts
+ *     at byte X of a row reads its 8 pixels with ONE aligned 64-bit load from plane X & 3 — no funnel shifts in the search loop
+ *     (the first version spent 54 of them per 128 abs-diffs);
+ *   - work item = (macroblock, dx, all 33 dy): each of the 40 window rows it reads is used by up to 8 of its 33 candidates, whose
+ *     SADs build up in 33 registers: 40 loads + 528 VABSDIFF4.ACC + 3 instructions of cost / minimum per candidate, all offsets
+ *     and candidate constants immediate.
+ * 8 macroblocks x 33 dx = 264 items = one per thread of a 9-warp CTA.  The winner per macroblock is the minimum of
+ * (cost << 11 | candidate index) over its 33 threads (shared-memory atomicMin): the lowest index wins ties, as in the oracle. */
+#define L1_NTHR 288        /* 9 warps: 264 work items */
+#define L1_QROW 23         /* pairs per plane row: window start words 0 .. 22 (X = 8 * 7 + 32 = 88 at most) */
+#define L1_QPLANE 932      /* pairs per phase plane: 40 * 23 = 920, padded so that the four phases of a half-warp's loads fall on different banks (932 = 4 mod 16) */
 #ifndef CC_EMU_BUILD
-__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k, const __grid_constant__ CUtensorMap tmap) {
+__global__ void __launch_bounds__(L1_NTHR, 7) k_me_l1(cc_kparams k, const __grid_constant__ CUtensorMap tmap) {
 #else
-__global__ void __launch_bounds__(ME_WARPS * 32) k_me_l1(cc_kparams k) {
+__global__ void __launch_bounds__(L1_NTHR, 7) k_me_l1(cc_kparams k) {
 #endif
-    __shared__ __align__(128) uint32_t win[L1_ROWS * L1_PITCHW];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int mbx0 = blockIdx.x * ME_WARPS, mbx = mbx0 + wid, mby = blockIdx.y;
+    /* the tile lives in the tail of the planes' own storage (it is dead once they are built): 30 KB of shared memory and 32 registers
+     * let seven CTAs share an SM, which makes the 1020 CTAs of a 1080p frame one wave on 148 SMs */
+    __shared__ __align__(128) uint2 Q[4 * L1_QPLANE];
+    uint32_t *const win = (uint32_t *)(Q + 4 * L1_QPLANE) - L1_ROWS * L1_PITCHW;
+    __shared__ __align__(16) uint32_t scur[L1_MBS][16]; /* the macroblocks' 8x8 half-resolution source blocks: 8 rows x 2 words */
+    __shared__ unsigned smin[L1_MBS];
+    const int tid = threadIdx.x;
+    const int mbx0 = blockIdx.x * L1_MBS, mby = blockIdx.y;
 #ifndef CC_EMU_BUILD
     __shared__ __align__(8) unsigned long long mbar;
     const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar), win_a = (uint32_t)__cvta_generic_to_shared(win);
-    if (threadIdx.x == 0) {
+    if (tid == 0) { /* tile origin in allocation coordinates: the plane starts CC_PADC rows / columns into it */
+        const int tx = CC_PADC + mbx0 * 8 - CC_L1R, ty = CC_PADC + mby * 8 - CC_L1R;
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) { /* tile origin in allocation coordinates: the plane starts CC_PADC rows / columns into it */
-        const int tx = CC_PADC + mbx0 * 8 - CC_L1R, ty = CC_PADC + mby * 8 - CC_L1R;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_a), "r"(L1_ROWS * L1_PITCHW * 4) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                      ::"r"(win_a), "l"((unsigned long long)&tmap), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
     }
-#else
-    {
-        const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx0 * 8 - CC_L1R); /* 4-byte aligned */
-        for (int i = threadIdx.x; i < L1_ROWS * L1_PITCHW; i += blockDim.x) {
-            const int r = i / L1_PITCHW, c = i - r * L1_PITCHW;
-            win[i] = *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c);
-        }
-        __syncthreads();
-    }
 #endif
-    if (mbx >= k.mb_w) return; /* whole warp exits together (after the CTA-wide barrier above) */
-    const int mb = mby * k.mb_w + mbx;
-    const uint8_t *cur = k.l1cur + (size_t)(mby * 8) * k.sc + mbx * 8;
-    const uint32_t *w = win + 2 * wid; /* this macroblock's 40-pixel window starts 8 pixels per macroblock into the tile */
-    uint32_t c0[8], c1[8];
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-        c0[r] = *(const uint32_t *)(cur + (size_t)r * k.sc);
-        c1[r] = *(const uint32_t *)(cur + (size_t)r * k.sc + 4);
+    if (tid < L1_MBS * 16) { /* source blocks; a macroblock past the right edge repeats the last one (its result is not stored) */
+        const int w = tid >> 4, i = tid & 15, mbx = min(mbx0 + w, k.mb_w - 1);
+        scur[w][i] = *(const uint32_t *)(k.l1cur + (size_t)(mby * 8 + (i >> 1)) * k.sc + mbx * 8 + 4 * (i & 1));
     }
+    if (tid < L1_MBS) smin[tid] = 0xffffffffu;
+    __syncthreads();
 #ifndef CC_EMU_BUILD
-    { /* the tile has landed when the mbarrier's phase 0 completes */
+    if (tid < 4 * L1_ROWS) { /* the tile has landed when the mbarrier's phase 0 completes (only the threads that read it wait) */
         uint32_t ok;
         do {
             asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a) : "memory");
         } while (!ok);
     }
-#endif
-    unsigned best = 0xffffffffu;
-    for (int item = lane; item < 17 * 9; item += 32) {
-        const int dyp = item / 9, g = item - dyp * 9, dy = 2 * dyp; /* window coordinates: dy, dy + 1 in 0..32, dx = 4g .. 4g+3 */
-        const uint32_t *p = w + dy * L1_PITCHW + g;
-        uint32_t s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
-#pragma unroll
-        for (int r = 0; r < 9; r++) {
-            const uint32_t w0 = p[r * L1_PITCHW], w1 = p[r * L1_PITCHW + 1], w2 = p[r * L1_PITCHW + 2];
-            uint32_t a[4], b[4];
-            a[0] = w0; b[0] = w1;
-#pragma unroll
-            for (int i = 1; i < 4; i++) { a[i] = __funnelshift_r(w0, w1, 8 * i); b[i] = __funnelshift_r(w1, w2, 8 * i); }
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                if (r < 8) s[0][i] = cc_sad4_acc(a[i], c0[r], cc_sad4_acc(b[i], c1[r], s[0][i]));
-                if (r >= 1) s[1][i] = cc_sad4_acc(a[i], c0[r - 1], cc_sad4_acc(b[i], c1[r - 1], s[1][i]));
-            }
+#else
+    { /* bytes past the allocation's row are never used by a stored result: clamp the read instead of a TMA's zero fill */
+        const uint8_t *ref = k.l1ref + (ptrdiff_t)(mby * 8 - CC_L1R) * k.sc + (mbx0 * 8 - CC_L1R); /* 4-byte aligned */
+        const int avail = (k.sc - (CC_PADC + mbx0 * 8 - CC_L1R)) / 4; /* words left in the allocation's row */
+        for (int i = tid; i < L1_ROWS * L1_PITCHW; i += L1_NTHR) {
+            const int r = i / L1_PITCHW, c = i - r * L1_PITCHW;
+            win[i] = c < avail ? *(const uint32_t *)(ref + (ptrdiff_t)r * k.sc + 4 * c) : 0u;
         }
-        const int dx = 4 * g - 16;
+        __syncthreads();
+    }
+#endif
+    /* phase planes: Q[p][row][j] = bytes 4 j + p .. 4 j + p + 7 of the tile row; thread = (phase, row), sliding along the row */
+    {
+        const int p = tid & 3, row = tid >> 2;
+        uint32_t r[L1_QROW + 2];
+        if (tid < 4 * L1_ROWS) {
+            const uint32_t *wp = win + row * L1_PITCHW;
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-            if (dy + j > 32) continue;
-            const unsigned ady = (unsigned)cc_iabs(dy + j - 16), idx = (unsigned)((dy + j) * 33 + 4 * g);
-            best = min(best, ((4u * s[j][0] + (unsigned)cc_iabs(dx) + ady) << 11) | idx);
-            if (g < 8) { /* dx = 32 is the only candidate of the last group */
-                best = min(best, ((4u * s[j][1] + (unsigned)cc_iabs(dx + 1) + ady) << 11) | (idx + 1));
-                best = min(best, ((4u * s[j][2] + (unsigned)cc_iabs(dx + 2) + ady) << 11) | (idx + 2));
-                best = min(best, ((4u * s[j][3] + (unsigned)cc_iabs(dx + 3) + ady) << 11) | (idx + 3));
+            for (int j = 0; j < L1_QROW + 2; j++) r[j] = wp[j];
+        }
+        __syncthreads(); /* every row is in registers: the planes may now overwrite the tile */
+        if (tid < 4 * L1_ROWS) {
+            uint2 *qp = Q + p * L1_QPLANE + row * L1_QROW;
+            uint32_t a = __funnelshift_r(r[0], r[1], 8 * p);
+#pragma unroll
+            for (int j = 0; j < L1_QROW; j++) {
+                const uint32_t b = __funnelshift_r(r[j + 1], r[j + 2], 8 * p);
+                qp[j] = make_uint2(a, b);
+                a = b;
             }
         }
     }
-    best = __reduce_min_sync(FULL, best);
-    if (lane == 0) {
-        int idx = (int)(best & 2047u);
+    __syncthreads();
+    if (tid < L1_MBS * 33) {
+        const int w = tid / 33, dx = tid - w * 33; /* window coordinates: dx, dy in 0..32 */
+        const int X = 8 * w + dx;
+        const uint2 *q = Q + (X & 3) * L1_QPLANE + (X >> 2);
+        uint32_t c0[8], c1[8];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint4 v = *(const uint4 *)&scur[w][4 * i];
+            c0[2 * i] = v.x; c1[2 * i] = v.y; c0[2 * i + 1] = v.z; c1[2 * i + 1] = v.w;
+        }
+        uint32_t acc[33];
+#pragma unroll
+        for (int d = 0; d < 33; d++) acc[d] = 0;
+#pragma unroll
+        for (int rr = 0; rr < L1_ROWS; rr++) {
+            const uint2 ab = q[rr * L1_QROW];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const int d = rr - i;
+                if (d >= 0 && d < 33) acc[d] = cc_sad4_acc(ab.x, c0[i], cc_sad4_acc(ab.y, c1[i], acc[d]));
+            }
+        }
+        /* key = (4 SAD + |dx - 16| + |dy - 16|) << 11 | (33 dy + dx) = SAD * 8192 + (the thread's part) + (a constant per dy) */
+        const unsigned base = ((unsigned)cc_iabs(dx - 16) << 11) + (unsigned)dx;
+        unsigned best = 0xffffffffu;
+#pragma unroll
+        for (int d = 0; d < 33; d++)
+            best = min(best, acc[d] * 8192u + (base + (unsigned)(((d < 16 ? 16 - d : d - 16) << 11) + 33 * d)));
+        atomicMin(&smin[w], best);
+    }
+    __syncthreads();
+    if (tid < L1_MBS && mbx0 + tid < k.mb_w) {
+        const int idx = (int)(smin[tid] & 2047u), mb = mby * k.mb_w + mbx0 + tid;
         k.me[mb].l1_mv[0] = (int16_t)(idx % 33 - 16);
         k.me[mb].l1_mv[1] = (int16_t)(idx / 33 - 16);
     }
@@ -438,13 +469,13 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
 }
 
 extern "C" int cck_me_l1(const cc_kparams *k, cudaStream_t st) {
-    const dim3 grid((unsigned)((k->mb_w + ME_WARPS - 1) / ME_WARPS), (unsigned)k->mb_h);
+    const dim3 grid((unsigned)((k->mb_w + L1_MBS - 1) / L1_MBS), (unsigned)k->mb_h);
 #ifndef CC_EMU_BUILD
     CUtensorMap tm;
     memcpy(&tm, k->tmap_l1, sizeof tm);
-    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k, tm);
+    CC_LAUNCH(k_me_l1, grid, dim3(L1_NTHR), st, *k, tm);
 #else
-    CC_LAUNCH(k_me_l1, grid, dim3(ME_WARPS * 32), st, *k);
+    CC_LAUNCH(k_me_l1, grid, dim3(L1_NTHR), st, *k);
 #endif
     return 1;
 }
