@@ -1013,8 +1013,10 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 cost_i16 = analyse_i16(c, ip, &mode16);
                 const long long tb = k.cyc ? clock64() : 0;
                 /* Intra4x4 wins only if cost_i4 < cost_i16 and (P frames) cost_i4 + 8 lambda < cost_inter */
-                if (k.cyc && lane == 0 && (k.is_idr || cost_i16 * 4 <= cost_inter * 5)) k.cyc[(size_t)row * CC_CYC_N + 20] += 1;
-                if (k.is_idr || cost_i16 * 4 <= cost_inter * 5) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda), !k.is_idr);
+                /* the margin shrinks with the quantiser (oracle/ref_mb.c ref_mb_encode states the rule and what it costs) */
+                const bool start_i4 = k.is_idr || (long long)cost_i16 * 8 <= (long long)cost_inter * (8 + (qp < 28 ? 2 : (qp < 34 ? 1 : 0)));
+                if (k.cyc && lane == 0 && start_i4) k.cyc[(size_t)row * CC_CYC_N + 20] += 1;
+                if (start_i4) cost_i4 = analyse_i4(k, c, k.is_idr ? cost_i16 : min(cost_i16, cost_inter - 8 * c.lambda), !k.is_idr);
                 if (k.cyc && lane == 0) {
                     unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                     cy[11] += (unsigned long long)(tb - ta); cy[12] += (unsigned long long)(clock64() - tb); cy[13] += cost_i4 < (1 << 30);

@@ -396,6 +396,10 @@ static void intra_chroma(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, i
     encode_chroma(e, mbx, mby, predC, 1, mi, coef);
 }
 
+/* decision-rule constants {numerator, denominator}; ref_x_set_rules() overrides them for what-if measurements (tools/rule_eval.py) */
+static int g_x_gate[2] = {9, 8};  /* intra gate: source-based estimate within 12.5 % of the inter cost */
+static int g_x_i4[2] = {0, 0};    /* Intra4x4 analysis: real Intra16x16 cost within a margin of the inter cost; {0, 0} = the product's rule (below) */
+void ref_x_set_rules(int gate_num, int gate_den, int i4_num, int i4_den) { g_x_gate[0] = gate_num; g_x_gate[1] = gate_den; g_x_i4[0] = i4_num; g_x_i4[1] = i4_den; }
 void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     const int sy = e->sy, sc = e->sc, lambda = ref_lambda[e->qp];
     ref_mb_info *mi = MBI(e, mbx, mby);
@@ -457,12 +461,18 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         int dummy;
         const int est = analyse_i16(e, mbx, mby, &dummy, e->cur[0]);
         mi->dbg_est_intra = est; mi->dbg_cost_inter = cost_inter;
-        gate = est * 8 <= cost_inter * 9;
+        gate = est * g_x_gate[1] <= cost_inter * g_x_gate[0];
     }
     cost_i16 = 1 << 30;
     if (gate) {
         cost_i16 = analyse_i16(e, mbx, mby, &mode16, e->rec[0]);
-        if (e->is_idr || cost_i16 * 4 <= cost_inter * 5)
+        /* P frames: the Intra4x4 analysis starts only when the real Intra16x16 cost is within a margin of the inter cost, and the
+         * margin shrinks with the quantiser — 25 % below QP 28, 12.5 % below QP 34, none from there on: at coarse quantisers one
+         * analysis in a hundred ends in an Intra4x4 macroblock (QP 32: 0.1 % of the macroblocks, QP 38: 0.03 %), yet 85 - 90 % of the
+         * gated macroblocks used to start it.  Measured with tools/rule_eval.py on S2 1080p: +0.10 % BD-rate against a flat 25 %
+         * (only QP 34 moves, +0.26 % bits), for a third fewer started analyses at QP 28 - 33 and 55 - 80 % fewer from QP 34. */
+        const int i4m = e->qp < 28 ? 2 : (e->qp < 34 ? 1 : 0); /* margin in eighths */
+        if (e->is_idr || (g_x_i4[1] ? (long long)cost_i16 * g_x_i4[1] <= (long long)cost_inter * g_x_i4[0] : (long long)cost_i16 * 8 <= (long long)cost_inter * (8 + i4m)))
             cost_i4 = analyse_i4(e, mbx, mby, c4, m4, n4, e->is_idr ? 0 : (cost_i16 < cost_inter - 8 * lambda ? cost_i16 : cost_inter - 8 * lambda));
         if (!e->is_idr) { cost_i16 += 8 * lambda; if (cost_i4 < (1 << 30)) cost_i4 += 8 * lambda; } /* intra mb_type/chroma-mode overhead in P slices */
     }
