@@ -346,6 +346,8 @@ void cc_enc_close(cc_enc *e) {
                     s[16] * f, s[18] * f, s[17] * f, s[19] * f, s[21] * f, s[20] * f);
             fprintf(stderr, "ceracuda P_Skip predicted in the wavefront without a probe, per MB row per frame: at the search vector (speculation lost) %.1f, at the zero vector %.1f (%.1f of them with the candidate probe also passing), other %.1f\n",
                     s[22] * f, s[23] * f, s[25] * f, s[24] * f);
+            if (s[28]) fprintf(stderr, "ceracuda intra macroblocks of P frames: %.2f per MB row per frame, %.0f cycles each to code (transform, chroma, publish), %.0f to emit\n",
+                               s[28] * f, (double)s[26] / s[28], (double)s[27] / s[28]);
         }
         free(h);
     }

@@ -84,21 +84,25 @@ __device__ __forceinline__ void mc_luma16(const cc_kparams &k, const MbCtx &c, i
 __device__ __forceinline__ int luma_lane_quad(int lane) { return ((lane >> 4) << 1) | (lane & 1); }
 __device__ __forceinline__ int chroma_lane_quad(int lane) { return (((lane >> 3) & 1) << 1) | (lane & 1); }
 __device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8);
-/* 8x8 chroma predictors (both planes), H.264 8.4.2.2.2; lane = (plane, row, half) */
+/* 8x8 chroma predictors (both planes), H.264 8.4.2.2.2; lane = (plane, row, half): four pixels from the 5 x 2 samples around them.
+ * The samples come as two aligned words per row (five bytes from any alignment fit in eight), and the bilinear sum
+ * ((8-fx)(8-fy) A + fx (8-fy) B + (8-fx) fy C + fx fy D + 32) >> 6 runs on two pixels at a time in the 16-bit halves of a register
+ * (the weights add up to 64, so a half never exceeds 64 * 255 + 32): the same integers as the per-pixel formula. */
 __device__ __forceinline__ void mc_chroma8(const cc_kparams &k, const MbCtx &c, int mvx, int mvy, uint32_t (*dstC)[16] = nullptr) {
     if (!dstC) dstC = c.m->predC;
     const int pl = c.lane >> 4, row = (c.lane >> 1) & 7, half = c.lane & 1, fx = mvx & 7, fy = mvy & 7;
     const uint8_t *p = k.ref[1 + pl] + (ptrdiff_t)(c.mby * 8 + row + (mvy >> 3)) * k.sc + c.mbx * 8 + half * 4 + (mvx >> 3);
-    uint32_t w = 0;
-    int a = p[0], b = p[k.sc];
-#pragma unroll
-    for (int x = 0; x < 4; x++) {
-        int a1 = p[x + 1], b1 = p[k.sc + x + 1];
-        int v = ((8 - fx) * (8 - fy) * a + fx * (8 - fy) * a1 + (8 - fx) * fy * b + fx * fy * b1 + 32) >> 6;
-        w |= (uint32_t)v << (8 * x);
-        a = a1; b = b1;
-    }
-    dstC[pl][row * 2 + half] = w;
+    const uintptr_t a = (uintptr_t)p;
+    const unsigned sh = (unsigned)(a & 3) * 8u;
+    const uint32_t *q0 = (const uint32_t *)(a & ~(uintptr_t)3), *q1 = (const uint32_t *)((const uint8_t *)q0 + k.sc); /* sc is a multiple of 4 */
+    const uint32_t a0 = q0[0], a1 = q0[1], b0 = q1[0], b1 = q1[1];
+    const uint32_t aL = __funnelshift_r(a0, a1, sh), aR = __funnelshift_rc(a0, a1, sh + 8u);
+    const uint32_t bL = __funnelshift_r(b0, b1, sh), bR = __funnelshift_rc(b0, b1, sh + 8u);
+    const uint32_t w00 = (uint32_t)((8 - fx) * (8 - fy)), w01 = (uint32_t)(fx * (8 - fy)), w10 = (uint32_t)((8 - fx) * fy), w11 = (uint32_t)(fx * fy);
+    const uint32_t M = 0x00ff00ffu;
+    const uint32_t ve = (w00 * (aL & M) + w01 * (aR & M) + w10 * (bL & M) + w11 * (bR & M) + 0x00200020u) >> 6;
+    const uint32_t vo = (w00 * ((aL >> 8) & M) + w01 * ((aR >> 8) & M) + w10 * ((bL >> 8) & M) + w11 * ((bR >> 8) & M) + 0x00200020u) >> 6;
+    dstC[pl][row * 2 + half] = (ve & M) | ((vo & M) << 8);
 }
 
 __device__ __forceinline__ void mc_mb8(const cc_kparams &k, const MbCtx &c, const cc_me8 &m8) {
@@ -743,9 +747,9 @@ __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, 
 /* Two P_Skip tests in one pass (the pre-pass probes its two likeliest skip vectors): prediction A in predY / predC, prediction B
  * in the Intra4x4 level scratch c4 (unused by the pre-pass; recY / recC keep the macroblock's reconstruction); lanes 0-15 run the luma blocks of A and lanes 16-31 those of B, lanes 0-7 / 8-15 the chroma
  * blocks.  Same arithmetic as inter_luma / encode_chroma in probe mode.  Returns bit 0: nothing survives at A, bit 1: at B. */
+__device__ __forceinline__ int probe_eval2(const cc_kparams &k, const MbCtx &c, const uint32_t *aY, const uint32_t (*aC)[16], const uint32_t *bY, const uint32_t (*bC)[16]);
 __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, int ax, int ay, int bx2, int by2) {
     WarpMem *m = c.m;
-    const int lane = c.lane;
     mc_luma16(k, c, ax, ay);
     mc_chroma8(k, c, ax, ay);
     uint32_t *const bY = (uint32_t *)m->c4;
@@ -753,10 +757,16 @@ __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, 
     mc_luma16(k, c, bx2, by2, bY);
     mc_chroma8(k, c, bx2, by2, bC);
     __syncwarp();
+    return probe_eval2(k, c, m->predY, m->predC, bY, bC);
+}
+/* the two tests on predictions that are in shared memory already: A = (aY, aC), B = (bY, bC) */
+__device__ __forceinline__ int probe_eval2(const cc_kparams &k, const MbCtx &c, const uint32_t *aY, const uint32_t (*aC)[16], const uint32_t *bY, const uint32_t (*bC)[16]) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
     unsigned nzl;
     { /* luma */
         const int b = lane & 15, bx = c_blk_x[b], by = c_blk_y[b];
-        const uint32_t *pred = lane < 16 ? m->predY : bY;
+        const uint32_t *pred = lane < 16 ? aY : bY;
         uint32_t cw[4], pw[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) { cw[r] = m->curY[(by * 4 + r) * 4 + bx]; pw[r] = pred[(by * 4 + r) * 4 + bx]; }
@@ -776,7 +786,7 @@ __device__ __forceinline__ int probe_zero2(const cc_kparams &k, const MbCtx &c, 
     unsigned nzc;
     { /* chroma: lanes 0-15 = (probe, plane, block) */
         const int sel = (lane >> 3) & 1, pl = (lane >> 2) & 1, b = lane & 3, bx = b & 1, by = b >> 1;
-        const uint32_t *pred = sel ? bC[pl] : m->predC[pl];
+        const uint32_t *pred = sel ? bC[pl] : aC[pl];
         const uint16_t *mf = k.qmf[3], *bias = k.qbias[3];
         uint32_t cw[4], pw[4];
 #pragma unroll
@@ -1080,6 +1090,7 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
                 if (k.cyc && lane == 0) {
                     unsigned long long *cy = k.cyc + (size_t)row * CC_CYC_N;
                     cy[14] += (unsigned long long)(td - tc); cy[15] += (unsigned long long)(clock64() - td);
+                    if (!k.is_idr) { cy[26] += (unsigned long long)(td - tc); cy[27] += (unsigned long long)(clock64() - td); cy[28] += 1; }
                 }
             }
         }
@@ -1129,12 +1140,6 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
     }
 }
 
-/* search vector of quadrant q of macroblock n (its 16x16 vector unless the search chose P_8x8) */
-__device__ __forceinline__ void search_mv(const cc_kparams &k, int n, int q, int mv[2]) {
-    if (k.me[n].part) { mv[0] = k.me8[n].mv[q][0]; mv[1] = k.me8[n].mv[q][1]; }
-    else { mv[0] = k.me[n].mv[0]; mv[1] = k.me[n].mv[1]; }
-}
-
 /* ---- P-frame pre-pass: every macroblock coded as P_L0_16x16 at its search vector, fully parallel ------------------------ */
 /* Warps (macroblocks) per CTA.  The kernel is 114 KB of straight-line code and a warp runs through ~50 KB of it per macroblock:
  * with small CTAs the two dozen warps of an SM sit at unrelated places of it and instruction fetch, not data, is what they wait for
@@ -1170,16 +1175,51 @@ __global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k)
     /* a warp past the last macroblock codes the last one again (same values to the same places): the CTA's warps meet at barriers */
     const int mb = min((int)(blockIdx.x * PC_WARPS) + wid, mw * k.mb_h - 1);
     X8Mem *x8 = &x8m[wid];
-    x8->zz[lane] = c_zigzag8[lane]; x8->zz[lane + 32] = c_zigzag8[lane + 32];
     MbCtx c;
     c.lane = lane; c.mbx = mb % mw; c.mby = mb / mw; c.mb = mb; c.px = c.mbx * 16; c.py = c.mby * 16;
     c.qp = k.qp; c.qpc = c_chroma_qp[k.qp]; c.lambda = c_lambda[k.qp]; c.m = &wm[wid];
     c.L = c.mbx > 0; c.T = c.mby > (c.mby / k.rps) * k.rps; c.TR = c.T && c.mbx + 1 < mw;
     WarpMem *m = c.m;
-    const cc_me *me = k.me + mb;
-    const int mvx = me->mv[0], mvy = me->mv[1], part = me->part;
-    int satd4 = me->satd;
+    /* Everything the macroblock reads from global memory is requested in two rounds at the top, not where it is used (the kernel
+     * used to make five dependent round trips per macroblock).  Round 1: the search result, the search results of the three
+     * neighbours the P_Skip vector is predicted from (a lane each, 16x16 and 8x8 records both, no dependent second load), the
+     * source pixels, the source neighbours of the intra estimate. */
+    const cc_me me_r = k.me[mb];
+    int nbx = 0, nby = 0; /* lanes 0..2: search vector of the neighbour's quadrant next to this macroblock (A: left, B: top, C: top-right or top-left) */
+    {
+        const bool useC = c.TR, useD = !c.TR && c.T && c.L;
+        const int n = lane == 0 ? mb - 1 : (lane == 1 ? mb - mw : (useC ? mb - mw + 1 : mb - mw - 1));
+        const int q = lane == 0 ? 1 : (lane == 1 ? 2 : (useC ? 2 : 3));
+        const bool have = lane == 0 ? c.L : (lane == 1 ? c.T : (lane == 2 && (useC || useD)));
+        if (have) {
+            const cc_me nm = k.me[n];
+            const uint32_t v8 = ((const uint32_t *)k.me8[n].mv)[q];
+            nbx = nm.part ? (int)(int16_t)(v8 & 0xffffu) : nm.mv[0];
+            nby = nm.part ? (int)(int16_t)(v8 >> 16) : nm.mv[1];
+        }
+    }
+    int src_top = 0, src_left = 0; /* source neighbours: lanes 0..16 the row above (from x = -1), lanes 16..31 the column to the left */
+    {
+        const uint8_t *sy0 = k.cur[0] + (size_t)c.py * k.sy + c.px;
+        if (lane < 17 && c.T && (lane > 0 || c.L)) src_top = sy0[-(ptrdiff_t)k.sy + lane - 1];
+        if (lane >= 16 && c.L) src_left = sy0[(size_t)(lane - 16) * k.sy - 1];
+    }
+    x8->zz[lane] = g_zigzag8[lane]; x8->zz[lane + 32] = g_zigzag8[lane + 32];
     stage_cur(k, c);
+    const int mvx = me_r.mv[0], mvy = me_r.mv[1], part = me_r.part;
+    int satd4 = me_r.satd;
+    /* likeliest P_Skip vector: 8.4.1.1 applied to the neighbours' search vectors */
+    int cand[2], mvp[2], a[2], b[2], cc[2];
+    a[0] = __shfl_sync(FULL, nbx, 0); a[1] = __shfl_sync(FULL, nby, 0);
+    b[0] = __shfl_sync(FULL, nbx, 1); b[1] = __shfl_sync(FULL, nby, 1);
+    cc[0] = __shfl_sync(FULL, nbx, 2); cc[1] = __shfl_sync(FULL, nby, 2);
+    predict_mv_core(c.L, c.T, c.L ? 0 : -2, a, c.T ? 0 : -2, b, (c.TR || (c.T && c.L)) ? 0 : -2, cc, mvp, cand);
+    /* a P_8x8 search result says nothing about the 16x16 coding at one vector: both probes run for real */
+    const bool c_is_me = !part && cand[0] == mvx && cand[1] == mvy, z_is_me = !part && mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
+    /* Round 2: the three predictions — at the search vector (predY / predC), at the P_Skip candidate (A, in the record / pixel rings
+     * this kernel does not use) and at the zero vector (B, in the Intra4x4 level scratch) */
+    uint32_t *const aY = (uint32_t *)m->pc, *const bY = (uint32_t *)m->c4;
+    uint32_t (*const aC)[16] = (uint32_t (*)[16])(aY + 64), (*const bC)[16] = (uint32_t (*)[16])(bY + 64);
     if (part) { /* P_8x8: each quadrant predicted with its own vector (chroma: the 4x4 block it covers) */
         const cc_me8 m8 = k.me8[mb];
         mc_mb8(k, c, m8);
@@ -1188,6 +1228,14 @@ __global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k)
         mc_luma16(k, c, mvx, mvy);
         mc_chroma8(k, c, mvx, mvy);
     }
+    if (!c_is_me) { mc_luma16(k, c, cand[0], cand[1], aY); mc_chroma8(k, c, cand[0], cand[1], aC); }
+    if (!z_is_me && !z_is_c) { /* the co-located block: aligned, no interpolation */
+        const uint2 v = *(const uint2 *)(k.ref[0] + (size_t)(c.py + (lane >> 1)) * k.sy + c.px + 8 * (lane & 1));
+        bY[lane * 2] = v.x; bY[lane * 2 + 1] = v.y;
+        bC[lane >> 4][lane & 15] = *(const uint32_t *)(k.ref[1 + (lane >> 4)] + (size_t)(c.mby * 8 + ((lane >> 1) & 7)) * k.sc + c.mbx * 8 + 4 * (lane & 1));
+    }
+    if (lane < 17) m->tile[0][3 + lane] = (uint8_t)src_top;
+    if (lane >= 16) m->tile[1 + lane - 16][3] = (uint8_t)src_left;
     __syncwarp();
     PC_BAR();
     unsigned nzmask;
@@ -1205,53 +1253,39 @@ __global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k)
     /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
     int est;
     {
-        const uint8_t *sy0 = k.cur[0] + (size_t)c.py * k.sy + c.px;
-        if (lane < 17) m->tile[0][3 + lane] = (c.T && (lane > 0 || c.L)) ? sy0[-(ptrdiff_t)k.sy + lane - 1] : 0;
-        if (lane >= 16) m->tile[1 + lane - 16][3] = c.L ? sy0[(size_t)(lane - 16) * k.sy - 1] : 0;
-        __syncwarp();
         I16Params ip;
         int dummy;
         i16_params(c, ip);
         est = analyse_i16(c, ip, &dummy);
     }
     PC_BAR();
-    /* likeliest P_Skip vector: 8.4.1.1 applied to the neighbours' search vectors */
-    int cand[2], mvp[2], a[2] = {0, 0}, b[2] = {0, 0}, cc[2] = {0, 0};
-    int rA = -2, rB = -2, rC = -2;
-    if (c.L) { rA = 0; search_mv(k, mb - 1, 1, a); }
-    if (c.T) { rB = 0; search_mv(k, mb - mw, 2, b); }
-    if (c.TR) { rC = 0; search_mv(k, mb - mw + 1, 2, cc); }
-    else if (c.T && c.L) { rC = 0; search_mv(k, mb - mw - 1, 3, cc); }
-    predict_mv_core(c.L, c.T, rA, a, rB, b, rC, cc, mvp, cand);
+    /* P_Skip tests at the candidate and at zero: known from the coding above where the vector is the search vector, else both
+     * evaluated in one pass on the predictions staged at the top (a test that is not needed rides along on the other one's data) */
     int ok = 0;
-    /* a P_8x8 search result says nothing about the 16x16 coding at one vector: both probes run for real */
-    const bool c_is_me = !part && cand[0] == mvx && cand[1] == mvy, z_is_me = !part && mvx == 0 && mvy == 0, z_is_c = cand[0] == 0 && cand[1] == 0;
-    if (!c_is_me && !z_is_me && !z_is_c) ok = probe_zero2(k, c, cand[0], cand[1], 0, 0);
-    else {
-        if (c_is_me) ok |= cbp == 0; else ok |= probe_zero(k, c, cand[0], cand[1]) ? 1 : 0;
-        if (z_is_me) ok |= (cbp == 0) << 1; else if (z_is_c) ok |= (ok & 1) << 1; else ok |= probe_zero(k, c, 0, 0) ? 2 : 0;
+    {
+        const bool needA = !c_is_me, needB = !z_is_me && !z_is_c;
+        int r = 0;
+        if (needA || needB) r = probe_eval2(k, c, needA ? aY : bY, needA ? aC : bC, needB ? bY : aY, needB ? bC : aC);
+        ok |= c_is_me ? (cbp == 0) : (r & 1);
+        ok |= z_is_me ? ((cbp == 0) << 1) : (z_is_c ? ((ok & 1) << 1) : (r & 2));
     }
     /* Most macroblocks of a moving picture end up P_Skip at the predicted skip vector, which is rarely the search vector to the
      * quarter pel: their reconstruction is the prediction at that vector.  When the probe at `cand` leaves nothing (and cand is not
-     * the search vector anyway), the pre-pass therefore publishes THAT prediction — it sits in predY / predC (in every branch
-     * above that sets bit 0 for such a macroblock, the last prediction made is the one at cand) — and parks the P_L0_16x16
-     * reconstruction in a side buffer.  The wavefront then has nothing to move for the common outcome (P_Skip at cand) and
-     * restores the parked pixels in the rare other ones.
+     * the search vector anyway), the pre-pass therefore publishes THAT prediction and parks the P_L0_16x16 reconstruction in a
+     * side buffer.  The wavefront then has nothing to move for the common outcome (P_Skip at cand) and restores the parked pixels
+     * in the rare other ones.
      * Which of the two, when both probes pass: the zero vector.  8.4.1.1 forces the skip vector to zero next to a neighbour that
      * does not move, so one macroblock skipped at zero (every first macroblock of a slice row is, if at all) hands the zero vector on
      * to its right and lower neighbours for as long as their zero probe passes — at the coarse quantisers of a rate-starved stream
      * that is most of the picture (measured on the bench workload: 52 of 67 in-wavefront P_Skip reconstructions per macroblock row
      * were at the zero vector, 48 of them with the candidate's prediction published in vain). */
     PC_BAR();
-    const bool pub0 = (ok & 2) && !z_is_me && !z_is_c, two = !c_is_me && !z_is_me && !z_is_c;
+    const bool pub0 = (ok & 2) && !z_is_me && !z_is_c;
     if (pub0 || ((ok & 1) && !c_is_me)) {
         ok |= pub0 ? 8 : 4;
         uint32_t *park = (uint32_t *)(k.park + (size_t)mb * 384);
         park[lane] = m->recY[lane]; park[lane + 32] = m->recY[lane + 32]; park[64 + lane] = m->recC[lane >> 4][lane & 15];
-        /* the prediction at zero: B of probe_zero2 (in the Intra4x4 level scratch) when both probes ran as a pair, else the last
-         * prediction made (pub0 without the pair means the candidate is the search vector, and the zero probe ran last) */
-        const uint32_t *sY = (pub0 && two) ? (const uint32_t *)m->c4 : m->predY;
-        const uint32_t *sC = (pub0 && two) ? (const uint32_t *)m->c4 + 64 : &m->predC[0][0];
+        const uint32_t *sY = pub0 ? bY : aY, *sC = pub0 ? &bC[0][0] : &aC[0][0];
         m->recY[lane] = sY[lane]; m->recY[lane + 32] = sY[lane + 32];
         m->recC[lane >> 4][lane & 15] = sC[lane];
         __syncwarp();

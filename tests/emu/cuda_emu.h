@@ -146,6 +146,7 @@ static inline unsigned __byte_perm(unsigned a, unsigned b, unsigned s) {
     return r;
 }
 static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned sh) { uint64_t v = ((uint64_t)hi << 32) | lo; return (unsigned)(v >> (sh & 31)); }
+static inline unsigned __funnelshift_rc(unsigned lo, unsigned hi, unsigned sh) { uint64_t v = ((uint64_t)hi << 32) | lo; return (unsigned)(v >> (sh > 32 ? 32 : sh)); }
 static inline unsigned __funnelshift_l(unsigned lo, unsigned hi, unsigned sh) { uint64_t v = ((uint64_t)hi << 32) | lo; return (unsigned)((v << (sh & 31)) >> 32); }
 static inline unsigned __vsadu4(unsigned a, unsigned b) { unsigned s = 0; for (int i = 0; i < 4; i++) { int x = (a >> (8 * i)) & 255, y = (b >> (8 * i)) & 255; s += (unsigned)(x > y ? x - y : y - x); } return s; }
 static inline unsigned __vabsdiffu4(unsigned a, unsigned b) { unsigned r = 0; for (int i = 0; i < 4; i++) { int x = (a >> (8 * i)) & 255, y = (b >> (8 * i)) & 255; r |= (unsigned)(x > y ? x - y : y - x) << (8 * i); } return r; }
