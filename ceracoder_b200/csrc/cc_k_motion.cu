@@ -222,7 +222,8 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, c
         unsigned acc[5][2];
 #pragma unroll
         for (int dx = 0; dx < 5; dx++) acc[dx][0] = acc[dx][1] = 0;
-        if (lane < 20) sad_strip5(k.ref[0] + (ptrdiff_t)(py + fby + dyi - 2 + 4 * g) * k.sy + px + fbx - 2, k.sy, sc + 16 * g, acc);
+        /* the strips lie inside the staged window (plane G: columns fbx - 2 .. fbx + 25, rows fby - 2 .. fby + 17 of it) */
+        if (lane < 20) sad_strip5(tiles + (fby + dyi - 2 + 4 * g - wy) * SP_W + fbx - 2 - wx, SP_W, sc + 16 * g, acc);
         unsigned kl = 0xffffffffu, kr = 0xffffffffu;
         const int my = fby + dyi - 2;
         const int bits_y = cc_se_bits(4 * (my - pm[1]));
