@@ -166,7 +166,7 @@ __device__ __forceinline__ void cc_qpel4x4(const cc_kparams &k, int px, int py, 
  * (wx, wy) relative to the macroblock origin; (bx, by) = the block's offset inside the macroblock */
 #define SP_W 48 /* 32 columns are needed; the window starts on a 16-byte boundary of the plane (TMA), up to 15 columns further left */
 #define SP_H 28
-#define SP_ORG 4 /* the window starts (at least) 4 samples left of / above the best full-pel position */
+#define SP_ORG 4 /* the window starts (at least) 4 samples left of / above the vector it is staged around (the coarse vector minus one: 5 left of / above it) */
 #define SP_PLANE 1408 /* bytes from one plane's tile to the next: SP_W * SP_H rounded up to the 128 bytes a TMA destination must be aligned to */
 __device__ __forceinline__ void cc_qpel4x4_s(const uint8_t *tiles, int wx, int wy, int bx, int by, int mvx, int mvy, uint32_t out[4]) {
     const int e = c_qpel[(mvy & 3) * 4 + (mvx & 3)];
@@ -333,6 +333,71 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
     /* approximate predictor: median of the neighbours' coarse vectors, in full-pel units */
     const cc_me *me = k.me + mb;
     const int L = mbx > 0, T = mby > (mby / k.rps) * k.rps, C = T && mbx + 1 < mw, TL = T && L;
+    const int l1x = 2 * me->l1_mv[0], l1y = 2 * me->l1_mv[1];
+    /* The window of the four planes (G, b, h, j) is requested as soon as the coarse vector is known, around it: columns from the
+     * 16-byte boundary of the plane at or left of l1x - 5, rows from l1y - 5.  48 x 28 samples from there hold everything the search
+     * reads when the best full-pel vector lies within +-2 of the coarse one — the 5 x 5 full-pel strips, the sub-pel predictors, the
+     * +-2 strips and predictors of the 8x8 quadrants — so the full-pel search no longer goes to global memory either.  When the
+     * predictor or the zero vector wins from further away, the window is staged again around the winner. */
+    uint8_t *const tiles = swin[wid];
+    int wx, wy;
+#ifndef CC_EMU_BUILD
+    __shared__ __align__(8) unsigned long long mbar[ME0_WARPS];
+    const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar[wid]), win_a = (uint32_t)__cvta_generic_to_shared(swin[wid]);
+    uint32_t phase = 0;
+    if (lane == 0 && k.dbg != 1) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+#endif
+    auto stage = [&](int cx, int cy) { /* window around the full-pel vector (cx, cy); origin relative to the macroblock in (wx, wy) */
+        wy = cy - SP_ORG;
+        wx = cx - SP_ORG - ((px + cx - SP_ORG) & 15); /* the plane's origin is 16-byte aligned and CC_PAD is a multiple of 16: the same boundary in allocation coordinates */
+#ifndef CC_EMU_BUILD
+        if (k.dbg != 1) {
+            const int tx = CC_PAD + px + wx, ty = CC_PAD + py + wy; /* allocation coordinates: the plane starts CC_PAD in */
+            __syncwarp(); /* nobody still reads the previous window */
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_a), "r"(4 * SP_W * SP_H) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(win_a), "l"((unsigned long long)&tmG), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(win_a + SP_PLANE), "l"((unsigned long long)&tmB), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(win_a + 2 * SP_PLANE), "l"((unsigned long long)&tmH), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(win_a + 3 * SP_PLANE), "l"((unsigned long long)&tmJ), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
+            }
+            return;
+        }
+#endif
+        { /* the same window by plain loads (the CPU emulation build; CC_DBG_ME=1 on the device) */
+            const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
+            __syncwarp();
+            for (int p = 0; p < 4; p++)
+                for (int i = lane; i < SP_W * SP_H / 4; i += 32) {
+                    const int r = i / (SP_W / 4), cw4 = i - r * (SP_W / 4);
+                    *(uint32_t *)(swin[wid] + p * SP_PLANE + r * SP_W + 4 * cw4) =
+                        *(const uint32_t *)(pl[p] + (ptrdiff_t)(py + wy + r) * k.sy + px + wx + 4 * cw4);
+                }
+            __syncwarp();
+        }
+    };
+    auto stage_wait = [&]() {
+#ifndef CC_EMU_BUILD
+        if (k.dbg != 1) {
+            uint32_t ok;
+            do {
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a), "r"(phase) : "memory");
+            } while (!ok);
+            phase ^= 1u;
+        }
+#endif
+    };
+#ifndef CC_EMU_BUILD
+    __syncwarp(); /* the mbarrier is initialised before anybody waits on it */
+#endif
+    stage(l1x - 1, l1y - 1); /* origin l1 - 5 */
     int pm[2];
 #pragma unroll
     for (int c = 0; c < 2; c++) {
@@ -340,13 +405,13 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
         int cc = C ? 2 * me[-mw + 1].l1_mv[c] : (TL ? 2 * me[-mw - 1].l1_mv[c] : 0);
         pm[c] = (!T && !(C || TL) && L) ? a : cc_median3(a, b, cc);
     }
-    const int l1x = 2 * me->l1_mv[0], l1y = 2 * me->l1_mv[1];
     __syncwarp();
     const uint32_t *sc = scur[wid];
+    stage_wait();
 
     /* full-pel, 27 candidates: the predictor (0), the zero vector (1), 5 x 5 around the coarse vector (2 + 5 dy + dx).
-     * lanes 0..19 = (candidate row, four source rows) of the 5 x 5 window, five candidates each (sad_strip5);
-     * lanes 20..23 / 24..27 = the predictor / the zero vector as the centre of a strip of their own */
+     * lanes 0..19 = (candidate row, four source rows) of the 5 x 5 window, five candidates each (sad_strip5), from the staged
+     * window; lanes 20..23 / 24..27 = the predictor / the zero vector as the centre of a strip of their own, from global memory */
     unsigned key = 0xffffffffu;
     {
         const int g = lane & 3, dyi = lane >> 2;
@@ -356,7 +421,8 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
         unsigned acc[5][2];
 #pragma unroll
         for (int dx = 0; dx < 5; dx++) acc[dx][0] = acc[dx][1] = 0;
-        if (lane < 28) sad_strip5(k.ref[0] + (ptrdiff_t)(py + syy + 4 * g) * k.sy + px + sx, k.sy, sc + 16 * g, acc);
+        const uint8_t *sp = lane < 20 ? tiles + (syy + 4 * g - wy) * SP_W + sx - wx : k.ref[0] + (ptrdiff_t)(py + syy + 4 * g) * k.sy + px + sx;
+        if (lane < 28) sad_strip5(sp, lane < 20 ? SP_W : k.sy, sc + 16 * g, acc);
         const int bits_y = cc_se_bits(4 * (syy - pm[1]));
 #pragma unroll
         for (int dx = 0; dx < 5; dx++) {
@@ -374,53 +440,9 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
     /* best full-pel vector: centre of the 8x8 searches */
     const int fbx = bl == 0 ? pm[0] : (bl == 1 ? 0 : l1x + (bl - 2) % 5 - 2), fby = bl == 0 ? pm[1] : (bl == 1 ? 0 : l1y + (bl - 2) / 5 - 2);
     int bx = 4 * fbx, by = 4 * fby;
-
-    /* stage the sub-pel window of the four planes */
-    const uint8_t *tiles = swin[wid];
-    /* window origin relative to the macroblock: rows from fby - 4; columns from the 16-byte boundary of the plane at or left of
-     * fbx - 4 (the plane's origin is 16-byte aligned and CC_PAD is a multiple of 16, so the boundary is the same in allocation
-     * coordinates) */
-    const int wy = fby - SP_ORG, wx = fbx - SP_ORG - ((px + fbx - SP_ORG) & 15);
-    {
-        const int tx = CC_PAD + px + wx, ty = CC_PAD + py + wy; /* allocation coordinates: the plane starts CC_PAD in */
-#ifndef CC_EMU_BUILD
-        __shared__ __align__(8) unsigned long long mbar[ME0_WARPS];
-        const uint32_t mbar_a = (uint32_t)__cvta_generic_to_shared(&mbar[wid]), win_a = (uint32_t)__cvta_generic_to_shared(swin[wid]);
-        if (k.dbg != 1) {
-        if (lane == 0) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_a) : "memory");
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_a), "r"(4 * SP_W * SP_H) : "memory");
-            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a), "l"((unsigned long long)&tmG), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
-            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + SP_PLANE), "l"((unsigned long long)&tmB), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
-            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + 2 * SP_PLANE), "l"((unsigned long long)&tmH), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
-            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(win_a + 3 * SP_PLANE), "l"((unsigned long long)&tmJ), "r"(tx), "r"(ty), "r"(mbar_a) : "memory");
-        }
-        __syncwarp();
-        {
-            uint32_t ok;
-            do {
-                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mbar_a) : "memory");
-            } while (!ok);
-        }
-        } else
-#else
-        (void)tx; (void)ty;
-#endif
-        { /* the same window by plain loads (the CPU emulation build; CC_DBG_ME=1 on the device) */
-            const uint8_t *pl[4] = {k.ref[0], k.hb, k.hh, k.hj};
-            for (int p = 0; p < 4; p++)
-                for (int i = lane; i < SP_W * SP_H / 4; i += 32) {
-                    const int r = i / (SP_W / 4), cw4 = i - r * (SP_W / 4);
-                    *(uint32_t *)(swin[wid] + p * SP_PLANE + r * SP_W + 4 * cw4) =
-                        *(const uint32_t *)(pl[p] + (ptrdiff_t)(py + wy + r) * k.sy + px + wx + 4 * cw4);
-                }
-            __syncwarp();
-        }
+    if (cc_iabs(fbx - l1x) > 2 || cc_iabs(fby - l1y) > 2) { /* the predictor or the zero vector won from outside the window (warp-uniform) */
+        stage(fbx - 1, fby - 1);
+        stage_wait();
     }
 
     /* sub-pel: half-warp = candidate, lane&15 = 4x4 block (raster within the MB) */
