@@ -228,17 +228,19 @@ __device__ __forceinline__ int encode_chroma(const cc_kparams &k, const MbCtx &c
 
 /* ---- intra 16x16 ----------------------------------------------------------------------------------------- */
 struct I16Params { int dc, a, b, c; };
+/* the sums of 8.3.3 over the 16 + 16 + 1 neighbour samples, one sample (or two) per lane and two warp reductions: lane l holds the
+ * top sample x = l - 1 (l <= 16; x = -1 is the corner) and the left sample y = l (l < 16).  H and V are the standard's sums
+ * sum (i + 1) (p[8 + i] - p[6 - i]) rewritten as sum (x - 7) p[x] over x = -1 .. 15. */
 __device__ __forceinline__ void i16_params(const MbCtx &c, I16Params &p) {
     const WarpMem *m = c.m;
-    int st = 0, sl = 0, H = 0, V = 0;
-#pragma unroll
-    for (int i = 0; i < 16; i++) { st += m->tile[0][4 + i]; sl += m->tile[1 + i][3]; }
+    const int l = c.lane;
+    const int t = l < 17 ? m->tile[0][3 + l] : 0, lf = l < 16 ? m->tile[1 + l][3] : 0;
+    const int sums = __reduce_add_sync(FULL, ((l >= 1 && l < 17) ? t : 0) | (lf << 16)); /* top | left << 16, each at most 4080 */
+    const int st = sums & 0xffff, sl = sums >> 16;
+    /* H + 65536 V: |H|, |V| <= 72 * 255 */
+    const int hv = __reduce_add_sync(FULL, (l - 8) * t + (((l < 16 ? (l - 7) * lf : 0) + (l == 0 ? -8 * t : 0)) << 16));
+    const int H = (int)(int16_t)(hv & 0xffff), V = (hv - H) >> 16;
     p.dc = (c.T && c.L) ? (st + sl + 16) >> 5 : (c.T ? (st + 8) >> 4 : (c.L ? (sl + 8) >> 4 : 128));
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-        H += (i + 1) * (m->tile[0][4 + 8 + i] - m->tile[0][4 + 6 - i]);  /* tile[0][3] is the top-left sample (x = -1) */
-        V += (i + 1) * (m->tile[1 + 8 + i][3] - (i == 7 ? m->tile[0][3] : m->tile[1 + 6 - i][3]));
-    }
     p.a = 16 * (m->tile[16][3] + m->tile[0][4 + 15]); p.b = (5 * H + 32) >> 6; p.c = (5 * V + 32) >> 6;
 }
 /* predictor words of 4x4 block (bx,by) for intra-16x16 mode (0 V, 1 H, 2 DC, 3 plane) */

@@ -177,6 +177,16 @@ __device__ __forceinline__ void cc_qpel4x4_s(const uint8_t *tiles, int wx, int w
 #pragma unroll
     for (int r = 0; r < 4; r++) out[r] = __vavgu4(cc_ld32u(A + r * SP_W), cc_ld32u(B + r * SP_W));
 }
+/* the same for a vector whose components are both even (integer and half-pel positions): the sample IS one plane's sample */
+__device__ __forceinline__ void cc_hpel4x4_s(const uint8_t *tiles, int wx, int wy, int bx, int by, int mvx, int mvy, uint32_t out[4]) {
+    const int pa = ((mvx >> 1) & 1) | (mvy & 2); /* G, b, h, j */
+    const uint8_t *A = tiles + pa * SP_PLANE + (by + (mvy >> 2) - wy) * SP_W + bx + (mvx >> 2) - wx;
+    const uintptr_t a = (uintptr_t)A;
+    const uint32_t *q = (const uint32_t *)(a & ~(uintptr_t)3);
+    const unsigned sh = (unsigned)(a & 3) * 8u;
+#pragma unroll
+    for (int r = 0; r < 4; r++) out[r] = __funnelshift_r(q[r * (SP_W / 4)], q[r * (SP_W / 4) + 1], sh);
+}
 
 /* Full-pel SADs of five horizontally adjacent candidates at once.  A lane takes four source rows (4 g .. 4 g + 3) of one
  * candidate row: it loads the 24-byte strip of the reference row once (six aligned words, realigned with five funnel shifts) and
@@ -270,11 +280,12 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, c
             const int o = 2 * ps + slot + (step == 2 ? 0 : 1);
             const bool valid = o <= 8;
             int dx = 0, dy = 0;
-            if (o >= 1) { int i = o <= 4 ? o - 1 : o; dx = (i % 3 - 1) * step; dy = (i / 3 - 1) * step; }
+            if (o >= 1) { const int i = o <= 4 ? o - 1 : o, i3 = (i * 11) >> 5; dx = (i - 3 * i3 - 1) * step; dy = (i3 - 1) * step; }
             int satd = 0;
             if (valid) {
                 uint32_t pw[4];
-                cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
+                if (step == 2) cc_hpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
+                else cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
             satd += __shfl_xor_sync(FULL, satd, 1);
@@ -460,11 +471,12 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
             int o = 2 * p + half + (step == 2 ? 0 : 1);
             bool valid = o <= 8;
             int dx = 0, dy = 0;
-            if (o >= 1) { int i = o <= 4 ? o - 1 : o; dx = (i % 3 - 1) * step; dy = (i / 3 - 1) * step; }
+            if (o >= 1) { const int i = o <= 4 ? o - 1 : o, i3 = (i * 11) >> 5; /* i / 3 for i < 9 */ dx = (i - 3 * i3 - 1) * step; dy = (i3 - 1) * step; }
             int satd = 0;
             if (valid) { /* uniform within each half-warp; no collectives inside */
                 uint32_t pw[4];
-                cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
+                if (step == 2) cc_hpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw); /* the half-pel ring around a full-pel centre */
+                else cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
                 satd = cc_satd4x4_words(cw, pw);
             }
 #pragma unroll
