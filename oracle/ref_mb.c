@@ -399,6 +399,8 @@ static void intra_chroma(struct ref_enc *e, int mbx, int mby, ref_mb_info *mi, i
 /* decision-rule constants {numerator, denominator}; ref_x_set_rules() overrides them for what-if measurements (tools/rule_eval.py) */
 static int g_x_gate[2] = {9, 8};  /* intra gate: source-based estimate within 12.5 % of the inter cost */
 static int g_x_i4[2] = {0, 0};    /* Intra4x4 analysis: real Intra16x16 cost within a margin of the inter cost; {0, 0} = the product's rule (below) */
+static int g_x_nocbp = 0;
+void ref_x_set_nocbp(int on) { g_x_nocbp = on; }
 void ref_x_set_rules(int gate_num, int gate_den, int i4_num, int i4_den) { g_x_gate[0] = gate_num; g_x_gate[1] = gate_den; g_x_i4[0] = i4_num; g_x_i4[1] = i4_den; }
 void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
     const int sy = e->sy, sc = e->sc, lambda = ref_lambda[e->qp];
@@ -462,6 +464,15 @@ void ref_mb_encode(struct ref_enc *e, int mbx, int mby) {
         const int est = analyse_i16(e, mbx, mby, &dummy, e->cur[0]);
         mi->dbg_est_intra = est; mi->dbg_cost_inter = cost_inter;
         gate = est * g_x_gate[1] <= cost_inter * g_x_gate[0];
+        if (gate && g_x_nocbp) { /* what-if: no intra analysis for a macroblock whose inter coding leaves no coefficient */
+            ref_mb_info keep = *mi;
+            int16_t keepc[COEF_PER_MB];
+            memcpy(keepc, coef, sizeof keepc);
+            code_inter_at_me(e, mbx, mby, mi, coef, -1);
+            const int cbp0 = mi->cbp;
+            *mi = keep; memcpy(coef, keepc, sizeof keepc);
+            if (g_x_nocbp == 1 ? cbp0 == 0 : (cbp0 & 15) == 0) gate = 0;
+        }
     }
     cost_i16 = 1 << 30;
     if (gate) {

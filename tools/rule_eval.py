@@ -11,8 +11,8 @@ from oracle_lib import OracleEncoder, lib, MbInfo  # noqa: E402
 
 W, H = 1920, 1080
 QPS = (22, 26, 30, 34, 38)
-RULES = {"gate 9/8, i4 5/4 (flat 25 %)": (9, 8, 5, 4), "i4 by QP: 10/8 below 28, 9/8 below 34, 8/8 above (product)": (9, 8, 0, 0), "i4 9/8": (9, 8, 9, 8), "i4 1/1": (9, 8, 1, 1),
-         "gate 17/16": (17, 16, 5, 4), "gate 1/1": (1, 1, 5, 4)}
+RULES = {"gate 9/8, i4 5/4 (flat 25 %)": (9, 8, 5, 4, 0), "i4 by QP: 10/8 below 28, 9/8 below 34, 8/8 above (product)": (9, 8, 0, 0, 0), "i4 9/8": (9, 8, 9, 8, 0), "i4 1/1": (9, 8, 1, 1, 0),
+         "gate 17/16": (17, 16, 5, 4, 0), "gate 1/1": (1, 1, 5, 4, 0), "product + no intra analysis when the inter coding has cbp 0": (9, 8, 0, 0, 1)}
 
 
 def main():
@@ -22,7 +22,7 @@ def main():
     L = lib()
     L.ref_set_threads(os.cpu_count())
     for name, r in RULES.items():
-        L.ref_x_set_rules(*r)
+        L.ref_x_set_rules(*r[:4]); L.ref_x_set_nocbp(r[4])
         for qp in QPS:
             enc = OracleEncoder(W, H, 60, 8)
             bits, psnr, n_i16 = [], [], 0
@@ -40,7 +40,7 @@ def main():
             enc.close()
             print(json.dumps({"config": name, "qp": qp, "frames": n, "kbps_at_60fps": float(np.mean(bits) * 60 / 1e3), "y_psnr_db": float(np.mean(psnr)),
                               "intra_analyses_per_p_frame": n_gate / (n - 1)}), flush=True)
-    L.ref_x_set_rules(9, 8, 0, 0)
+    L.ref_x_set_rules(9, 8, 0, 0); L.ref_x_set_nocbp(0)
 
 
 if __name__ == "__main__":
