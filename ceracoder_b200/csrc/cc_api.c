@@ -74,6 +74,13 @@ struct cc_enc {
     long staged_frames;
     unsigned long long tmaps[5 * 16] __attribute__((aligned(64))); /* five CUtensorMap (k_me_l0's sub-pel windows) */
     int debug_sync;
+    /* upload of the NEXT frame while this one is coded (cc_enc_encode_sequence, planar I420 in page-locked host or device memory): a second
+     * set of source planes, filled on a stream of its own; cc_enc_submit of that frame swaps the sets instead of copying */
+    uint8_t *cur_alt[3];
+    cudaStream_t st_up;
+    cudaEvent_t ev_up;
+    const uint8_t *pf_plane0; /* plane[0] of the frame sitting in cur_alt, or NULL */
+    long prefetched_frames;
     int dbg_dup, dbg_skip; /* CC_DBG_DUP / CC_DBG_SKIP: stage bit masks (1 << CC_STAGE_*) — launch a stage twice / not at all (marginal-cost experiments) */
     int bs_dirty;                /* a frame was abandoned: the slice bit buffers may hold stray bits, clear them before the next frame */
     size_t bs_bytes;
@@ -246,6 +253,17 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
         k->cur[1] = chr[0] + co; k->cur[2] = chr[1] + co; k->rec[1] = chr[2] + co; k->rec[2] = chr[3] + co;
         k->ref[1] = chr[4] + co; k->ref[2] = chr[5] + co; k->l1cur = chr[6] + co; k->l1ref = chr[7] + co;
     }
+    if (rc == CC_OK && p->format == CC_FMT_I420) {
+        uint8_t *alt[3] = {NULL, NULL, NULL};
+        rc = dev_alloc(e, (void **)&alt[0], lsz);
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&alt[1], csz);
+        if (rc == CC_OK) rc = dev_alloc(e, (void **)&alt[2], csz);
+        if (rc == CC_OK) {
+            cudaMemset(alt[0], 0, lsz); cudaMemset(alt[1], 0, csz); cudaMemset(alt[2], 0, csz);
+            e->cur_alt[0] = alt[0] + (size_t)CC_PAD * k->sy + CC_PAD;
+            e->cur_alt[1] = alt[1] + (size_t)CC_PADC * k->sc + CC_PADC; e->cur_alt[2] = alt[2] + (size_t)CC_PADC * k->sc + CC_PADC;
+        }
+    }
     if (rc == CC_OK && p->format == CC_FMT_NV12) rc = dev_alloc(e, (void **)&k->uvstage, (size_t)k->sy * (k->H / 2 + 1));
     if (rc == CC_OK && (p->format == CC_FMT_YUY2 || p->format == CC_FMT_BGRX)) {
         k->pks = (int)roundup((size_t)k->w * (p->format == CC_FMT_YUY2 ? 2 : 4), 128);
@@ -305,6 +323,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK) rc = pool_start(e, p->threads);
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st2, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st_up, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    if (rc == CC_OK && cudaEventCreateWithFlags(&e->ev_up, cudaEventDisableTiming) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreateWithFlags(&e->ev_enc, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ev_tail, cudaEventDisableTiming) != cudaSuccess)) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
     for (int i = 0; i < 2 * (CC_N_STAGES + 2) && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) != cudaSuccess) rc = CC_ERR_CUDA;
@@ -332,6 +352,7 @@ void cc_enc_close(cc_enc *e) {
     bind_device(e);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st2) cudaStreamSynchronize(e->st2);
+    if (e->st_up) cudaStreamSynchronize(e->st_up);
     if (e->k.cyc && e->frame_idx > 0) { /* CC_DEBUG_CYCLES=1: where the wavefront kernel's warps spent their cycles */
         size_t n = (size_t)e->k.mb_h * CC_CYC_N;
         unsigned long long *h = (unsigned long long *)calloc(n, 8), s[CC_CYC_N] = {0};
@@ -362,6 +383,8 @@ void cc_enc_close(cc_enc *e) {
     if (e->ev_tail) cudaEventDestroy(e->ev_tail);
     if (e->st) cudaStreamDestroy(e->st);
     if (e->st2) cudaStreamDestroy(e->st2);
+    if (e->ev_up) cudaEventDestroy(e->ev_up);
+    if (e->st_up) cudaStreamDestroy(e->st_up);
     free(e->au); free(e->rbsp); free(e->cav.nnz);
     free(e);
 }
@@ -470,7 +493,8 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
      * (tight rows), then upload from there like a pinned frame. */
     const uint8_t *pl[3] = {in->plane[0], in->plane[1], in->plane[2]};
     int st[3] = {in->stride[0], in->stride[1], in->stride[2]};
-    if (!(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) {
+    if (e->pf_plane0 && e->pf_plane0 != in->plane[0]) e->pf_plane0 = NULL; /* another frame than the one announced: the upload is dropped */
+    if (!e->pf_plane0 && !(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) {
         uint8_t *d = e->stage_host;
         const int nplanes = packed ? 1 : (nv12 ? 2 : 3);
         for (int i = 0; i < nplanes; i++) {
@@ -483,7 +507,12 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
         }
         e->staged_frames++;
     }
-    if (packed) {
+    if (e->pf_plane0 && e->pf_plane0 == in->plane[0] && fmt == CC_FMT_I420) { /* this frame was uploaded while the previous one was coded */
+        for (int i = 0; i < 3; i++) { uint8_t *t = k->cur[i]; k->cur[i] = e->cur_alt[i]; e->cur_alt[i] = t; }
+        CUCHECK(cudaStreamWaitEvent(e->st, e->ev_up, 0));
+        e->pf_plane0 = NULL;
+        e->prefetched_frames++;
+    } else if (packed) {
         CUCHECK(cudaMemcpy2DAsync(k->pkstage, (size_t)k->pks, pl[0], (size_t)st[0], (size_t)k->w * (fmt == CC_FMT_YUY2 ? 2 : 4), (size_t)k->h, kind, e->st));
     } else {
         CUCHECK(cudaMemcpy2DAsync(k->cur[0], (size_t)k->sy, pl[0], (size_t)st[0], (size_t)k->w, (size_t)k->h, kind, e->st));
@@ -675,6 +704,23 @@ int cc_enc_encode(cc_enc *e, const cc_frame *in, unsigned flags, cc_packet *out)
     return rc != CC_OK ? rc : cc_enc_collect(e, out);
 }
 
+/* starts the upload of the frame that will be submitted next (planar I420 in page-locked host memory or device memory only; any
+ * other frame is simply uploaded by its own cc_enc_submit).  The set of source planes it goes to was last read by the frame before
+ * the one in flight, which has been collected. */
+static void enc_prefetch(cc_enc *e, const cc_frame *in, unsigned flags) {
+    cc_kparams *k = &e->k;
+    if (e->p.format != CC_FMT_I420 || !e->cur_alt[0] || !in->plane[0] || !in->plane[1] || !in->plane[2]) return;
+    if (in->stride[0] < k->w || in->stride[1] < k->w / 2 || in->stride[2] < k->w / 2) return;
+    if (!(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) return;
+    const enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (cudaMemcpy2DAsync(e->cur_alt[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st_up) != cudaSuccess ||
+        cudaMemcpy2DAsync(e->cur_alt[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
+        cudaMemcpy2DAsync(e->cur_alt[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
+        cudaEventRecord(e->ev_up, e->st_up) != cudaSuccess) { cudaGetLastError(); return; }
+    e->pf_plane0 = in->plane[0];
+}
+long cc_enc_prefetched_frames(const cc_enc *e) { return e ? e->prefetched_frames : 0; }
+
 int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate_bps, int n, unsigned flags, cc_seq_stats *acc, cc_packet *last) {
     if (!e || !frames || !acc || n < 0) return CC_ERR_PARAM;
     cc_packet pkt;
@@ -682,6 +728,7 @@ int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate
     for (int i = 0; i < n; i++) {
         if (bitrate_bps && bitrate_bps[i] != cc_enc_get_bitrate(e)) cc_enc_set_bitrate(e, bitrate_bps[i]);
         int rc = cc_enc_submit(e, &frames[i], flags);
+        if (rc == CC_OK && i + 1 < n) enc_prefetch(e, &frames[i + 1], flags); /* the next frame's upload runs next to this frame's kernels */
         if (rc == CC_OK) rc = cc_enc_collect(e, &pkt);
         if (rc != CC_OK) return rc;
         acc->frames++; acc->au_bytes += pkt.size; acc->sym_bytes += pkt.sym_bytes;

@@ -191,3 +191,68 @@ def test_one_slice_per_picture_under_rate_control_many_frames(lib):
     run(solo, 0); run(solo, 1)
     for k in range(8):
         assert res[k] == solo[k % 2], f"stream {k} differs from its solo run"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("where", ["pinned", "device"])
+def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where):
+    """cc_enc_encode_sequence uploads frame i + 1 into a second set of source planes while frame i is coded (page-locked host or device
+    frames): same access units and reconstruction as one pageable frame at a time, and every frame but the first arrives that way."""
+    import ctypes as C
+    import zlib
+    from ceracoder_b200 import CudaH264Enc, load_library
+    from ceracoder_b200.synth import make_source
+    L = load_library()
+    L.cc_enc_prefetched_frames.restype = C.c_long
+    L.cc_enc_prefetched_frames.argtypes = [C.c_void_p]
+    L.cc_dev_alloc.restype = C.c_void_p
+    L.cc_dev_alloc.argtypes = [C.c_size_t]
+    L.cc_dev_free.argtypes = [C.c_void_p]
+    L.cc_dev_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    w, h, n = 640, 368, 9
+    src = make_source("pan", w, h)
+    frames = [src.frame(i) for i in range(n)]
+    rates = [3000] * 4 + [800] * 5
+    fsz = w * h * 3 // 2
+    if where == "pinned":
+        base = L.cc_host_alloc(n * fsz)
+    else:
+        base = L.cc_dev_alloc(n * fsz)
+    assert base
+    planes = []
+    for i, (y, u, v) in enumerate(frames):
+        tight = np.concatenate([y.ravel(), u.ravel(), v.ravel()])
+        p = base + i * fsz
+        if where == "pinned":
+            C.memmove(p, tight.ctypes.data, fsz)
+        else:
+            assert L.cc_dev_upload(p, tight.ctypes.data, fsz) == 0
+        planes.append((p, p + w * h, p + w * h * 5 // 4))
+    a = CudaH264Enc(w, h, fps=(60, 1), lib=L)
+    from ceracoder_b200.encoder import Frame
+    arr = (Frame * n)()
+    for i, pl in enumerate(planes):
+        for j in range(3):
+            arr[i].plane[j] = pl[j]
+            arr[i].stride[j] = w if j == 0 else w // 2
+        arr[i].pts = i
+    br = (C.c_int * n)(*[r * 1000 for r in rates])
+    seq = (arr, br, n, None)
+    st = a.encode_sequence(seq, device_frame=(where == "device"))
+    last_crc = zlib.crc32(C.string_at(a.last.data, a.last.size))
+    assert a.last.size > 0
+    assert L.cc_enc_prefetched_frames(a._h) == n - 1
+    b = CudaH264Enc(w, h, fps=(60, 1), lib=L)
+    sizes = []
+    for (y, u, v), r in zip(frames, rates):
+        b.set_property("bitrate", r)
+        au = b.encode(y, u, v)
+        sizes.append(len(au))
+    assert st.frames == n and st.au_bytes == sum(sizes) and zlib.crc32(au) == last_crc
+    (ya, ua, va), (yb, ub, vb) = a.recon(), b.recon()
+    assert (ya == yb).all() and (ua == ub).all() and (va == vb).all()
+    a.close(); b.close()
+    if where == "pinned":
+        L.cc_host_free(C.c_void_p(base))
+    else:
+        L.cc_dev_free(C.c_void_p(base))
