@@ -474,9 +474,9 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     cudaEvent_t *pev = e->pevs[e->pb];
     int *pev_used = e->pevs_used[e->pb];
     if (e->pevs_tail[e->pb]) { /* the stages that ran behind the collect of the frame before the previous one */
-        for (int i = CC_STAGE_DEBLOCK; i < CC_N_STAGES; i++) {
+        for (int i = CC_STAGE_DEBLOCK; i <= CC_STAGE_L1REF; i++) {
             float ms = 0;
-            if (pev_used[i] && cudaEventElapsedTime(&ms, pev[i], pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
+            if (pev_used[i] && cudaEventElapsedTime(&ms, pev[i], i == CC_STAGE_L1REF ? pev[CC_N_STAGES] : pev[i + 1]) == cudaSuccess) { e->stage_ms[i] += ms; e->stage_n[i]++; }
         }
         e->pevs_tail[e->pb] = 0;
     }
@@ -538,6 +538,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
      * neighbour records). */
     STAGE(CC_STAGE_ME_COARSE);
     if (!is_idr) { e->launches += cck_l1border(k, e->st); e->launches += cck_me_l1(k, e->st); if (DUP(CC_STAGE_ME_COARSE)) cck_me_l1(k, e->st); }
+    STAGE(CC_STAGE_WAIT_REF);
     CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
     STAGE(CC_STAGE_ME_FINE);
     if (!is_idr) { e->launches += cck_me_l0(k, e->st); if (DUP(CC_STAGE_ME_FINE)) cck_me_l0(k, e->st); }
@@ -622,11 +623,15 @@ static int collect_inner(cc_enc *e, cc_packet *out) {
     if (e->profile)
         for (int i = 0; i < CC_STAGE_DEBLOCK; i++) {
             float ms = 0;
-            cudaEvent_t end = i == CC_STAGE_PACK ? e->pevs[e->pb][CC_N_STAGES + 1] : e->pevs[e->pb][i + 1];
+            cudaEvent_t end = i == CC_STAGE_PACK ? e->pevs[e->pb][CC_N_STAGES + 1] : (i == CC_STAGE_ME_COARSE ? e->pevs[e->pb][CC_STAGE_WAIT_REF] : e->pevs[e->pb][i + 1]);
             if ((i == CC_STAGE_UPLOAD || e->pevs_used[e->pb][i]) && cudaEventElapsedTime(&ms, e->pevs[e->pb][i], end) == cudaSuccess) {
                 if (!is_idr_prof(e) || (i != CC_STAGE_ME_COARSE && i != CC_STAGE_ME_FINE && i != CC_STAGE_P_CODE)) { e->stage_ms[i] += ms; e->stage_n[i]++; }
             }
         }
+    if (e->profile && e->pevs_used[e->pb][CC_STAGE_WAIT_REF]) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, e->pevs[e->pb][CC_STAGE_WAIT_REF], e->pevs[e->pb][CC_STAGE_ME_FINE]) == cudaSuccess) { e->stage_ms[CC_STAGE_WAIT_REF] += ms; e->stage_n[CC_STAGE_WAIT_REF]++; }
+    }
     double t0 = now_ms();
     const int nmb = k->mb_w * k->mb_h, is_idr = e->cur_is_idr;
     const cc_rowhdr *rh = (const cc_rowhdr *)e->out_host;

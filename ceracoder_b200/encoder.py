@@ -243,7 +243,7 @@ class CudaH264Enc:
         _check(self.L, self.L.cc_enc_get_mbinfo(self._h, a.ctypes.data), "cc_enc_get_mbinfo")
         return a
 
-    STAGES = ("upload", "ingest", "me_coarse", "me_fine", "p_code", "mb_encode", "pack", "deblock", "border", "hpel", "l1ref")
+    STAGES = ("upload", "ingest", "me_coarse", "me_fine", "p_code", "mb_encode", "pack", "deblock", "border", "hpel", "l1ref", "wait_ref")
 
     def set_profile(self, on=True):
         _check(self.L, self.L.cc_enc_set_profile(self._h, int(on)), "cc_enc_set_profile")

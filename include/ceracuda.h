@@ -139,8 +139,10 @@ int cc_enc_get_mbinfo(cc_enc *h, uint8_t *dst8);
 size_t cc_enc_device_bytes(const cc_enc *h);
 /* per-stage device timing with CUDA events on the encoder's own stream (bench.py's roofline figures) */
 enum { CC_STAGE_UPLOAD = 0, CC_STAGE_INGEST, CC_STAGE_ME_COARSE, CC_STAGE_ME_FINE, CC_STAGE_P_CODE, CC_STAGE_MB_ENCODE, CC_STAGE_PACK,
-       CC_STAGE_DEBLOCK, CC_STAGE_BORDER, CC_STAGE_HPEL, CC_STAGE_L1REF, CC_STAGE_COUNT }; /* in execution order; the access unit is
-       complete after CC_STAGE_PACK, the later stages run while the host writes the bitstream */
+       CC_STAGE_DEBLOCK, CC_STAGE_BORDER, CC_STAGE_HPEL, CC_STAGE_L1REF, CC_STAGE_WAIT_REF, CC_STAGE_COUNT }; /* in execution order; the
+       access unit is complete after CC_STAGE_PACK, the later stages run while the host writes the bitstream.  CC_STAGE_WAIT_REF is
+       not a kernel: the time the frame's stream waited, between the coarse and the fine search, for the previous frame's
+       reference planes (in-loop filter, borders, half-pel planes) to be finished */
 int cc_enc_set_profile(cc_enc *h, int on);
 int cc_enc_get_stage_ms(const cc_enc *h, double *ms_sum /*[CC_STAGE_COUNT]*/, long *count /*[CC_STAGE_COUNT]*/);
 /* Frames handed to cc_enc_submit / cc_enc_encode in pageable host memory (a mapped GstBuffer) are first copied, by the calling
