@@ -151,4 +151,31 @@ __device__ __forceinline__ int cc_satd4x4_words(const uint32_t c[4], const uint3
     }
     return s >> 1;
 }
+/* The same with the source block's half of the horizontal transform taken out of the loop over candidates: the Hadamard transform is
+ * linear, so H(c - p) = H(c) + H(-p).  tc[r * 4 + k] = row r of the source block times Hadamard row k (cc_satd4x4_src), and every
+ * candidate costs 16 dot products instead of 32. */
+__device__ __forceinline__ void cc_satd4x4_src(const uint32_t c[4], int tc[16]) {
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        tc[r * 4 + 0] = cc_dp4a_us(c[r], CC_H0, 0); tc[r * 4 + 1] = cc_dp4a_us(c[r], CC_H1, 0);
+        tc[r * 4 + 2] = cc_dp4a_us(c[r], CC_H2, 0); tc[r * 4 + 3] = cc_dp4a_us(c[r], CC_H3, 0);
+    }
+}
+__device__ __forceinline__ int cc_satd4x4_pre(const int tc[16], const uint32_t p[4]) {
+    int t[16];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        t[r * 4 + 0] = cc_dp4a_us(p[r], CC_NEG4(CC_H0), tc[r * 4 + 0]);
+        t[r * 4 + 1] = cc_dp4a_us(p[r], CC_NEG4(CC_H1), tc[r * 4 + 1]);
+        t[r * 4 + 2] = cc_dp4a_us(p[r], CC_NEG4(CC_H2), tc[r * 4 + 2]);
+        t[r * 4 + 3] = cc_dp4a_us(p[r], CC_NEG4(CC_H3), tc[r * 4 + 3]);
+    }
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int s01 = t[i] + t[4 + i], m01 = t[i] - t[4 + i], s23 = t[8 + i] + t[12 + i], m23 = t[8 + i] - t[12 + i];
+        s += cc_iabs(s01 + s23) + cc_iabs(s01 - s23) + cc_iabs(m01 - m23) + cc_iabs(m01 + m23);
+    }
+    return s >> 1;
+}
 #endif

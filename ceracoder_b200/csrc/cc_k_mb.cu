@@ -267,6 +267,8 @@ __device__ __forceinline__ int analyse_i16(const MbCtx &c, const I16Params &p, i
     uint32_t cw[4];
 #pragma unroll
     for (int r = 0; r < 4; r++) cw[r] = m->curY[(by * 4 + r) * 4 + bx];
+    int tc[16];
+    cc_satd4x4_src(cw, tc);
     unsigned best = 0xffffffffu;
     for (int pass = 0; pass < 2; pass++) {
         const int mode = pass * 2 + half;
@@ -275,7 +277,7 @@ __device__ __forceinline__ int analyse_i16(const MbCtx &c, const I16Params &p, i
         if (ok) {
             uint32_t pw[4];
             i16_pred_block(c, p, mode, bx, by, pw);
-            satd = cc_satd4x4_words(cw, pw);
+            satd = cc_satd4x4_pre(tc, pw);
         }
 #pragma unroll
         for (int s = 8; s; s >>= 1) satd += __shfl_xor_sync(FULL, satd, s);
@@ -652,18 +654,32 @@ __device__ __forceinline__ unsigned emit_block(const MbCtx &c, int16_t *out, uns
 }
 
 /* all residual blocks of one macroblock in syntax order; the slot length is padded to a 4-byte multiple */
+template <int UNROLL = 16> /* 1: the block loops stay loops (code size: k_p_code is bound by instruction fetch before anything else) */
 __device__ __forceinline__ unsigned emit_mb(const MbCtx &c, int16_t *out, unsigned off, int type, int cbp) {
     const int cl = cbp & 15, cc = cbp >> 4;
     if (type == CC_MB_I16 || cbp) {
         unsigned mo = off;
         off += (unsigned)mb_nblocks(type, cbp);
         if (type == CC_MB_I16) off = emit_block(c, out, mo++, off, 24, 16);
-        for (int blk = 0; blk < 16; blk++)
-            if (cl & (1 << (blk >> 2))) off = emit_block(c, out, mo++, off, blk, type == CC_MB_I16 ? 15 : 16);
+        if (UNROLL == 1) {
+#pragma unroll 1
+            for (int blk = 0; blk < 16; blk++)
+                if (cl & (1 << (blk >> 2))) off = emit_block(c, out, mo++, off, blk, type == CC_MB_I16 ? 15 : 16);
+        } else {
+            for (int blk = 0; blk < 16; blk++)
+                if (cl & (1 << (blk >> 2))) off = emit_block(c, out, mo++, off, blk, type == CC_MB_I16 ? 15 : 16);
+        }
         if (cc) {
             off = emit_block(c, out, mo++, off, 25, 4);
             off = emit_block(c, out, mo++, off, 26, 4);
-            if (cc & 2) for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, mo++, off, blk, 15);
+            if (cc & 2) {
+                if (UNROLL == 1) {
+#pragma unroll 1
+                    for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, mo++, off, blk, 15);
+                } else {
+                    for (int blk = 16; blk < 24; blk++) off = emit_block(c, out, mo++, off, blk, 15);
+                }
+            }
         }
     }
     if (off & 1u) { if (c.lane == 0) out[off] = 0; off++; }
@@ -695,12 +711,17 @@ __device__ __forceinline__ int wait_progress_global(const uint32_t *flag, uint32
 /* does the macroblock coded at (mvx,mvy) leave nothing after quantisation + decimation?  (P_Skip test) */
 /* One pass: lanes 0-15 take the luma blocks, lanes 16-23 the chroma blocks (same arithmetic as inter_luma / encode_chroma in
  * probe mode; the two only differ in quantiser tables, the DC handling of chroma and the decimation rule). */
+__device__ __forceinline__ bool probe_eval1(const cc_kparams &k, const MbCtx &c, const uint32_t *pY, const uint32_t (*pC)[16]);
 __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, int mvx, int mvy) {
-    WarpMem *m = c.m;
-    const int lane = c.lane;
     mc_luma16(k, c, mvx, mvy);
     mc_chroma8(k, c, mvx, mvy);
     __syncwarp();
+    return probe_eval1(k, c, c.m->predY, c.m->predC);
+}
+/* the test on a prediction that is in shared memory already */
+__device__ __forceinline__ bool probe_eval1(const cc_kparams &k, const MbCtx &c, const uint32_t *pY, const uint32_t (*pC)[16]) {
+    WarpMem *m = c.m;
+    const int lane = c.lane;
     const bool chroma = lane >= 16;
     const int pl = (lane >> 2) & 1, b = chroma ? (lane & 3) : lane;
     const int bx = chroma ? (b & 1) : c_blk_x[b], by = chroma ? (b >> 1) : c_blk_y[b];
@@ -708,7 +729,7 @@ __device__ __forceinline__ bool probe_zero(const cc_kparams &k, const MbCtx &c, 
 #pragma unroll
     for (int r = 0; r < 4; r++) {
         cw[r] = chroma ? m->curC[pl][(by * 4 + r) * 2 + bx] : m->curY[(by * 4 + r) * 4 + bx];
-        pw[r] = chroma ? m->predC[pl][(by * 4 + r) * 2 + bx] : m->predY[(by * 4 + r) * 4 + bx];
+        pw[r] = chroma ? pC[pl][(by * 4 + r) * 2 + bx] : pY[(by * 4 + r) * 4 + bx];
     }
     uint16_t mf[3], bias[3];
 #pragma unroll
@@ -1250,7 +1271,7 @@ __global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k)
     __syncwarp();
     PC_BAR();
     int16_t *out = (int16_t *)(k.rowbuf + (size_t)mb * CC_ROW_PAYLOAD_PER_MB);
-    const unsigned off = emit_mb(c, out, part ? 8 : 0, CC_MB_P16, cbp); /* P_8x8: 8 int16 left free for the four mvd */
+    const unsigned off = emit_mb<1>(c, out, part ? 8 : 0, CC_MB_P16, cbp); /* P_8x8: 8 int16 left free for the four mvd */
     PC_BAR();
     /* intra gate: Intra16x16 cost estimated from SOURCE neighbours (no dependency on other macroblocks) */
     int est;
@@ -1261,13 +1282,15 @@ __global__ void __launch_bounds__(PC_WARPS * 32, PC_MINB) k_p_code(cc_kparams k)
         est = analyse_i16(c, ip, &dummy);
     }
     PC_BAR();
-    /* P_Skip tests at the candidate and at zero: known from the coding above where the vector is the search vector, else both
-     * evaluated in one pass on the predictions staged at the top (a test that is not needed rides along on the other one's data) */
+    /* P_Skip tests at the candidate and at zero: known from the coding above where the vector is the search vector, else evaluated on
+     * the predictions staged at the top — both in one pass (lanes split between them) when both are needed */
     int ok = 0;
     {
         const bool needA = !c_is_me, needB = !z_is_me && !z_is_c;
         int r = 0;
-        if (needA || needB) r = probe_eval2(k, c, needA ? aY : bY, needA ? aC : bC, needB ? bY : aY, needB ? bC : aC);
+        if (needA && needB) r = probe_eval2(k, c, aY, aC, bY, bC);
+        else if (needA) r = probe_eval1(k, c, aY, aC) ? 1 : 0;
+        else if (needB) r = probe_eval1(k, c, bY, bC) ? 2 : 0;
         ok |= c_is_me ? (cbp == 0) : (r & 1);
         ok |= z_is_me ? ((cbp == 0) << 1) : (z_is_c ? ((ok & 1) << 1) : (r & 2));
     }

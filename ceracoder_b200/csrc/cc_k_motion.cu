@@ -461,6 +461,8 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
     uint32_t cw[4];
 #pragma unroll
     for (int r = 0; r < 4; r++) cw[r] = sc[(oy + r) * 4 + (blk & 3)];
+    int tc[16]; /* the source block's share of every candidate's SATD */
+    cc_satd4x4_src(cw, tc);
     unsigned bestkey = 0xffffffffu; /* cost<<5 | order; this half-warp's best so far */
     int bestsatd = 0, bestx = bx, besty = by;
     for (int step = 2; step >= 1; step--) {
@@ -477,7 +479,7 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
                 uint32_t pw[4];
                 if (step == 2) cc_hpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw); /* the half-pel ring around a full-pel centre */
                 else cc_qpel4x4_s(tiles, wx, wy, ox, oy, cx + dx, cy + dy, pw);
-                satd = cc_satd4x4_words(cw, pw);
+                satd = cc_satd4x4_pre(tc, pw);
             }
 #pragma unroll
             for (int s = 8; s; s >>= 1) satd += __shfl_xor_sync(FULL, satd, s); /* 16-lane sum (both halves at once) */
