@@ -321,8 +321,12 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     e->cav.nnz = (uint8_t *)calloc((size_t)nmb, 24);
     if (!e->au || !e->rbsp || !e->cav.nnz) rc = CC_ERR_NOMEM;
     if (rc == CC_OK) rc = pool_start(e, p->threads);
-    if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
-    if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st2, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
+    { /* experiment knob CC_PRIO: bit 0 = the coding stream, bit 1 = the reference-finishing stream at the highest priority */
+        int lo = 0, hi = 0, pr = getenv("CC_PRIO") ? atoi(getenv("CC_PRIO")) : 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        if (rc == CC_OK && cudaStreamCreateWithPriority(&e->st, cudaStreamNonBlocking, (pr & 1) ? hi : lo) != cudaSuccess) rc = CC_ERR_CUDA;
+        if (rc == CC_OK && cudaStreamCreateWithPriority(&e->st2, cudaStreamNonBlocking, (pr & 2) ? hi : lo) != cudaSuccess) rc = CC_ERR_CUDA;
+    }
     if (rc == CC_OK && cudaStreamCreateWithFlags(&e->st_up, cudaStreamNonBlocking) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && cudaEventCreateWithFlags(&e->ev_up, cudaEventDisableTiming) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreateWithFlags(&e->ev_enc, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ev_tail, cudaEventDisableTiming) != cudaSuccess)) rc = CC_ERR_CUDA;

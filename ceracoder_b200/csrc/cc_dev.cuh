@@ -143,13 +143,14 @@ __device__ __forceinline__ int cc_satd4x4_words(const uint32_t c[4], const uint3
         t[r * 4 + 2] = cc_dp4a_us(c[r], CC_H2, cc_dp4a_us(p[r], CC_NEG4(CC_H2), 0));
         t[r * 4 + 3] = cc_dp4a_us(c[r], CC_H3, cc_dp4a_us(p[r], CC_NEG4(CC_H3), 0));
     }
+    /* second butterfly stage folded into the sum: |x + y| + |x - y| = 2 max(|x|, |y|), and the 2 is the SATD's final halving */
     int s = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         int s01 = t[i] + t[4 + i], m01 = t[i] - t[4 + i], s23 = t[8 + i] + t[12 + i], m23 = t[8 + i] - t[12 + i];
-        s += cc_iabs(s01 + s23) + cc_iabs(s01 - s23) + cc_iabs(m01 - m23) + cc_iabs(m01 + m23);
+        s += max(cc_iabs(s01), cc_iabs(s23)) + max(cc_iabs(m01), cc_iabs(m23));
     }
-    return s >> 1;
+    return s;
 }
 /* The same with the source block's half of the horizontal transform taken out of the loop over candidates: the Hadamard transform is
  * linear, so H(c - p) = H(c) + H(-p).  tc[r * 4 + k] = row r of the source block times Hadamard row k (cc_satd4x4_src), and every
@@ -170,12 +171,13 @@ __device__ __forceinline__ int cc_satd4x4_pre(const int tc[16], const uint32_t p
         t[r * 4 + 2] = cc_dp4a_us(p[r], CC_NEG4(CC_H2), tc[r * 4 + 2]);
         t[r * 4 + 3] = cc_dp4a_us(p[r], CC_NEG4(CC_H3), tc[r * 4 + 3]);
     }
+    /* second butterfly stage folded into the sum: |x + y| + |x - y| = 2 max(|x|, |y|), and the 2 is the SATD's final halving */
     int s = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         int s01 = t[i] + t[4 + i], m01 = t[i] - t[4 + i], s23 = t[8 + i] + t[12 + i], m23 = t[8 + i] - t[12 + i];
-        s += cc_iabs(s01 + s23) + cc_iabs(s01 - s23) + cc_iabs(m01 - m23) + cc_iabs(m01 + m23);
+        s += max(cc_iabs(s01), cc_iabs(s23)) + max(cc_iabs(m01), cc_iabs(m23));
     }
-    return s >> 1;
+    return s;
 }
 #endif

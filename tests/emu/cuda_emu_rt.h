@@ -49,6 +49,8 @@ static inline cudaError_t cudaPointerGetAttributes(struct cudaPointerAttributes 
 static inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t st) { (void)st; memset(d, v, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned f) { (void)f; *s = 0; return 0; }
+static inline cudaError_t cudaStreamCreateWithPriority(cudaStream_t *s, unsigned f, int p) { (void)f; (void)p; *s = 0; return 0; }
+static inline cudaError_t cudaDeviceGetStreamPriorityRange(int *lo, int *hi) { *lo = 0; *hi = 0; return 0; }
 static inline cudaError_t cudaStreamCreate(cudaStream_t *s) { *s = 0; return 0; }
 static inline cudaError_t cudaStreamDestroy(cudaStream_t s) { (void)s; return 0; }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t s) { (void)s; return 0; }
