@@ -218,38 +218,13 @@ __device__ __forceinline__ void sad_strip5(const uint8_t *r, int sy, const uint3
 }
 
 /* 8x8 partitions (north_star: "motion estimation over 16x16/8x8 partitions"; oracle/ref_enc.c me_l0, second half).
- * Every quadrant searches +-2 full-pel around the macroblock's best full-pel vector by SAD (lane = candidate, the four
- * quadrant SADs of a candidate come out of one pass over the 16 rows), then refines to half and quarter-pel by SATD
- * exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x four 4x4 blocks
- * (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
+ * Every quadrant takes its best of the 5 x 5 full-pel candidates around the coarse vector by SAD — the strips of the 16x16 search
+ * hold the four quadrant SADs of every candidate already (key4: per quadrant the lane's best (cost << 5 | candidate)) — then refines
+ * to half and quarter-pel by SATD exactly like the 16x16 search, all four quadrants at once: 8 lanes per quadrant = 2 candidates x
+ * four 4x4 blocks (skipped unless the full-pel quadrant costs already beat the full-pel 16x16 cost).
+ * (cx8, cy8) = the centre of the 5 x 5 window, full-pel.
  * Returns the P_8x8 cost (sum of the quadrant costs + 8 lambda of mb_type / sub_mb_type overhead) in all lanes. */
-__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, const uint8_t *tiles, int wx, int wy, int mb, int px, int py, int fbx, int fby, unsigned full16, const int pm[2], int lambda, int lane) {
-    /* lanes 0..19 = (candidate row dy = lane >> 2, source rows 4 g .. 4 g + 3 with g = lane & 3): rows of g < 2 belong to the top
-     * quadrants, the others to the bottom ones */
-    unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-    {
-        const int dyi = lane >> 2, g = lane & 3;
-        unsigned acc[5][2];
-#pragma unroll
-        for (int dx = 0; dx < 5; dx++) acc[dx][0] = acc[dx][1] = 0;
-        /* the strips lie inside the staged window (plane G: columns fbx - 2 .. fbx + 25, rows fby - 2 .. fby + 17 of it) */
-        if (lane < 20) sad_strip5(tiles + (fby + dyi - 2 + 4 * g - wy) * SP_W + fbx - 2 - wx, SP_W, sc + 16 * g, acc);
-        unsigned kl = 0xffffffffu, kr = 0xffffffffu;
-        const int my = fby + dyi - 2;
-        const int bits_y = cc_se_bits(4 * (my - pm[1]));
-#pragma unroll
-        for (int dx = 0; dx < 5; dx++) {
-            const unsigned sl = acc[dx][0] + __shfl_xor_sync(FULL, acc[dx][0], 1), sr = acc[dx][1] + __shfl_xor_sync(FULL, acc[dx][1], 1);
-            const unsigned bits = (unsigned)(lambda * (cc_se_bits(4 * (fbx + dx - 2 - pm[0])) + bits_y));
-            const unsigned cand = (unsigned)(dyi * 5 + dx);
-            kl = min(kl, ((sl + bits) << 5) | cand);
-            kr = min(kr, ((sr + bits) << 5) | cand);
-        }
-        if (lane < 20) {
-            if (g < 2) { key4[0] = kl; key4[1] = kr; }
-            else { key4[2] = kl; key4[3] = kr; }
-        }
-    }
+__device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, const uint8_t *tiles, int wx, int wy, int mb, const unsigned key4[4], int cx8, int cy8, unsigned full16, const int pm[2], int lambda, int lane) {
     const int p = lane >> 3, slot = (lane >> 2) & 1, b4 = lane & 3;
     int fi = 0;
     unsigned full8 = (unsigned)(8 * lambda);
@@ -259,7 +234,7 @@ __device__ __forceinline__ int me_8x8(const cc_kparams &k, const uint32_t *sc, c
         full8 += bq >> 5;
         if (q == p) fi = (int)(bq & 31u);
     }
-    int qx = 4 * (fbx + fi % 5 - 2), qy = 4 * (fby + fi / 5 - 2);
+    int qx = 4 * (cx8 + fi % 5 - 2), qy = 4 * (cy8 + fi / 5 - 2);
     /* partitions pay only where parts of the macroblock move differently: unless the four full-pel quadrant costs plus the
      * partition overhead already beat the full-pel 16x16 cost, the sub-pel refinement is not run and the macroblock stays one
      * partition */
@@ -424,6 +399,7 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
      * lanes 0..19 = (candidate row, four source rows) of the 5 x 5 window, five candidates each (sad_strip5), from the staged
      * window; lanes 20..23 / 24..27 = the predictor / the zero vector as the centre of a strip of their own, from global memory */
     unsigned key = 0xffffffffu;
+    unsigned key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu}; /* 8x8 quadrants: best full-pel candidate of the window, per lane */
     {
         const int g = lane & 3, dyi = lane >> 2;
         int sx = l1x - 2, syy = l1y + dyi - 2;
@@ -436,14 +412,23 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
         if (lane < 28) sad_strip5(sp, lane < 20 ? SP_W : k.sy, sc + 16 * g, acc);
         const int bits_y = cc_se_bits(4 * (syy - pm[1]));
 #pragma unroll
+        unsigned kl = 0xffffffffu, kr = 0xffffffffu;
         for (int dx = 0; dx < 5; dx++) {
-            unsigned sad = acc[dx][0] + acc[dx][1];
-            sad += __shfl_xor_sync(FULL, sad, 1);
+            /* rows 4 g .. 4 g + 3 of the left / right eight columns; with the lane next door (g ^ 1) that is a quadrant */
+            const unsigned sl = acc[dx][0] + __shfl_xor_sync(FULL, acc[dx][0], 1), sr = acc[dx][1] + __shfl_xor_sync(FULL, acc[dx][1], 1);
+            unsigned sad = sl + sr;
             sad += __shfl_xor_sync(FULL, sad, 2);
-            const unsigned cost = sad + (unsigned)(lambda * (cc_se_bits(4 * (sx + dx - pm[0])) + bits_y));
+            const unsigned bits = (unsigned)(lambda * (cc_se_bits(4 * (sx + dx - pm[0])) + bits_y));
+            const unsigned cost = sad + bits;
             const bool ok = lane < 20 || (lane < 28 && dx == 2);
             const unsigned cand = lane < 20 ? (unsigned)(2 + dyi * 5 + dx) : (lane < 24 ? 0u : 1u);
             if (ok) key = min(key, (cost << 5) | cand);
+            kl = min(kl, ((sl + bits) << 5) | (unsigned)(dyi * 5 + dx));
+            kr = min(kr, ((sr + bits) << 5) | (unsigned)(dyi * 5 + dx));
+        }
+        if (lane < 20) {
+            if (g < 2) { key4[0] = kl; key4[1] = kr; }
+            else { key4[2] = kl; key4[3] = kr; }
         }
     }
     const unsigned bk = __reduce_min_sync(FULL, key);
@@ -499,7 +484,13 @@ __global__ void __launch_bounds__(ME0_WARPS * 32) k_me_l0(cc_kparams k) {
     }
     const int cost16 = (int)(bestkey >> 5);
     int part = 0;
-    if (k.part8) part = me_8x8(k, sc, tiles, wx, wy, mb, px, py, fbx, fby, bk >> 5, pm, lambda, lane) < cost16;
+    if (k.part8) {
+        /* the quadrants search the same 5 x 5 window as the macroblock; when the predictor or the zero vector won from outside it,
+         * the macroblock stays one partition (oracle/ref_enc.c me_l0) */
+        if (cc_iabs(fbx - l1x) > 2 || cc_iabs(fby - l1y) > 2) {
+            if (lane < 8) { ((uint32_t *)k.me8[mb].mv)[lane & 3] = 0u; ((uint32_t *)k.me8[mb].satd)[lane & 3] = 0u; }
+        } else part = me_8x8(k, sc, tiles, wx, wy, mb, key4, l1x, l1y, bk >> 5, pm, lambda, lane) < cost16;
+    }
     if (lane == 0) {
         k.me[mb].mv[0] = (int16_t)bx; k.me[mb].mv[1] = (int16_t)by; k.me[mb].satd = bestsatd; k.me[mb].part = part;
     }

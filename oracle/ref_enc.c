@@ -176,12 +176,18 @@ static void me_l0(ref_enc *e, int mbx, int mby) {
      * summed cost plus 8 lambda (mb_type + four sub_mb_type code lengths over P_L0_16x16) beats the 16x16 cost. */
     int cost8 = 8 * lambda, f8[4][2];
     unsigned full8 = (unsigned)(8 * lambda);
+    /* The quadrants search the 5 x 5 full-pel window of the macroblock's own search (around the coarse vector): the product gets
+     * their SADs from the strips it has just read.  When the predictor or the zero vector won from outside that window the
+     * macroblock stays one partition.  (The upper-bound mode centres the window on its own winner.) */
+    const int cx8 = e->effort ? bmx : 2 * mi->l1_mv[0], cy8 = e->effort ? bmy : 2 * mi->l1_mv[1];
+    memset(mi->me_mv8, 0, sizeof mi->me_mv8); memset(mi->me_satd8, 0, sizeof mi->me_satd8);
+    if (iabs(bmx - cx8) > 2 || iabs(bmy - cy8) > 2) return;
     for (int p = 0; p < 4; p++) {
         const uint8_t *c8 = cur + (p >> 1) * 8 * sy + (p & 1) * 8, *r8 = ref + (p >> 1) * 8 * sy + (p & 1) * 8;
         unsigned b8 = ~0u;
-        int fx = bmx, fy = bmy;
+        int fx = cx8, fy = cy8;
         for (int i = 0; i < 25; i++) {
-            int mx = bmx + i % 5 - 2, my = bmy + i / 5 - 2;
+            int mx = cx8 + i % 5 - 2, my = cy8 + i / 5 - 2;
             unsigned c = (unsigned)ref_sad(c8, sy, r8 + my * sy + mx, sy, 8, 8) +
                          (unsigned)(lambda * (ref_mv_bits(4 * (mx - pm[0])) + ref_mv_bits(4 * (my - pm[1]))));
             unsigned key = (c << 5) | (unsigned)i;
