@@ -125,6 +125,25 @@ __device__ __forceinline__ int cc_dp4a_us(uint32_t a, uint32_t b, int c) {
     return d;
 #endif
 }
+/* c + (signed low half of a) * (signed byte 0 of b) + (signed high half of a) * (signed byte 1 of b): IDP.2A.LO; _hi: bytes 2 and 3 of b */
+__device__ __forceinline__ int cc_dp2a_lo(uint32_t a, uint32_t b, int c) {
+#ifdef CC_EMU_BUILD
+    return c + (int)(int16_t)(a & 0xffffu) * (int)(int8_t)(b & 255u) + (int)(int16_t)(a >> 16) * (int)(int8_t)((b >> 8) & 255u);
+#else
+    int d;
+    asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#endif
+}
+__device__ __forceinline__ int cc_dp2a_hi(uint32_t a, uint32_t b, int c) {
+#ifdef CC_EMU_BUILD
+    return c + (int)(int16_t)(a & 0xffffu) * (int)(int8_t)((b >> 16) & 255u) + (int)(int16_t)(a >> 16) * (int)(int8_t)(b >> 24);
+#else
+    int d;
+    asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#endif
+}
 /* rows of the 4-point Hadamard matrix and their negatives as packed signed bytes (pixel 0 = low byte) */
 #define CC_H0 0x01010101u /* + + + + */
 #define CC_H1 0xffff0101u /* + + - - */

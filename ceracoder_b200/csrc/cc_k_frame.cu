@@ -130,10 +130,25 @@ __global__ void k_border(cc_kparams k) {
 #define HP_TH 16
 __device__ __forceinline__ int cc_tap6(int a, int b, int c, int d, int e, int f) { return a - 5 * b + 20 * c + 20 * d - 5 * e + f; }
 
-/* CTA = 256 threads, output tile 64x16; reads the border-extended reconstruction (run after k_border) */
+/* CTA = 256 threads, output tile 64x16; reads the border-extended reconstruction (run after k_border).
+ * The 6-tap filter (1, -5, 20, 20, -5, 1) runs as dot products on packed samples: horizontally the six bytes of an output sit in
+ * two (funnel-shifted) words -> two IDP.4A; vertically a 4x4 byte transpose (PRMT) puts a column's first four rows into one word ->
+ * two IDP.4A per output; the centre plane filters the 16-bit horizontal sums vertically with three IDP.2A per output.
+ * thread = four horizontally adjacent outputs of each plane. */
+#define HP_A 0x1414fb01u  /* ( 1, -5, 20, 20) as signed bytes, first tap in the low byte */
+#define HP_B0 0x01fb0000u /* ( 0,  0, -5,  1) */
+#define HP_B1 0x000001fbu /* (-5,  1,  0,  0) */
+#define HP_B3 0x0001fb00u /* ( 0, -5,  1,  0) */
+__device__ __forceinline__ void hp_row4(const uint32_t *gw, int t[4]) { /* gw: the aligned word left of the four outputs, then theirs, then the next */
+    const uint32_t w0 = gw[0], w1 = gw[1], w2 = gw[2];
+    t[0] = cc_dp4a_us(w1, HP_B0, cc_dp4a_us(__funnelshift_r(w0, w1, 16), HP_A, 0));
+    t[1] = cc_dp4a_us(__funnelshift_r(w1, w2, 24), HP_B1, cc_dp4a_us(__funnelshift_r(w0, w1, 24), HP_A, 0));
+    t[2] = cc_dp4a_us(w2, HP_B1, cc_dp4a_us(w1, HP_A, 0));
+    t[3] = cc_dp4a_us(w2, HP_B3, cc_dp4a_us(__funnelshift_r(w1, w2, 8), HP_A, 0));
+}
 __global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
-    __shared__ uint8_t g[HP_TH + 5][HP_TW + 8];  /* rows y-2..y+18, cols x-2..x+69 (72 used) */
-    __shared__ int16_t t[HP_TH + 5][HP_TW];      /* unrounded horizontal 6-tap of every staged row */
+    __shared__ uint32_t g[HP_TH + 5][18];        /* rows y-2..y+18, bytes x-4..x+67 */
+    __shared__ uint32_t t2[HP_TH + 5][HP_TW / 2]; /* unrounded horizontal 6-tap of every staged row, two int16 per word */
     const int x0 = -CC_HPAD + (int)blockIdx.x * HP_TW, y0 = -CC_HPAD + (int)blockIdx.y * HP_TH;
     const int xmax = k.W + CC_PAD - 1, ymax = k.H + CC_PAD - 1; /* last valid sample of the bordered plane */
     const uint8_t *G = k.rec[0];
@@ -143,30 +158,52 @@ __global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
         uint32_t v = 0;
         if (x + 3 <= xmax) v = *(const uint32_t *)(G + (ptrdiff_t)y * k.sy + x);
         else for (int b = 0; b < 4; b++) v |= (uint32_t)G[(ptrdiff_t)y * k.sy + min(x + b, xmax)] << (8 * b);
-        *(uint32_t *)&g[r][4 * c] = v;
+        g[r][c] = v;
     }
     __syncthreads();
-    /* g[r][cx] holds sample (x0-4+cx, y0-2+r) */
-    for (int i = threadIdx.x; i < (HP_TH + 5) * HP_TW; i += 256) {
-        int r = i / HP_TW, c = i % HP_TW;
-        const uint8_t *p = &g[r][c + 4];
-        t[r][c] = (int16_t)cc_tap6(p[-2], p[-1], p[0], p[1], p[2], p[3]);
+    /* g[r] byte cx holds sample (x0-4+cx, y0-2+r) */
+    const int r = threadIdx.x >> 4, gi = threadIdx.x & 15;
+    uint32_t vb;
+    { /* horizontal sums of the thread's own output row (staged row r + 2): plane b comes straight from them */
+        int t[4];
+        hp_row4(&g[r + 2][gi], t);
+        t2[r + 2][2 * gi] = ((uint32_t)t[0] & 0xffffu) | ((uint32_t)t[1] << 16);
+        t2[r + 2][2 * gi + 1] = ((uint32_t)t[2] & 0xffffu) | ((uint32_t)t[3] << 16);
+        vb = (uint32_t)cc_clip255((t[0] + 16) >> 5) | ((uint32_t)cc_clip255((t[1] + 16) >> 5) << 8) |
+             ((uint32_t)cc_clip255((t[2] + 16) >> 5) << 16) | ((uint32_t)cc_clip255((t[3] + 16) >> 5) << 24);
+    }
+    if (threadIdx.x < 80) { /* the five staged rows above / below the tile's own sixteen */
+        const int q = threadIdx.x >> 4, rr = q < 2 ? q : 16 + q;
+        int t[4];
+        hp_row4(&g[rr][gi], t);
+        t2[rr][2 * gi] = ((uint32_t)t[0] & 0xffffu) | ((uint32_t)t[1] << 16);
+        t2[rr][2 * gi + 1] = ((uint32_t)t[2] & 0xffffu) | ((uint32_t)t[3] << 16);
     }
     __syncthreads();
-    /* each thread: 4 horizontally adjacent outputs of each plane */
-    int r = threadIdx.x >> 4, c4 = (threadIdx.x & 15) * 4;
-    int y = y0 + r, x = x0 + c4;
+    const int y = y0 + r, x = x0 + 4 * gi;
     if (x >= k.W + CC_HPAD || y >= k.H + CC_HPAD) return;
-    uint32_t vb = 0, vh = 0, vj = 0;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        int c = c4 + i;
-        int b = cc_clip255((t[r + 2][c] + 16) >> 5);
-        int hv = cc_clip255((cc_tap6(g[r][c + 4], g[r + 1][c + 4], g[r + 2][c + 4], g[r + 3][c + 4], g[r + 4][c + 4], g[r + 5][c + 4]) + 16) >> 5);
-        int j = cc_clip255((cc_tap6(t[r][c], t[r + 1][c], t[r + 2][c], t[r + 3][c], t[r + 4][c], t[r + 5][c]) + 512) >> 10);
-        vb |= (uint32_t)b << (8 * i); vh |= (uint32_t)hv << (8 * i); vj |= (uint32_t)j << (8 * i);
+    uint32_t vh, vj;
+    { /* plane h: vertical filter of the samples; rows r .. r + 5 of the thread's own word */
+        const uint32_t R0 = g[r][gi + 1], R1 = g[r + 1][gi + 1], R2 = g[r + 2][gi + 1], R3 = g[r + 3][gi + 1], R4 = g[r + 4][gi + 1], R5 = g[r + 5][gi + 1];
+        const uint32_t a0 = __byte_perm(R0, R1, 0x5140), a1 = __byte_perm(R2, R3, 0x5140), a2 = __byte_perm(R0, R1, 0x7362), a3 = __byte_perm(R2, R3, 0x7362);
+        const uint32_t u0 = __byte_perm(R4, R5, 0x5140), u1 = __byte_perm(R4, R5, 0x7362);
+        const int h0 = cc_dp4a_us(u0, HP_B1, cc_dp4a_us(__byte_perm(a0, a1, 0x5410), HP_A, 16));
+        const int h1 = cc_dp4a_us(u0, HP_B0, cc_dp4a_us(__byte_perm(a0, a1, 0x7632), HP_A, 16));
+        const int h2 = cc_dp4a_us(u1, HP_B1, cc_dp4a_us(__byte_perm(a2, a3, 0x5410), HP_A, 16));
+        const int h3 = cc_dp4a_us(u1, HP_B0, cc_dp4a_us(__byte_perm(a2, a3, 0x7632), HP_A, 16));
+        vh = (uint32_t)cc_clip255(h0 >> 5) | ((uint32_t)cc_clip255(h1 >> 5) << 8) | ((uint32_t)cc_clip255(h2 >> 5) << 16) | ((uint32_t)cc_clip255(h3 >> 5) << 24);
     }
-    ptrdiff_t o = (ptrdiff_t)y * k.sy + x;
+    { /* plane j: vertical filter of the horizontal sums */
+        int j[4];
+#pragma unroll
+        for (int w = 0; w < 2; w++) {
+            const uint32_t T0 = t2[r][2 * gi + w], T1 = t2[r + 1][2 * gi + w], T2 = t2[r + 2][2 * gi + w], T3 = t2[r + 3][2 * gi + w], T4 = t2[r + 4][2 * gi + w], T5 = t2[r + 5][2 * gi + w];
+            j[2 * w] = cc_dp2a_lo(__byte_perm(T4, T5, 0x5410), HP_B1, cc_dp2a_hi(__byte_perm(T2, T3, 0x5410), HP_A, cc_dp2a_lo(__byte_perm(T0, T1, 0x5410), HP_A, 512)));
+            j[2 * w + 1] = cc_dp2a_lo(__byte_perm(T4, T5, 0x7632), HP_B1, cc_dp2a_hi(__byte_perm(T2, T3, 0x7632), HP_A, cc_dp2a_lo(__byte_perm(T0, T1, 0x7632), HP_A, 512)));
+        }
+        vj = (uint32_t)cc_clip255(j[0] >> 10) | ((uint32_t)cc_clip255(j[1] >> 10) << 8) | ((uint32_t)cc_clip255(j[2] >> 10) << 16) | ((uint32_t)cc_clip255(j[3] >> 10) << 24);
+    }
+    const ptrdiff_t o = (ptrdiff_t)y * k.sy + x;
     *(uint32_t *)(k.hb + o) = vb;
     *(uint32_t *)(k.hh + o) = vh;
     *(uint32_t *)(k.hj + o) = vj;
