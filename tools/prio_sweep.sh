@@ -1,4 +1,4 @@
-for pr in 0 2 1 3; do for s in 8 16; do
+for pr in ${PRS:-0 2 1 3}; do for s in ${STREAMS_LIST:-8 16}; do
 CC_PRIO=$pr python bench.py --no-cpu-baseline --streams $s --steps 6 > gpurun_out/pr_${pr}_$s.json 2>/dev/null
 python - <<PY
 import json

@@ -1,4 +1,4 @@
-for kb in 0 64 120 180; do for s in 8 16; do
+for kb in ${KBS:-0 64 120 180}; do for s in ${STREAMS_LIST:-8 16}; do
 CC_WAVEFRONT_SMEM_KB=$kb python bench.py --no-cpu-baseline --streams $s --steps 6 > gpurun_out/sm_${kb}_$s.json 2>/dev/null
 python - <<PY
 import json
