@@ -42,7 +42,7 @@ sys.path.insert(0, ROOT)
 W, H, FPS = 1920, 1080, 60
 FSZ = W * H * 3 // 2
 STREAMS = 8
-FRAMES_PER_STEP = 160           # per stream; the driver's --steps 20 gives 3200 timed frames per stream (> 5 s)
+FRAMES_PER_STEP = 200           # per stream; the driver's --steps 20 gives 4000 timed frames per stream (> 5 s at 6000 frames/s)
 POOL = 900                      # S2 frames 0..899: scenes of 300, looped -> a cut every 300 frames
 STREAM_SHIFT = 113              # stream k plays the loop 113 frames ahead of stream k - 1
 GOP_PHASE = 7                   # and sits 7 frames further into its GOP (live streams do not emit their IDR frames in the same instant)
