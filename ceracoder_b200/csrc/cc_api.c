@@ -563,11 +563,10 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
 #define STAGE2(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st2); pev_used[i] = 1; } } while (0)
     STAGE2(CC_STAGE_DEBLOCK);
     if (!(e->dbg_skip & (1 << CC_STAGE_DEBLOCK))) e->launches += cck_deblock(k, e->st2);
-    STAGE2(CC_STAGE_BORDER);
-    e->launches += cck_border(k, e->st2);
+    STAGE2(CC_STAGE_BORDER); /* no launch of its own any more: the border CTAs ride behind the half-pel tiles */
     STAGE2(CC_STAGE_HPEL);
-    e->launches += cck_hpel(k, e->st2);
-    if (DUP(CC_STAGE_HPEL)) cck_hpel(k, e->st2);
+    e->launches += cck_hpel_border(k, e->st2);
+    if (DUP(CC_STAGE_HPEL)) cck_hpel_border(k, e->st2);
     STAGE2(CC_STAGE_L1REF); /* nothing left here: the half-resolution reference is written with the reconstruction */
     STAGE2(CC_N_STAGES);
 #undef STAGE2

@@ -145,6 +145,7 @@ int cck_ingest(const cc_kparams *k, int fmt, cudaStream_t st);
 int cck_finish_ref(const cc_kparams *k, cudaStream_t st); /* rec -> borders, half-pel planes */
 int cck_border(const cc_kparams *k, cudaStream_t st);
 int cck_hpel(const cc_kparams *k, cudaStream_t st);
+int cck_hpel_border(const cc_kparams *k, cudaStream_t st); /* both in one launch (k_hpel reads the picture only) */
 int cck_l1border(const cc_kparams *k, cudaStream_t st); /* edge replication of the half-resolution reference (before the coarse search) */
 int cck_me_l1_prepare(cc_kparams *k); /* builds k->tmap_l1 (after the planes are allocated); CC_OK or CC_ERR_CUDA */
 int cck_me_l1(const cc_kparams *k, cudaStream_t st);

@@ -95,8 +95,8 @@ __global__ void k_ingest_packed(cc_kparams k) {
 
 /* ---- k_border ---------------------------------------------------------------------------------------- */
 /* grid.y = plane (0 luma, 1 Cb, 2 Cr); one thread per border byte-quad */
-__global__ void k_border(cc_kparams k) {
-    int pl = blockIdx.y;
+/* blk of nblk blocks of plane pl (256 threads each, grid-stride) */
+__device__ __forceinline__ void border_work(const cc_kparams &k, int pl, int blk, int nblk) {
     int W = pl ? k.W >> 1 : k.W, H = pl ? k.H >> 1 : k.H, pad = pl ? CC_PADC : CC_PAD, s = pl ? k.sc : k.sy;
     uint8_t *P = k.rec[pl];
     int fullw = W + 2 * pad;
@@ -104,7 +104,7 @@ __global__ void k_border(cc_kparams k) {
     int groups_lr = (2 * pad) >> 2;   /* left+right groups in a picture row */
     int groups_full = fullw >> 2;     /* groups of a row entirely in the top/bottom border */
     int n_mid = H * groups_lr, n_tb = 2 * pad * groups_full;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_mid + n_tb; i += gridDim.x * blockDim.x) {
+    for (int i = blk * 256 + threadIdx.x; i < n_mid + n_tb; i += nblk * 256) {
         int y, x;
         if (i < n_mid) {
             y = i / groups_lr;
@@ -124,6 +124,7 @@ __global__ void k_border(cc_kparams k) {
         *(uint32_t *)(P + (ptrdiff_t)y * s + x) = v;
     }
 }
+__global__ void __launch_bounds__(256) k_border(cc_kparams k) { border_work(k, blockIdx.y, blockIdx.x, gridDim.x); }
 
 /* ---- k_hpel ------------------------------------------------------------------------------------------ */
 #define HP_TW 64
@@ -146,18 +147,19 @@ __device__ __forceinline__ void hp_row4(const uint32_t *gw, int t[4]) { /* gw: t
     t[2] = cc_dp4a_us(w2, HP_B1, cc_dp4a_us(w1, HP_A, 0));
     t[3] = cc_dp4a_us(w2, HP_B3, cc_dp4a_us(__funnelshift_r(w1, w2, 8), HP_A, 0));
 }
-__global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
+__device__ __forceinline__ void hpel_tile(const cc_kparams &k, int bx, int by) {
     __shared__ uint32_t g[HP_TH + 5][18];        /* rows y-2..y+18, bytes x-4..x+67 */
     __shared__ uint32_t t2[HP_TH + 5][HP_TW / 2]; /* unrounded horizontal 6-tap of every staged row, two int16 per word */
-    const int x0 = -CC_HPAD + (int)blockIdx.x * HP_TW, y0 = -CC_HPAD + (int)blockIdx.y * HP_TH;
-    const int xmax = k.W + CC_PAD - 1, ymax = k.H + CC_PAD - 1; /* last valid sample of the bordered plane */
+    const int x0 = -CC_HPAD + bx * HP_TW, y0 = -CC_HPAD + by * HP_TH;
     const uint8_t *G = k.rec[0];
+    /* samples outside the picture are the nearest picture sample (what k_border replicates into the plane's border): the reads are
+     * clamped to the picture, so this kernel does not wait for k_border */
     for (int i = threadIdx.x; i < (HP_TH + 5) * 18; i += 256) { /* 18 words per staged row */
         int r = i / 18, c = i % 18;
-        int y = min(y0 - 2 + r, ymax), x = x0 - 4 + 4 * c; /* staged cols start at x0-4 (aligned); col index = x-(x0-4) */
+        int y = min(max(y0 - 2 + r, 0), k.H - 1), x = x0 - 4 + 4 * c; /* staged cols start at x0-4 (aligned); col index = x-(x0-4) */
         uint32_t v = 0;
-        if (x + 3 <= xmax) v = *(const uint32_t *)(G + (ptrdiff_t)y * k.sy + x);
-        else for (int b = 0; b < 4; b++) v |= (uint32_t)G[(ptrdiff_t)y * k.sy + min(x + b, xmax)] << (8 * b);
+        if (x >= 0 && x + 3 <= k.W - 1) v = *(const uint32_t *)(G + (ptrdiff_t)y * k.sy + x);
+        else for (int b = 0; b < 4; b++) v |= (uint32_t)G[(ptrdiff_t)y * k.sy + min(max(x + b, 0), k.W - 1)] << (8 * b);
         g[r][c] = v;
     }
     __syncthreads();
@@ -208,6 +210,16 @@ __global__ void __launch_bounds__(256) k_hpel(cc_kparams k) {
     *(uint32_t *)(k.hh + o) = vh;
     *(uint32_t *)(k.hj + o) = vj;
 }
+__global__ void __launch_bounds__(256) k_hpel(cc_kparams k) { hpel_tile(k, (int)blockIdx.x, (int)blockIdx.y); }
+/* What finishes a reconstruction into a reference in ONE launch: the half-pel tiles (which read the picture only) and, in the CTAs
+ * behind them, the border replication of the three planes — nothing in either depends on the other, and the in-loop filter's tail
+ * is on every stream's critical cycle (a launch less is 0.03 ms of it).  gx x gy tiles, then HB_BLOCKS border CTAs per plane. */
+#define HB_BLOCKS 48
+__global__ void __launch_bounds__(256) k_hpel_border(cc_kparams k, int gx, int ntiles) {
+    const int id = (int)blockIdx.x;
+    if (id < ntiles) hpel_tile(k, id % gx, id / gx);
+    else border_work(k, (id - ntiles) / HB_BLOCKS, (id - ntiles) % HB_BLOCKS, HB_BLOCKS);
+}
 
 /* ---- k_l1border -------------------------------------------------------------------------------------- */
 /* The half-resolution reference is written macroblock by macroblock where the reconstruction is published (cc_k_mb.cu
@@ -240,6 +252,11 @@ extern "C" int cck_border(const cc_kparams *k, cudaStream_t st) {
 extern "C" int cck_hpel(const cc_kparams *k, cudaStream_t st) {
     dim3 gh((unsigned)((k->W + 2 * CC_HPAD + HP_TW - 1) / HP_TW), (unsigned)((k->H + 2 * CC_HPAD + HP_TH - 1) / HP_TH));
     CC_LAUNCH(k_hpel, gh, dim3(256), st, *k);
+    return 1;
+}
+extern "C" int cck_hpel_border(const cc_kparams *k, cudaStream_t st) {
+    const int gx = (k->W + 2 * CC_HPAD + HP_TW - 1) / HP_TW, gy = (k->H + 2 * CC_HPAD + HP_TH - 1) / HP_TH;
+    CC_LAUNCH(k_hpel_border, dim3((unsigned)(gx * gy + 3 * HB_BLOCKS)), dim3(256), st, *k, gx, gx * gy);
     return 1;
 }
 extern "C" int cck_l1border(const cc_kparams *k, cudaStream_t st) {
