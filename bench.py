@@ -531,7 +531,7 @@ def main():
                     "au_bytes_per_step": int(r_e2e["au_bytes"] / args.steps), "ms_per_step": ms_e2e / args.steps, "host_frames": "page-locked (cc_host_register)"},
             "e2e_pageable": {"value": e2e_pg, "unit": "frames/s", "frames": int(f_pg), "staged_frames": int(r_page["staged"]),
                              "note": "pageable host frames, as gst_video_frame_map hands them to the element: each frame is copied by the calling thread into the handle's "
-                                     "pinned staging frame (cc_enc_submit), then uploaded asynchronously"},
+                                     "pinned staging frame, then uploaded asynchronously; inside cc_enc_encode_sequence that copy (and the upload) of frame i + 1 runs while the device codes frame i"},
             "timed_region": {"frames_per_stream": fps_step * args.steps, "frames": int(f_dev), "idr_frames_rank0": int(r_dev["n_idr"]), "frames_rank0": int(r_dev["frames"]),
                              "seconds": ms_dev / 1e3, "scene_cuts_per_stream": (fps_step * args.steps) // 300 if n_pool >= POOL else 0},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "int_roofline": introof, "cpu_baseline": cpu, "quality": quality,

@@ -77,6 +77,7 @@ struct cc_enc {
     /* upload of the NEXT frame while this one is coded (cc_enc_encode_sequence, planar I420 in page-locked host or device memory): a second
      * set of source planes, filled on a stream of its own; cc_enc_submit of that frame swaps the sets instead of copying */
     uint8_t *cur_alt[3];
+    uint8_t *stage_host_alt;  /* a second pinned staging frame: a pageable frame that runs ahead is copied here */
     cudaStream_t st_up;
     cudaEvent_t ev_up;
     const uint8_t *pf_plane0; /* plane[0] of the frame sitting in cur_alt, or NULL */
@@ -315,6 +316,7 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     e->rbsp_cap = (size_t)k->rps * k->mb_w * CC_BS_BYTES_PER_MB + 4096;
     e->stage_bytes = (size_t)k->w * k->h * (p->format == CC_FMT_BGRX ? 4 : (p->format == CC_FMT_YUY2 ? 2 : 1)) * (p->format <= CC_FMT_NV12 ? 3 : 2) / 2;
     if (rc == CC_OK && cudaHostAlloc((void **)&e->stage_host, e->stage_bytes, cudaHostAllocDefault) != cudaSuccess) rc = CC_ERR_NOMEM;
+    if (rc == CC_OK && e->p.format == CC_FMT_I420 && cudaHostAlloc((void **)&e->stage_host_alt, e->stage_bytes, cudaHostAllocDefault) != cudaSuccess) rc = CC_ERR_NOMEM;
     e->au = (uint8_t *)malloc(e->au_cap);
     e->rbsp = (uint8_t *)malloc(e->rbsp_cap);
     e->cav.mb_w = k->mb_w; e->cav.mb_h = k->mb_h; e->cav.rps = k->rps;
@@ -380,6 +382,7 @@ void cc_enc_close(cc_enc *e) {
     pool_stop(e);
     if (e->out_host) cudaFreeHost(e->out_host);
     if (e->stage_host) cudaFreeHost(e->stage_host);
+    if (e->stage_host_alt) cudaFreeHost(e->stage_host_alt);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (int i = 0; i < 2 * (CC_N_STAGES + 2); i++) if (e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) cudaEventDestroy(e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]);
@@ -712,18 +715,33 @@ int cc_enc_encode(cc_enc *e, const cc_frame *in, unsigned flags, cc_packet *out)
     return rc != CC_OK ? rc : cc_enc_collect(e, out);
 }
 
-/* starts the upload of the frame that will be submitted next (planar I420 in page-locked host memory or device memory only; any
- * other frame is simply uploaded by its own cc_enc_submit).  The set of source planes it goes to was last read by the frame before
+/* starts the upload of the frame that will be submitted next (planar I420; any other format is simply uploaded by its own
+ * cc_enc_submit).  The set of source planes it goes to was last read by the frame before
  * the one in flight, which has been collected. */
 static void enc_prefetch(cc_enc *e, const cc_frame *in, unsigned flags) {
     cc_kparams *k = &e->k;
     if (e->p.format != CC_FMT_I420 || !e->cur_alt[0] || !in->plane[0] || !in->plane[1] || !in->plane[2]) return;
     if (in->stride[0] < k->w || in->stride[1] < k->w / 2 || in->stride[2] < k->w / 2) return;
-    if (!(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) return;
+    const uint8_t *pl[3] = {in->plane[0], in->plane[1], in->plane[2]};
+    int st[3] = {in->stride[0], in->stride[1], in->stride[2]};
+    if (!(flags & CC_FRAME_DEVICE) && !host_is_pinned(in->plane[0])) {
+        /* pageable memory (a mapped GstBuffer): the calling thread copies the frame into the second pinned staging frame now, while the
+         * device codes the frame before it; the buffer's previous upload has long finished, but that is waited for, not assumed */
+        if (!e->stage_host_alt || cudaEventSynchronize(e->ev_up) != cudaSuccess) { cudaGetLastError(); return; }
+        uint8_t *d = e->stage_host_alt;
+        for (int i = 0; i < 3; i++) {
+            const size_t rowb = i == 0 ? (size_t)k->w : (size_t)k->w / 2, rows = i == 0 ? (size_t)k->h : (size_t)k->h / 2;
+            if ((size_t)in->stride[i] == rowb) memcpy(d, in->plane[i], rowb * rows);
+            else for (size_t r = 0; r < rows; r++) memcpy(d + r * rowb, in->plane[i] + r * (size_t)in->stride[i], rowb);
+            pl[i] = d; st[i] = (int)rowb;
+            d += rowb * rows;
+        }
+        e->staged_frames++;
+    }
     const enum cudaMemcpyKind kind = (flags & CC_FRAME_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    if (cudaMemcpy2DAsync(e->cur_alt[0], (size_t)k->sy, in->plane[0], (size_t)in->stride[0], (size_t)k->w, (size_t)k->h, kind, e->st_up) != cudaSuccess ||
-        cudaMemcpy2DAsync(e->cur_alt[1], (size_t)k->sc, in->plane[1], (size_t)in->stride[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
-        cudaMemcpy2DAsync(e->cur_alt[2], (size_t)k->sc, in->plane[2], (size_t)in->stride[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
+    if (cudaMemcpy2DAsync(e->cur_alt[0], (size_t)k->sy, pl[0], (size_t)st[0], (size_t)k->w, (size_t)k->h, kind, e->st_up) != cudaSuccess ||
+        cudaMemcpy2DAsync(e->cur_alt[1], (size_t)k->sc, pl[1], (size_t)st[1], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
+        cudaMemcpy2DAsync(e->cur_alt[2], (size_t)k->sc, pl[2], (size_t)st[2], (size_t)k->w / 2, (size_t)k->h / 2, kind, e->st_up) != cudaSuccess ||
         cudaEventRecord(e->ev_up, e->st_up) != cudaSuccess) { cudaGetLastError(); return; }
     e->pf_plane0 = in->plane[0];
 }

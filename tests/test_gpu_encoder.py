@@ -194,7 +194,7 @@ def test_one_slice_per_picture_under_rate_control_many_frames(lib):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("where", ["pinned", "device"])
+@pytest.mark.parametrize("where", ["pinned", "device", "pageable"])
 def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where):
     """cc_enc_encode_sequence uploads frame i + 1 into a second set of source planes while frame i is coded (page-locked host or device
     frames): same access units and reconstruction as one pageable frame at a time, and every frame but the first arrives that way."""
@@ -214,8 +214,12 @@ def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where)
     frames = [src.frame(i) for i in range(n)]
     rates = [3000] * 4 + [800] * 5
     fsz = w * h * 3 // 2
+    keep = None
     if where == "pinned":
         base = L.cc_host_alloc(n * fsz)
+    elif where == "pageable":  # what gst_video_frame_map hands the element: staged through the second pinned frame
+        keep = np.zeros(n * fsz, np.uint8)
+        base = keep.ctypes.data
     else:
         base = L.cc_dev_alloc(n * fsz)
     assert base
@@ -223,7 +227,7 @@ def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where)
     for i, (y, u, v) in enumerate(frames):
         tight = np.concatenate([y.ravel(), u.ravel(), v.ravel()])
         p = base + i * fsz
-        if where == "pinned":
+        if where != "device":
             C.memmove(p, tight.ctypes.data, fsz)
         else:
             assert L.cc_dev_upload(p, tight.ctypes.data, fsz) == 0
@@ -254,5 +258,5 @@ def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where)
     a.close(); b.close()
     if where == "pinned":
         L.cc_host_free(C.c_void_p(base))
-    else:
+    elif where == "device":
         L.cc_dev_free(C.c_void_p(base))
