@@ -149,8 +149,9 @@ int cc_enc_get_stage_ms(const cc_enc *h, double *ms_sum /*[CC_STAGE_COUNT]*/, lo
  * thread, into a pinned frame the handle owns, so that the upload itself is asynchronous; page-locked frames (cc_host_alloc) and
  * device frames are used where they lie.  Count of frames that took the staging copy since open: */
 long cc_enc_staged_frames(const cc_enc *h);
-/* cc_enc_encode_sequence starts the upload of frame i + 1 while frame i is being coded (planar I420 in page-locked host memory or in
- * device memory; a second set of source planes per handle).  Count of frames that arrived that way since open: */
+/* cc_enc_encode_sequence starts the upload of frame i + 1 while frame i is being coded (planar I420; a second set of source planes
+ * per handle; pageable frames are copied to a second pinned staging frame by the calling thread first).  Count of frames that
+ * arrived that way since open: */
 long cc_enc_prefetched_frames(const cc_enc *h);
 /* number of kernel launches issued by this handle since open */
 long cc_enc_kernel_launches(const cc_enc *h);
