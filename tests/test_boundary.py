@@ -119,3 +119,12 @@ def test_parameter_errors_on_emulated_library():
             CudaH264Enc(w, h, lib=L)
     assert L.cc_strerror(-5).decode().startswith("output buffer")
     assert b"ceracuda" in L.cc_version()
+
+
+def test_stage_names_of_the_mirror_match_the_header():
+    """CudaH264Enc.STAGES names the CC_STAGE_* enum of include/ceracuda.h in order (bench.py's stage_ms_per_frame keys)"""
+    from ceracoder_b200.encoder import CudaH264Enc
+    hdr = open(os.path.join(ROOT, "include", "ceracuda.h")).read()
+    m = re.search(r"enum \{ (CC_STAGE_UPLOAD.*?CC_STAGE_COUNT) \}", hdr, re.S)
+    names = [n.strip()[len("CC_STAGE_"):].lower() for n in m.group(1).replace("= 0", "").split(",")]
+    assert names[-1] == "count" and tuple(names[:-1]) == CudaH264Enc.STAGES
