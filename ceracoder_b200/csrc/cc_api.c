@@ -16,6 +16,7 @@
 #define CC_MIN_BPS 300000   /* /root/reference/src/core/bitrate_control.h:30 */
 #define CC_MAX_BPS 30000000 /* /root/reference/src/core/bitrate_control.h:31 */
 #define CC_N_STAGES CC_STAGE_COUNT
+#define CC_N_PEV (CC_N_STAGES + 2) /* per stage its start; [CC_N_STAGES]: end of the tail; [+ 1]: end of the entropy coder */
 
 struct cc_enc {
     cc_enc_params p;
@@ -44,9 +45,9 @@ struct cc_enc {
     long launches;
     int last_was_p;
     int profile;                 /* per-kernel CUDA events on */
-    cudaEvent_t pevs[2][CC_N_STAGES + 2]; /* two sets, alternating per frame: the stages behind ev1 (reference finishing) are read when the set
+    cudaEvent_t pevs[2][CC_N_PEV]; /* two sets, alternating per frame: the stages behind ev1 (reference finishing) are read when the set
                                            * comes round again, two frames later, when they are certainly complete */
-    int pevs_used[2][CC_N_STAGES + 2];
+    int pevs_used[2][CC_N_PEV];
     int pevs_tail[2];            /* set holds unread tail stages */
     int pb;                      /* set of the frame in flight */
     double stage_ms[CC_N_STAGES];
@@ -79,6 +80,11 @@ struct cc_enc {
     uint8_t *cur_alt[3];
     uint8_t *stage_host_alt;  /* a second pinned staging frame: a pageable frame that runs ahead is copied here */
     cudaStream_t st_up;
+    int cav_on_st2;        /* the entropy coder of the last frame submitted ran on the second stream */
+    int counted;           /* this handle is in g_open_handles */
+    int overlap_max;       /* CC_OVERLAP_MAX_HANDLES: the default policy overlaps while the process has at most that many handles open */
+    int trail_pct;         /* CC_TRAIL_PCT: k_deblock is released when k_mb_encode is that far through its rows (percent) */
+    int overlap;           /* CC_OVERLAP: 1 the in-loop filter runs next to k_mb_encode, 0 after it, -1 (default) by the number of open handles */
     cudaEvent_t ev_up;
     const uint8_t *pf_plane0; /* plane[0] of the frame sitting in cur_alt, or NULL */
     long prefetched_frames;
@@ -199,6 +205,10 @@ static void pool_stop(cc_enc *e) {
     free(e->slice_out); free(e->slice_len); e->slice_out = NULL; e->slice_len = NULL;
     for (int t = 0; t < 17; t++) { free(e->worker_rbsp[t]); e->worker_rbsp[t] = NULL; }
 }
+
+/* handles open per device (process-wide): the default overlap policy of cc_enc_submit reads it */
+#define CC_MAX_DEVICES 64
+static int g_open_handles[CC_MAX_DEVICES];
 
 int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (!h || !p) return CC_ERR_PARAM;
@@ -333,11 +343,15 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     if (rc == CC_OK && cudaEventCreateWithFlags(&e->ev_up, cudaEventDisableTiming) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreateWithFlags(&e->ev_enc, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ev_tail, cudaEventDisableTiming) != cudaSuccess)) rc = CC_ERR_CUDA;
     if (rc == CC_OK && (cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess)) rc = CC_ERR_CUDA;
-    for (int i = 0; i < 2 * (CC_N_STAGES + 2) && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) != cudaSuccess) rc = CC_ERR_CUDA;
+    for (int i = 0; i < 2 * CC_N_PEV && rc == CC_OK; i++) if (cudaEventCreate(&e->pevs[i / CC_N_PEV][i % CC_N_PEV]) != cudaSuccess) rc = CC_ERR_CUDA;
     if (rc != CC_OK) { cc_enc_close(e); return rc; }
     e->pending_bps = e->p.bitrate_bps;
     { const char *v = getenv("CERACUDA_WAIT"); e->sleep_wait = !(v && !strcmp(v, "spin")); }
     e->debug_sync = getenv("CC_DEBUG_SYNC") != NULL;
+    e->trail_pct = getenv("CC_TRAIL_PCT") ? atoi(getenv("CC_TRAIL_PCT")) : 70;
+    if (e->trail_pct < 0) e->trail_pct = 0;
+    e->overlap = getenv("CC_OVERLAP") ? atoi(getenv("CC_OVERLAP")) : -1;
+    e->overlap_max = getenv("CC_OVERLAP_MAX_HANDLES") ? atoi(getenv("CC_OVERLAP_MAX_HANDLES")) : 8;
     e->dbg_dup = getenv("CC_DBG_DUP") ? atoi(getenv("CC_DBG_DUP")) : 0;
     e->dbg_skip = getenv("CC_DBG_SKIP") ? atoi(getenv("CC_DBG_SKIP")) : 0;
     { const char *v = getenv("CC_DBG_ME"); e->k.dbg = v ? atoi(v) : 0; }
@@ -345,6 +359,8 @@ int cc_enc_open(cc_enc **h, const cc_enc_params *p) {
     cudaStreamSynchronize(e->st);
     cudaDeviceSynchronize();
     if (rc == CC_OK) cudaEventRecord(e->ev_tail, e->st2); /* so that the first frame's wait finds a recorded event */
+    __atomic_add_fetch(&g_open_handles[e->p.device & (CC_MAX_DEVICES - 1)], 1, __ATOMIC_RELAXED);
+    e->counted = 1;
     *h = e;
     return CC_OK;
 }
@@ -355,6 +371,7 @@ static int bind_device(const cc_enc *e) { return cudaSetDevice(e->p.device) == c
 
 void cc_enc_close(cc_enc *e) {
     if (!e) return;
+    if (e->counted) { __atomic_sub_fetch(&g_open_handles[e->p.device & (CC_MAX_DEVICES - 1)], 1, __ATOMIC_RELAXED); e->counted = 0; }
     bind_device(e);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st2) cudaStreamSynchronize(e->st2);
@@ -385,7 +402,7 @@ void cc_enc_close(cc_enc *e) {
     if (e->stage_host_alt) cudaFreeHost(e->stage_host_alt);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
-    for (int i = 0; i < 2 * (CC_N_STAGES + 2); i++) if (e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]) cudaEventDestroy(e->pevs[i / (CC_N_STAGES + 2)][i % (CC_N_STAGES + 2)]);
+    for (int i = 0; i < 2 * CC_N_PEV; i++) if (e->pevs[i / CC_N_PEV][i % CC_N_PEV]) cudaEventDestroy(e->pevs[i / CC_N_PEV][i % CC_N_PEV]);
     if (e->ev_enc) cudaEventDestroy(e->ev_enc);
     if (e->ev_tail) cudaEventDestroy(e->ev_tail);
     if (e->st) cudaStreamDestroy(e->st);
@@ -534,7 +551,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
 #define STAGE(i) do { if (e->debug_sync) { cudaError_t er_ = cudaStreamSynchronize(e->st); if (er_ == cudaSuccess) er_ = cudaStreamSynchronize(e->st2); \
                                            if (er_ != cudaSuccess) { fprintf(stderr, "ceracuda: device fault before stage %d of frame %d: %s\n", (int)(i), e->frame_idx, cudaGetErrorString(er_)); return CC_ERR_CUDA; } } \
                       if (e->profile) { cudaEventRecord(pev[i], e->st); pev_used[i] = 1; } } while (0)
-    for (int i = 0; i <= CC_N_STAGES + 1; i++) pev_used[i] = 0;
+    for (int i = 0; i < CC_N_PEV; i++) pev_used[i] = 0;
 #define DUP(i) (e->dbg_dup & (1 << (i)))
     STAGE(CC_STAGE_INGEST);
     e->launches += cck_ingest(k, fmt, e->st);
@@ -549,32 +566,59 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     CUCHECK(cudaStreamWaitEvent(e->st, e->ev_tail, 0));
     STAGE(CC_STAGE_ME_FINE);
     if (!is_idr) { e->launches += cck_me_l0(k, e->st); if (DUP(CC_STAGE_ME_FINE)) cck_me_l0(k, e->st); }
+    /* The in-loop filter runs NEXT TO k_mb_encode instead of after it (k->trail): k_deblock is the next kernel in the same stream,
+     * launched with programmatic stream serialisation — it begins when every CTA of k_mb_encode has come trail_at macroblocks into
+     * its rows — and follows the encoder's progress words macroblock by macroblock.  The tail (filter, half-pel planes) therefore
+     * sits on the first stream, behind k_mb_encode, and the entropy coder moves to the second.  This takes most of the filter out
+     * of the cycle me_l0 -> p_code -> mb_encode -> deblock -> hpel that bounds ONE stream's frame rate (1 stream: +18 % frames/s;
+     * 8: +1.5 %); it buys nothing once enough streams keep every SM busy anyway, where the waiting filter CTAs cost 2 % (16 streams)
+     * — hence the default: on while the process has at most overlap_max handles open.  Off while profiling, so that the per-stage
+     * times stay times of stages. */
+    const int ovl = e->profile || e->debug_sync ? 0 : (e->overlap >= 0 ? e->overlap & 1 : __atomic_load_n(&g_open_handles[e->p.device & (CC_MAX_DEVICES - 1)], __ATOMIC_RELAXED) <= e->overlap_max);
+    k->trail = ovl;
+    k->trail_at = k->mb_w * e->trail_pct / 100;
+    if (k->trail_at > k->mb_w - 1) k->trail_at = k->mb_w - 1;
+    /* the entropy coder of the frame before (second stream when the filter trails) reads the symbol slots the pre-pass is about to overwrite */
+    if (e->cav_on_st2) CUCHECK(cudaStreamWaitEvent(e->st, e->ev1, 0));
+    e->cav_on_st2 = k->trail;
     STAGE(CC_STAGE_P_CODE);
-    if (!is_idr) { e->launches += cck_p_code(k, e->st); if (DUP(CC_STAGE_P_CODE)) cck_p_code(k, e->st); }
+    if (!is_idr) {
+        e->launches += cck_p_code(k, e->st);
+        if (DUP(CC_STAGE_P_CODE)) cck_p_code(k, e->st);
+    }
     STAGE(CC_STAGE_MB_ENCODE);
     e->launches += cck_encode(k, e->st);
-    if (DUP(CC_STAGE_MB_ENCODE)) cck_encode(k, e->st);
-    STAGE(CC_STAGE_PACK);
-    CUCHECK(cudaEventRecord(e->ev_enc, e->st));
-    e->launches += k->dev_entropy ? cck_cavlc(k, e->st) : cck_pack(k, e->st);
+    if (DUP(CC_STAGE_MB_ENCODE) && !k->trail) cck_encode(k, e->st);
+#define STAGE2(i) do { if (e->profile) { cudaEventRecord(pev[i], tail_st); pev_used[i] = 1; } } while (0)
+    cudaStream_t tail_st, cav_st;
+    if (k->trail) { /* st: k_mb_encode, the filter next to it, the half-pel planes; st2: the entropy coder once the filter (hence the encoder) is done */
+        tail_st = e->st; cav_st = e->st2;
+        if (!(e->dbg_skip & (1 << CC_STAGE_DEBLOCK))) e->launches += cck_deblock(k, e->st, 1);
+        CUCHECK(cudaEventRecord(e->ev_enc, e->st));
+        CUCHECK(cudaStreamWaitEvent(e->st2, e->ev_enc, 0));
+    } else {    /* st: k_mb_encode, the entropy coder; st2: the tail, next to the entropy coder */
+        tail_st = e->st2; cav_st = e->st;
+        CUCHECK(cudaEventRecord(e->ev_enc, e->st));
+        CUCHECK(cudaStreamWaitEvent(e->st2, e->ev_enc, 0));
+    }
+    if (e->profile) { cudaEventRecord(pev[CC_STAGE_PACK], cav_st); pev_used[CC_STAGE_PACK] = 1; }
+    e->launches += k->dev_entropy ? cck_cavlc(k, cav_st) : cck_pack(k, cav_st);
     /* the access unit's bits (or symbols) are in host memory here: cc_enc_collect waits for ev1 only */
-    CUCHECK(cudaEventRecord(e->ev1, e->st));
-    if (e->profile) { cudaEventRecord(pev[CC_N_STAGES + 1], e->st); pev_used[CC_N_STAGES + 1] = 1; }
+    CUCHECK(cudaEventRecord(e->ev1, cav_st));
+    if (e->profile) { cudaEventRecord(pev[CC_N_STAGES + 1], cav_st); pev_used[CC_N_STAGES + 1] = 1; }
     /* The kernels that turn the reconstruction into the next frame's reference need nothing from the entropy coder and nothing it
-     * writes: they run on the second stream next to it, and then on while the host packages the access unit. */
-    CUCHECK(cudaStreamWaitEvent(e->st2, e->ev_enc, 0));
-#define STAGE2(i) do { if (e->profile) { cudaEventRecord(pev[i], e->st2); pev_used[i] = 1; } } while (0)
+     * writes: they run on the other stream next to it, and then on while the host packages the access unit. */
     STAGE2(CC_STAGE_DEBLOCK);
-    if (!(e->dbg_skip & (1 << CC_STAGE_DEBLOCK))) e->launches += cck_deblock(k, e->st2);
+    if (!k->trail && !(e->dbg_skip & (1 << CC_STAGE_DEBLOCK))) e->launches += cck_deblock(k, tail_st, 0);
     STAGE2(CC_STAGE_BORDER); /* no launch of its own any more: the border CTAs ride behind the half-pel tiles */
     STAGE2(CC_STAGE_HPEL);
-    e->launches += cck_hpel_border(k, e->st2);
-    if (DUP(CC_STAGE_HPEL)) cck_hpel_border(k, e->st2);
+    e->launches += cck_hpel_border(k, tail_st);
+    if (DUP(CC_STAGE_HPEL)) cck_hpel_border(k, tail_st);
     STAGE2(CC_STAGE_L1REF); /* nothing left here: the half-resolution reference is written with the reconstruction */
     STAGE2(CC_N_STAGES);
 #undef STAGE2
 #undef DUP
-    CUCHECK(cudaEventRecord(e->ev_tail, e->st2));
+    CUCHECK(cudaEventRecord(e->ev_tail, tail_st));
 #undef STAGE
     e->pevs_tail[e->pb] = e->profile;
     CUCHECK(cudaGetLastError());

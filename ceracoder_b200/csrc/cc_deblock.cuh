@@ -7,7 +7,7 @@
  * macroblock plus the 4 pixels left of / above it into shared memory once (172 coalesced word loads), every lane
  * then filters one whole pixel line in registers (lanes 0-15: a luma row / column across its 4 edges, lanes 16-31:
  * a chroma row / column of Cb or Cr across its 2 edges), and the tile is stored back once.
- * Boundary strengths come from the slice's shared-memory neighbour lines (type, nz flags, mv of current, left, top).
+ * Boundary strengths come from the neighbour records k_mb_encode left in global memory (type, nz flags, mv of current, left, top).
  * Oracle counterpart: oracle/ref_mb.c ref_mb_deblock.
  */
 #ifndef CC_DEBLOCK_CUH
@@ -104,8 +104,11 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
  * of the slice's CTA as independent wavefronts — in one warp their different code paths would be serialised).
  * L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
 template <int PL>
-/* xband: the row above was filtered by another CTA (a slice taller than a band): its pixels are read past the L1 */
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec *nbl, int lane, int mbx, int mby, int L, int T, bool xband) {
+/* All pixel loads go past the L1 (ld.cg): the kernel runs NEXT TO k_mb_encode, which is still writing the macroblocks to the right
+ * of and below this one, and a 32-byte sector fetched for this macroblock's right half also holds 16 samples of the next one — cached
+ * in the L1 they would be read back stale when that macroblock's turn comes.  (The rows a band above filtered, in another CTA,
+ * needed the same.) */
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec &nq, const NbRec &nl, const NbRec &nt, int lane, int mbx, int mby, int L, int T) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
@@ -114,7 +117,7 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
     const int g = luma ? li >> 2 : (li & 7) >> 1;
     const int cpl = li >> 3, ci = li & 7;
     /* ---- boundary strengths first: most macroblocks of a P frame have nothing to filter ---- */
-    const NbRec nq = nbl[mbx], nl = nbl[L ? mbx - 1 : mbx], nt = T ? nbl[mbx - k.mb_w] : nq; /* shared-memory neighbour lines */
+    /* nq, nl, nt: the records of this macroblock, its left and its top neighbour (= nq where there is none) */
     { /* The common P-frame case first (warp-uniform, ~20 instructions instead of the eight strength computations): the macroblock
        * and its left / top neighbours are inter-coded without luma coefficients and all move with one vector — every boundary
        * strength is 0 (8.7.2.1: no intra, no coefficients, equal vectors), nothing to filter, not even a pixel to load. */
@@ -130,14 +133,14 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
         for (int it = 0; it < 4; it++) {
             const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
             const uint32_t *src = (const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw);
-            ly[it] = idx < 100 ? ((xband && r < 4) ? __ldcg(src) : *src) : 0u;
+            ly[it] = idx < 100 ? __ldcg(src) : 0u;
         }
     } else {
 #pragma unroll
         for (int it = 0; it < 3; it++) {
             const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
             const uint32_t *src = (const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw);
-            lc[it] = idx < 72 ? ((xband && r < 4) ? __ldcg(src) : *src) : 0u;
+            lc[it] = idx < 72 ? __ldcg(src) : 0u;
         }
     }
     const uint32_t q0 = nq.x;

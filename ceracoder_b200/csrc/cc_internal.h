@@ -115,6 +115,8 @@ typedef struct {
     uint32_t *nbrec;   /* per MB 5 words {type | t8 << 8 | nz_luma << 16, mv of quadrants 0..3}: what k_deblock needs from k_mb_encode */
     cc_mbhost *mbh;    /* device copy */
     cc_pre *pre;
+    int trail;           /* 1: k_deblock runs next to k_mb_encode and follows its progress words (0: it is launched after it) */
+    int trail_at;        /* k_mb_encode releases the launch of k_deblock when its CTAs' top rows reach this macroblock column */
     uint8_t *park;     /* per MB 384 bytes (16x16 luma, 8x8 Cb, 8x8 Cr as in WarpMem.recY / recC): see cc_pre.skip_ok bit 2 */
     uint16_t *symlen;  /* per MB: int16 units used in its symbol slot (even; 0 for P_Skip) */
     uint8_t *ubot[3];  /* unfiltered bottom sample line of every MB row: [mb_h][sy] luma, [mb_h][sc] per chroma plane */
@@ -154,7 +156,7 @@ int cck_me_l0_prepare(cc_kparams *k, uint8_t *const planes[5], void *maps); /* t
 int cck_motion(const cc_kparams *k, cudaStream_t st);
 int cck_p_code(const cc_kparams *k, cudaStream_t st);
 int cck_encode(const cc_kparams *k, cudaStream_t st);
-int cck_deblock(const cc_kparams *k, cudaStream_t st);
+int cck_deblock(const cc_kparams *k, cudaStream_t st, int after_trigger); /* after_trigger: programmatic stream serialisation behind k_mb_encode, the kernel before it in st (0: a plain launch) */
 int cck_pack(const cc_kparams *k, cudaStream_t st);
 int cck_cavlc(const cc_kparams *k, cudaStream_t st); /* k_cavlc_size + k_cavlc_write: slice RBSPs into the mapped host buffer */
 

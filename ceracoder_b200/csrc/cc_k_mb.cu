@@ -694,13 +694,14 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
 }
 
 /* the same across CTAs: *flag is a frame-tagged progress word in global memory (tag + macroblocks done); returns the count */
+template <int SLEEP_NS = 0>
 __device__ __forceinline__ int wait_progress_global(const uint32_t *flag, uint32_t tag, int need, int lane) {
     uint32_t v = 0;
     if (lane == 0) {
         for (;;) {
             v = *(const volatile uint32_t *)flag;
             if ((int)(v - (tag + (uint32_t)need)) >= 0) break;
-            CC_SPIN_PAUSE();
+            if (SLEEP_NS) __nanosleep(SLEEP_NS); else CC_SPIN_PAUSE();
         }
     }
     v = __shfl_sync(FULL, v, 0);
@@ -969,6 +970,13 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
             const uint32_t *slot = (const uint32_t *)m->pc[mbx & 3];
             m->curY[lane] = slot[lane]; m->curY[lane + 32] = slot[lane + 32]; m->curC[lane >> 4][lane & 15] = slot[64 + lane];
         }
+#ifndef CC_EMU_BUILD
+        /* The in-loop filter, next in the stream, is launched when every CTA of this kernel has come this far (a no-op unless that
+         * launch carries the programmatic attribute).  Not at the top: the filter is more than twice as fast as this kernel, and a
+         * filter CTA that was resident from the start would hold its SM's registers for the whole wavefront just to wait; released
+         * at k.trail_at macroblocks it runs at its own speed and catches up with the encoder near the end of the row. */
+        if (k.trail && w == 0 && mbx == k.trail_at) asm volatile("griddepcontrol.launch_dependents;");
+#endif
         const long long t0 = k.cyc ? clock64() : 0;
         if (xband) { /* the band above: its progress word, then the records it published since */
             const int have = min(wait_progress_global(k.gprog + row - 1, tag, min(mbx + 2, mw), lane), mw);
@@ -1144,7 +1152,9 @@ __device__ void encode_row(const cc_kparams &k, WarpMem *m, NbRec *nbline, volat
         if (type == CC_MB_PSKIP) n_skip++; else if (type == CC_MB_P16) n_inter++; else n_intra++;
         total += off;
         __syncwarp();
-        if (last) { /* the band below reads what this row published (records, unfiltered lines) from global memory */
+        /* the band below reads what this row published (records, unfiltered lines) from global memory; so does the in-loop filter,
+         * which runs next to this kernel and follows the band's bottom row (k_deblock) — for it every fourth macroblock is enough */
+        if (last || (k.trail && (w == k.band - 1 || row == k.mb_h - 1) && (((mbx + 1) & 3) == 0 || mbx == mw - 1))) {
             __threadfence();
             if (lane == 0) *(volatile uint32_t *)(k.gprog + row) = tag + (uint32_t)(mbx + 1);
         } else __threadfence_block();
@@ -1352,28 +1362,26 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
 
 /* In-loop filter: CTA = one band of a slice (the same bands as k_mb_encode); per macroblock row one luma warp and one chroma warp,
  * each 2 macroblocks behind the warp of the same kind in the row above (H.264 8.7 is raster-ordered; luma and chroma are
- * independent wavefronts).  The neighbour records the encode kernel left in global memory are staged into shared memory first
- * (line 0 = the row above the band).  A band whose slice started further up chains to the band above through frame-tagged
- * progress words, and reads the pixels that band filtered past the L1 (deblock_mb's xband). */
+ * independent wavefronts).  A band whose slice started further up chains to the band above through frame-tagged progress words.
+ *
+ * The kernel runs NEXT TO k_mb_encode (k.trail; cc_enc_submit launches it behind it in the same stream with programmatic stream
+ * serialisation: it begins once every CTA of k_mb_encode is resident) and follows it macroblock by macroblock: the filter of a macroblock needs the reconstruction and the records of that
+ * macroblock and of those left of and above it, all of which k_mb_encode has published by the time it is done with the macroblock
+ * (it keeps its own copies of the unfiltered neighbour samples — ubot / uright — and never reads k.rec back).  What tells the
+ * filter how far the encoder is, is the progress word of the band's BOTTOM row (gprog[0]): when that row has finished P >= 1
+ * macroblocks, the row j rows above it has finished at least P + j (the wavefront's lag), so no other word is needed.  The records
+ * come straight from global memory (past the L1, a chunk ahead where the encoder is known to be further). */
 #ifndef CC_DB_MINBLOCKS
 #define CC_DB_MINBLOCKS 1
 #endif
 __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress2[2][MB_MAX_RPS];
-    CC_DYN_SMEM(dsm);
-    NbRec *nbline = (NbRec *)dsm;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int pl = wid >= k.band, w = pl ? wid - k.band : wid; /* warps [0, band): luma rows, [band, 2 band): chroma rows */
     const int row0 = blockIdx.x * k.band, row = row0 + w;
-    const int rows = min(k.band, k.mb_h - row0);
+    const int rows = min(k.band, k.mb_h - row0), mw = k.mb_w;
     const int srow0 = (row0 / k.rps) * k.rps, send = min(srow0 + k.rps, k.mb_h);
-    {
-        const int above = row0 > srow0; /* the slice started further up: stage the last row of the band above as well */
-        const uint32_t *src = (const uint32_t *)k.nbrec + (size_t)(row0 - above) * k.mb_w * 5;
-        uint32_t *dst = (uint32_t *)(nbline + (1 - above) * k.mb_w);
-        for (int i = threadIdx.x; i < (rows + above) * k.mb_w * 5; i += blockDim.x) dst[i] = src[i];
-    }
     if (lane == 0) progress2[pl][w] = 0;
     __syncthreads();
     if (row >= k.mb_h) return;
@@ -1381,13 +1389,49 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_debloc
     const bool T = row > srow0, xband = T && w == 0, last = w == k.band - 1 && row + 1 < send;
     const uint32_t tag = (uint32_t)k.frame_seq << 12;
     uint32_t *gp = k.gprog + (size_t)(1 + pl) * k.mb_h; /* [0]: k_mb_encode's, [1]: luma filter, [2]: chroma filter */
-    for (int mbx = 0; mbx < k.mb_w; mbx++) {
+    const uint32_t *ep = k.gprog + row0 + rows - 1;     /* k_mb_encode's progress word of the band's bottom row */
+    const int above = rows - 1 - w;                     /* this row is that many rows above it */
+    const uint32_t *rq = k.nbrec + (size_t)row * mw * 5, *rt = rq - (size_t)mw * 5;
+    int enc_have = k.trail ? 0 : mw;                    /* macroblocks of this row k_mb_encode is known to have published */
+    /* records by chunks of 4 macroblocks (20 words, one per lane: a single coalesced load for the row and one for the row above), the
+     * next chunk on its way while this one is filtered where the encoder is known to be that far; a macroblock's record is then
+     * five shuffles.  4 is also the step of the encoder's progress word. */
+    uint32_t cq = 0, ct = 0, xq = 0, xt = 0;
+    bool have_next = false;
+    NbRec nq, nt, nl;
+    for (int mbx = 0; mbx < mw; mbx++) {
         const long long t1 = k.cyc ? clock64() : 0;
-        if (xband) wait_progress_global(gp + row - 1, tag, min(mbx + 2, k.mb_w), lane);
-        else if (T) wait_progress(prog + w - 1, min(mbx + 2, k.mb_w), lane);
+        const int j = mbx & 3;
+        if (j == 0) {
+            const int cend = min(mbx + 4, mw);
+            if (enc_have < cend) { /* the word moves every fourth macroblock of the encoder (tens of microseconds): poll slowly */
+                const int p = wait_progress_global<1000>(ep, tag, max(1, cend - above), lane);
+                enc_have = min(p + above, mw);
+            }
+            const int wi = mbx * 5 + lane; /* the row above is at least as far as this one, in the encoder and hence in its records */
+            if (have_next) { cq = xq; ct = xt; }
+            else {
+                cq = (lane < 20 && wi < mw * 5) ? __ldcg(rq + wi) : 0u;
+                ct = (T && lane < 20 && wi < mw * 5) ? __ldcg(rt + wi) : 0u;
+            }
+            have_next = mbx + 4 < mw && enc_have >= min(mbx + 8, mw);
+            if (have_next) {
+                xq = (lane < 20 && wi + 20 < mw * 5) ? __ldcg(rq + wi + 20) : 0u;
+                xt = (T && lane < 20 && wi + 20 < mw * 5) ? __ldcg(rt + wi + 20) : 0u;
+            }
+        }
+        if (xband) wait_progress_global(gp + row - 1, tag, min(mbx + 2, mw), lane);
+        else if (T) wait_progress(prog + w - 1, min(mbx + 2, mw), lane);
         const long long t2 = k.cyc ? clock64() : 0;
-        if (pl) deblock_mb<1>(k, &dbm[w], nbline + (w + 1) * k.mb_w, lane, mbx, row, mbx > 0, T, xband);
-        else deblock_mb<0>(k, &dbm[w], nbline + (w + 1) * k.mb_w, lane, mbx, row, mbx > 0, T, xband);
+        nq.x = __shfl_sync(FULL, cq, j * 5);
+        nt.x = __shfl_sync(FULL, ct, j * 5);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { nq.mv[i] = __shfl_sync(FULL, cq, j * 5 + 1 + i); nt.mv[i] = __shfl_sync(FULL, ct, j * 5 + 1 + i); }
+        if (!T) nt = nq;
+        if (mbx == 0) nl = nq;
+        if (pl) deblock_mb<1>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T);
+        else deblock_mb<0>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T);
+        nl = nq;
         if (last) {
             __threadfence();
             if (lane == 0) *(volatile uint32_t *)(gp + row) = tag + (uint32_t)(mbx + 1);
@@ -1475,13 +1519,30 @@ extern "C" int cck_encode(const cc_kparams *k, cudaStream_t st) {
     else CC_LAUNCH_SMEM(k_mb_encode<MB_MAX_RPS>, dim3((unsigned)ns), dim3((unsigned)k->band * 32), dyn, st, *k);
     return 1;
 }
-extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st) {
+extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st, int after_trigger) {
     const int ns = (k->mb_h + k->band - 1) / k->band;
-    const size_t dyn = (size_t)(k->band + 1) * k->mb_w * sizeof(NbRec);
 #ifndef CC_EMU_BUILD
-    if (dyn > 32 * 1024) cudaFuncSetAttribute(k_deblock, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    if (after_trigger) {
+        /* programmatic stream serialisation: this launch may begin when every CTA of the kernel before it in the stream
+         * (k_mb_encode) has executed griddepcontrol.launch_dependents — whatever this kernel then spins on (the encoder's progress
+         * words) is produced by CTAs that are already running, so the spinning CTAs cannot keep them off the machine.
+         * (The same dependency ACROSS streams — cudaLaunchAttributeProgrammaticEvent with triggerAtBlockStart — was measured to
+         * release the dependent only when the kernel has ended, on this driver: tools/probes/pdl_probe.cu.) */
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3((unsigned)ns); cfg.blockDim = dim3((unsigned)k->band * 64); cfg.stream = st;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaError_t er = cudaLaunchKernelEx(&cfg, k_deblock, *k);
+        (void)er;
+        return 1;
+    }
+#else
+    (void)after_trigger;
 #endif
-    CC_LAUNCH_SMEM(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->band * 64), dyn, st, *k);
+    CC_LAUNCH(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->band * 64), st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

@@ -260,3 +260,37 @@ def test_encode_sequence_with_uploads_running_ahead_equals_frame_by_frame(where)
         L.cc_host_free(C.c_void_p(base))
     elif where == "device":
         L.cc_dev_free(C.c_void_p(base))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rps,pct", [(0, 70), (0, 0), (68, 30), (16, 100)])
+def test_filter_running_next_to_the_encoder_equals_filter_after_it(lib, monkeypatch, rps, pct):
+    """k_deblock launched behind k_mb_encode with programmatic stream serialisation (it follows the encoder's progress words while the
+    encoder is still running: CC_OVERLAP=1, released pct % into the rows) against the same kernels one after the other (CC_OVERLAP=0):
+    identical access units and reconstruction, 1080p under rate control, four streams at once so that the CTAs really share the GPU;
+    default slices, one slice per picture and slices of two bands (the filter then also chains across its own CTAs)."""
+    import threading
+    import zlib
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    w, h, n = 1920, 1080, 14
+    src = make_source("pan", w, h)
+    frames = [src.frame(i) for i in range(7)]
+
+    def run(out, k):
+        e = CudaH264Enc(w, h, fps=(60, 1), lib=lib, bitrate=3000 + 4000 * (k % 2), key_int_max=9, rows_per_slice=rps)
+        aus = [e.encode(*frames[i % 7]) for i in range(n)]
+        out[k] = (aus, [zlib.crc32(np.ascontiguousarray(p).tobytes()) for p in e.recon()])
+        e.close()
+
+    monkeypatch.setenv("CC_TRAIL_PCT", str(pct))
+    monkeypatch.setenv("CC_OVERLAP", "1")  # read by cc_enc_open
+    res = {}
+    ths = [threading.Thread(target=run, args=(res, k)) for k in range(4)]
+    [t.start() for t in ths]; [t.join() for t in ths]
+    monkeypatch.setenv("CC_OVERLAP", "0")
+    solo = {}
+    run(solo, 0); run(solo, 1)
+    for k in range(4):
+        assert res[k][0] == solo[k % 2][0], f"stream {k}: access units differ"
+        assert res[k][1] == solo[k % 2][1], f"stream {k}: reconstruction differs"
