@@ -104,11 +104,11 @@ __device__ __forceinline__ void db_line_chroma(int v[12], const int bs[4], int f
  * of the slice's CTA as independent wavefronts — in one warp their different code paths would be serialised).
  * L / T: left / top neighbour inside the slice (disable_deblocking_filter_idc = 2). */
 template <int PL>
-/* All pixel loads go past the L1 (ld.cg): the kernel runs NEXT TO k_mb_encode, which is still writing the macroblocks to the right
- * of and below this one, and a 32-byte sector fetched for this macroblock's right half also holds 16 samples of the next one — cached
- * in the L1 they would be read back stale when that macroblock's turn comes.  (The rows a band above filtered, in another CTA,
- * needed the same.) */
-__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec &nq, const NbRec &nl, const NbRec &nt, int lane, int mbx, int mby, int L, int T) {
+/* cg_all: all pixel loads go past the L1 (ld.cg) — the kernel is running NEXT TO k_mb_encode, which is still writing the macroblocks
+ * to the right of and below this one, and a 32-byte sector fetched for this macroblock's right half also holds 16 samples of the
+ * next one: cached in the L1 they would be read back stale when that macroblock's turn comes.
+ * xband: the row above was filtered by another CTA (a slice taller than a band): its pixels are read past the L1 in any case. */
+__device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const NbRec &nq, const NbRec &nl, const NbRec &nt, int lane, int mbx, int mby, int L, int T, bool cg_all, bool xband) {
     const int qp = k.qp, qpc = c_chroma_qp[qp];
     const int px = mbx * 16, py = mby * 16, cx = mbx * 8, cy = mby * 8;
     if (c_alpha[qp] == 0) return; /* qp < 16: alpha = 0 for luma and chroma (qpc <= qp), the filter is the identity */
@@ -133,14 +133,14 @@ __device__ __forceinline__ void deblock_mb(const cc_kparams &k, DbMem *db, const
         for (int it = 0; it < 4; it++) {
             const int idx = lane + 32 * it, r = idx / 5, cw = idx - r * 5;
             const uint32_t *src = (const uint32_t *)(k.rec[0] + (ptrdiff_t)(py + r - 4) * k.sy + px - 4 + 4 * cw);
-            ly[it] = idx < 100 ? __ldcg(src) : 0u;
+            ly[it] = idx < 100 ? ((cg_all || (xband && r < 4)) ? __ldcg(src) : *src) : 0u;
         }
     } else {
 #pragma unroll
         for (int it = 0; it < 3; it++) {
             const int idx = lane + 32 * it, pl = idx >= 36, rem = idx - 36 * pl, r = rem / 3, cw = rem - r * 3;
             const uint32_t *src = (const uint32_t *)(k.rec[1 + pl] + (ptrdiff_t)(cy + r - 4) * k.sc + cx - 4 + 4 * cw);
-            lc[it] = idx < 72 ? __ldcg(src) : 0u;
+            lc[it] = idx < 72 ? ((cg_all || (xband && r < 4)) ? __ldcg(src) : *src) : 0u;
         }
     }
     const uint32_t q0 = nq.x;

@@ -1374,6 +1374,7 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
 #ifndef CC_DB_MINBLOCKS
 #define CC_DB_MINBLOCKS 1
 #endif
+template <bool TRAIL> /* TRAIL: launched next to k_mb_encode (k.trail) */
 __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress2[2][MB_MAX_RPS];
@@ -1392,7 +1393,7 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_debloc
     const uint32_t *ep = k.gprog + row0 + rows - 1;     /* k_mb_encode's progress word of the band's bottom row */
     const int above = rows - 1 - w;                     /* this row is that many rows above it */
     const uint32_t *rq = k.nbrec + (size_t)row * mw * 5, *rt = rq - (size_t)mw * 5;
-    int enc_have = k.trail ? 0 : mw;                    /* macroblocks of this row k_mb_encode is known to have published */
+    int enc_have = TRAIL ? 0 : mw;                      /* macroblocks of this row k_mb_encode is known to have published */
     /* records by chunks of 4 macroblocks (20 words, one per lane: a single coalesced load for the row and one for the row above), the
      * next chunk on its way while this one is filtered where the encoder is known to be that far; a macroblock's record is then
      * five shuffles.  4 is also the step of the encoder's progress word. */
@@ -1429,8 +1430,8 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_debloc
         for (int i = 0; i < 4; i++) { nq.mv[i] = __shfl_sync(FULL, cq, j * 5 + 1 + i); nt.mv[i] = __shfl_sync(FULL, ct, j * 5 + 1 + i); }
         if (!T) nt = nq;
         if (mbx == 0) nl = nq;
-        if (pl) deblock_mb<1>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T);
-        else deblock_mb<0>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T);
+        if (pl) deblock_mb<1>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T, TRAIL, xband);
+        else deblock_mb<0>(k, &dbm[w], nq, nl, nt, lane, mbx, row, mbx > 0, T, TRAIL, xband);
         nl = nq;
         if (last) {
             __threadfence();
@@ -1535,14 +1536,15 @@ extern "C" int cck_deblock(const cc_kparams *k, cudaStream_t st, int after_trigg
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = dim3((unsigned)ns); cfg.blockDim = dim3((unsigned)k->band * 64); cfg.stream = st;
         cfg.attrs = at; cfg.numAttrs = 1;
-        cudaError_t er = cudaLaunchKernelEx(&cfg, k_deblock, *k);
+        cudaError_t er = cudaLaunchKernelEx(&cfg, k_deblock<true>, *k);
         (void)er;
         return 1;
     }
 #else
     (void)after_trigger;
 #endif
-    CC_LAUNCH(k_deblock, dim3((unsigned)ns), dim3((unsigned)k->band * 64), st, *k);
+    if (k->trail) CC_LAUNCH(k_deblock<true>, dim3((unsigned)ns), dim3((unsigned)k->band * 64), st, *k); /* the emulator's build */
+    else CC_LAUNCH(k_deblock<false>, dim3((unsigned)ns), dim3((unsigned)k->band * 64), st, *k);
     return 1;
 }
 extern "C" int cck_p_code(const cc_kparams *k, cudaStream_t st) {

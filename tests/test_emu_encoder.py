@@ -176,3 +176,12 @@ def test_slices_taller_than_a_band(lib, w, h, rps, qps):
     """rows_per_slice > 8: the slice's wavefront chains 8-row bands across CTAs (frame-tagged progress words, neighbour records and
     unfiltered lines through global memory) in the encode and the filter kernel; bytes and reconstruction stay the oracle's"""
     run_parity(lib, "pan", w, h, qps, rps=rps, gop=60)
+
+
+@pytest.mark.parametrize("w,h,rps,qps", [(176, 144, 4, [30, 27, 33, 25]), (64, 320, 16, [28, 30, 26])])
+def test_filter_after_the_encoder_instead_of_next_to_it(lib, monkeypatch, w, h, rps, qps):
+    """CC_OVERLAP=0: k_deblock<false> (launched after k_mb_encode: no progress words of the encoder to follow, pixel loads through
+    the L1) — what a handle runs while it is profiled or while more than 8 handles are open; the other tests run the default, the
+    filter as it is launched next to the encoder."""
+    monkeypatch.setenv("CC_OVERLAP", "0")  # read by cc_enc_open
+    run_parity(lib, "pan", w, h, qps, rps=rps, gop=60)
