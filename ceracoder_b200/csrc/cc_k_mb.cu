@@ -1369,8 +1369,10 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
  * macroblock and of those left of and above it, all of which k_mb_encode has published by the time it is done with the macroblock
  * (it keeps its own copies of the unfiltered neighbour samples — ubot / uright — and never reads k.rec back).  What tells the
  * filter how far the encoder is, is the progress word of the band's BOTTOM row (gprog[0]): when that row has finished P >= 1
- * macroblocks, the row j rows above it has finished at least P + j (the wavefront's lag), so no other word is needed.  The records
- * come straight from global memory (past the L1, a chunk ahead where the encoder is known to be further). */
+ * macroblocks, the row j rows above it has finished at least P + j (the wavefront's lag), so no other word is needed — and what
+ * those rows stored is visible with it: each row's warp releases its stores to the row below at CTA scope (fence + shared-memory
+ * progress word, read + fence), the bottom row releases at GPU scope, and the PTX memory model's causality order is transitive
+ * across those scopes (fences are cumulative).  The records come straight from global memory (past the L1, a chunk ahead where the encoder is known to be further). */
 #ifndef CC_DB_MINBLOCKS
 #define CC_DB_MINBLOCKS 1
 #endif
