@@ -80,6 +80,7 @@ struct cc_enc {
     uint8_t *cur_alt[3];
     uint8_t *stage_host_alt;  /* a second pinned staging frame: a pageable frame that runs ahead is copied here */
     cudaStream_t st_up;
+    long overlapped_frames; /* frames whose filter was launched next to k_mb_encode */
     int cav_on_st2;        /* the entropy coder of the last frame submitted ran on the second stream */
     int counted;           /* this handle is in g_open_handles */
     int overlap_max;       /* CC_OVERLAP_MAX_HANDLES: the default policy overlaps while the process has at most that many handles open */
@@ -581,6 +582,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     /* the entropy coder of the frame before (second stream when the filter trails) reads the symbol slots the pre-pass is about to overwrite */
     if (e->cav_on_st2) CUCHECK(cudaStreamWaitEvent(e->st, e->ev1, 0));
     e->cav_on_st2 = k->trail;
+    e->overlapped_frames += k->trail;
     STAGE(CC_STAGE_P_CODE);
     if (!is_idr) {
         e->launches += cck_p_code(k, e->st);
@@ -790,6 +792,7 @@ static void enc_prefetch(cc_enc *e, const cc_frame *in, unsigned flags) {
     e->pf_plane0 = in->plane[0];
 }
 long cc_enc_prefetched_frames(const cc_enc *e) { return e ? e->prefetched_frames : 0; }
+long cc_enc_overlapped_frames(const cc_enc *e) { return e ? e->overlapped_frames : 0; }
 
 int cc_enc_encode_sequence(cc_enc *e, const cc_frame *frames, const int *bitrate_bps, int n, unsigned flags, cc_seq_stats *acc, cc_packet *last) {
     if (!e || !frames || !acc || n < 0) return CC_ERR_PARAM;

@@ -75,6 +75,8 @@ def load_library(path=None):
     L.cc_enc_kernel_launches.restype = C.c_long
     L.cc_enc_staged_frames.argtypes = [vp]
     L.cc_enc_staged_frames.restype = C.c_long
+    L.cc_enc_overlapped_frames.argtypes = [vp]
+    L.cc_enc_overlapped_frames.restype = C.c_long
     L.cc_enc_set_profile.argtypes = [vp, ci]
     L.cc_enc_get_stage_ms.argtypes = [vp, vp, vp]
     L.cc_host_alloc.restype = vp
@@ -257,6 +259,10 @@ class CudaH264Enc:
     def staged_frames(self):
         """frames that arrived in pageable host memory and went through the handle's pinned staging frame"""
         return self.L.cc_enc_staged_frames(self._h)
+
+    def overlapped_frames(self):
+        """Frames whose in-loop filter was launched next to the macroblock kernel (cc_enc_overlapped_frames, include/ceracuda.h)."""
+        return self.L.cc_enc_overlapped_frames(self._h)
 
     def kernel_launches(self):
         return self.L.cc_enc_kernel_launches(self._h)

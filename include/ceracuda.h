@@ -153,6 +153,11 @@ long cc_enc_staged_frames(const cc_enc *h);
  * per handle; pageable frames are copied to a second pinned staging frame by the calling thread first).  Count of frames that
  * arrived that way since open: */
 long cc_enc_prefetched_frames(const cc_enc *h);
+/* Launch order of the frames coded so far: how many of them ran the in-loop filter NEXT TO the macroblock kernel
+ * (programmatic dependent launch) rather than after it.  The default does so while the handle's device has at most 8 handles open
+ * in this process (CC_OVERLAP / CC_OVERLAP_MAX_HANDLES / CC_TRAIL_PCT in the environment override it; a handle with stage timing
+ * on never does).  Both orders produce the same bytes.  No counterpart in x264enc. */
+long cc_enc_overlapped_frames(const cc_enc *h);
 /* number of kernel launches issued by this handle since open */
 long cc_enc_kernel_launches(const cc_enc *h);
 

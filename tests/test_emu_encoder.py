@@ -185,3 +185,32 @@ def test_filter_after_the_encoder_instead_of_next_to_it(lib, monkeypatch, w, h, 
     filter as it is launched next to the encoder."""
     monkeypatch.setenv("CC_OVERLAP", "0")  # read by cc_enc_open
     run_parity(lib, "pan", w, h, qps, rps=rps, gop=60)
+
+
+def test_launch_order_follows_the_number_of_open_handles(lib, monkeypatch):
+    """cc_enc_submit's default: the in-loop filter is launched next to the macroblock kernel while the device has at most 8 handles
+    open in the process (CC_OVERLAP_MAX_HANDLES), after it beyond that; CC_OVERLAP forces either; stage timing turns it off.  The
+    bytes do not depend on it."""
+    from ceracoder_b200 import CudaH264Enc
+    from ceracoder_b200.synth import make_source
+    monkeypatch.delenv("CC_OVERLAP", raising=False)
+    monkeypatch.setenv("CC_OVERLAP_MAX_HANDLES", "2")
+    w, h = 64, 48
+    f = [make_source("pan", w, h).frame(i) for i in range(3)]
+    a = CudaH264Enc(w, h, lib=lib, qp_fixed=28)
+    b = CudaH264Enc(w, h, lib=lib, qp_fixed=28)
+    au = [a.encode(*f[0])]
+    assert a.overlapped_frames() == 1          # two handles open: within the limit
+    c = CudaH264Enc(w, h, lib=lib, qp_fixed=28)
+    au.append(a.encode(*f[1]))
+    assert a.overlapped_frames() == 1          # three: the filter goes after the encoder
+    c.close()
+    a.set_profile(True)
+    au.append(a.encode(*f[2]))
+    assert a.overlapped_frames() == 1          # per-stage events: never next to it
+    a.close()
+    monkeypatch.setenv("CC_OVERLAP", "0")
+    d = CudaH264Enc(w, h, lib=lib, qp_fixed=28)
+    ref = [d.encode(*x) for x in f]
+    assert d.overlapped_frames() == 0 and ref == au
+    d.close(); b.close()
