@@ -416,7 +416,8 @@ def main():
         if world > 1:
             dist.barrier()
         tot.update(ms=ms, wall_ms=wall_ms, launches=sum(e.kernel_launches() for e in encs) - launches0,
-                   staged=sum(e.staged_frames() for e in encs) - staged0, qps=[e.last.qp for e in encs], stages={})
+                   staged=sum(e.staged_frames() for e in encs) - staged0, qps=[e.last.qp for e in encs], stages={},
+                   overlapped=sum(e.overlapped_frames() for e in encs))
         if profile:
             for e in encs:
                 for s, (tms, n) in e.stage_ms().items():
@@ -546,6 +547,8 @@ def main():
                                   "cavlc_nal": round(r_e2e["host_ms"] / nf, 4), "device_frame_latency": round(r_e2e["gpu_ms"] / nf, 4),
                                   "submit_api_pageable": round(r_page["submit_ms"] / max(r_page["frames"], 1), 4)},
             "frame_store": {"path": store.path, "generate_s": round(store.gen_s, 1)},
+            "launch_order": {"filter_next_to_mb_encode_frames": {"value_leg": r_dev["overlapped"], "e2e_leg": r_e2e["overlapped"], "stage_timing_pass": r_prof["overlapped"]},
+                             "note": "frames since open (warm-up included) whose k_deblock was launched behind k_mb_encode by programmatic stream serialisation; DESIGN.md 5"},
             "wall_ms": {"value_leg": r_dev["wall_ms"], "e2e_leg": r_e2e["wall_ms"], "e2e_pageable_leg": r_page["wall_ms"]}}
     print(json.dumps(line))
     L.cc_host_unregister(hbase)
