@@ -81,6 +81,8 @@ struct cc_enc {
     uint8_t *stage_host_alt;  /* a second pinned staging frame: a pageable frame that runs ahead is copied here */
     cudaStream_t st_up;
     long overlapped_frames; /* frames whose filter was launched next to k_mb_encode */
+    int prev_trail;        /* launch order of the frame before */
+    int last_trail_seq;    /* cc_kparams.frame_seq of the last frame whose filter ran next to the encoder (0: none yet) */
     int cav_on_st2;        /* the entropy coder of the last frame submitted ran on the second stream */
     int counted;           /* this handle is in g_open_handles */
     int overlap_max;       /* CC_OVERLAP_MAX_HANDLES: the default policy overlaps while the process has at most that many handles open */
@@ -583,6 +585,14 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
     if (e->cav_on_st2) CUCHECK(cudaStreamWaitEvent(e->st, e->ev1, 0));
     e->cav_on_st2 = k->trail;
     e->overlapped_frames += k->trail;
+    if (k->trail) {
+        /* k_mb_encode keeps the progress words of its bands' bottom rows current only in this launch order, and k_deblock takes a word
+         * for this frame's when its tag is this frame's (20 bits): a word left by the last frame of an earlier stretch of this order
+         * must not carry it — which it could after exactly 2^20 - 1 frames of the other order */
+        if (!e->prev_trail && k->frame_seq == e->last_trail_seq) { k->frame_seq = (k->frame_seq + 1) & 0xfffff; if (!k->frame_seq) k->frame_seq = 1; }
+        e->last_trail_seq = k->frame_seq;
+    }
+    e->prev_trail = k->trail;
     STAGE(CC_STAGE_P_CODE);
     if (!is_idr) {
         e->launches += cck_p_code(k, e->st);

@@ -694,19 +694,37 @@ __device__ __forceinline__ void wait_progress(volatile int *flag, int need, int 
 }
 
 /* the same across CTAs: *flag is a frame-tagged progress word in global memory (tag + macroblocks done); returns the count */
-template <int SLEEP_NS = 0>
 __device__ __forceinline__ int wait_progress_global(const uint32_t *flag, uint32_t tag, int need, int lane) {
     uint32_t v = 0;
     if (lane == 0) {
         for (;;) {
             v = *(const volatile uint32_t *)flag;
             if ((int)(v - (tag + (uint32_t)need)) >= 0) break;
-            if (SLEEP_NS) __nanosleep(SLEEP_NS); else CC_SPIN_PAUSE();
+            CC_SPIN_PAUSE();
         }
     }
     v = __shfl_sync(FULL, v, 0);
     __threadfence();
     return (int)(v - tag);
+}
+
+/* k_deblock following k_mb_encode: the word must carry THIS frame's tag exactly.  The signed distance test above is right for words
+ * that are rewritten every frame; this one is only written while the filter runs next to the encoder, so a handle that switches
+ * launch orders could meet a word from 2^19 or more frames ago, which the distance test would take for "ahead" (and cc_enc_submit
+ * sees to it that the last word of an earlier stretch never carries the tag of the frame that resumes).  Counts stay below 4096
+ * (8192 / 16 macroblocks per row at most). */
+__device__ __forceinline__ int wait_encoder_progress(const uint32_t *flag, uint32_t tag, int need, int lane) {
+    uint32_t v = 0;
+    if (lane == 0) {
+        for (;;) {
+            v = *(const volatile uint32_t *)flag;
+            if (((v ^ tag) >> 12) == 0 && (int)(v & 4095u) >= need) break;
+            __nanosleep(1000); /* the word moves every fourth macroblock of the encoder (tens of microseconds): poll slowly */
+        }
+    }
+    v = __shfl_sync(FULL, v, 0);
+    __threadfence();
+    return (int)(v & 4095u);
 }
 
 /* does the macroblock coded at (mvx,mvy) leave nothing after quantisation + decimation?  (P_Skip test) */
@@ -1407,8 +1425,8 @@ __global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_debloc
         const int j = mbx & 3;
         if (j == 0) {
             const int cend = min(mbx + 4, mw);
-            if (enc_have < cend) { /* the word moves every fourth macroblock of the encoder (tens of microseconds): poll slowly */
-                const int p = wait_progress_global<1000>(ep, tag, max(1, cend - above), lane);
+            if (enc_have < cend) {
+                const int p = wait_encoder_progress(ep, tag, max(1, cend - above), lane);
                 enc_have = min(p + above, mw);
             }
             const int wi = mbx * 5 + lane; /* the row above is at least as far as this one, in the encoder and hence in its records */
