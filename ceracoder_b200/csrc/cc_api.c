@@ -25,7 +25,8 @@ struct cc_enc {
     cudaStream_t st;             /* upload, search, coding, entropy coding: what the access unit waits for */
     cudaStream_t st2;            /* in-loop filter and reference finishing of the same frame, concurrent with the entropy coder */
     cudaEvent_t ev0, ev1;
-    cudaEvent_t ev_enc, ev_tail; /* st -> st2 after k_mb_encode; st2 -> st before the next frame touches what the tail reads */
+    cudaEvent_t ev_enc, ev_tail; /* ev_enc: st -> st2 after k_mb_encode (after k_deblock when the filter runs next to it: then st2 carries the
+                                  * entropy coder); ev_tail: end of the tail (either stream) -> st before the next frame touches what it reads */
     void *dev_alloc[48];
     int n_dev_alloc;
     size_t dev_bytes;
@@ -575,7 +576,7 @@ int cc_enc_submit(cc_enc *e, const cc_frame *in, unsigned flags) {
      * sits on the first stream, behind k_mb_encode, and the entropy coder moves to the second.  This takes most of the filter out
      * of the cycle me_l0 -> p_code -> mb_encode -> deblock -> hpel that bounds ONE stream's frame rate (1 stream: +18 % frames/s;
      * 8: +1.5 %); it buys nothing once enough streams keep every SM busy anyway, where the waiting filter CTAs cost 2 % (16 streams)
-     * — hence the default: on while the process has at most overlap_max handles open.  Off while profiling, so that the per-stage
+     * — hence the default: on while the device has at most overlap_max handles open in this process.  Off while profiling, so that the per-stage
      * times stay times of stages. */
     const int ovl = e->profile || e->debug_sync ? 0 : (e->overlap >= 0 ? e->overlap & 1 : __atomic_load_n(&g_open_handles[e->p.device & (CC_MAX_DEVICES - 1)], __ATOMIC_RELAXED) <= e->overlap_max);
     k->trail = ovl;
