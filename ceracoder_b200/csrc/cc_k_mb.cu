@@ -1394,8 +1394,11 @@ __global__ void CC_MB_BOUNDS(RPS) k_mb_encode(cc_kparams k) {
 #ifndef CC_DB_MINBLOCKS
 #define CC_DB_MINBLOCKS 1
 #endif
+#ifndef CC_DB_MINBLOCKS_TRAIL /* experiment knob: CTAs per SM the instantiation that runs next to the encoder is compiled for */
+#define CC_DB_MINBLOCKS_TRAIL CC_DB_MINBLOCKS
+#endif
 template <bool TRAIL> /* TRAIL: launched next to k_mb_encode (k.trail) */
-__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, CC_DB_MINBLOCKS) k_deblock(cc_kparams k) {
+__global__ void __launch_bounds__(2 * MB_MAX_RPS * 32, TRAIL ? CC_DB_MINBLOCKS_TRAIL : CC_DB_MINBLOCKS) k_deblock(cc_kparams k) {
     __shared__ DbMem dbm[MB_MAX_RPS];
     __shared__ volatile int progress2[2][MB_MAX_RPS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
